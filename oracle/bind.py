@@ -1,0 +1,179 @@
+"""TEST INFRASTRUCTURE ONLY: one ctypes binding for both CPU checkers, which export the same C shapes:
+
+* ``ref()``  — oracle/_ref/libatray_ref.so: the reference's own hot-path sources (/root/reference/Source, built by
+  oracle/ref/build_ref.sh) behind oracle/ref/ref_harness.cpp (prefix ``ref_``);
+* ``port()`` — oracle/liboracle.so: the plain-C restatement oracle/atray_oracle.c (prefix ``or_``).
+
+Only tests/, __graft_entry__.smoke() and bench.py may import this module; the product (atray_b200/) never does."""
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "_ref", "libatray_ref.so")
+ASSETS = os.path.join(HERE, "_ref", "assets")
+MISS = 0xFFFFFFFF
+
+DEFAULT_EYE = (0.1, 2.0, 0.0)       # app.cpp:88
+DEFAULT_FACING = (-0.1, -0.5, -1.0)
+DEFAULT_HFOV = 1.0
+
+
+PORT_PATH = os.path.join(HERE, "liboracle.so")
+
+
+class Backend:
+    def __init__(self, path, prefix):
+        self.path, self.prefix = path, prefix
+        L = C.CDLL(path)
+        g = lambda n: getattr(L, prefix + n)
+        self.scene_create = g("scene_create")
+        self.scene_create.restype = C.c_void_p
+        self.scene_create.argtypes = [C.c_char_p, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int, C.c_uint]
+        self.scene_destroy = g("scene_destroy"); self.scene_destroy.argtypes = [C.c_void_p]
+        self.counts = g("counts"); self.counts.argtypes = [C.c_void_p, C.c_void_p]
+        self.model_dump = g("model_dump"); self.model_dump.argtypes = [C.c_void_p] + [C.c_void_p] * 7
+        self.tree_dump = g("tree_dump"); self.tree_dump.argtypes = [C.c_void_p] + [C.c_void_p] * 6
+        self.camera = g("camera"); self.camera.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_float, C.c_void_p]
+        self.trace_primary = g("trace_primary")
+        self.trace_primary.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_float, C.c_int,
+                                       C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        self.trace_rays = g("trace_rays")
+        self.trace_rays.argtypes = [C.c_void_p, C.c_longlong, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
+        self.render_jitter = g("render_jitter")
+        self.render_jitter.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_uint, C.c_int, C.c_ulonglong, C.c_void_p,
+                                       C.c_void_p, C.c_float, C.c_int, C.c_void_p, C.c_void_p]
+        self.pcg32 = g("pcg32"); self.pcg32.argtypes = [C.c_ulonglong, C.c_ulonglong, C.c_int, C.c_void_p]
+        self.render = None
+        self.trace_primary_ex = None
+        if prefix == "ref_":
+            self.render = g("render")
+            self.render.restype = C.c_double
+            self.render.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_uint, C.c_int, C.c_int, C.c_int, C.c_void_p,
+                                    C.c_void_p, C.c_float, C.c_void_p, C.c_void_p]
+        else:
+            self.trace_primary_ex = g("trace_primary_ex")
+            self.trace_primary_ex.argtypes = self.trace_primary.argtypes + [C.c_void_p]
+
+
+_backends = {}
+
+
+def ref_available():
+    return os.path.exists(LIB_PATH)
+
+
+def port_available():
+    return os.path.exists(PORT_PATH)
+
+
+def ref():
+    if "ref" not in _backends:
+        _backends["ref"] = Backend(LIB_PATH, "ref_")
+    return _backends["ref"]
+
+
+def port():
+    if "port" not in _backends:
+        _backends["port"] = Backend(PORT_PATH, "or_")
+    return _backends["port"]
+
+
+def _f3(v):
+    return np.asarray(v, dtype=np.float32).copy()
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+class Scene:
+    """One model loaded, placed and tree-built by a CPU checker backend (ref() or port())."""
+
+    def __init__(self, backend, obj_path, loader_threads=1, rescale=40.0, translate=(0.0, -15.0, -38.0), method=1, cap=300):
+        self.b = backend
+        self.h = backend.scene_create(os.fsencode(obj_path), loader_threads, rescale, translate[0], translate[1],
+                                        translate[2], method, cap)
+        c = np.zeros(8, dtype=np.uint32)
+        self.b.counts(self.h, _p(c))
+        (self.n_vertices, self.n_normals, self.n_tex, self.n_faces, self.n_nodes, self.n_refs, self.n_inner,
+         self.max_leaf) = [int(x) for x in c]
+
+    def close(self):
+        if self.h:
+            self.b.scene_destroy(self.h)
+            self.h = None
+
+    def model(self):
+        v = np.zeros((self.n_vertices, 3), np.float32)
+        n = np.zeros((self.n_normals, 3), np.float32)
+        t = np.zeros((self.n_tex, 3), np.float32)
+        fv = np.zeros((self.n_faces, 3), np.int32)
+        fvt = np.zeros((self.n_faces, 3), np.int32)
+        fvn = np.zeros((self.n_faces, 3), np.int32)
+        box = np.zeros(6, np.float32)
+        self.b.model_dump(self.h, _p(v), _p(n), _p(t), _p(fv), _p(fvt), _p(fvn), _p(box))
+        return dict(vertices=v, normals=n, tex_coords=t, face_v=fv, face_vt=fvt, face_vn=fvn, aabb=box)
+
+    def tree(self):
+        boxes = np.zeros((self.n_nodes, 6), np.float32)
+        child = np.zeros(self.n_nodes, np.int32)
+        cnt = np.zeros(self.n_nodes, np.uint32)
+        first = np.zeros(self.n_nodes, np.uint32)
+        tri = np.zeros((self.n_refs, 9), np.float32)
+        face = np.zeros(self.n_refs, np.uint32)
+        self.b.tree_dump(self.h, _p(boxes), _p(child), _p(cnt), _p(first), _p(tri), _p(face))
+        return dict(boxes=boxes, children_start=child, prim_count=cnt, prim_first=first, tri=tri, face=face)
+
+    def render(self, W, H, spp=1, aa=0, bounce=1, threads=1, eye=DEFAULT_EYE, facing=DEFAULT_FACING, hfov=DEFAULT_HFOV):
+        out = np.zeros((H, W), np.uint32)
+        casts = C.c_longlong(0)
+        e, f = _f3(eye), _f3(facing)
+        sec = self.b.render(self.h, W, H, spp, aa, bounce, threads, _p(e), _p(f), hfov, _p(out), C.byref(casts))
+        return out, sec, casts.value
+
+    def trace_primary(self, W, H, threads=1, eye=DEFAULT_EYE, facing=DEFAULT_FACING, hfov=DEFAULT_HFOV, want_uv=False):
+        face = np.zeros((H, W), np.uint32)
+        t = np.zeros((H, W), np.float32)
+        uv = np.zeros((H, W, 2), np.float32) if want_uv else None
+        img = np.zeros((H, W), np.uint32)
+        e, f = _f3(eye), _f3(facing)
+        self.b.trace_primary(self.h, W, H, _p(e), _p(f), hfov, threads, _p(face), _p(t), _p(uv), _p(img))
+        return (face, t, img, uv) if want_uv else (face, t, img)
+
+    def primary_counters(self, W, H, threads=1, eye=DEFAULT_EYE, facing=DEFAULT_FACING, hfov=DEFAULT_HFOV):
+        """port() only: work counters of one primary-ray frame (box tests, triangle tests, ... per frame)."""
+        ct = np.zeros(8, np.uint64)
+        e, f = _f3(eye), _f3(facing)
+        self.b.trace_primary_ex(self.h, W, H, _p(e), _p(f), hfov, threads, None, None, None, None, _p(ct))
+        names = ["box_tests", "tri_tests", "pass_det", "pass_u", "pass_v", "inner_pops", "leaves_listed", "leaves_scanned"]
+        return dict(zip(names, [int(x) for x in ct]))
+
+    def trace_rays(self, rays, threads=1):
+        rays = np.ascontiguousarray(rays, dtype=np.float32).reshape(-1, 6)
+        n = rays.shape[0]
+        face = np.zeros(n, np.uint32)
+        t = np.zeros(n, np.float32)
+        self.b.trace_rays(self.h, n, _p(rays), threads, _p(face), _p(t))
+        return face, t
+
+    def render_jitter(self, W, H, spp, seed, threads=1, bounce=1, eye=DEFAULT_EYE, facing=DEFAULT_FACING, hfov=DEFAULT_HFOV):
+        img = np.zeros((H, W), np.uint32)
+        hits = np.zeros((H, W), np.uint32)
+        e, f = _f3(eye), _f3(facing)
+        self.b.render_jitter(self.h, W, H, spp, bounce, seed, _p(e), _p(f), hfov, threads, _p(img), _p(hits))
+        return img, hits
+
+
+def camera(backend, W, H, eye=DEFAULT_EYE, facing=DEFAULT_FACING, hfov=DEFAULT_HFOV):
+    out = np.zeros(19, np.float32)
+    e, f = _f3(eye), _f3(facing)
+    backend.camera(W, H, _p(e), _p(f), hfov, _p(out))
+    return out
+
+
+def pcg32(backend, state, stream, n):
+    out = np.zeros(n, np.uint32)
+    backend.pcg32(state, stream, n, _p(out))
+    return out
