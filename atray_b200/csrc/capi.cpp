@@ -1,0 +1,620 @@
+// C ABI (include/atray_b200.h) over the host data model (host_model.cpp) and the sm_100a kernels (render.cu).
+// No CPU fallback: every device entry point fails with ATRAY_ECUDA if CUDA or the device is unavailable.
+#include "../../include/atray_b200.h"
+#include "device_types.h"
+#include "host_model.h"
+
+#include <chrono>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <thread>
+#include <vector>
+
+using namespace atray;
+
+struct atray_model { HostModel m; };
+
+struct atray_ctx
+{
+    int device = 0;
+    int sm_count = 0;
+    cudaStream_t stream = nullptr;
+    LaunchCfg cfg{};
+    float4* d_nodes = nullptr;
+    float4* d_tris = nullptr;
+    DevScene scene{};
+    bool has_scene = false;
+    DevScratch scratch{};
+    unsigned int* d_tile_counter = nullptr;
+    DevCounters* d_counters = nullptr;
+    bool counters_valid = false;
+    // frame planes owned by the context (atray_render_begin)
+    uint32_t* d_bgrx = nullptr; float* d_t = nullptr; uint32_t* d_prim = nullptr;
+    size_t frame_cap_px = 0;
+    // pinned staging for callers that pass pageable host memory
+    uint32_t* h_bgrx = nullptr; float* h_t = nullptr; uint32_t* h_prim = nullptr;
+    size_t stage_cap_px = 0;
+    AtrayFrame pending_user{};   // where staged planes still have to be copied on completion
+    size_t pending_px = 0;
+    bool stage_bgrx = false, stage_t = false, stage_prim = false;
+    bool in_flight = false;
+    cudaEvent_t ev_k0 = nullptr, ev_k1 = nullptr, ev_done = nullptr;
+    bool have_kernel_time = false;
+    // ray-list buffers (atray_trace_rays)
+    float* d_rays = nullptr; uint32_t* d_rprim = nullptr; float* d_rt = nullptr;
+    size_t ray_cap = 0;
+};
+
+static thread_local std::string g_err;
+static int fail(int code, const std::string& msg) { g_err = msg; return code; }
+static int cuda_fail(cudaError_t e, const char* what)
+{
+    g_err = std::string(what) + ": " + cudaGetErrorString(e);
+    return ATRAY_ECUDA;
+}
+#define CU(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) return cuda_fail(e__, #call); } while (0)
+
+extern "C" {
+
+const char* atray_last_error(void) { return g_err.c_str(); }
+int atray_version(void) { return 100; }
+
+// ---- host side --------------------------------------------------------------------------------------------------
+int atray_model_load_obj(const char* path, int loader_threads, atray_model** out)
+{
+    if (!path || !out) return fail(ATRAY_EINVAL, "null argument");
+    atray_model* m = new atray_model();
+    std::string err;
+    int rc = load_obj(path, loader_threads, m->m, err);
+    if (rc != 0) { delete m; return fail(rc == -2 ? ATRAY_EIO : ATRAY_EINVAL, err); }
+    *out = m;
+    return ATRAY_OK;
+}
+
+int atray_model_from_arrays(const float* vertices, uint32_t n_vertices, const int32_t* fvi, uint32_t n_faces, atray_model** out)
+{
+    if ((!vertices && n_vertices) || (!fvi && n_faces) || !out) return fail(ATRAY_EINVAL, "null argument");
+    atray_model* m = new atray_model();
+    m->m.vertices.resize(n_vertices);
+    if (n_vertices) std::memcpy(m->m.vertices.data(), vertices, size_t(n_vertices) * 12);
+    m->m.faces.resize(n_faces);
+    for (uint32_t i = 0; i < n_faces; ++i)
+        for (int k = 0; k < 3; ++k)
+        {
+            int32_t v = fvi[3 * size_t(i) + k];
+            if (v < 0 || uint32_t(v) >= n_vertices) { delete m; return fail(ATRAY_EINVAL, "face index out of range"); }
+            m->m.faces[i].v[k] = v;
+            m->m.faces[i].vt[k] = -1;
+            m->m.faces[i].vn[k] = -1;
+        }
+    *out = m;
+    return ATRAY_OK;
+}
+
+void atray_model_free(atray_model* m) { delete m; }
+
+int atray_model_compute_aabb(atray_model* m, float* out6)
+{
+    if (!m) return fail(ATRAY_EINVAL, "null model");
+    compute_aabb(m->m);
+    if (out6) std::memcpy(out6, &m->m.aabb, 24);
+    return ATRAY_OK;
+}
+int atray_model_resize_scale(atray_model* m, float s)
+{
+    if (!m) return fail(ATRAY_EINVAL, "null model");
+    if (!m->m.has_aabb) return fail(ATRAY_ESTATE, "resize_scale before compute_aabb");
+    resize_scale(m->m, s);
+    return ATRAY_OK;
+}
+int atray_model_translate_to(atray_model* m, const float* c)
+{
+    if (!m || !c) return fail(ATRAY_EINVAL, "null argument");
+    if (!m->m.has_aabb) return fail(ATRAY_ESTATE, "translate_to before compute_aabb");
+    translate_to(m->m, Vec3{c[0], c[1], c[2]});
+    return ATRAY_OK;
+}
+int atray_model_build_tree(atray_model* m, int method, uint32_t cap)
+{
+    if (!m) return fail(ATRAY_EINVAL, "null model");
+    if (method != ATRAY_DIV_CENTER && method != ATRAY_DIV_SAH) return fail(ATRAY_EINVAL, "unknown division method");
+    std::string err;
+    int rc = build_tree(m->m, method, cap, err);
+    if (rc != 0) return fail(ATRAY_ELIMIT, err);
+    return ATRAY_OK;
+}
+int atray_model_counts(const atray_model* m, uint32_t* c)
+{
+    if (!m || !c) return fail(ATRAY_EINVAL, "null argument");
+    c[0] = uint32_t(m->m.vertices.size()); c[1] = uint32_t(m->m.normals.size()); c[2] = uint32_t(m->m.tex_coords.size());
+    c[3] = uint32_t(m->m.faces.size()); c[4] = uint32_t(m->m.tree.size());
+    uint32_t refs = 0, inner = 0, big = 0;
+    for (const TreeNode& n : m->m.tree)
+    {
+        if (n.children_start) { ++inner; continue; }
+        refs += uint32_t(n.prims.size());
+        if (n.prims.size() > big) big = uint32_t(n.prims.size());
+    }
+    c[5] = refs; c[6] = inner; c[7] = big;
+    return ATRAY_OK;
+}
+int atray_model_dump(const atray_model* m, float* v, float* n, float* t, int32_t* fv, int32_t* fvt, int32_t* fvn, float* aabb6)
+{
+    if (!m) return fail(ATRAY_EINVAL, "null model");
+    const HostModel& h = m->m;
+    if (v && !h.vertices.empty()) std::memcpy(v, h.vertices.data(), h.vertices.size() * 12);
+    if (n && !h.normals.empty()) std::memcpy(n, h.normals.data(), h.normals.size() * 12);
+    if (t && !h.tex_coords.empty()) std::memcpy(t, h.tex_coords.data(), h.tex_coords.size() * 12);
+    for (size_t i = 0; i < h.faces.size(); ++i)
+        for (int k = 0; k < 3; ++k)
+        {
+            if (fv) fv[3 * i + k] = h.faces[i].v[k];
+            if (fvt) fvt[3 * i + k] = h.faces[i].vt[k];
+            if (fvn) fvn[3 * i + k] = h.faces[i].vn[k];
+        }
+    if (aabb6) std::memcpy(aabb6, &h.aabb, 24);
+    return ATRAY_OK;
+}
+int atray_model_tree_dump(const atray_model* m, float* boxes, int32_t* child, uint32_t* cnt, uint32_t* first, float* tri9, uint32_t* face)
+{
+    if (!m) return fail(ATRAY_EINVAL, "null model");
+    uint32_t off = 0;
+    for (size_t i = 0; i < m->m.tree.size(); ++i)
+    {
+        const TreeNode& n = m->m.tree[i];
+        if (boxes) std::memcpy(boxes + 6 * i, &n.box, 24);
+        if (child) child[i] = n.children_start;
+        const uint32_t c = n.children_start ? 0u : uint32_t(n.prims.size());
+        if (cnt) cnt[i] = c;
+        if (first) first[i] = off;
+        for (uint32_t k = 0; k < c; ++k)
+        {
+            if (tri9) std::memcpy(tri9 + 9 * size_t(off + k), &n.prims[k], 36);
+            if (face) face[off + k] = n.prims[k].face;
+        }
+        off += c;
+    }
+    return ATRAY_OK;
+}
+int atray_model_flatten(const atray_model* m, uint32_t* n_nodes, uint32_t* n_slots, float* nodes, float* tris)
+{
+    if (!m) return fail(ATRAY_EINVAL, "null model");
+    if (m->m.tree.empty()) return fail(ATRAY_ESTATE, "flatten before build_tree");
+    FlatScene f;
+    flatten(m->m, f);
+    if (n_nodes) *n_nodes = f.n_nodes;
+    if (n_slots) *n_slots = f.n_slots;
+    if (nodes) std::memcpy(nodes, f.nodes.data(), f.nodes.size() * 4);
+    if (tris && !f.tris.empty()) std::memcpy(tris, f.tris.data(), f.tris.size() * 4);
+    return ATRAY_OK;
+}
+
+int atray_camera_set(AtrayCamera* cam, int32_t w, int32_t h, int32_t aa, uint32_t spp, int32_t bounce, const float* eye,
+                     const float* facing, float h_fov)
+{
+    if (!cam || !eye || !facing) return fail(ATRAY_EINVAL, "null argument");
+    if (w <= 0 || h <= 0 || spp == 0) return fail(ATRAY_EINVAL, "bad resolution or sample count");
+    CameraBasis b = make_camera(w, h, Vec3{eye[0], eye[1], eye[2]}, Vec3{facing[0], facing[1], facing[2]}, h_fov);
+    cam->width = w; cam->height = h; cam->anti_aliasing = aa; cam->samples_per_pixel = spp; cam->bounce_limit = bounce;
+    cam->aspect_ratio = b.aspect;
+    std::memcpy(cam->camera_z, &b.cz, 12); std::memcpy(cam->camera_x, &b.cx, 12); std::memcpy(cam->camera_y, &b.cy, 12);
+    std::memcpy(cam->eye, &b.eye, 12); std::memcpy(cam->frame_center, &b.fc, 12);
+    cam->h_fov = b.h_fov; cam->half_pixel_width = b.hpw; cam->half_pixel_height = b.hph;
+    return ATRAY_OK;
+}
+
+// ---- device side ------------------------------------------------------------------------------------------------
+int atray_device_count(int* n)
+{
+    if (!n) return fail(ATRAY_EINVAL, "null argument");
+    CU(cudaGetDeviceCount(n));
+    return ATRAY_OK;
+}
+
+int atray_ctx_create(int device, atray_ctx** out)
+{
+    if (!out) return fail(ATRAY_EINVAL, "null argument");
+    int n = 0;
+    CU(cudaGetDeviceCount(&n));
+    if (device < 0 || device >= n) return fail(ATRAY_ECUDA, "no such CUDA device");
+    CU(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10) return fail(ATRAY_ECUDA, std::string("device is not sm_100-class: ") + prop.name);
+    atray_ctx* c = new atray_ctx();
+    c->device = device;
+    c->sm_count = prop.multiProcessorCount;
+    c->cfg = render_launch_cfg(c->sm_count);
+    cudaError_t e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaMalloc(&c->d_tile_counter, sizeof(unsigned int));
+    if (e == cudaSuccess) e = cudaMalloc(&c->d_counters, sizeof(DevCounters));
+    if (e == cudaSuccess) e = cudaEventCreate(&c->ev_k0);
+    if (e == cudaSuccess) e = cudaEventCreate(&c->ev_k1);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_done, cudaEventDisableTiming);
+    if (e != cudaSuccess) { delete c; return cuda_fail(e, "context setup"); }
+    *out = c;
+    return ATRAY_OK;
+}
+
+static void free_scene(atray_ctx* c)
+{
+    cudaFree(c->d_nodes); cudaFree(c->d_tris); cudaFree(c->scratch.leaves); cudaFree(c->scratch.stack);
+    c->d_nodes = c->d_tris = nullptr;
+    c->scratch = DevScratch{};
+    c->has_scene = false;
+}
+
+void atray_ctx_destroy(atray_ctx* c)
+{
+    if (!c) return;
+    cudaSetDevice(c->device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    free_scene(c);
+    cudaFree(c->d_tile_counter); cudaFree(c->d_counters);
+    cudaFree(c->d_bgrx); cudaFree(c->d_t); cudaFree(c->d_prim);
+    cudaFreeHost(c->h_bgrx); cudaFreeHost(c->h_t); cudaFreeHost(c->h_prim);
+    cudaFree(c->d_rays); cudaFree(c->d_rprim); cudaFree(c->d_rt);
+    if (c->ev_k0) cudaEventDestroy(c->ev_k0);
+    if (c->ev_k1) cudaEventDestroy(c->ev_k1);
+    if (c->ev_done) cudaEventDestroy(c->ev_done);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+int atray_scene_upload(atray_ctx* c, const atray_model* m, const AtrayMaterial* sky, const AtrayMaterial* mat)
+{
+    if (!c || !m || !sky || !mat) return fail(ATRAY_EINVAL, "null argument");
+    if (m->m.tree.empty()) return fail(ATRAY_ESTATE, "scene_upload before build_tree");
+    if (c->in_flight) return fail(ATRAY_ESTATE, "render in flight");
+    CU(cudaSetDevice(c->device));
+    CU(cudaStreamSynchronize(c->stream));
+    free_scene(c);
+    FlatScene f;
+    flatten(m->m, f);
+    CU(cudaMalloc(&c->d_nodes, f.nodes.size() * 4));
+    CU(cudaMalloc(&c->d_tris, f.tris.size() * 4 + 16));
+    CU(cudaMemcpy(c->d_nodes, f.nodes.data(), f.nodes.size() * 4, cudaMemcpyHostToDevice));
+    if (!f.tris.empty()) CU(cudaMemcpy(c->d_tris, f.tris.data(), f.tris.size() * 4, cudaMemcpyHostToDevice));
+    const int warps = render_warps_in_flight(c->cfg);
+    c->scratch.leaf_cap = f.n_leaves + 2;
+    c->scratch.stack_cap = f.n_nodes + 8;
+    CU(cudaMalloc(&c->scratch.leaves, size_t(warps) * c->scratch.leaf_cap * sizeof(uint2)));
+    CU(cudaMalloc(&c->scratch.stack, size_t(warps) * c->scratch.stack_cap * sizeof(uint32_t)));
+    c->scene.nodes = c->d_nodes;
+    c->scene.tris = c->d_tris;
+    c->scene.n_nodes = f.n_nodes;
+    c->scene.root_is_leaf = m->m.tree[0].children_start == 0 ? 1u : 0u;
+    std::memcpy(c->scene.sky, sky->emission_color, 12);
+    std::memcpy(c->scene.mdl, mat->emission_color, 12);
+    c->has_scene = true;
+    return ATRAY_OK;
+}
+
+static int check_render_args(atray_ctx* c, const AtrayCamera* cam, const AtrayRenderOpts* o, const AtrayFrame* out)
+{
+    if (!c || !cam || !o || !out) return fail(ATRAY_EINVAL, "null argument");
+    if (!c->has_scene) return fail(ATRAY_ESTATE, "render before scene_upload");
+    if (cam->width <= 0 || cam->height <= 0 || cam->samples_per_pixel == 0) return fail(ATRAY_EINVAL, "bad camera");
+    if (cam->bounce_limit != 1) return fail(ATRAY_EINVAL, "this path implements bounce_limit = 1 (primary rays)");
+    if (o->part.world < 1 || o->part.rank < 0 || o->part.rank >= o->part.world) return fail(ATRAY_EINVAL, "bad partition");
+    if (o->part.band_rows < 4 || (o->part.band_rows & 3)) return fail(ATRAY_EINVAL, "band_rows must be a positive multiple of 4");
+    return ATRAY_OK;
+}
+
+static DevCamera to_dev(const AtrayCamera* cam)
+{
+    DevCamera d;
+    d.W = cam->width; d.H = cam->height; d.aa = cam->anti_aliasing; d.spp = cam->samples_per_pixel;
+    d.aspect = cam->aspect_ratio; d.h_fov = cam->h_fov; d.hpw = cam->half_pixel_width; d.hph = cam->half_pixel_height;
+    std::memcpy(d.eye, cam->eye, 12); std::memcpy(d.fc, cam->frame_center, 12);
+    std::memcpy(d.cx, cam->camera_x, 12); std::memcpy(d.cy, cam->camera_y, 12);
+    return d;
+}
+
+static int enqueue_render(atray_ctx* c, const AtrayCamera* cam, const AtrayRenderOpts* o, const DevOut& out)
+{
+    DevCounters* ctr = nullptr;
+    if (o->count_work)
+    {
+        CU(cudaMemsetAsync(c->d_counters, 0, sizeof(DevCounters), c->stream));
+        ctr = c->d_counters;
+        c->counters_valid = true;
+    }
+    DevPartition p{o->part.rank, o->part.world, o->part.band_rows};
+    CU(cudaEventRecord(c->ev_k0, c->stream));
+    CU(launch_render(c->scene, to_dev(cam), p, out, c->scratch, c->d_tile_counter, ctr, o->fp_mode == ATRAY_FP_FAST,
+                     o->jitter_seed, c->cfg, c->stream));
+    CU(cudaEventRecord(c->ev_k1, c->stream));
+    c->have_kernel_time = true;
+    return ATRAY_OK;
+}
+
+int atray_render_device(atray_ctx* c, const AtrayCamera* cam, const AtrayRenderOpts* o, const AtrayFrame* dev_out)
+{
+    int rc = check_render_args(c, cam, o, dev_out);
+    if (rc) return rc;
+    CU(cudaSetDevice(c->device));
+    DevOut out{dev_out->bgrx, dev_out->t, dev_out->prim};
+    return enqueue_render(c, cam, o, out);
+}
+
+static bool host_ptr_is_pinned(const void* p)
+{
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
+    return a.type == cudaMemoryTypeHost;
+}
+
+int atray_render_begin(atray_ctx* c, const AtrayCamera* cam, const AtrayRenderOpts* o, const AtrayFrame* host)
+{
+    int rc = check_render_args(c, cam, o, host);
+    if (rc) return rc;
+    if (c->in_flight) return fail(ATRAY_ESTATE, "a render is already in flight");
+    CU(cudaSetDevice(c->device));
+    const size_t px = size_t(cam->width) * size_t(cam->height);
+    if (px > c->frame_cap_px)
+    {
+        cudaFree(c->d_bgrx); cudaFree(c->d_t); cudaFree(c->d_prim);
+        c->d_bgrx = nullptr; c->d_t = nullptr; c->d_prim = nullptr; c->frame_cap_px = 0;
+        CU(cudaMalloc(&c->d_bgrx, px * 4)); CU(cudaMalloc(&c->d_t, px * 4)); CU(cudaMalloc(&c->d_prim, px * 4));
+        c->frame_cap_px = px;
+    }
+    c->stage_bgrx = host->bgrx && !host_ptr_is_pinned(host->bgrx);
+    c->stage_t = host->t && !host_ptr_is_pinned(host->t);
+    c->stage_prim = host->prim && !host_ptr_is_pinned(host->prim);
+    if ((c->stage_bgrx || c->stage_t || c->stage_prim) && px > c->stage_cap_px)
+    {
+        cudaFreeHost(c->h_bgrx); cudaFreeHost(c->h_t); cudaFreeHost(c->h_prim);
+        c->h_bgrx = nullptr; c->h_t = nullptr; c->h_prim = nullptr; c->stage_cap_px = 0;
+        CU(cudaMallocHost(&c->h_bgrx, px * 4)); CU(cudaMallocHost(&c->h_t, px * 4)); CU(cudaMallocHost(&c->h_prim, px * 4));
+        c->stage_cap_px = px;
+    }
+    DevOut out{host->bgrx ? c->d_bgrx : nullptr, host->t ? c->d_t : nullptr, host->prim ? c->d_prim : nullptr};
+    rc = enqueue_render(c, cam, o, out);
+    if (rc) return rc;
+    // With a partition (world > 1) only this rank's bands are defined on the device; whole planes are still copied and the
+    // caller merges bands (host layer) — single-process multi-GPU gathers on the device instead (atray_render_device).
+    if (host->bgrx) CU(cudaMemcpyAsync(c->stage_bgrx ? c->h_bgrx : host->bgrx, c->d_bgrx, px * 4, cudaMemcpyDeviceToHost, c->stream));
+    if (host->t) CU(cudaMemcpyAsync(c->stage_t ? c->h_t : host->t, c->d_t, px * 4, cudaMemcpyDeviceToHost, c->stream));
+    if (host->prim) CU(cudaMemcpyAsync(c->stage_prim ? c->h_prim : host->prim, c->d_prim, px * 4, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaEventRecord(c->ev_done, c->stream));
+    c->pending_user = *host;
+    c->pending_px = px;
+    c->in_flight = true;
+    return ATRAY_OK;
+}
+
+int atray_render_poll(atray_ctx* c, uint32_t timeout_ms)
+{
+    if (!c) return fail(ATRAY_EINVAL, "null context");
+    if (!c->in_flight) return 0;
+    CU(cudaSetDevice(c->device));
+    const auto deadline = std::chrono::steady_clock::now() + std::chrono::milliseconds(timeout_ms);
+    for (;;)
+    {
+        cudaError_t e = cudaEventQuery(c->ev_done);
+        if (e == cudaSuccess) break;
+        if (e != cudaErrorNotReady) { c->in_flight = false; return cuda_fail(e, "render"); }
+        if (timeout_ms != 0xffffffffu && std::chrono::steady_clock::now() >= deadline) return 1;  // still running
+        std::this_thread::yield();
+    }
+    const size_t bytes = c->pending_px * 4;
+    if (c->stage_bgrx) std::memcpy(c->pending_user.bgrx, c->h_bgrx, bytes);
+    if (c->stage_t) std::memcpy(c->pending_user.t, c->h_t, bytes);
+    if (c->stage_prim) std::memcpy(c->pending_user.prim, c->h_prim, bytes);
+    c->in_flight = false;
+    return 0;
+}
+
+int atray_render_cancel(atray_ctx* c)
+{
+    if (!c) return fail(ATRAY_EINVAL, "null context");
+    // A frame is one sub-millisecond kernel: cancelling = draining the stream and dropping the pending host copy-out.
+    CU(cudaSetDevice(c->device));
+    CU(cudaStreamSynchronize(c->stream));
+    c->in_flight = false;
+    return ATRAY_OK;
+}
+
+int atray_ctx_sync(atray_ctx* c)
+{
+    if (!c) return fail(ATRAY_EINVAL, "null context");
+    CU(cudaSetDevice(c->device));
+    CU(cudaStreamSynchronize(c->stream));
+    return ATRAY_OK;
+}
+
+int atray_last_kernel_ms(atray_ctx* c, float* ms)
+{
+    if (!c || !ms) return fail(ATRAY_EINVAL, "null argument");
+    if (!c->have_kernel_time) return fail(ATRAY_ESTATE, "no kernel has been launched");
+    CU(cudaSetDevice(c->device));
+    CU(cudaEventSynchronize(c->ev_k1));
+    CU(cudaEventElapsedTime(ms, c->ev_k0, c->ev_k1));
+    return ATRAY_OK;
+}
+
+// ---- ray lists ------------------------------------------------------------------------------------------------------
+int atray_trace_rays_device(atray_ctx* c, const float* rays_dev, uint64_t n, int32_t fp_mode, int32_t count_work,
+                            uint32_t* prim_dev, float* t_dev)
+{
+    if (!c || (!rays_dev && n) || (!prim_dev && n) || (!t_dev && n)) return fail(ATRAY_EINVAL, "null argument");
+    if (!c->has_scene) return fail(ATRAY_ESTATE, "trace before scene_upload");
+    if (n == 0) return ATRAY_OK;
+    if (n > (uint64_t(1) << 36)) return fail(ATRAY_EINVAL, "ray list too long for one call (split it)");
+    CU(cudaSetDevice(c->device));
+    DevCounters* ctr = nullptr;
+    if (count_work)
+    {
+        CU(cudaMemsetAsync(c->d_counters, 0, sizeof(DevCounters), c->stream));
+        ctr = c->d_counters;
+        c->counters_valid = true;
+    }
+    CU(cudaEventRecord(c->ev_k0, c->stream));
+    CU(launch_trace(c->scene, rays_dev, n, prim_dev, t_dev, c->scratch, c->d_tile_counter, ctr, fp_mode == ATRAY_FP_FAST, c->cfg,
+                    c->stream));
+    CU(cudaEventRecord(c->ev_k1, c->stream));
+    c->have_kernel_time = true;
+    return ATRAY_OK;
+}
+
+int atray_trace_rays(atray_ctx* c, const float* rays, uint64_t n, int32_t fp_mode, int32_t count_work, uint32_t* prim, float* t)
+{
+    if (!c || (!rays && n) || (!prim && n) || (!t && n)) return fail(ATRAY_EINVAL, "null argument");
+    if (!c->has_scene) return fail(ATRAY_ESTATE, "trace before scene_upload");
+    if (n == 0) return ATRAY_OK;
+    CU(cudaSetDevice(c->device));
+    if (n > c->ray_cap)
+    {
+        cudaFree(c->d_rays); cudaFree(c->d_rprim); cudaFree(c->d_rt);
+        c->d_rays = nullptr; c->d_rprim = nullptr; c->d_rt = nullptr; c->ray_cap = 0;
+        CU(cudaMalloc(&c->d_rays, n * 24)); CU(cudaMalloc(&c->d_rprim, n * 4)); CU(cudaMalloc(&c->d_rt, n * 4));
+        c->ray_cap = n;
+    }
+    CU(cudaMemcpyAsync(c->d_rays, rays, n * 24, cudaMemcpyHostToDevice, c->stream));
+    int rc = atray_trace_rays_device(c, c->d_rays, n, fp_mode, count_work, c->d_rprim, c->d_rt);
+    if (rc) return rc;
+    CU(cudaMemcpyAsync(prim, c->d_rprim, n * 4, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaMemcpyAsync(t, c->d_rt, n * 4, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    return ATRAY_OK;
+}
+
+int atray_get_counters(atray_ctx* c, AtrayCounters* out)
+{
+    if (!c || !out) return fail(ATRAY_EINVAL, "null argument");
+    if (!c->counters_valid) return fail(ATRAY_ESTATE, "no counted frame yet (set count_work)");
+    static_assert(sizeof(AtrayCounters) == sizeof(DevCounters), "counter layouts differ");
+    CU(cudaSetDevice(c->device));
+    CU(cudaStreamSynchronize(c->stream));
+    CU(cudaMemcpy(out, c->d_counters, sizeof(DevCounters), cudaMemcpyDeviceToHost));
+    return ATRAY_OK;
+}
+
+// ---- memory helpers ----------------------------------------------------------------------------------------------
+int atray_dev_alloc(atray_ctx* c, size_t bytes, void** out)
+{
+    if (!c || !out) return fail(ATRAY_EINVAL, "null argument");
+    CU(cudaSetDevice(c->device));
+    CU(cudaMalloc(out, bytes ? bytes : 1));
+    return ATRAY_OK;
+}
+int atray_dev_free(atray_ctx* c, void* p)
+{
+    if (!c) return fail(ATRAY_EINVAL, "null context");
+    CU(cudaSetDevice(c->device));
+    CU(cudaFree(p));
+    return ATRAY_OK;
+}
+int atray_dev_copy_to_host(atray_ctx* c, void* host, const void* dev, size_t bytes)
+{
+    if (!c || !host || !dev) return fail(ATRAY_EINVAL, "null argument");
+    CU(cudaSetDevice(c->device));
+    CU(cudaMemcpyAsync(host, dev, bytes, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    return ATRAY_OK;
+}
+int atray_dev_copy_from_host(atray_ctx* c, void* dev, const void* host, size_t bytes)
+{
+    if (!c || !host || !dev) return fail(ATRAY_EINVAL, "null argument");
+    CU(cudaSetDevice(c->device));
+    CU(cudaMemcpyAsync(dev, host, bytes, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    return ATRAY_OK;
+}
+int atray_host_alloc_pinned(size_t bytes, void** out)
+{
+    if (!out) return fail(ATRAY_EINVAL, "null argument");
+    CU(cudaMallocHost(out, bytes ? bytes : 1));
+    return ATRAY_OK;
+}
+int atray_host_free_pinned(void* p)
+{
+    CU(cudaFreeHost(p));
+    return ATRAY_OK;
+}
+int atray_ipc_export(atray_ctx* c, void* dev, unsigned char* handle64)
+{
+    if (!c || !dev || !handle64) return fail(ATRAY_EINVAL, "null argument");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    CU(cudaSetDevice(c->device));
+    cudaIpcMemHandle_t h;
+    CU(cudaIpcGetMemHandle(&h, dev));
+    std::memcpy(handle64, &h, 64);
+    return ATRAY_OK;
+}
+int atray_ipc_open(atray_ctx* c, const unsigned char* handle64, void** out)
+{
+    if (!c || !handle64 || !out) return fail(ATRAY_EINVAL, "null argument");
+    CU(cudaSetDevice(c->device));
+    cudaIpcMemHandle_t h;
+    std::memcpy(&h, handle64, 64);
+    CU(cudaIpcOpenMemHandle(out, h, cudaIpcMemLazyEnablePeerAccess));
+    return ATRAY_OK;
+}
+int atray_ipc_close(atray_ctx* c, void* p)
+{
+    if (!c) return fail(ATRAY_EINVAL, "null context");
+    CU(cudaSetDevice(c->device));
+    CU(cudaIpcCloseMemHandle(p));
+    return ATRAY_OK;
+}
+
+// ---- K0 ------------------------------------------------------------------------------------------------------------
+int atray_microbench(atray_ctx* c, double* fp32_lane_ops_per_s, double* l2_read_gbs)
+{
+    if (!c) return fail(ATRAY_EINVAL, "null context");
+    CU(cudaSetDevice(c->device));
+    float* sink = nullptr;
+    CU(cudaMalloc(&sink, 16));
+    cudaEvent_t a, b;
+    CU(cudaEventCreate(&a)); CU(cudaEventCreate(&b));
+    float ms = 0.f;
+    if (fp32_lane_ops_per_s)
+    {
+        LaunchCfg cfg{c->sm_count * 8, 256};
+        const int iters = 4096;
+        CU(launch_microbench_fp32(sink, 64, cfg, c->stream));  // warm-up
+        double best = 0.0;
+        for (int rep = 0; rep < 3; ++rep)
+        {
+            CU(cudaEventRecord(a, c->stream));
+            CU(launch_microbench_fp32(sink, iters, cfg, c->stream));
+            CU(cudaEventRecord(b, c->stream));
+            CU(cudaEventSynchronize(b));
+            CU(cudaEventElapsedTime(&ms, a, b));
+            const double ops = double(cfg.grid) * cfg.block * double(iters) * 64.0;  // one FFMA = one issue slot per lane
+            if (ops / (ms * 1e-3) > best) best = ops / (ms * 1e-3);
+        }
+        *fp32_lane_ops_per_s = best;
+    }
+    if (l2_read_gbs)
+    {
+        const size_t bytes = size_t(32) << 20;  // 32 MiB: L2-resident on B200 (126 MB), larger than any L1
+        float4* buf = nullptr;
+        CU(cudaMalloc(&buf, bytes));
+        CU(cudaMemsetAsync(buf, 0, bytes, c->stream));
+        LaunchCfg cfg{c->sm_count * 8, 256};
+        const int passes = 16;
+        CU(launch_microbench_l2(buf, bytes / 16, 2, sink, cfg, c->stream));
+        double best = 0.0;
+        for (int rep = 0; rep < 3; ++rep)
+        {
+            CU(cudaEventRecord(a, c->stream));
+            CU(launch_microbench_l2(buf, bytes / 16, passes, sink, cfg, c->stream));
+            CU(cudaEventRecord(b, c->stream));
+            CU(cudaEventSynchronize(b));
+            CU(cudaEventElapsedTime(&ms, a, b));
+            const double gbs = double(bytes) * passes / (ms * 1e-3) / 1e9;
+            if (gbs > best) best = gbs;
+        }
+        *l2_read_gbs = best;
+        CU(cudaFree(buf));
+    }
+    CU(cudaEventDestroy(a)); CU(cudaEventDestroy(b));
+    CU(cudaFree(sink));
+    return ATRAY_OK;
+}
+
+}  // extern "C"

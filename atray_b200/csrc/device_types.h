@@ -1,0 +1,58 @@
+// Types shared between the CUDA kernels (render.cu) and the C-ABI host code (capi.cpp).
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace atray {
+
+struct DevScene
+{
+    const float4* nodes;   // 2 float4 per node
+    const float4* tris;    // blocks of 32 slots: 32×A | 32×AB | 32×AC
+    uint32_t n_nodes;
+    uint32_t root_is_leaf;
+    float sky[3];          // materials[0].emission_color (renderer.cpp:152, 226)
+    float mdl[3];          // model material emission_color (renderer.cpp:258)
+};
+
+struct DevCamera
+{
+    int32_t W, H;
+    int32_t aa;
+    uint32_t spp;
+    float aspect, h_fov, hpw, hph;
+    float eye[3], fc[3], cx[3], cy[3];
+};
+
+struct DevPartition { int32_t rank, world, band_rows; };
+
+struct DevOut { uint32_t* bgrx; float* t; uint32_t* prim; };
+
+struct DevCounters  // mirrors AtrayCounters
+{
+    unsigned long long rays, box_tests, tri_tests, pass_det, pass_u, pass_v, leaves_listed, leaves_scanned, overflow_rays;
+};
+
+// Per-warp spill area for rays whose leaf list / inner-node stack outgrow the per-lane arrays.
+struct DevScratch
+{
+    uint2* leaves;        // warps × leaf_cap
+    uint32_t* stack;      // warps × stack_cap
+    uint32_t leaf_cap, stack_cap;
+};
+
+struct LaunchCfg { int grid, block; };
+
+// host-callable launchers (render.cu)
+cudaError_t launch_render(const DevScene& sc, const DevCamera& cam, const DevPartition& part, const DevOut& out,
+                          const DevScratch& scratch, unsigned int* tile_counter, DevCounters* counters, int fp_fast,
+                          unsigned long long jitter_seed, LaunchCfg cfg, cudaStream_t stream);
+cudaError_t launch_trace(const DevScene& sc, const float* rays, unsigned long long n, uint32_t* prim, float* t,
+                         const DevScratch& scratch, unsigned int* tile_counter, DevCounters* counters, int fp_fast,
+                         LaunchCfg cfg, cudaStream_t stream);
+cudaError_t launch_microbench_fp32(float* sink, int iters, LaunchCfg cfg, cudaStream_t stream);
+cudaError_t launch_microbench_l2(const float4* buf, size_t n_vec, int passes, float* sink, LaunchCfg cfg, cudaStream_t stream);
+LaunchCfg render_launch_cfg(int sm_count);
+int render_warps_in_flight(LaunchCfg cfg);
+
+}  // namespace atray

@@ -1,0 +1,54 @@
+// Host-side data model of the render path: mesh arrays, model box, the 8-way spatial tree and its flat GPU form.
+// These are the ☆ rows of SURVEY.md §2 — they stay on the CPU and run once per scene; the renderer proper is CUDA.
+#pragma once
+#include <cstdint>
+#include <string>
+#include <vector>
+
+namespace atray {
+
+struct Vec3 { float x, y, z; };
+struct Box { Vec3 lo, hi; };
+struct Face { int32_t v[3]; int32_t vt[3]; int32_t vn[3]; };
+struct PrimRef { Vec3 a, b, c; uint32_t face; };  // KD_Primitive: leaf-local copy of the triangle + original face index
+
+struct TreeNode
+{
+    Box box;
+    int32_t children_start = 0;      // 0 ⇔ leaf (reference keeps has_children in the same word)
+    std::vector<PrimRef> prims;      // leaves only (inner nodes hand their list to the children)
+};
+
+struct HostModel
+{
+    std::vector<Vec3> vertices, normals, tex_coords;
+    std::vector<Face> faces;
+    Box aabb{};                      // Model::surrounding_aabb
+    bool has_aabb = false;
+    std::vector<TreeNode> tree;      // node order identical to the reference's DBuffer<KD_Node>
+    uint32_t max_faces_per_node = 0;
+    int division_method = 1;
+};
+
+// Flat, 16-byte-aligned GPU form.
+struct FlatScene
+{
+    // node i = two float4: {lo.xyz, w0} {hi.xyz, w1}; inner: w0 = children_start (>0), w1 = 0;
+    // leaf: w0 = ~first_slot (<0, first_slot multiple of 32), w1 = primitive count.
+    std::vector<float> nodes;        // n_nodes * 8
+    // triangle slots in blocks of 32: block b = 32×{a.xyz, face} | 32×{ab.xyz, 0} | 32×{ac.xyz, 0}
+    std::vector<float> tris;         // n_slots/32 * 96 * 4
+    uint32_t n_nodes = 0, n_slots = 0, n_leaves = 0, max_leaf_prims = 0;
+};
+
+int load_obj(const char* path, int threads, HostModel& m, std::string& err);
+void compute_aabb(HostModel& m);
+void resize_scale(HostModel& m, float new_max_scale);
+void translate_to(HostModel& m, Vec3 new_center);
+int build_tree(HostModel& m, int method, uint32_t cap, std::string& err);
+void flatten(const HostModel& m, FlatScene& out);
+
+struct CameraBasis { float aspect; Vec3 cz, cx, cy, eye, fc; float h_fov, hpw, hph; };
+CameraBasis make_camera(int w, int h, Vec3 eye, Vec3 facing, float h_fov);
+
+}  // namespace atray

@@ -1,0 +1,545 @@
+// sm_100a kernels of the ATRay render path: camera ray generation → 8-way tree traversal → culled Möller–Trumbore →
+// flat shade → {t, primitive id, BGRX} store. Replaces the reference's tile thread pool and everything below it:
+//   render_tile_from_camera  engine/renderer/renderer.cpp:294-369   (pixel loop, film coordinates, SetRay, pack)
+//   cast_ray @ bounce 1      renderer.cpp:213-262                    (sky / model emission, 3 RNG draws per hit)
+//   get_intersection_data    renderer.cpp:34-57                      (Optimized_Ray, accept t in (1e-4, MAX_FLOAT))
+//   traverse_oct_tree_new    engine/renderer/kd_tree.cpp:337-465     (two-phase traversal)
+//   ray/box slab tests       engine/renderer/aabb.h:29-93
+//   triangle test            engine/renderer/model.h:75-103
+//
+// Execution model: persistent CTAs; each warp pulls 8×4-pixel tiles (or 32-ray groups) from an atomic
+// counter. Phase 1 runs one ray per lane: LIFO walk over inner nodes with the ≤5-accepted-children cut, leaves
+// collected into a per-lane list kept sorted by entry distance (stable insertion). Phase 2 is warp-cooperative: the
+// warp takes its rays one at a time, the 32 lanes test 32 consecutive triangle slots of the current leaf with
+// coalesced float4 loads of precomputed-edge records, a lexicographic (t, slot) warp arg-min reproduces the
+// reference's sequential strict-< scan, and the ray stops after the first leaf that yields a hit.
+//
+// Arithmetic: in STRICT mode every decision-critical float op is an explicit round-to-nearest intrinsic
+// (__fmul_rn/__fadd_rn/__fsub_rn never contract into FMA; __frcp_rn / __fdiv_rn / __fsqrt_rn are IEEE) in the
+// reference's operation order → bit-identical t and ids. FAST mode lets the triangle test contract into FMA.
+#include "device_types.h"
+
+namespace atray {
+
+#define FULL_MASK 0xffffffffu
+static constexpr float kTol = 0.0001f;               // ray.h:5
+static constexpr float kMaxFloat = 3.402823466e+38F;  // PL_base_defs.h:70
+static constexpr int kLeafCap = 48;                   // per-lane leaf list (local memory); overflow → per-warp spill area
+static constexpr int kStackCap = 48;                  // per-lane inner-node stack
+static constexpr int kBlock = 256;                    // 8 warps per CTA
+
+struct RayL { float ox, oy, oz, dx, dy, dz; };
+
+__device__ __forceinline__ float mulr(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ float addr(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ float subr(float a, float b) { return __fsub_rn(a, b); }
+
+template <bool STRICT> struct Fp
+{
+    static __device__ __forceinline__ float mul(float a, float b) { return STRICT ? __fmul_rn(a, b) : a * b; }
+    static __device__ __forceinline__ float add(float a, float b) { return STRICT ? __fadd_rn(a, b) : a + b; }
+    static __device__ __forceinline__ float sub(float a, float b) { return STRICT ? __fsub_rn(a, b) : a - b; }
+    // dot = (ax*bx + ay*by) + az*bz ; cross component = p*q - r*s  (PL_math.h:416, 422)
+    static __device__ __forceinline__ float dot(float ax, float ay, float az, float bx, float by, float bz)
+    {
+        return add(add(mul(ax, bx), mul(ay, by)), mul(az, bz));
+    }
+    static __device__ __forceinline__ float crs(float p, float q, float r, float s) { return sub(mul(p, q), mul(r, s)); }
+};
+
+struct WorkCount
+{
+    unsigned int box, tri, pdet, pu, pv, listed, scanned, ovf;
+    __device__ void clear() { box = tri = pdet = pu = pv = listed = scanned = ovf = 0; }
+};
+
+// ---- ray/box slab tests (aabb.h). `near`/`far` selection by the sign of 1/d is the reference's bounds[sign] indexing.
+struct BoxT { float tmin, tmax; bool ok; };
+
+__device__ __forceinline__ BoxT slab_xy_z(const RayL& r, float ix, float iy, float iz, float4 lo, float4 hi, bool full)
+{
+    BoxT o;
+    const bool sx = ix < 0.0f, sy = iy < 0.0f, sz = iz < 0.0f;
+    float tmin = mulr(subr(sx ? hi.x : lo.x, r.ox), ix);
+    float tmax = mulr(subr(sx ? lo.x : hi.x, r.ox), ix);
+    const float tymin = mulr(subr(sy ? hi.y : lo.y, r.oy), iy);
+    const float tymax = mulr(subr(sy ? lo.y : hi.y, r.oy), iy);
+    o.ok = !((tmin > tymax) || (tymin > tmax));
+    if (tymin > tmin) tmin = tymin;
+    if (tymax < tmax) tmax = tymax;
+    const float tzmin = mulr(subr(sz ? hi.z : lo.z, r.oz), iz);
+    const float tzmax = mulr(subr(sz ? lo.z : hi.z, r.oz), iz);
+    o.ok = o.ok && !((tmin > tzmax) || (tzmin > tmax));
+    if (full)
+    {
+        if (tzmin > tmin) tmin = tzmin;
+        if (tzmax < tmax) tmax = tzmax;
+    }
+    o.tmin = tmin;
+    o.tmax = tmax;
+    return o;
+}
+// check_ray_AABB_intersection, aabb.h:65-93 (no sign test: boxes behind the ray pass)
+__device__ __forceinline__ bool box_check(const RayL& r, float ix, float iy, float iz, float4 lo, float4 hi)
+{
+    return slab_xy_z(r, ix, iy, iz, lo, hi, false).ok;
+}
+// get_ray_AABB_intersection, aabb.h:29-63: tmin if > 0, else tmax if > 0, else 0
+__device__ __forceinline__ float box_entry(const RayL& r, float ix, float iy, float iz, float4 lo, float4 hi)
+{
+    BoxT b = slab_xy_z(r, ix, iy, iz, lo, hi, true);
+    if (!b.ok) return 0.0f;
+    if (b.tmin > 0.0f) return b.tmin;
+    if (b.tmax > 0.0f) return b.tmax;
+    return 0.0f;
+}
+
+// ---- phase 1: collect the sorted leaf list of one ray (kd_tree.cpp:363-435). Returns false on capacity overflow.
+template <bool COUNT>
+__device__ bool collect_leaves(const float4* __restrict__ nodes, const RayL& r, float ix, float iy, float iz, uint32_t* stack,
+                               int stack_cap, uint2* leaves, int leaf_cap, int& nleaf, WorkCount& wc)
+{
+    nleaf = 0;
+    int sp = 1;
+    stack[0] = 0u;
+    while (sp > 0)
+    {
+        const uint32_t cur = stack[--sp];
+        const uint32_t c0 = (uint32_t)__float_as_int(__ldg(&nodes[2 * cur]).w);
+        int accepted = 0;
+#pragma unroll 1
+        for (int i = 0; i < 8 && accepted <= 4; ++i)  // at most 5 accepted children (kd_tree.cpp:374)
+        {
+            const uint32_t ch = c0 + i;
+            const float4 lo = __ldg(&nodes[2 * ch]);
+            const float4 hi = __ldg(&nodes[2 * ch + 1]);
+            if (COUNT) wc.box++;
+            if (__float_as_int(lo.w) > 0)  // inner child
+            {
+                if (box_check(r, ix, iy, iz, lo, hi))
+                {
+                    ++accepted;
+                    if (sp >= stack_cap) return false;
+                    stack[sp++] = ch;
+                }
+            }
+            else  // leaf child (possibly empty)
+            {
+                const float dis = box_entry(r, ix, iy, iz, lo, hi);
+                if (dis > 0.0f)
+                {
+                    ++accepted;
+                    if (nleaf >= leaf_cap) return false;
+                    int k = nleaf;  // stable insertion from the back: ties and later arrivals go after existing entries
+                    while (k > 0 && dis < __uint_as_float(leaves[k - 1].y))
+                    {
+                        leaves[k] = leaves[k - 1];
+                        --k;
+                    }
+                    leaves[k] = make_uint2(ch, __float_as_uint(dis));
+                    ++nleaf;
+                    if (COUNT) wc.listed++;
+                }
+            }
+        }
+    }
+    return true;
+}
+
+// ---- phase 2: warp-cooperative scan of ONE ray's leaf list (kd_tree.cpp:437-462). All 32 lanes call this with the
+// same `src` lane; the ray and the list entries are broadcast from that lane. Lane `src` receives the result.
+template <bool STRICT, bool COUNT>
+__device__ __forceinline__ void scan_ray_leaves(const DevScene& sc, int lane, int src, const RayL& mine, const uint2* my_list,
+                                                int my_nleaf, float& out_t, uint32_t& out_face, WorkCount& wc)
+{
+    typedef Fp<STRICT> F;
+    const float ox = __shfl_sync(FULL_MASK, mine.ox, src), oy = __shfl_sync(FULL_MASK, mine.oy, src),
+                oz = __shfl_sync(FULL_MASK, mine.oz, src);
+    const float dx = __shfl_sync(FULL_MASK, mine.dx, src), dy = __shfl_sync(FULL_MASK, mine.dy, src),
+                dz = __shfl_sync(FULL_MASK, mine.dz, src);
+    const int n = __shfl_sync(FULL_MASK, my_nleaf, src);
+    for (int k = 0; k < n; ++k)
+    {
+        uint32_t node = 0;
+        if (lane == src) node = my_list[k].x;
+        node = __shfl_sync(FULL_MASK, node, src);
+        const uint32_t first = ~(uint32_t)__float_as_int(__ldg(&sc.nodes[2 * node]).w);
+        const uint32_t cnt = (uint32_t)__float_as_int(__ldg(&sc.nodes[2 * node + 1]).w);
+        if (COUNT && lane == src) wc.scanned++;
+        float bt = kMaxFloat;
+        uint32_t bpos = 0xffffffffu, bface = 0xffffffffu;
+        const float4* blk = sc.tris + (size_t)(first >> 5) * 96 + lane;
+        for (uint32_t base = 0; base < cnt; base += 32, blk += 96)
+        {
+            const float4 A = __ldg(blk);
+            const float4 AB = __ldg(blk + 32);
+            const float4 AC = __ldg(blk + 64);
+            const bool real = base + lane < cnt;
+            // get_triangle_ray_intersection_culled, model.h:75-103 (ab, ac precomputed with the same f32 subtraction)
+            const float px = F::crs(dy, AC.z, dz, AC.y), py = F::crs(dz, AC.x, dx, AC.z), pz = F::crs(dx, AC.y, dy, AC.x);
+            const float det = F::dot(AB.x, AB.y, AB.z, px, py, pz);
+            bool alive = !(det < kTol);
+            if (COUNT) { wc.tri += real ? 1u : 0u; wc.pdet += (real && alive) ? 1u : 0u; }
+            if (!__any_sync(FULL_MASK, alive)) continue;
+            const float det_inv = __frcp_rn(det);  // 1 / det, IEEE round-to-nearest
+            const float tx = F::sub(ox, A.x), ty = F::sub(oy, A.y), tz = F::sub(oz, A.z);
+            const float u = F::mul(F::dot(tx, ty, tz, px, py, pz), det_inv);
+            alive = alive && !(u < 0.0f || u > 1.0f);
+            if (COUNT) wc.pu += (real && alive) ? 1u : 0u;
+            if (!__any_sync(FULL_MASK, alive)) continue;
+            const float qx = F::crs(ty, AB.z, tz, AB.y), qy = F::crs(tz, AB.x, tx, AB.z), qz = F::crs(tx, AB.y, ty, AB.x);
+            const float v = F::mul(F::dot(dx, dy, dz, qx, qy, qz), det_inv);
+            alive = alive && !(v < 0.0f || F::add(u, v) > 1.0f);
+            if (COUNT) wc.pv += (real && alive) ? 1u : 0u;
+            if (!__any_sync(FULL_MASK, alive)) continue;
+            const float t = F::mul(F::dot(qx, qy, qz, AC.x, AC.y, AC.z), det_inv);
+            if (alive && t < bt && t > kTol)  // caller's accept: distance < closest && distance > tolerance
+            {
+                bt = t;
+                bpos = base + lane;
+                bface = __float_as_uint(A.w);
+            }
+        }
+        // sequential strict-< scan ≡ lexicographic arg-min over (t, slot)
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1)
+        {
+            const float ot = __shfl_xor_sync(FULL_MASK, bt, off);
+            const uint32_t op = __shfl_xor_sync(FULL_MASK, bpos, off);
+            const uint32_t of = __shfl_xor_sync(FULL_MASK, bface, off);
+            if (ot < bt || (ot == bt && op < bpos)) { bt = ot; bpos = op; bface = of; }
+        }
+        if (bt < kMaxFloat)  // this leaf produced a hit → stop (kd_tree.cpp:457-460)
+        {
+            if (lane == src) { out_t = bt; out_face = bface; }
+            break;
+        }
+    }
+}
+
+// ---- one warp traces up to 32 rays (one per lane). Result: t (MAX_FLOAT on miss) and face (MISS) per lane.
+template <bool STRICT, bool COUNT>
+__device__ __forceinline__ void trace_warp(const DevScene& sc, const DevScratch& scratch, int warp_slot, int lane, bool active,
+                                           const RayL& ray, float& t_out, uint32_t& face_out, WorkCount& wc)
+{
+    uint2 leaves[kLeafCap];
+    uint32_t stack[kStackCap];
+    t_out = kMaxFloat;
+    face_out = 0xffffffffu;
+    int nleaf = 0;
+    bool overflow = false;
+    // Optimized_Ray, renderer.cpp:41-44
+    const float ix = __frcp_rn(ray.dx), iy = __frcp_rn(ray.dy), iz = __frcp_rn(ray.dz);
+    if (active)
+    {
+        const float4 lo = __ldg(&sc.nodes[0]);
+        const float4 hi = __ldg(&sc.nodes[1]);
+        if (COUNT) wc.box++;
+        if (box_check(ray, ix, iy, iz, lo, hi))  // kd_tree.cpp:339
+        {
+            if (sc.root_is_leaf)  // kd_tree.cpp:344-361: scan the root's primitives, no entry-distance filter
+            {
+                leaves[0] = make_uint2(0u, 0u);
+                nleaf = 1;
+            }
+            else
+                overflow = !collect_leaves<COUNT>(sc.nodes, ray, ix, iy, iz, stack, kStackCap, leaves, kLeafCap, nleaf, wc);
+            if (overflow) nleaf = 0;
+        }
+    }
+    unsigned todo = __ballot_sync(FULL_MASK, nleaf > 0);
+    while (todo)
+    {
+        const int src = __ffs(todo) - 1;
+        todo &= todo - 1;
+        scan_ray_leaves<STRICT, COUNT>(sc, lane, src, ray, leaves, nleaf, t_out, face_out, wc);
+    }
+    // rare: list or stack outgrew the per-lane arrays → redo that ray with the warp's spill area in global memory
+    unsigned spill = __ballot_sync(FULL_MASK, overflow);
+    while (spill)
+    {
+        const int src = __ffs(spill) - 1;
+        spill &= spill - 1;
+        uint2* gl = scratch.leaves + (size_t)warp_slot * scratch.leaf_cap;
+        uint32_t* gs = scratch.stack + (size_t)warp_slot * scratch.stack_cap;
+        int gn = 0;
+        if (lane == src)
+        {
+            if (COUNT) wc.ovf++;
+            WorkCount dummy;
+            dummy.clear();
+            // the aborted first attempt already counted a partial walk; the redo is not counted again
+            collect_leaves<false>(sc.nodes, ray, ix, iy, iz, gs, (int)scratch.stack_cap, gl, (int)scratch.leaf_cap, gn, dummy);
+        }
+        __syncwarp();
+        scan_ray_leaves<STRICT, COUNT>(sc, lane, src, ray, gl, gn, t_out, face_out, wc);
+        __syncwarp();
+    }
+}
+
+// ---- camera ray, renderer.cpp:317,329,350-351 + SetRay ray.h:24-29 + normalize PL_math.h:387-392 (always strict)
+__device__ __forceinline__ RayL camera_ray(const DevCamera& cm, float fx, float fy)
+{
+    RayL r;
+    r.ox = cm.eye[0]; r.oy = cm.eye[1]; r.oz = cm.eye[2];
+    const float px = addr(addr(cm.fc[0], mulr(cm.cx[0], fx)), mulr(cm.cy[0], fy));
+    const float py = addr(addr(cm.fc[1], mulr(cm.cx[1], fx)), mulr(cm.cy[1], fy));
+    const float pz = addr(addr(cm.fc[2], mulr(cm.cx[2], fx)), mulr(cm.cy[2], fy));
+    const float dx = subr(px, r.ox), dy = subr(py, r.oy), dz = subr(pz, r.oz);
+    const float len2 = addr(addr(mulr(dx, dx), mulr(dy, dy)), mulr(dz, dz));
+    const float inv = __fdiv_rn(1.0f, __fsqrt_rn(len2));
+    r.dx = mulr(dx, inv); r.dy = mulr(dy, inv); r.dz = mulr(dz, inv);
+    return r;
+}
+__device__ __forceinline__ float film_coord(int i, int n) { return addr(-1.0f, mulr(2.0f, __fdiv_rn((float)i, (float)n))); }
+
+// clamp (PL_math.h:430-436), rgb_float_to_byte (:489, truncation), Set_Pixel packing (texture.h:27-38)
+__device__ __forceinline__ uint32_t pack_bgrx(float r, float g, float b)
+{
+    r = 0.0f > (r > 1.0f ? 1.0f : r) ? 0.0f : (r > 1.0f ? 1.0f : r);
+    g = 0.0f > (g > 1.0f ? 1.0f : g) ? 0.0f : (g > 1.0f ? 1.0f : g);
+    b = 0.0f > (b > 1.0f ? 1.0f : b) ? 0.0f : (b > 1.0f ? 1.0f : b);
+    const uint32_t R = (uint32_t)(unsigned char)(int)mulr(r, 255.0f), G = (uint32_t)(unsigned char)(int)mulr(g, 255.0f),
+                   B = (uint32_t)(unsigned char)(int)mulr(b, 255.0f);
+    return B | (G << 8) | (R << 16);
+}
+
+// PCG32 (PL_math.h:506-541) with the per-pixel stream of SURVEY §8(d) C3
+struct Pcg { unsigned long long state, stream; };
+__device__ __forceinline__ unsigned long long splitmix64(unsigned long long x)
+{
+    x += 0x9e3779b97f4a7c15ULL;
+    x = (x ^ (x >> 30)) * 0xbf58476d1ce4e5b9ULL;
+    x = (x ^ (x >> 27)) * 0x94d049bb133111ebULL;
+    return x ^ (x >> 31);
+}
+__device__ __forceinline__ uint32_t pcg_u32(Pcg& s)
+{
+    const unsigned long long old = s.state;
+    s.state = old * 6364136223846793005ULL + (s.stream | 1ULL);
+    const uint32_t xs = (uint32_t)(((old >> 18u) ^ old) >> 27u);
+    const uint32_t rot = (uint32_t)(old >> 59u);
+    return (xs >> rot) | (xs << ((0u - rot) & 31u));
+}
+__device__ __forceinline__ float pcg_bi(Pcg& s) { return addr(-1.0f, mulr(2.0f, mulr((float)pcg_u32(s), 2.328306437e-10F))); }
+
+__device__ __forceinline__ void flush_counters(DevCounters* c, const WorkCount& wc, unsigned int rays)
+{
+    auto red = [](unsigned int v) {
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) v += __shfl_xor_sync(FULL_MASK, v, off);
+        return (unsigned long long)v;
+    };
+    const unsigned long long r = red(rays), b = red(wc.box), t = red(wc.tri), d = red(wc.pdet), u = red(wc.pu), v = red(wc.pv),
+                             l = red(wc.listed), s = red(wc.scanned), o = red(wc.ovf);
+    if ((threadIdx.x & 31) == 0)
+    {
+        atomicAdd(&c->rays, r); atomicAdd(&c->box_tests, b); atomicAdd(&c->tri_tests, t); atomicAdd(&c->pass_det, d);
+        atomicAdd(&c->pass_u, u); atomicAdd(&c->pass_v, v); atomicAdd(&c->leaves_listed, l); atomicAdd(&c->leaves_scanned, s);
+        atomicAdd(&c->overflow_rays, o);
+    }
+}
+
+// ---- K1: fused primary-ray render (replaces render_tile_from_camera and the tile thread pool) ----------------
+template <bool STRICT, bool COUNT>
+__global__ void __launch_bounds__(kBlock) k_render(DevScene sc, DevCamera cm, DevPartition part, DevOut out, DevScratch scratch,
+                                                   unsigned int* tile_counter, DevCounters* counters,
+                                                   unsigned long long jitter_seed)
+{
+    const int lane = threadIdx.x & 31;
+    const int warp_slot = (blockIdx.x * kBlock + threadIdx.x) >> 5;
+    const int tiles_x = (cm.W + 7) >> 3;
+    const int rows_per_band = part.band_rows >> 2;  // tile rows per band (band_rows is a multiple of 4)
+    const int n_bands = (cm.H + part.band_rows - 1) / part.band_rows;
+    const int my_bands = part.rank < n_bands ? (n_bands - part.rank + part.world - 1) / part.world : 0;
+    const unsigned int tiles_per_band = (unsigned int)(tiles_x * rows_per_band);
+    const unsigned int n_tiles = (unsigned int)my_bands * tiles_per_band;
+    WorkCount wc;
+    wc.clear();
+    unsigned int rays_done = 0;
+    for (;;)
+    {
+        unsigned int tile = 0;
+        if (lane == 0) tile = atomicAdd(tile_counter, 1u);
+        tile = __shfl_sync(FULL_MASK, tile, 0);
+        if (tile >= n_tiles) break;
+        const unsigned int lb = tile / tiles_per_band, rem = tile - lb * tiles_per_band;
+        const int trow = (int)(rem / (unsigned int)tiles_x), tcol = (int)(rem - (unsigned int)trow * (unsigned int)tiles_x);
+        const int x = tcol * 8 + (lane & 7);
+        const int y = ((int)lb * part.world + part.rank) * part.band_rows + trow * 4 + (lane >> 3);
+        const bool active = x < cm.W && y < cm.H;
+        const float film_y = film_coord(y, cm.H);                                                    // renderer.cpp:317
+        const float film_x = mulr(mulr(film_coord(x, cm.W), cm.h_fov), cm.aspect);                  // renderer.cpp:329
+        float t = kMaxFloat;
+        uint32_t face = 0xffffffffu;
+        float cr = 0.0f, cg = 0.0f, cb = 0.0f;
+        if (!cm.aa)
+        {
+            const RayL ray = camera_ray(cm, film_x, film_y);  // renderer.cpp:350-351
+            trace_warp<STRICT, COUNT>(sc, scratch, warp_slot, lane, active, ray, t, face, wc);
+            const bool hit = face != 0xffffffffu;
+            const float er = hit ? sc.mdl[0] : sc.sky[0], eg = hit ? sc.mdl[1] : sc.sky[1], eb = hit ? sc.mdl[2] : sc.sky[2];
+            for (uint32_t s = 0; s < cm.spp; ++s) { cr = addr(cr, er); cg = addr(cg, eg); cb = addr(cb, eb); }  // :353-356
+            if (active) rays_done += 1;
+        }
+        else
+        {
+            const unsigned long long p = (unsigned long long)y * (unsigned long long)cm.W + (unsigned long long)x;
+            Pcg rng;
+            rng.state = splitmix64(jitter_seed ^ p);
+            rng.stream = 2ULL * p + 1ULL;
+            for (uint32_t s = 0; s < cm.spp; ++s)  // renderer.cpp:336-347
+            {
+                const float x_off = addr(mulr(pcg_bi(rng), cm.hpw), film_x);
+                const float y_off = addr(mulr(pcg_bi(rng), cm.hph), film_y);
+                const RayL ray = camera_ray(cm, x_off, y_off);
+                trace_warp<STRICT, COUNT>(sc, scratch, warp_slot, lane, active, ray, t, face, wc);
+                const bool hit = face != 0xffffffffu;
+                if (hit) { pcg_bi(rng); pcg_bi(rng); pcg_bi(rng); }  // cast_ray's random bounce draws (renderer.cpp:246)
+                cr = addr(cr, hit ? sc.mdl[0] : sc.sky[0]);
+                cg = addr(cg, hit ? sc.mdl[1] : sc.sky[1]);
+                cb = addr(cb, hit ? sc.mdl[2] : sc.sky[2]);
+                if (active) rays_done += 1;
+            }
+        }
+        if (active)
+        {
+            const float n = (float)cm.spp;
+            const size_t idx = (size_t)y * (size_t)cm.W + (size_t)x;
+            if (out.bgrx) out.bgrx[idx] = pack_bgrx(__fdiv_rn(cr, n), __fdiv_rn(cg, n), __fdiv_rn(cb, n));  // :358-365
+            if (out.t) out.t[idx] = t;
+            if (out.prim) out.prim[idx] = face;
+        }
+    }
+    if (COUNT) flush_counters(counters, wc, rays_done);
+}
+
+// ---- K2: ray-list trace (get_intersection_data model branch for arbitrary rays) ---------------------------------
+template <bool STRICT, bool COUNT>
+__global__ void __launch_bounds__(kBlock) k_trace(DevScene sc, const float* __restrict__ rays, unsigned long long n, uint32_t* prim,
+                                                  float* tout, DevScratch scratch, unsigned int* tile_counter, DevCounters* counters)
+{
+    const int lane = threadIdx.x & 31;
+    const int warp_slot = (blockIdx.x * kBlock + threadIdx.x) >> 5;
+    const unsigned long long n_groups = (n + 31ULL) >> 5;
+    WorkCount wc;
+    wc.clear();
+    unsigned int rays_done = 0;
+    for (;;)
+    {
+        unsigned int g = 0;
+        if (lane == 0) g = atomicAdd(tile_counter, 1u);
+        g = __shfl_sync(FULL_MASK, g, 0);
+        if ((unsigned long long)g >= n_groups) break;
+        const unsigned long long i = ((unsigned long long)g << 5) + (unsigned long long)lane;
+        const bool active = i < n;
+        RayL ray = {0.f, 0.f, 0.f, 0.f, 0.f, 1.f};
+        if (active)
+        {
+            const float2* q = reinterpret_cast<const float2*>(rays + 6ULL * i);
+            const float2 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2);
+            ray.ox = a.x; ray.oy = a.y; ray.oz = b.x; ray.dx = b.y; ray.dy = c.x; ray.dz = c.y;
+        }
+        float t;
+        uint32_t face;
+        trace_warp<STRICT, COUNT>(sc, scratch, warp_slot, lane, active, ray, t, face, wc);
+        if (active)
+        {
+            prim[i] = face;
+            tout[i] = t;
+            rays_done += 1;
+        }
+    }
+    if (COUNT) flush_counters(counters, wc, rays_done);
+}
+
+// ---- K0: microbenchmarks for the roofline denominators ------------------------------------------------------------
+__global__ void k_fp32_issue(float* sink, int iters)
+{
+    float a0 = threadIdx.x * 1e-3f, a1 = a0 + 1.f, a2 = a0 + 2.f, a3 = a0 + 3.f, a4 = a0 + 4.f, a5 = a0 + 5.f, a6 = a0 + 6.f, a7 = a0 + 7.f;
+    const float m = 0.999f, c = 1e-3f;
+    for (int i = 0; i < iters; ++i)
+    {
+#pragma unroll
+        for (int u = 0; u < 8; ++u)
+        {
+            a0 = fmaf(a0, m, c); a1 = fmaf(a1, m, c); a2 = fmaf(a2, m, c); a3 = fmaf(a3, m, c);
+            a4 = fmaf(a4, m, c); a5 = fmaf(a5, m, c); a6 = fmaf(a6, m, c); a7 = fmaf(a7, m, c);
+        }
+    }
+    const float s = ((a0 + a1) + (a2 + a3)) + ((a4 + a5) + (a6 + a7));
+    if (s == 123456.789f) sink[0] = s;
+}
+__global__ void k_l2_read(const float4* __restrict__ buf, size_t n_vec, int passes, float* sink)
+{
+    float acc = 0.f;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (int p = 0; p < passes; ++p)
+        for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_vec; i += stride)
+        {
+            const float4 v = __ldcg(buf + i);  // L2 only (bypass L1) so the figure is an L2 read rate
+            acc += v.x + v.y + v.z + v.w;
+        }
+    if (acc == 123456.789f) sink[0] = acc;
+}
+
+// ---- launchers ------------------------------------------------------------------------------------------------------
+LaunchCfg render_launch_cfg(int sm_count)
+{
+    LaunchCfg c;
+    c.block = kBlock;
+    c.grid = sm_count * 4;  // persistent: 4 resident CTAs of 8 warps per SM (B200: 148 SMs → 592 CTAs)
+    return c;
+}
+int render_warps_in_flight(LaunchCfg cfg) { return cfg.grid * (cfg.block / 32); }
+
+cudaError_t launch_render(const DevScene& sc, const DevCamera& cam, const DevPartition& part, const DevOut& out,
+                          const DevScratch& scratch, unsigned int* tile_counter, DevCounters* counters, int fp_fast,
+                          unsigned long long jitter_seed, LaunchCfg cfg, cudaStream_t stream)
+{
+    cudaError_t e = cudaMemsetAsync(tile_counter, 0, sizeof(unsigned int), stream);
+    if (e != cudaSuccess) return e;
+    if (counters)
+    {
+        if (fp_fast) k_render<false, true><<<cfg.grid, cfg.block, 0, stream>>>(sc, cam, part, out, scratch, tile_counter, counters, jitter_seed);
+        else k_render<true, true><<<cfg.grid, cfg.block, 0, stream>>>(sc, cam, part, out, scratch, tile_counter, counters, jitter_seed);
+    }
+    else
+    {
+        if (fp_fast) k_render<false, false><<<cfg.grid, cfg.block, 0, stream>>>(sc, cam, part, out, scratch, tile_counter, counters, jitter_seed);
+        else k_render<true, false><<<cfg.grid, cfg.block, 0, stream>>>(sc, cam, part, out, scratch, tile_counter, counters, jitter_seed);
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t launch_trace(const DevScene& sc, const float* rays, unsigned long long n, uint32_t* prim, float* t,
+                         const DevScratch& scratch, unsigned int* tile_counter, DevCounters* counters, int fp_fast,
+                         LaunchCfg cfg, cudaStream_t stream)
+{
+    cudaError_t e = cudaMemsetAsync(tile_counter, 0, sizeof(unsigned int), stream);
+    if (e != cudaSuccess) return e;
+    if (counters)
+    {
+        if (fp_fast) k_trace<false, true><<<cfg.grid, cfg.block, 0, stream>>>(sc, rays, n, prim, t, scratch, tile_counter, counters);
+        else k_trace<true, true><<<cfg.grid, cfg.block, 0, stream>>>(sc, rays, n, prim, t, scratch, tile_counter, counters);
+    }
+    else
+    {
+        if (fp_fast) k_trace<false, false><<<cfg.grid, cfg.block, 0, stream>>>(sc, rays, n, prim, t, scratch, tile_counter, counters);
+        else k_trace<true, false><<<cfg.grid, cfg.block, 0, stream>>>(sc, rays, n, prim, t, scratch, tile_counter, counters);
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t launch_microbench_fp32(float* sink, int iters, LaunchCfg cfg, cudaStream_t stream)
+{
+    k_fp32_issue<<<cfg.grid, cfg.block, 0, stream>>>(sink, iters);
+    return cudaGetLastError();
+}
+cudaError_t launch_microbench_l2(const float4* buf, size_t n_vec, int passes, float* sink, LaunchCfg cfg, cudaStream_t stream)
+{
+    k_l2_read<<<cfg.grid, cfg.block, 0, stream>>>(buf, n_vec, passes, sink);
+    return cudaGetLastError();
+}
+
+}  // namespace atray

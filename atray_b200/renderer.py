@@ -1,0 +1,194 @@
+"""Device side of the Python mirror: prep_scene / start_render_from_camera / wait_for_render_from_camera_to_finish
+(renderer.h:32-35) on top of the C ABI. Every call here ends in a CUDA kernel of libatray_b200.so."""
+import ctypes as C
+
+import numpy as np
+
+from . import api
+from .api import _L, _ck, _p, _vp
+
+
+class PinnedArray:
+    """numpy view over page-locked host memory (the host bitmap of Setup_Texture, texture.cpp:133-146)."""
+
+    def __init__(self, shape, dtype):
+        self.nbytes = int(np.prod(shape)) * np.dtype(dtype).itemsize
+        ptr = _vp()
+        _ck(_L.atray_host_alloc_pinned(self.nbytes, C.byref(ptr)))
+        self.ptr = ptr.value
+        buf = (C.c_char * self.nbytes).from_address(self.ptr)
+        self.array = np.frombuffer(buf, dtype=dtype).reshape(shape)
+
+    def free(self):
+        if self.ptr:
+            self.array = None
+            _L.atray_host_free_pinned(self.ptr)
+            self.ptr = None
+
+
+class Context:
+    """One GPU: uploaded scene + stream (atray_ctx)."""
+
+    def __init__(self, device=0):
+        h = _vp()
+        _ck(_L.atray_ctx_create(device, C.byref(h)))
+        self.h = h
+        self.device = device
+        self._keep = None
+
+    def close(self):
+        if getattr(self, "h", None):
+            _L.atray_ctx_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        self.close()
+
+    # -- scene ------------------------------------------------------------------------------------------------------
+    def upload(self, model, sky=api.SKY_MATERIAL, material=api.MODEL_MATERIAL):
+        s, m = api.make_material(sky), api.make_material(material)
+        _ck(_L.atray_scene_upload(self.h, model.h, C.byref(s), C.byref(m)))
+
+    # -- frames -----------------------------------------------------------------------------------------------------
+    @staticmethod
+    def opts(fp_mode=api.FP_STRICT, count_work=False, seed=api.DEFAULT_SEED, rank=0, world=1, band_rows=8):
+        return api.RenderOpts(fp_mode, 1 if count_work else 0, seed, api.Partition(rank, world, band_rows))
+
+    def render_begin(self, cam, opts, bgrx=None, t=None, prim=None):
+        fr = api.Frame(_p(bgrx) if bgrx is not None else None, _p(t) if t is not None else None,
+                       _p(prim) if prim is not None else None)
+        self._keep = (bgrx, t, prim)
+        _ck(_L.atray_render_begin(self.h, C.byref(cam), C.byref(opts), C.byref(fr)))
+
+    def render_poll(self, timeout_ms=0xFFFFFFFF):
+        return _ck(_L.atray_render_poll(self.h, timeout_ms))
+
+    def render(self, cam, opts=None, want=("bgrx", "t", "prim")):
+        """Synchronous convenience: one frame into fresh numpy arrays (row 0 = bottom scanline)."""
+        opts = opts or self.opts()
+        H, W = cam.height, cam.width
+        out = {"bgrx": np.zeros((H, W), np.uint32) if "bgrx" in want else None,
+               "t": np.zeros((H, W), np.float32) if "t" in want else None,
+               "prim": np.zeros((H, W), np.uint32) if "prim" in want else None}
+        self.render_begin(cam, opts, out["bgrx"], out["t"], out["prim"])
+        while self.render_poll(1000):
+            pass
+        return out
+
+    def render_device(self, cam, opts, d_bgrx=0, d_t=0, d_prim=0):
+        fr = api.Frame(d_bgrx or None, d_t or None, d_prim or None)
+        _ck(_L.atray_render_device(self.h, C.byref(cam), C.byref(opts), C.byref(fr)))
+
+    def sync(self):
+        _ck(_L.atray_ctx_sync(self.h))
+
+    def last_kernel_ms(self):
+        ms = C.c_float(0)
+        _ck(_L.atray_last_kernel_ms(self.h, C.byref(ms)))
+        return ms.value
+
+    def counters(self):
+        c = api.Counters()
+        _ck(_L.atray_get_counters(self.h, C.byref(c)))
+        return c.as_dict()
+
+    # -- ray lists ----------------------------------------------------------------------------------------------------
+    def trace_rays(self, rays, fp_mode=api.FP_STRICT, count_work=False):
+        rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 6)
+        n = rays.shape[0]
+        prim = np.zeros(n, np.uint32)
+        t = np.zeros(n, np.float32)
+        _ck(_L.atray_trace_rays(self.h, _p(rays), n, fp_mode, 1 if count_work else 0, _p(prim), _p(t)))
+        return prim, t
+
+    def trace_rays_device(self, d_rays, n, d_prim, d_t, fp_mode=api.FP_STRICT, count_work=False):
+        _ck(_L.atray_trace_rays_device(self.h, d_rays, n, fp_mode, 1 if count_work else 0, d_prim, d_t))
+
+    # -- memory -------------------------------------------------------------------------------------------------------
+    def dev_alloc(self, nbytes):
+        p = _vp()
+        _ck(_L.atray_dev_alloc(self.h, nbytes, C.byref(p)))
+        return p.value
+
+    def dev_free(self, p):
+        _ck(_L.atray_dev_free(self.h, p))
+
+    def to_host(self, dev_ptr, arr):
+        _ck(_L.atray_dev_copy_to_host(self.h, _p(arr), dev_ptr, arr.nbytes))
+        return arr
+
+    def from_host(self, dev_ptr, arr):
+        arr = np.ascontiguousarray(arr)
+        _ck(_L.atray_dev_copy_from_host(self.h, dev_ptr, _p(arr), arr.nbytes))
+
+    def ipc_export(self, dev_ptr):
+        h = np.zeros(64, np.uint8)
+        _ck(_L.atray_ipc_export(self.h, dev_ptr, _p(h)))
+        return h.tobytes()
+
+    def ipc_open(self, handle_bytes):
+        h = np.frombuffer(handle_bytes, np.uint8).copy()
+        p = _vp()
+        _ck(_L.atray_ipc_open(self.h, _p(h), C.byref(p)))
+        return p.value
+
+    def ipc_close(self, p):
+        _ck(_L.atray_ipc_close(self.h, p))
+
+    def microbench(self):
+        a, b = C.c_double(0), C.c_double(0)
+        _ck(_L.atray_microbench(self.h, C.byref(a), C.byref(b)))
+        return {"fp32_lane_ops_per_s": a.value, "l2_read_gbs": b.value}
+
+
+# ---- reference-named entry points (renderer.h:32-35) -----------------------------------------------------------------
+class Scene:
+    """Scene (scene.h:13-24) restricted to what the path uses: materials[0] = sky, one model with its material."""
+
+    def __init__(self, model, sky=api.SKY_MATERIAL, material=api.MODEL_MATERIAL, division_method=api.DIV_SAH,
+                 max_no_faces_per_node=300):
+        self.model, self.sky, self.material = model, sky, material
+        self.division_method, self.max_no_faces_per_node = division_method, max_no_faces_per_node
+        self.ctx = None
+
+
+class RenderInfo:
+    """RenderInfo (renderer.h:17-30): camera, scene, camera_tex (host BGRX bitmap) + the two extra planes."""
+
+    def __init__(self, camera, scene, camera_tex, t=None, prim=None, opts=None):
+        self.camera, self.scene, self.camera_tex, self.t, self.prim = camera, scene, camera_tex, t, prim
+        self.opts = opts
+        self.jobs_done, self.jobs_size = 0, 0
+        self.total_ray_casts = 0
+
+
+def prep_scene(scene, device=0):
+    """prep_scene(Scene&, uint32&) — renderer.cpp:264-291: build the tree if the model has none, then (new) flatten and
+    upload once. Returns the node count (kd_tree_max_nodes)."""
+    n = scene.model.counts()
+    if n["nodes"] == 0:
+        api.build_KD_tree(scene.model, scene.division_method, scene.max_no_faces_per_node)
+        n = scene.model.counts()
+    if scene.ctx is None:
+        scene.ctx = Context(device)
+    scene.ctx.upload(scene.model, scene.sky, scene.material)
+    return n["nodes"]
+
+
+def start_render_from_camera(info, tpool=None):
+    """start_render_from_camera(RenderInfo&, ThreadPool&) — renderer.cpp:403-455. Returns immediately; `tpool` is
+    accepted for signature parity and ignored (the tile thread pool is replaced by the kernel)."""
+    opts = info.opts or Context.opts()
+    info.jobs_size, info.jobs_done = 1, 0
+    info.scene.ctx.render_begin(info.camera, opts, info.camera_tex, info.t, info.prim)
+
+
+def wait_for_render_from_camera_to_finish(info, tpool=None, ms_to_wait_for=33):
+    """renderer.cpp:457-471: TRUE (1) while still running, FALSE (0) when finished."""
+    running = info.scene.ctx.render_poll(ms_to_wait_for)
+    if not running:
+        info.jobs_done = info.jobs_size
+        # ray_casts counts non-sky bounce iterations (renderer.cpp:222-231,260): at bounce 1 = samples that hit geometry
+        if info.prim is not None and info.camera.samples_per_pixel == 1:
+            info.total_ray_casts = int((info.prim != api.MISS).sum())
+    return running

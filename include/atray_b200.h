@@ -1,0 +1,174 @@
+/* atray_b200 — C ABI of the B200-native (sm_100a) implementation of ATRay's per-pixel render path.
+ *
+ * This is the drop-in boundary: plain pointers and sizes, no C++/torch types. Each entry point names the
+ * reference interface it replaces (paths relative to the reference's Source/ directory). The reference has no
+ * FFI of its own: its boundary is the C++ function surface app.cpp calls, which the host layer
+ * Source/engine/ in this repo re-exposes (same names/signatures) on top of this ABI. See INTEGRATION.md.
+ *
+ * All functions return 0 (ATRAY_OK) on success or a negative ATRAY_E* code; atray_last_error() returns a
+ * thread-local message. There is NO CPU fallback: every render/trace entry fails with ATRAY_ECUDA when no
+ * sm_100-class device is usable.
+ */
+#ifndef ATRAY_B200_H
+#define ATRAY_B200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ATRAY_OK 0
+#define ATRAY_EINVAL (-1)   /* bad argument */
+#define ATRAY_EIO (-2)      /* file could not be read */
+#define ATRAY_ECUDA (-3)    /* CUDA error / no device */
+#define ATRAY_ESTATE (-4)   /* call order violated (e.g. render before upload) */
+#define ATRAY_ELIMIT (-5)   /* tree build exceeded the node/primitive guard (reference: no guard, kd_tree.cpp:74-286) */
+
+#define ATRAY_MISS 0xffffffffu          /* primitive id written for rays that hit nothing */
+#define ATRAY_MAX_FLOAT 3.402823466e+38F /* t written for misses (PL/PL_base_defs.h:70, renderer.cpp:36) */
+
+#define ATRAY_DIV_CENTER 0 /* KD_Division_Method::CENTER, engine/renderer/kd_tree.h:13-16 */
+#define ATRAY_DIV_SAH 1    /* KD_Division_Method::SAH */
+
+#define ATRAY_FP_STRICT 0 /* reference arithmetic: no FMA contraction, IEEE division — bit-exact parity mode */
+#define ATRAY_FP_FAST 1   /* FMA contraction allowed; ids/t inside north_star tolerances, not bit-exact */
+
+typedef struct atray_model atray_model; /* host: ModelData + Model + KD_Tree (model.h:30-71, kd_tree.h:38-47) */
+typedef struct atray_ctx atray_ctx;     /* one GPU: uploaded scene, streams, frame buffers */
+
+/* Material, engine/renderer/material.h:4-9 (28 bytes, same layout) */
+typedef struct AtrayMaterial { float emission_color[3]; float reflection_color[3]; float scatter; } AtrayMaterial;
+
+/* Camera + RenderSettings as the kernel consumes them: the values set_camera/update_camera_pos compute
+ * (engine/renderer/camera.h:9-45, settings.h:4-10). Filled by atray_camera_set on the host. */
+typedef struct AtrayCamera
+{
+    int32_t width, height;            /* RenderSettings.resolution */
+    int32_t anti_aliasing;            /* RenderSettings.anti_aliasing (b32) */
+    uint32_t samples_per_pixel;       /* RenderSettings.samples_per_pixel */
+    int32_t bounce_limit;             /* RenderSettings.bounce_limit; this path implements 1 (SURVEY §8f row 1 = next) */
+    float aspect_ratio;
+    float camera_z[3], camera_x[3], camera_y[3];
+    float eye[3], frame_center[3];
+    float h_fov, half_pixel_width, half_pixel_height;
+} AtrayCamera;
+
+/* Which part of the image this context renders (replaces the tile work queue of renderer.cpp:403-445):
+ * bands of band_rows scanlines, band b belongs to partition (b % world); world = 1 renders everything. */
+typedef struct AtrayPartition { int32_t rank, world, band_rows; } AtrayPartition;
+
+/* Per-frame options. */
+typedef struct AtrayRenderOpts
+{
+    int32_t fp_mode;        /* ATRAY_FP_STRICT / ATRAY_FP_FAST */
+    int32_t count_work;     /* non-zero: accumulate AtrayCounters (slower instrumented kernel) */
+    uint64_t jitter_seed;   /* anti_aliasing: pixel p uses RNG_Stream{splitmix64(seed ^ p), 2p+1} */
+    AtrayPartition part;
+} AtrayRenderOpts;
+
+/* Host frame the renderer fills (replaces Texture/BitmapBuffer, engine/tools/texture.h:10-23, plus the two
+ * extra per-pixel planes north_star asks for). Row 0 = bottom scanline, index y*width + x (texture.h:27-38).
+ * Any plane may be NULL. */
+typedef struct AtrayFrame
+{
+    uint32_t* bgrx;   /* 0x00RRGGBB (B,G,R,0 in memory) — Set_Pixel packing */
+    float* t;         /* hit distance, ATRAY_MAX_FLOAT on miss */
+    uint32_t* prim;   /* face index (KD_Primitive.face_index), ATRAY_MISS on miss */
+} AtrayFrame;
+
+/* Work counters of the last counted frame/trace (SURVEY §8d roofline formula). */
+typedef struct AtrayCounters
+{
+    uint64_t rays, box_tests, tri_tests, pass_det, pass_u, pass_v, leaves_listed, leaves_scanned, overflow_rays;
+} AtrayCounters;
+
+const char* atray_last_error(void);
+int atray_version(void);
+
+/* ---- host side: loader, transforms, tree (the ☆ rows of SURVEY §2) ---------------------------------------- */
+/* load_model_data(ModelData&, const char*, ThreadPool&) — engine/tools/OBJ_loader.cpp:278-361 */
+int atray_model_load_obj(const char* path, int loader_threads, atray_model** out);
+/* builds a model from arrays (no reference counterpart; for embedders that already hold a mesh) */
+int atray_model_from_arrays(const float* vertices, uint32_t n_vertices, const int32_t* face_vertex_indices,
+                            uint32_t n_faces, atray_model** out);
+void atray_model_free(atray_model* m);
+/* model.surrounding_aabb = get_AABB(model.data) — engine/renderer/model.h:41-61; out6 = min.xyz,max.xyz (may be NULL) */
+int atray_model_compute_aabb(atray_model* m, float* out6);
+/* resize_scale(Model&, f32) — model.h:108-121 */
+int atray_model_resize_scale(atray_model* m, float new_max_scale);
+/* translate_to(Model&, vec3f) — model.h:136-152 */
+int atray_model_translate_to(atray_model* m, const float* new_center3);
+/* build_KD_tree(ModelData, KD_Tree&) with KD_Tree.division_method / max_no_faces_per_node — kd_tree.cpp:20-288 */
+int atray_model_build_tree(atray_model* m, int division_method, uint32_t max_no_faces_per_node);
+/* counts[8] = vertices, normals, tex_coords, faces, tree nodes, primitive refs, inner nodes, largest leaf */
+int atray_model_counts(const atray_model* m, uint32_t* counts8);
+/* copies of the loader output (any pointer may be NULL): vertices/normals/tex n×3 f32, face index triplets n_faces×3 i32 */
+int atray_model_dump(const atray_model* m, float* vertices, float* normals, float* tex_coords, int32_t* face_v,
+                     int32_t* face_vt, int32_t* face_vn, float* aabb6);
+/* the tree as the reference holds it, one row per node in DBuffer order (for 1:1 comparison, north_star):
+ * boxes n×6, children_start n (0 = leaf), prim_count n, prim_first n (offset into the concatenated per-leaf
+ * primitive arrays), tri9 refs×9 (a,b,c), face_index refs */
+int atray_model_tree_dump(const atray_model* m, float* boxes, int32_t* children_start, uint32_t* prim_count,
+                          uint32_t* prim_first, float* tri9, uint32_t* face_index);
+/* sizes and contents of the flattened GPU form: nodes = n_nodes×2 float4, tris = n_slots/32 blocks of
+ * 3×32 float4 {a.xyz,face}{ab.xyz,0}{ac.xyz,0}. Either output pointer may be NULL to query sizes only. */
+int atray_model_flatten(const atray_model* m, uint32_t* n_nodes, uint32_t* n_slots, float* nodes, float* tris);
+
+/* set_camera(Camera&, eye, facing, RenderSettings&, h_fov) — engine/renderer/camera.h:23-45 */
+int atray_camera_set(AtrayCamera* cam, int32_t width, int32_t height, int32_t anti_aliasing, uint32_t samples_per_pixel,
+                     int32_t bounce_limit, const float* eye3, const float* facing3, float h_fov);
+
+/* ---- device side --------------------------------------------------------------------------------------------- */
+int atray_device_count(int* n);
+int atray_ctx_create(int device, atray_ctx** out);
+void atray_ctx_destroy(atray_ctx* ctx);
+/* prep_scene(Scene&, uint32&) tail: flatten + upload once — renderer.cpp:264-291. materials[0] = sky
+ * (renderer.cpp:152), materials[1] = the model's material (model.data.material). */
+int atray_scene_upload(atray_ctx* ctx, const atray_model* m, const AtrayMaterial* sky, const AtrayMaterial* model_mat);
+
+/* start_render_from_camera(RenderInfo&, ThreadPool&) — renderer.cpp:403-455: returns immediately; kernels and the
+ * device→host copies of the frame planes are queued on the context's stream. */
+int atray_render_begin(atray_ctx* ctx, const AtrayCamera* cam, const AtrayRenderOpts* opts, const AtrayFrame* host_out);
+/* wait_for_render_from_camera_to_finish(RenderInfo&, ThreadPool&, ms) — renderer.cpp:457-471:
+ * returns 1 while still running (timed out), 0 when finished, negative on error. */
+int atray_render_poll(atray_ctx* ctx, uint32_t timeout_ms);
+/* info.twq.clear() cancel path — app.cpp:165-172 */
+int atray_render_cancel(atray_ctx* ctx);
+/* Same frame, outputs left resident in device memory (planes are device pointers, may live on a peer GPU);
+ * asynchronous on the context stream; pair with atray_ctx_sync. Used for the HBM-resident bench leg. */
+int atray_render_device(atray_ctx* ctx, const AtrayCamera* cam, const AtrayRenderOpts* opts, const AtrayFrame* device_out);
+int atray_ctx_sync(atray_ctx* ctx);
+/* device time of the last completed atray_render_device / atray_render_begin kernel(s), CUDA events, ms */
+int atray_last_kernel_ms(atray_ctx* ctx, float* ms);
+
+/* get_intersection_data model branch for an arbitrary ray list — renderer.cpp:34-57 + kd_tree.cpp:302-313.
+ * rays = n × {ox,oy,oz,dx,dy,dz} (direction used as given). Host pointers; synchronous. */
+int atray_trace_rays(atray_ctx* ctx, const float* rays, uint64_t n, int32_t fp_mode, int32_t count_work, uint32_t* prim,
+                     float* t);
+/* same with device pointers, asynchronous on the context stream */
+int atray_trace_rays_device(atray_ctx* ctx, const float* rays_dev, uint64_t n, int32_t fp_mode, int32_t count_work,
+                            uint32_t* prim_dev, float* t_dev);
+int atray_get_counters(atray_ctx* ctx, AtrayCounters* out);
+
+/* device memory helpers for embedders without a CUDA runtime binding of their own */
+int atray_dev_alloc(atray_ctx* ctx, size_t bytes, void** out);
+int atray_dev_free(atray_ctx* ctx, void* p);
+int atray_dev_copy_to_host(atray_ctx* ctx, void* host, const void* dev, size_t bytes);
+int atray_dev_copy_from_host(atray_ctx* ctx, void* dev, const void* host, size_t bytes);
+int atray_host_alloc_pinned(size_t bytes, void** out);
+int atray_host_free_pinned(void* p);
+/* cross-process gather target (multi-GPU, one process per GPU): export a device allocation of this context and
+ * open it in a peer process; the opened pointer can be used as AtrayFrame planes of atray_render_device
+ * (the kernel stores straight into GPU 0's frame over NVLink). handle64 = 64 bytes. */
+int atray_ipc_export(atray_ctx* ctx, void* dev, unsigned char* handle64);
+int atray_ipc_open(atray_ctx* ctx, const unsigned char* handle64, void** out);
+int atray_ipc_close(atray_ctx* ctx, void* p);
+
+/* K0 microbenchmarks for the roofline denominators: FP32 issue slots/s and L2 read GB/s. */
+int atray_microbench(atray_ctx* ctx, double* fp32_lane_ops_per_s, double* l2_read_gbs);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
