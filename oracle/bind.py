@@ -95,6 +95,8 @@ class Scene:
         self.b = backend
         self.h = backend.scene_create(os.fsencode(obj_path), loader_threads, rescale, translate[0], translate[1],
                                         translate[2], method, cap)
+        if not self.h:
+            raise RuntimeError("oracle scene_create failed for %s (missing file or degenerate tree)" % obj_path)
         c = np.zeros(8, dtype=np.uint32)
         self.b.counts(self.h, _p(c))
         (self.n_vertices, self.n_normals, self.n_tex, self.n_faces, self.n_nodes, self.n_refs, self.n_inner,
