@@ -99,6 +99,7 @@ _SIGS = {
     "atray_dev_free": [_vp, _vp],
     "atray_dev_copy_to_host": [_vp, _vp, _vp, _sz],
     "atray_dev_copy_from_host": [_vp, _vp, _vp, _sz],
+    "atray_dev_memset": [_vp, _vp, C.c_int, _sz],
     "atray_host_alloc_pinned": [_sz, C.POINTER(_vp)],
     "atray_host_free_pinned": [_vp],
     "atray_ipc_export": [_vp, _vp, _vp],

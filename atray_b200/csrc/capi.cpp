@@ -523,6 +523,13 @@ int atray_dev_copy_from_host(atray_ctx* c, void* dev, const void* host, size_t b
     CU(cudaStreamSynchronize(c->stream));
     return ATRAY_OK;
 }
+int atray_dev_memset(atray_ctx* c, void* dev, int value, size_t bytes)
+{
+    if (!c || !dev) return fail(ATRAY_EINVAL, "null argument");
+    CU(cudaSetDevice(c->device));
+    CU(cudaMemsetAsync(dev, value, bytes, c->stream));
+    return ATRAY_OK;
+}
 int atray_host_alloc_pinned(size_t bytes, void** out)
 {
     if (!out) return fail(ATRAY_EINVAL, "null argument");

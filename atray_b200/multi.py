@@ -1,0 +1,62 @@
+"""Multi-GPU plumbing for the render path: one process per GPU, scene replicated, image split into interleaved
+scanline bands (band b → rank b mod world), every rank's kernel stores its bands straight into GPU 0's frame through
+a CUDA-IPC mapping (peer stores over NVLink) — there is no collective on the data path and NCCL is not needed for it
+(north_star). torch.distributed is used only to hand the 64-byte IPC handles around and for barriers.
+
+The reference's counterpart is the tile work queue of renderer.cpp:403-445 (tiles pulled by 8 threads)."""
+import numpy as np
+
+PLANES = ("bgrx", "t", "prim")
+
+
+def n_bands(height, band_rows):
+    return (height + band_rows - 1) // band_rows
+
+
+def rows_of_rank(height, band_rows, rank, world):
+    """Scanlines owned by `rank` (same arithmetic as k_render's tile → (x, y) mapping)."""
+    rows = np.arange(height)
+    return rows[(rows // band_rows) % world == rank]
+
+
+def rays_of_rank(width, height, spp, band_rows, rank, world):
+    return int(rows_of_rank(height, band_rows, rank, world).size) * width * spp
+
+
+def exchange_handles(dist, rank, payload):
+    """Rank 0's payload (dict of plane → 64-byte IPC handle) is broadcast to every rank; works on gloo and nccl."""
+    box = [payload if rank == 0 else None]
+    dist.broadcast_object_list(box, src=0)
+    return box[0]
+
+
+class FrameGather:
+    """GPU 0 owns the frame planes; other ranks map them. `planes[p]` is a device pointer valid in this process."""
+
+    def __init__(self, ctx, dist, rank, world, width, height, planes=PLANES):
+        self.ctx, self.rank, self.world = ctx, rank, world
+        self.nbytes = width * height * 4
+        self.planes, self._owned, self._opened = {}, [], []
+        handles = None
+        if rank == 0:
+            handles = {}
+            for p in planes:
+                ptr = ctx.dev_alloc(self.nbytes)
+                self._owned.append(ptr)
+                self.planes[p] = ptr
+                if world > 1:
+                    handles[p] = ctx.ipc_export(ptr)
+        if world > 1:
+            handles = exchange_handles(dist, rank, handles)
+            if rank != 0:
+                for p in planes:
+                    ptr = ctx.ipc_open(handles[p])
+                    self._opened.append(ptr)
+                    self.planes[p] = ptr
+
+    def close(self):
+        for p in self._opened:
+            self.ctx.ipc_close(p)
+        for p in self._owned:
+            self.ctx.dev_free(p)
+        self._opened, self._owned = [], []

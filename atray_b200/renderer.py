@@ -121,6 +121,9 @@ class Context:
         arr = np.ascontiguousarray(arr)
         _ck(_L.atray_dev_copy_from_host(self.h, dev_ptr, _p(arr), arr.nbytes))
 
+    def dev_memset(self, dev_ptr, value, nbytes):
+        _ck(_L.atray_dev_memset(self.h, dev_ptr, value, nbytes))
+
     def ipc_export(self, dev_ptr):
         h = np.zeros(64, np.uint8)
         _ck(_L.atray_ipc_export(self.h, dev_ptr, _p(h)))

@@ -1,0 +1,360 @@
+#!/usr/bin/env python3
+"""bench.py — primary-ray throughput of the ATRay render path (BASELINE.json metric) on N B200s.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--fp strict|fast]
+
+Workload (config.workload): BASELINE.json configs[3] — the 139 264-face Dragon stand-in (Assets/Dragon.obj is missing
+from the reference checkout; tools/gen_standin_obj.py, spec "standin-v1"), 3840×2160, 1 spp, bounce 1, default camera
+(app.cpp:88), tree SAH / 300 (app.cpp:76-77). A "step" = one complete frame: ray generation → traversal →
+intersection → {t, prim, BGRX} stores. N > 1: the frame is split into interleaved scanline bands, one rank per GPU,
+every rank storing its bands straight into GPU 0's frame over NVLink (strong scaling, no collective).
+
+value   = W·H·spp·K / (sum of the K per-step CUDA-event durations, max over ranks)   [frame resident in HBM]
+e2e     = same frames through the reference-facing call (start_render_from_camera / wait_… → atray_render_begin/poll)
+          with the host bitmap as output: kernel + device→host copy inside the timed region
+--impl reference: the reference's own CPU renderer (oracle/_ref, start_render_from_camera with all host threads)."""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+W, H, SPP = 3840, 2160, 1
+BAND_ROWS = 8
+METRIC = "Mrays/s primary rays (Dragon 139k tris, 4K)"
+WORKLOAD = "C4: Dragon stand-in (standin-v1, 139264 faces) 3840x2160 1spp primary rays, SAH cap 300"
+MESH_CACHE = os.environ.get("ATRAY_MESH_CACHE", "/tmp/atray_meshes")
+
+
+def mesh_path():
+    from tools import gen_standin_obj
+    return gen_standin_obj.ensure(os.path.join(MESH_CACHE, "standin_272x256.obj"))
+
+
+def host_threads():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return float(d["hbm_gbs"]), "MEASURED_PEAKS.json (burst copy)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks/throttle reasons during the timed region (B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.idx, self.rows, self.stop_flag, self.th = gpu_index, [], False, None
+
+    def _loop(self):
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits"],
+                                     stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([c.strip() for c in out.splitlines()[0].split(",")])
+            except Exception:
+                pass
+            time.sleep(0.05)
+
+    def start(self):
+        self.th = threading.Thread(target=self._loop, daemon=True)
+        self.th.start()
+
+    def stop(self):
+        self.stop_flag = True
+        if self.th:
+            self.th.join(timeout=6)
+        sm = [float(r[1]) for r in self.rows if len(r) >= 9 and r[1].replace(".", "").isdigit()]
+        mx = [float(r[2]) for r in self.rows if len(r) >= 9 and r[2].replace(".", "").isdigit()]
+        reasons = set()
+        for r in self.rows:
+            if len(r) >= 9:
+                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[5:9]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ---- CPU side: the reference's own renderer (oracle/_ref) or, if it could not be built, the C port -----------------
+def cpu_scene():
+    from oracle import bind as B
+    path = mesh_path()
+    if B.ref_available():
+        return B, B.Scene(B.ref(), path, loader_threads=min(8, host_threads()), rescale=0.0), "reference"
+    if not B.port_available():
+        subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle"), "liboracle.so"], stdout=subprocess.DEVNULL)
+    return B, B.Scene(B.port(), path, rescale=0.0), "port"
+
+
+def cpu_frame_seconds(scene, kind, threads):
+    """One full 4K frame on the host cores. reference: through start_render_from_camera / wait_… with `threads` pool
+    threads (renderer.cpp:403-471); port: the oracle's row-parallel loop."""
+    if kind == "reference":
+        _, sec, _ = scene.render(W, H, threads=threads)
+        return sec
+    t0 = time.perf_counter()
+    scene.trace_primary(W, H, threads=threads)
+    return time.perf_counter() - t0
+
+
+def base_line(n_gpus, steps, warmup):
+    return {"metric": METRIC, "unit": "Mrays/s", "n_gpus": n_gpus, "steps": steps, "warmup": warmup,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "resolution": [W, H], "spp": SPP, "bounce_limit": 1, "tree": "SAH/300",
+                       "mesh": "standin-v1 (Assets/Dragon.obj absent from the reference checkout)"}}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    _, scene, kind = cpu_scene()
+    threads = host_threads()
+    for _ in range(max(1, min(args.warmup, 2))):
+        cpu_frame_seconds(scene, kind, threads)
+    secs = [cpu_frame_seconds(scene, kind, threads) for _ in range(args.steps)]
+    total = sum(secs)
+    val = W * H * SPP * len(secs) / total / 1e6
+    line = base_line(args.gpus, args.steps, args.warmup)
+    line.update({"impl": "reference", "value": val, "ms_per_step": 1e3 * total / len(secs),
+                 "cpu_baseline": {"value": val, "unit": "Mrays/s", "cores": threads, "kind": kind,
+                                  "sample": "%d full 4K frames (8294400 rays each) through the reference's tile thread pool" % len(secs)},
+                 "e2e": {"value": val, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                 "gpu_launches": 0})
+    line["config"]["host_threads"] = threads
+    print(json.dumps(line), flush=True)
+
+
+# ---- our arm -----------------------------------------------------------------------------------------------------------
+def ops_and_bytes_per_ray(c):
+    """SURVEY §8(d) formula from the kernel's own work counters (one counted frame outside the timed region)."""
+    rays = max(1, c["rays"])
+    ops = (12 * c["box_tests"] + 14 * c["tri_tests"] + 10 * c["pass_det"] + 16 * c["pass_u"] + 6 * c["pass_v"]) / rays + 40
+    byts = (32 * c["box_tests"] + 48 * c["tri_tests"]) / rays + 12
+    return ops, byts
+
+
+def load_traffic():
+    """dram bytes per launch of the render kernel from the committed ncu capture (profiles/), or None."""
+    p = os.path.join(ROOT, "profiles", "render_kernel_traffic.json")
+    if os.path.exists(p):
+        try:
+            return json.load(open(p)).get("dram_bytes_per_launch")
+        except Exception:
+            return None
+    return None
+
+
+def run_ours(args):
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    dist = None
+    if world > 1:
+        import torch
+        import torch.distributed as dist_mod
+        torch.cuda.set_device(local_rank)
+        dist_mod.init_process_group(backend="nccl", device_id=torch.device("cuda", local_rank))
+        dist = dist_mod
+    if args.gpus != world:
+        raise SystemExit("--gpus %d but WORLD_SIZE=%d (launch N>1 with torch.distributed.run)" % (args.gpus, world))
+
+    import atray_b200 as A
+    from atray_b200 import multi
+
+    fp_mode = A.FP_FAST if args.fp == "fast" else A.FP_STRICT
+    path = mesh_path() if rank == 0 else None
+    if dist is not None:
+        dist.barrier()
+        path = mesh_path()
+    t_setup = time.perf_counter()
+    model = A.load_model_data(path, min(8, host_threads()))
+    A.place_default(model, rescale=0.0)               # app.cpp:68-72 (no resize for the dragon)
+    scene = A.Scene(model, division_method=A.DIV_SAH, max_no_faces_per_node=300)
+    A.prep_scene(scene, device=local_rank)            # build + flatten + upload once
+    setup_s = time.perf_counter() - t_setup
+    ctx = scene.ctx
+    cam = A.set_camera(W, H, samples_per_pixel=SPP)
+    gather = multi.FrameGather(ctx, dist, rank, world, W, H)
+    opts = ctx.opts(fp_mode=fp_mode, rank=rank, world=world, band_rows=BAND_ROWS)
+    my_rays = multi.rays_of_rank(W, H, SPP, BAND_ROWS, rank, world)
+    flush_bytes = 256 << 20                            # > 126 MB L2
+    d_flush = ctx.dev_alloc(flush_bytes)
+
+    def flush_l2():
+        # device-side write of a buffer larger than L2, on the context stream, outside the per-step event pair
+        ctx.dev_memset(d_flush, 0, flush_bytes)
+
+    def barrier():
+        ctx.sync()
+        if dist is not None:
+            import torch
+            torch.cuda.synchronize()
+            dist.barrier()
+
+    def step_device():
+        ctx.render_device(cam, opts, gather.planes["bgrx"], gather.planes["t"], gather.planes["prim"])
+
+    # ---- HBM-resident leg: `value` -------------------------------------------------------------------------------------
+    for _ in range(args.warmup):
+        flush_l2()
+        step_device()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    wall0 = time.perf_counter()
+    per_step_ms = []
+    for _ in range(args.steps):
+        flush_l2()
+        step_device()
+        per_step_ms.append(ctx.last_kernel_ms())       # waits for this step's stop event (device time on our stream)
+    barrier()
+    wall_ms = 1e3 * (time.perf_counter() - wall0)
+    clocks = sampler.stop() if rank == 0 else None
+    dev_ms = float(sum(per_step_ms))
+    if dist is not None:
+        import torch
+        tt = torch.tensor([dev_ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        dev_ms_max = float(tt.item())
+    else:
+        dev_ms_max = dev_ms
+    total_rays = W * H * SPP * args.steps
+    value = total_rays / (dev_ms_max * 1e-3) / 1e6
+
+    # ---- end-to-end leg through the reference-facing call with the HOST bitmap ---------------------------------------------
+    e2e = None
+    tex = A.PinnedArray((H, W), np.uint32) if rank == 0 else None
+    if world == 1:
+        info = A.RenderInfo(cam, scene, tex.array, opts=opts)
+        for _ in range(2):
+            A.start_render_from_camera(info)
+            while A.wait_for_render_from_camera_to_finish(info, None, 33):
+                pass
+        ctx.sync()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            A.start_render_from_camera(info)            # kernel + D2H of the BGRX bitmap queued
+            while A.wait_for_render_from_camera_to_finish(info, None, 33):
+                pass
+        e2e_s = time.perf_counter() - t0
+    else:
+        # every rank renders its bands into GPU 0's frame (peer stores), barrier, rank 0 copies the bitmap to the host
+        def e2e_step():
+            step_device()
+            barrier()
+            if rank == 0:
+                ctx.to_host(gather.planes["bgrx"], tex.array)
+        for _ in range(2):
+            e2e_step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            e2e_step()
+        barrier()
+        e2e_s = time.perf_counter() - t0
+    if dist is not None:
+        import torch
+        tt = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        e2e_s = float(tt.item())
+    e2e = {"value": total_rays / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": 136,
+           "d2h_bytes_per_step": W * H * 4, "ms_per_step": 1e3 * e2e_s / args.steps,
+           "note": "host BGRX bitmap (Texture.bmb.buffer_memory, pinned) is the output; input per step is the camera/settings "
+                   "struct passed as kernel parameters; the scene is uploaded once in prep_scene as the reference builds its tree once"}
+
+    # ---- explanation: work counters, K0 peaks, roofline, CPU baseline (rank 0, outside the timed regions) ------------------
+    line = None
+    if rank == 0:
+        one = ctx.opts(fp_mode=fp_mode, count_work=True, rank=0, world=1, band_rows=BAND_ROWS)
+        ctx.render_device(cam, one, gather.planes["bgrx"], gather.planes["t"], gather.planes["prim"])
+        ctx.sync()
+        ctr = ctx.counters()
+        ops_ray, bytes_ray = ops_and_bytes_per_ray(ctr)
+        k0 = ctx.microbench()
+        hbm_peak, peak_src = measured_peaks()
+        # dominant kernel = k_render: one launch per step per rank; per-launch algorithmic bytes = bytes/ray × rays of the launch
+        launch_ms = dev_ms / args.steps
+        launch_rays = my_rays
+        achieved_gbs = bytes_ray * launch_rays / (launch_ms * 1e-3) / 1e9
+        fp32_achieved = ops_ray * launch_rays / (launch_ms * 1e-3)
+        bound_fp32 = k0["fp32_lane_ops_per_s"] / ops_ray / 1e6         # Mrays/s per GPU
+        bound_hbm = hbm_peak * 1e9 / bytes_ray / 1e6
+        per_gpu = value / world
+        roofline = {"bound": "hbm", "achieved": achieved_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": achieved_gbs / hbm_peak,
+                    "traffic": load_traffic(), "peak_source": peak_src, "kernel": "k_render",
+                    "algorithmic_bytes_per_ray": bytes_ray, "algorithmic_fp32_ops_per_ray": ops_ray,
+                    "fp32": {"achieved_lane_ops_per_s": fp32_achieved, "peak_lane_ops_per_s": k0["fp32_lane_ops_per_s"],
+                             "frac": fp32_achieved / k0["fp32_lane_ops_per_s"], "peak_source": "K0 FFMA microbenchmark, this run"},
+                    "l2_read_gbs_measured": k0["l2_read_gbs"],
+                    "north_star_roofline_mrays_per_gpu": {"fp32_issue_bound": bound_fp32, "hbm_bytes_bound": bound_hbm,
+                                                          "slower": min(bound_fp32, bound_hbm),
+                                                          "achieved_frac_of_slower": per_gpu / min(bound_fp32, bound_hbm)},
+                    "note": "frac > 1 against HBM because the 10 MB scene is L2/L1-resident by design: the HBM figure is the "
+                            "north_star's bytes-per-ray bound, not the kernel's limiter (see fp32.frac and profiles/)"}
+        cpu_baseline = None
+        if world == 1 and not args.no_cpu_baseline:
+            _, cscene, kind = cpu_scene()
+            threads = host_threads()
+            cpu_frame_seconds(cscene, kind, threads)
+            secs = [cpu_frame_seconds(cscene, kind, threads) for _ in range(3)]
+            cpu_baseline = {"value": W * H * SPP / min(secs) / 1e6, "unit": "Mrays/s", "cores": threads, "kind": kind,
+                            "sample": "3 full 4K frames (8294400 primary rays each) after 1 warm-up, best of 3, "
+                                      "reference tile thread pool with %d threads" % threads,
+                            "seconds": secs}
+        line = base_line(args.gpus, args.steps, args.warmup)
+        line.update({"impl": "ours", "value": value, "ms_per_step": dev_ms_max / args.steps, "e2e": e2e, "roofline": roofline,
+                     "cpu_baseline": cpu_baseline, "clocks": clocks, "gpu_launches": args.steps * world,
+                     "wall_ms_bracket": wall_ms, "per_step_ms_rank0": per_step_ms, "counters": ctr, "setup_s": setup_s})
+        line["config"].update({"fp_mode": args.fp, "band_rows": BAND_ROWS, "parallelism": "bands%d" % world,
+                               "l2": "flushed between timed steps (256 MiB device memset outside the per-step event pair)",
+                               "timing": "CUDA events on the library's stream around each frame's launch, summed over K steps, max over ranks",
+                               "gather": "direct peer stores into GPU 0's frame through CUDA IPC" if world > 1 else "none (1 GPU)"})
+    barrier()
+    if tex is not None:
+        tex.free()
+    ctx.dev_free(d_flush)
+    gather.close()
+    if dist is not None:
+        dist.destroy_process_group()
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
+    ap.add_argument("--fp", choices=["strict", "fast"], default="strict")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.warmup < 3 and args.impl == "ours":
+        args.warmup = 3  # timing rule: at least 3 warm-up steps
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

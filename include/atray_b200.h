@@ -156,6 +156,8 @@ int atray_dev_alloc(atray_ctx* ctx, size_t bytes, void** out);
 int atray_dev_free(atray_ctx* ctx, void* p);
 int atray_dev_copy_to_host(atray_ctx* ctx, void* host, const void* dev, size_t bytes);
 int atray_dev_copy_from_host(atray_ctx* ctx, void* dev, const void* host, size_t bytes);
+/* asynchronous memset on the context stream (bench.py uses it to flush L2 between timed frames) */
+int atray_dev_memset(atray_ctx* ctx, void* dev, int value, size_t bytes);
 int atray_host_alloc_pinned(size_t bytes, void** out);
 int atray_host_free_pinned(void* p);
 /* cross-process gather target (multi-GPU, one process per GPU): export a device allocation of this context and
