@@ -275,3 +275,27 @@ def test_errors_on_device_side(A, meshes):
     out = ctx.render(A.set_camera(64, 64))
     assert (out["prim"] != A.MISS).any()
     ctx.close()
+
+
+def test_cpp_host_layer_replays_app_cpp(A, port, meshes, tmp_path):
+    """Source/engine (C++, reference entry-point names) driven by Source/engine/app_headless.cpp — the call order of
+    render_app (app.cpp:59-195) — produces the oracle's bitmap, t and primitive planes."""
+    import subprocess
+    from oracle import bind as B
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = os.path.join(root, "Source", "engine", "app_headless")
+    assert os.path.exists(exe), "run __graft_entry__.build()"
+    path, rescale = meshes["knot_mid"]
+    planes = str(tmp_path / "planes.bin")
+    bmp = str(tmp_path / "out.bmp")
+    W, H = 1280, 720
+    out = subprocess.run([exe, path, str(W), str(H), "0", bmp, planes], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    assert out.returncode == 0, out.stdout
+    raw = np.fromfile(planes, np.uint32).reshape(3, H, W)
+    o = B.Scene(port, path, rescale=0.0)
+    face, t, img = o.trace_primary(W, H, threads=NTHREADS)
+    assert (raw[0] == img).all() and (raw[1] == t.view(np.uint32)).all() and (raw[2] == face).all()
+    assert "total_ray_casts %d " % int((face != B.MISS).sum()) in out.stdout
+    b = open(bmp, "rb").read()
+    assert b[:2] == b"BM" and len(b) == 54 + W * H * 4 and np.frombuffer(b[54:], np.uint32).reshape(H, W)[5, 7] == img[5, 7]
+    o.close()

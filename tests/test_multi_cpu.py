@@ -1,0 +1,91 @@
+"""CPU: host-side multi-GPU logic — band partition arithmetic and the IPC-handle exchange — with world_size 2 on the
+gloo backend (no GPU). The data path itself (kernels storing into GPU 0's frame) is covered on the GPU by
+test_partition_union_equals_whole and by bench.py --gpus N."""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.mark.parametrize("H,band,world", [(2160, 8, 1), (2160, 8, 2), (2160, 8, 8), (301, 12, 3), (7, 4, 4), (1080, 16, 5)])
+def test_band_partition_covers_every_row_once(H, band, world, built):
+    from atray_b200 import multi
+    seen = np.zeros(H, int)
+    for r in range(world):
+        rows = multi.rows_of_rank(H, band, r, world)
+        seen[rows] += 1
+        assert ((rows // band) % world == r).all()
+        assert multi.rays_of_rank(100, H, 3, band, r, world) == rows.size * 300
+    assert (seen == 1).all()
+    assert multi.n_bands(H, band) == -(-H // band)
+    sizes = [multi.rows_of_rank(H, band, r, world).size for r in range(world)]
+    if H >= band * world:
+        assert max(sizes) - min(sizes) <= band  # interleaving balances the ranks to within one band
+
+
+def _worker(rank, world, port, q):
+    sys.path.insert(0, ROOT)
+    import torch.distributed as dist
+    from atray_b200 import multi
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+
+    class FakeCtx:  # stands in for the device context: records what FrameGather asks of it
+        def __init__(self):
+            self.log = []
+
+        def dev_alloc(self, n):
+            self.log.append(("alloc", n))
+            return 0x1000 * (len(self.log) + 1)
+
+        def dev_free(self, p):
+            self.log.append(("free", p))
+
+        def ipc_export(self, p):
+            return (b"H%015d" % p) * 4
+
+        def ipc_open(self, h):
+            self.log.append(("open", h))
+            return int(h[1:16]) + 7
+
+        def ipc_close(self, p):
+            self.log.append(("close", p))
+
+    ctx = FakeCtx()
+    g = multi.FrameGather(ctx, dist, rank, world, 64, 32)
+    planes = dict(g.planes)
+    g.close()
+    dist.barrier()
+    dist.destroy_process_group()
+    q.put((rank, planes, ctx.log))
+
+
+def test_frame_gather_handle_exchange_gloo_world2(built):
+    import torch.multiprocessing as mp
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = {}
+    for _ in range(2):
+        r, planes, log = q.get(timeout=120)
+        res[r] = (planes, log)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    p0, log0 = res[0]
+    p1, log1 = res[1]
+    assert set(p0) == set(p1) == {"bgrx", "t", "prim"}
+    assert [e[0] for e in log0] == ["alloc"] * 3 + ["free"] * 3 and all(e[1] == 64 * 32 * 4 for e in log0[:3])
+    for k in p0:  # rank 1 mapped exactly the allocations rank 0 exported
+        assert p1[k] == p0[k] + 7
+    assert [e[0] for e in log1] == ["open"] * 3 + ["close"] * 3
