@@ -171,8 +171,8 @@ def test_spill_path_long_leaf_lists(A, port, meshes):
     """Rays whose leaf list outgrows the per-lane array take the per-warp spill path; results stay bit-exact."""
     from oracle import bind as B
     path, rescale = meshes["knot_mid"]
-    sc = gpu_scene(A, path, rescale, 0, 2)  # CENTER, cap 2 → thousands of tiny leaves, long lists
-    o = B.Scene(port, path, rescale=rescale, method=0, cap=2)
+    sc = gpu_scene(A, path, rescale, 0, 6)  # CENTER, cap 6 → 30 k tiny leaves, long lists (caps < 6 trip the build guard)
+    o = B.Scene(port, path, rescale=rescale, method=0, cap=6)
     rays = random_rays(sc.model.dump()["aabb"], 200000, 3)
     prim, t = sc.ctx.trace_rays(rays, count_work=True)
     ctr = sc.ctx.counters()
