@@ -17,6 +17,7 @@ MISS = 0xFFFFFFFF
 MAX_FLOAT = np.float32(3.402823466e+38)
 DIV_CENTER, DIV_SAH = 0, 1
 FP_STRICT, FP_FAST = 0, 1
+RENDER_NO_CULL = 1
 
 # app.cpp:88,91,96
 DEFAULT_EYE = (0.1, 2.0, 0.0)
@@ -48,7 +49,8 @@ class Partition(C.Structure):
 
 
 class RenderOpts(C.Structure):
-    _fields_ = [("fp_mode", C.c_int32), ("count_work", C.c_int32), ("jitter_seed", C.c_uint64), ("part", Partition)]
+    _fields_ = [("fp_mode", C.c_int32), ("count_work", C.c_int32), ("jitter_seed", C.c_uint64), ("part", Partition),
+                ("flags", C.c_uint32)]
 
 
 class Frame(C.Structure):
@@ -57,7 +59,8 @@ class Frame(C.Structure):
 
 class Counters(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in ("rays", "box_tests", "tri_tests", "pass_det", "pass_u", "pass_v",
-                                          "leaves_listed", "leaves_scanned", "overflow_rays")]
+                                          "leaves_listed", "leaves_scanned", "overflow_rays", "rect_tests", "tiles_sky",
+                                          "tiles_busy")]
 
     def as_dict(self):
         return {n: int(getattr(self, n)) for n, _ in self._fields_}
@@ -82,6 +85,7 @@ _SIGS = {
     "atray_model_dump": [_vp] * 8,
     "atray_model_tree_dump": [_vp] * 7,
     "atray_model_flatten": [_vp, _vp, _vp, _vp, _vp],
+    "atray_debug_film_rects": [_vp, C.POINTER(CameraStruct), _vp, _vp, _vp, _vp],
     "atray_camera_set": [C.POINTER(CameraStruct), _i, _i, _i, _u, _i, _vp, _vp, _f],
     "atray_device_count": [C.POINTER(_i)],
     "atray_ctx_create": [_i, C.POINTER(_vp)],
@@ -182,9 +186,21 @@ class Model:
         nn, ns = C.c_uint32(0), C.c_uint32(0)
         _ck(_L.atray_model_flatten(self.h, C.byref(nn), C.byref(ns), None, None))
         nodes = np.zeros((nn.value, 2, 4), np.float32)
-        tris = np.zeros((ns.value // 32, 3, 32, 4), np.float32)
+        tris = np.zeros((ns.value // 8, 3, 8, 4), np.float32)
         _ck(_L.atray_model_flatten(self.h, None, None, _p(nodes), _p(tris)))
         return nodes, tris
+
+    def film_rects(self, cam):
+        """Host evaluation of the per-frame film rectangles (view_bounds.h): rects n_slots×4, owning leaf, position in
+        the reference's leaf order, busy flag per 8x4 tile."""
+        nn, ns = C.c_uint32(0), C.c_uint32(0)
+        _ck(_L.atray_model_flatten(self.h, C.byref(nn), C.byref(ns), None, None))
+        rects = np.zeros((ns.value, 4), np.float32)
+        leaf = np.zeros(ns.value, np.uint32)
+        pos = np.zeros(ns.value, np.uint32)
+        busy = np.zeros(((cam.height + 3) // 4, (cam.width + 7) // 8), np.uint8)
+        _ck(_L.atray_debug_film_rects(self.h, C.byref(cam), _p(rects), _p(leaf), _p(pos), _p(busy)))
+        return rects, leaf, pos, busy
 
 
 # ---- reference-named host functions (app.cpp:62-156 call order) ----------------------------------------------------

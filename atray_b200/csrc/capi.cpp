@@ -5,6 +5,7 @@
 #include "host_model.h"
 
 #include <chrono>
+#include <cmath>
 #include <cstdio>
 #include <cstring>
 #include <string>
@@ -26,6 +27,9 @@ struct atray_ctx
     DevScene scene{};
     bool has_scene = false;
     DevScratch scratch{};
+    DevView view{};              // per-frame film rectangles + tile stamps (k_view_bounds)
+    size_t stamp_cap = 0;        // tiles the stamp buffer holds
+    uint32_t frame_seq = 0;      // stamp value of the last frame (0 = buffer freshly cleared)
     unsigned int* d_tile_counter = nullptr;
     DevCounters* d_counters = nullptr;
     bool counters_valid = false;
@@ -240,6 +244,8 @@ int atray_ctx_create(int device, atray_ctx** out)
 static void free_scene(atray_ctx* c)
 {
     cudaFree(c->d_nodes); cudaFree(c->d_tris); cudaFree(c->scratch.leaves); cudaFree(c->scratch.stack);
+    cudaFree(c->view.tri_rect); cudaFree(c->view.pkt_rect); cudaFree(c->view.leaf_rect);
+    c->view.tri_rect = c->view.pkt_rect = c->view.leaf_rect = nullptr;
     c->d_nodes = c->d_tris = nullptr;
     c->scratch = DevScratch{};
     c->has_scene = false;
@@ -252,6 +258,7 @@ void atray_ctx_destroy(atray_ctx* c)
     if (c->stream) cudaStreamSynchronize(c->stream);
     free_scene(c);
     cudaFree(c->d_tile_counter); cudaFree(c->d_counters);
+    cudaFree(c->view.stamps); cudaFree(c->view.all_flag);
     cudaFree(c->d_bgrx); cudaFree(c->d_t); cudaFree(c->d_prim);
     cudaFreeHost(c->h_bgrx); cudaFreeHost(c->h_t); cudaFreeHost(c->h_prim);
     cudaFree(c->d_rays); cudaFree(c->d_rprim); cudaFree(c->d_rt);
@@ -281,9 +288,13 @@ int atray_scene_upload(atray_ctx* c, const atray_model* m, const AtrayMaterial* 
     c->scratch.stack_cap = f.n_nodes + 8;
     CU(cudaMalloc(&c->scratch.leaves, size_t(warps) * c->scratch.leaf_cap * sizeof(uint2)));
     CU(cudaMalloc(&c->scratch.stack, size_t(warps) * c->scratch.stack_cap * sizeof(uint32_t)));
+    CU(cudaMalloc(&c->view.tri_rect, size_t(f.n_slots ? f.n_slots : 1) * sizeof(float4)));
+    CU(cudaMalloc(&c->view.pkt_rect, size_t(f.n_slots / 8 + 1) * sizeof(float4)));
+    CU(cudaMalloc(&c->view.leaf_rect, size_t(f.n_nodes) * sizeof(float4)));
     c->scene.nodes = c->d_nodes;
     c->scene.tris = c->d_tris;
     c->scene.n_nodes = f.n_nodes;
+    c->scene.n_slots = f.n_slots;
     c->scene.root_is_leaf = m->m.tree[0].children_start == 0 ? 1u : 0u;
     std::memcpy(c->scene.sky, sky->emission_color, 12);
     std::memcpy(c->scene.mdl, mat->emission_color, 12);
@@ -312,6 +323,69 @@ static DevCamera to_dev(const AtrayCamera* cam)
     return d;
 }
 
+// Per-frame view parameters of the film-space culling (view_bounds.h), computed in double from the camera the kernel
+// uses. The ideal ray of film point (fx, fy) is eye + s*(F + cx*fx + cy*fy) with F = frame_center - eye and the float
+// camera vectors taken as exact reals; minv inverts [cx cy F]. `ang` bounds the angle between that ideal line and the
+// float ray camera_ray() produces: pixel_pos has a componentwise error <= u(2|fc_i| + 3|cx_i fx| + 3|cy_i fy|), the
+// subtraction of the eye adds u|d_i|, normalisation (three products, one division, three products) <= 3u relative; the
+// ideal direction is at least 1/||minv||_F long. The bound is doubled.
+static ViewParams make_view_params(const AtrayCamera* cam)
+{
+    ViewParams vp{};
+    const double U = 5.9604644775390625e-8;
+    double M[3][3];
+    for (int i = 0; i < 3; ++i)
+    {
+        vp.eye[i] = cam->eye[i];
+        M[i][0] = cam->camera_x[i];
+        M[i][1] = cam->camera_y[i];
+        M[i][2] = double(cam->frame_center[i]) - double(cam->eye[i]);
+    }
+    const double det = M[0][0] * (M[1][1] * M[2][2] - M[1][2] * M[2][1]) - M[0][1] * (M[1][0] * M[2][2] - M[1][2] * M[2][0]) +
+                       M[0][2] * (M[1][0] * M[2][1] - M[1][1] * M[2][0]);
+    vp.W = cam->width; vp.H = cam->height;
+    vp.tiles_x = (cam->width + 7) >> 3; vp.tiles_y = (cam->height + 3) >> 2;
+    vp.kx = double(cam->h_fov) * double(cam->aspect_ratio);
+    vp.valid = 0;
+    if (!(std::fabs(det) > 1e-3) || !std::isfinite(det) || !std::isfinite(vp.kx) || !(std::fabs(vp.kx) > 1e-9)) return vp;
+    const double id = 1.0 / det;
+    vp.minv[0][0] = (M[1][1] * M[2][2] - M[1][2] * M[2][1]) * id; vp.minv[0][1] = (M[0][2] * M[2][1] - M[0][1] * M[2][2]) * id;
+    vp.minv[0][2] = (M[0][1] * M[1][2] - M[0][2] * M[1][1]) * id; vp.minv[1][0] = (M[1][2] * M[2][0] - M[1][0] * M[2][2]) * id;
+    vp.minv[1][1] = (M[0][0] * M[2][2] - M[0][2] * M[2][0]) * id; vp.minv[1][2] = (M[0][2] * M[1][0] - M[0][0] * M[1][2]) * id;
+    vp.minv[2][0] = (M[1][0] * M[2][1] - M[1][1] * M[2][0]) * id; vp.minv[2][1] = (M[0][1] * M[2][0] - M[0][0] * M[2][1]) * id;
+    vp.minv[2][2] = (M[0][0] * M[1][1] - M[0][1] * M[1][0]) * id;
+    double fro = 0.0;
+    for (int r = 0; r < 3; ++r)
+    {
+        double n2 = 0.0;
+        for (int k = 0; k < 3; ++k) n2 += vp.minv[r][k] * vp.minv[r][k];
+        vp.row[r] = std::sqrt(n2) * (1.0 + 1e-9);
+        fro += n2;
+    }
+    const double aa_x = cam->anti_aliasing ? std::fabs(double(cam->half_pixel_width)) : 0.0;
+    const double aa_y = cam->anti_aliasing ? std::fabs(double(cam->half_pixel_height)) : 0.0;
+    const double fx_max = std::fabs(vp.kx) * (1.0 + 1e-6) + aa_x, fy_max = 1.0 + 1e-6 + aa_y;
+    double e2 = 0.0, eye_inf = 0.0;
+    for (int i = 0; i < 3; ++i)
+    {
+        const double e = U * (2.0 * std::fabs(double(cam->frame_center[i])) + 3.0 * std::fabs(M[i][0]) * fx_max +
+                              3.0 * std::fabs(M[i][1]) * fy_max);
+        e2 += e * e;
+        eye_inf = std::fmax(eye_inf, std::fabs(vp.eye[i]));
+    }
+    const double dmin = 1.0 / std::sqrt(fro);
+    vp.ang = 2.0 * (std::sqrt(e2) / dmin + 4.0 * U);
+    // film→pixel inversion slack: 6 roundings in film_x (rel. u each) ≈ 3u·W pixels; one full pixel is added on top,
+    // and half a pixel more when the samples are jittered (renderer.cpp:340-341: |rand_bi| <= 1)
+    vp.px_slack_x = 1.0 + 1e-6 * vp.W + (cam->anti_aliasing ? 0.51 : 0.0);
+    vp.px_slack_y = 1.0 + 1e-6 * vp.H + (cam->anti_aliasing ? 0.51 : 0.0);
+    bool fin = std::isfinite(vp.ang) && std::isfinite(eye_inf) && eye_inf < 1073741824.0;
+    for (int r = 0; r < 3; ++r)
+        for (int k = 0; k < 3; ++k) fin = fin && std::isfinite(vp.minv[r][k]);
+    vp.valid = fin ? 1 : 0;
+    return vp;
+}
+
 static int enqueue_render(atray_ctx* c, const AtrayCamera* cam, const AtrayRenderOpts* o, const DevOut& out)
 {
     DevCounters* ctr = nullptr;
@@ -322,9 +396,40 @@ static int enqueue_render(atray_ctx* c, const AtrayCamera* cam, const AtrayRende
         c->counters_valid = true;
     }
     DevPartition p{o->part.rank, o->part.world, o->part.band_rows};
+    ViewParams vp = make_view_params(cam);
+    const bool cull = !(o->flags & ATRAY_RENDER_NO_CULL) && vp.valid;
+    if (cull)
+    {
+        const size_t tiles = size_t(vp.tiles_x) * size_t(vp.tiles_y);
+        if (tiles > c->stamp_cap || c->frame_seq == 0xffffffffu)
+        {
+            if (tiles > c->stamp_cap)
+            {
+                cudaFree(c->view.stamps);
+                c->view.stamps = nullptr; c->stamp_cap = 0;
+                CU(cudaMalloc(&c->view.stamps, tiles * sizeof(uint32_t)));
+                c->stamp_cap = tiles;
+            }
+            if (!c->view.all_flag) CU(cudaMalloc(&c->view.all_flag, sizeof(uint32_t)));
+            CU(cudaMemsetAsync(c->view.stamps, 0, c->stamp_cap * sizeof(uint32_t), c->stream));
+            CU(cudaMemsetAsync(c->view.all_flag, 0, sizeof(uint32_t), c->stream));
+            c->frame_seq = 0;
+        }
+        vp.frame_id = ++c->frame_seq;
+        c->view.frame_id = vp.frame_id;
+        c->view.tiles_x = vp.tiles_x;
+    }
     CU(cudaEventRecord(c->ev_k0, c->stream));
-    CU(launch_render(c->scene, to_dev(cam), p, out, c->scratch, c->d_tile_counter, ctr, o->fp_mode == ATRAY_FP_FAST,
-                     o->jitter_seed, c->cfg, c->stream));
+    if (cull)
+    {
+        // the film rectangles depend on the camera: recomputed every frame, inside the timed region
+        CU(launch_view_bounds(c->scene, vp, c->view, c->stream));
+        CU(launch_render_culled(c->scene, to_dev(cam), p, out, c->scratch, c->view, c->d_tile_counter, ctr,
+                                o->fp_mode == ATRAY_FP_FAST, o->jitter_seed, c->cfg, c->stream));
+    }
+    else
+        CU(launch_render(c->scene, to_dev(cam), p, out, c->scratch, c->d_tile_counter, ctr, o->fp_mode == ATRAY_FP_FAST,
+                         o->jitter_seed, c->cfg, c->stream));
     CU(cudaEventRecord(c->ev_k1, c->stream));
     c->have_kernel_time = true;
     return ATRAY_OK;
@@ -489,6 +594,48 @@ int atray_get_counters(atray_ctx* c, AtrayCounters* out)
     CU(cudaSetDevice(c->device));
     CU(cudaStreamSynchronize(c->stream));
     CU(cudaMemcpy(out, c->d_counters, sizeof(DevCounters), cudaMemcpyDeviceToHost));
+    return ATRAY_OK;
+}
+
+// ---- verification aid: the film rectangles of view_bounds.h evaluated on the host ------------------------------------
+int atray_debug_film_rects(const atray_model* m, const AtrayCamera* cam, float* rects, uint32_t* slot_leaf, uint32_t* slot_pos,
+                           uint8_t* tile_busy)
+{
+    if (!m || !cam) return fail(ATRAY_EINVAL, "null argument");
+    if (m->m.tree.empty()) return fail(ATRAY_ESTATE, "film_rects before build_tree");
+    ViewParams vp = make_view_params(cam);
+    if (!vp.valid) return fail(ATRAY_ESTATE, "camera not usable for culling");
+    FlatScene f;
+    flatten(m->m, f);
+    const size_t tiles = size_t(vp.tiles_x) * size_t(vp.tiles_y);
+    if (tile_busy) std::memset(tile_busy, 0, tiles);
+    for (uint32_t s = 0; s < f.n_slots; ++s)
+    {
+        const float* pkt = &f.tris[size_t(s / 8) * 24 * 4];
+        const float* A = pkt + size_t(s % 8) * 4;
+        const float* AB = A + 32;
+        const float* AC = A + 64;
+        uint32_t face, pos;
+        std::memcpy(&face, A + 3, 4);
+        std::memcpy(&pos, AB + 3, 4);
+        FilmRect r = film_rect_empty();
+        if (face != 0xffffffffu) r = tri_film_rect(vp, A, AB, AC);
+        if (rects) { rects[4 * size_t(s)] = r.xlo; rects[4 * size_t(s) + 1] = r.ylo; rects[4 * size_t(s) + 2] = r.xhi; rects[4 * size_t(s) + 3] = r.yhi; }
+        if (slot_leaf) slot_leaf[s] = f.packet_leaf[s / 8];
+        if (slot_pos) slot_pos[s] = face != 0xffffffffu ? pos : 0xffffffffu;
+        if (tile_busy)
+        {
+            int tx0, tx1, ty0, ty1;
+            bool all = false;
+            if (film_rect_tiles(vp, r, tx0, tx1, ty0, ty1, all))
+            {
+                if (all) std::memset(tile_busy, 1, tiles);
+                else
+                    for (int ty = ty0; ty <= ty1; ++ty)
+                        for (int tx = tx0; tx <= tx1; ++tx) tile_busy[size_t(ty) * vp.tiles_x + tx] = 1;
+            }
+        }
+    }
     return ATRAY_OK;
 }
 

@@ -3,13 +3,16 @@
 #include <cstdint>
 #include <cuda_runtime.h>
 
+#include "view_bounds.h"
+
 namespace atray {
 
 struct DevScene
 {
     const float4* nodes;   // 2 float4 per node
-    const float4* tris;    // blocks of 32 slots: 32×A | 32×AB | 32×AC
+    const float4* tris;    // packets of 8 slots: 8×{a,face} | 8×{ab,pos} | 8×{ac,0}
     uint32_t n_nodes;
+    uint32_t n_slots;
     uint32_t root_is_leaf;
     float sky[3];          // materials[0].emission_color (renderer.cpp:152, 226)
     float mdl[3];          // model material emission_color (renderer.cpp:258)
@@ -31,6 +34,19 @@ struct DevOut { uint32_t* bgrx; float* t; uint32_t* prim; };
 struct DevCounters  // mirrors AtrayCounters
 {
     unsigned long long rays, box_tests, tri_tests, pass_det, pass_u, pass_v, leaves_listed, leaves_scanned, overflow_rays;
+    unsigned long long rect_tests, tiles_sky, tiles_busy;
+};
+
+// Per-frame film-space bounds written by k_view_bounds and read by the culled render kernel (view_bounds.h).
+struct DevView
+{
+    float4* tri_rect;      // n_slots   {xlo, ylo, xhi, yhi}
+    float4* pkt_rect;      // n_slots/8 union over the packet's slots
+    float4* leaf_rect;     // n_nodes   union over the leaf's packets (inner nodes: unused)
+    uint32_t* stamps;      // one per 8x4-pixel tile: == frame_id ⇔ some triangle rectangle may touch the tile
+    uint32_t* all_flag;    // == frame_id ⇔ an unbounded rectangle exists: every tile is busy
+    uint32_t frame_id;
+    int32_t tiles_x;
 };
 
 // Per-warp spill area for rays whose leaf list / inner-node stack outgrow the per-lane arrays.
@@ -47,6 +63,12 @@ struct LaunchCfg { int grid, block; };
 cudaError_t launch_render(const DevScene& sc, const DevCamera& cam, const DevPartition& part, const DevOut& out,
                           const DevScratch& scratch, unsigned int* tile_counter, DevCounters* counters, int fp_fast,
                           unsigned long long jitter_seed, LaunchCfg cfg, cudaStream_t stream);
+// culled frame = k_view_bounds (per-frame film rectangles + tile stamps) followed by k_render_culled
+cudaError_t launch_view_bounds(const DevScene& sc, const ViewParams& vp, const DevView& view, cudaStream_t stream);
+cudaError_t launch_render_culled(const DevScene& sc, const DevCamera& cam, const DevPartition& part, const DevOut& out,
+                                 const DevScratch& scratch, const DevView& view, unsigned int* tile_counter,
+                                 DevCounters* counters, int fp_fast, unsigned long long jitter_seed, LaunchCfg cfg,
+                                 cudaStream_t stream);
 cudaError_t launch_trace(const DevScene& sc, const float* rays, unsigned long long n, uint32_t* prim, float* t,
                          const DevScratch& scratch, unsigned int* tile_counter, DevCounters* counters, int fp_fast,
                          LaunchCfg cfg, cudaStream_t stream);

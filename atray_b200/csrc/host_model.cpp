@@ -7,6 +7,8 @@
 // Compile with -ffp-contract=off: every float expression below is evaluated in the reference's operation order.
 #include "host_model.h"
 
+#include <algorithm>
+
 #include <atomic>
 #include <cmath>
 #include <cstdio>
@@ -346,8 +348,58 @@ int build_tree(HostModel& m, int method, uint32_t cap, std::string& err)
 // ---------------------------------------------------------------------------------------------------------------
 // flat GPU form. Edges ab = b - a, ac = c - a are the first two operations of the reference's triangle
 // test (model.h:78-79); computing them here in f32 yields the same bits the CPU path computes per ray.
+// Within a leaf the records are stored in Morton order of their centroids (spatially compact packets of 8 for the
+// film-space culling of the render kernel); each record carries its position in the reference's leaf order, which is
+// what the sequential strict-< scan of kd_tree.cpp:437-462 breaks ties on.
 // ---------------------------------------------------------------------------------------------------------------
 static inline float bits_to_float(uint32_t u) { float f; std::memcpy(&f, &u, 4); return f; }
+
+static inline uint32_t spread10(uint32_t v)  // 10 bits → every third bit
+{
+    v &= 1023u;
+    v = (v | (v << 16)) & 0x030000FFu;
+    v = (v | (v << 8)) & 0x0300F00Fu;
+    v = (v | (v << 4)) & 0x030C30C3u;
+    v = (v | (v << 2)) & 0x09249249u;
+    return v;
+}
+
+static void morton_order(const std::vector<PrimRef>& prims, std::vector<uint32_t>& order)
+{
+    const size_t n = prims.size();
+    order.resize(n);
+    for (size_t i = 0; i < n; ++i) order[i] = uint32_t(i);
+    if (n <= 8) return;
+    double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
+    std::vector<double> ctr(n * 3);
+    for (size_t i = 0; i < n; ++i)
+    {
+        const PrimRef& t = prims[i];
+        const double c[3] = {(double(t.a.x) + t.b.x + t.c.x) / 3.0, (double(t.a.y) + t.b.y + t.c.y) / 3.0,
+                             (double(t.a.z) + t.b.z + t.c.z) / 3.0};
+        for (int k = 0; k < 3; ++k)
+        {
+            ctr[3 * i + k] = c[k];
+            if (c[k] < lo[k]) lo[k] = c[k];
+            if (c[k] > hi[k]) hi[k] = c[k];
+        }
+    }
+    std::vector<uint32_t> code(n, 0u);
+    for (size_t i = 0; i < n; ++i)
+    {
+        uint32_t q[3];
+        for (int k = 0; k < 3; ++k)
+        {
+            const double e = hi[k] - lo[k];
+            double f = e > 0.0 ? (ctr[3 * i + k] - lo[k]) / e : 0.0;
+            if (!(f >= 0.0)) f = 0.0;   // NaN-safe
+            if (f > 1.0) f = 1.0;
+            q[k] = uint32_t(f * 1023.0);
+        }
+        code[i] = (spread10(q[0]) << 2) | (spread10(q[1]) << 1) | spread10(q[2]);
+    }
+    std::stable_sort(order.begin(), order.end(), [&](uint32_t x, uint32_t y) { return code[x] < code[y]; });
+}
 
 void flatten(const HostModel& m, FlatScene& out)
 {
@@ -356,10 +408,12 @@ void flatten(const HostModel& m, FlatScene& out)
     out.nodes.assign(size_t(out.n_nodes) * 8, 0.f);
     uint32_t slots = 0;
     for (const TreeNode& n : m.tree)
-        if (n.children_start == 0) slots += (uint32_t(n.prims.size()) + 31u) & ~31u;
+        if (n.children_start == 0) slots += (uint32_t(n.prims.size()) + 7u) & ~7u;
     out.n_slots = slots;
-    out.tris.assign(size_t(slots / 32) * 96 * 4, 0.f);
+    out.tris.assign(size_t(slots / 8) * 24 * 4, 0.f);
+    out.packet_leaf.assign(slots / 8, 0u);
     uint32_t cursor = 0;
+    std::vector<uint32_t> order;
     for (uint32_t i = 0; i < out.n_nodes; ++i)
     {
         const TreeNode& n = m.tree[i];
@@ -377,23 +431,28 @@ void flatten(const HostModel& m, FlatScene& out)
         q[7] = bits_to_float(cnt);
         ++out.n_leaves;
         if (cnt > out.max_leaf_prims) out.max_leaf_prims = cnt;
-        const uint32_t padded = (cnt + 31u) & ~31u;
+        const uint32_t padded = (cnt + 7u) & ~7u;
+        morton_order(n.prims, order);
         for (uint32_t k = 0; k < padded; ++k)
         {
             const uint32_t slot = cursor + k;
-            float* blk = &out.tris[size_t(slot / 32) * 96 * 4];
-            float* A = blk + size_t(slot % 32) * 4;
-            float* AB = A + 32 * 4;
-            float* AC = A + 64 * 4;
+            float* pkt = &out.tris[size_t(slot / 8) * 24 * 4];
+            float* A = pkt + size_t(slot % 8) * 4;
+            float* AB = A + 8 * 4;
+            float* AC = A + 16 * 4;
+            out.packet_leaf[slot / 8] = i;
             if (k < cnt)
             {
-                const PrimRef& t = n.prims[k];
+                const PrimRef& t = n.prims[order[k]];
                 A[0] = t.a.x; A[1] = t.a.y; A[2] = t.a.z; A[3] = bits_to_float(t.face);
-                AB[0] = t.b.x - t.a.x; AB[1] = t.b.y - t.a.y; AB[2] = t.b.z - t.a.z;
+                AB[0] = t.b.x - t.a.x; AB[1] = t.b.y - t.a.y; AB[2] = t.b.z - t.a.z; AB[3] = bits_to_float(order[k]);
                 AC[0] = t.c.x - t.a.x; AC[1] = t.c.y - t.a.y; AC[2] = t.c.z - t.a.z;
             }
             else
+            {
                 A[3] = bits_to_float(0xffffffffu);  // padding slot: zero edges → det = 0 < tolerance → never a hit
+                AB[3] = bits_to_float(0xffffffffu);
+            }
         }
         cursor += padded;
     }

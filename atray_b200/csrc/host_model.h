@@ -34,10 +34,12 @@ struct HostModel
 struct FlatScene
 {
     // node i = two float4: {lo.xyz, w0} {hi.xyz, w1}; inner: w0 = children_start (>0), w1 = 0;
-    // leaf: w0 = ~first_slot (<0, first_slot multiple of 32), w1 = primitive count.
+    // leaf: w0 = ~first_slot (<0, first_slot multiple of 8), w1 = primitive count.
     std::vector<float> nodes;        // n_nodes * 8
-    // triangle slots in blocks of 32: block b = 32×{a.xyz, face} | 32×{ab.xyz, 0} | 32×{ac.xyz, 0}
-    std::vector<float> tris;         // n_slots/32 * 96 * 4
+    // triangle slots in packets of 8: packet p = 8×{a.xyz, face} | 8×{ab.xyz, position in the reference's leaf order}
+    // | 8×{ac.xyz, 0}; within a leaf the slots are in Morton order of the triangle centroids
+    std::vector<float> tris;         // n_slots/8 * 24 * 4
+    std::vector<uint32_t> packet_leaf;  // n_slots/8: node index of the leaf that owns the packet
     uint32_t n_nodes = 0, n_slots = 0, n_leaves = 0, max_leaf_prims = 0;
 };
 

@@ -49,8 +49,8 @@ template <bool STRICT> struct Fp
 
 struct WorkCount
 {
-    unsigned int box, tri, pdet, pu, pv, listed, scanned, ovf;
-    __device__ void clear() { box = tri = pdet = pu = pv = listed = scanned = ovf = 0; }
+    unsigned int box, tri, pdet, pu, pv, listed, scanned, ovf, rect, tsky, tbusy;
+    __device__ void clear() { box = tri = pdet = pu = pv = listed = scanned = ovf = rect = tsky = tbusy = 0; }
 };
 
 // ---- ray/box slab tests (aabb.h). `near`/`far` selection by the sign of 1/d is the reference's bounds[sign] indexing.
@@ -95,9 +95,13 @@ __device__ __forceinline__ float box_entry(const RayL& r, float ix, float iy, fl
 }
 
 // ---- phase 1: collect the sorted leaf list of one ray (kd_tree.cpp:363-435). Returns false on capacity overflow.
-template <bool COUNT>
+// CULL: a leaf whose film rectangle (k_view_bounds) does not contain the ray's film point cannot yield an accepted
+// triangle (view_bounds.h); it still counts as an accepted child for the ≤5 cut but is left out of the list. The stable
+// insertion keeps the relative order of the remaining leaves, so the scan order of the reference is preserved.
+template <bool COUNT, bool CULL>
 __device__ bool collect_leaves(const float4* __restrict__ nodes, const RayL& r, float ix, float iy, float iz, uint32_t* stack,
-                               int stack_cap, uint2* leaves, int leaf_cap, int& nleaf, WorkCount& wc)
+                               int stack_cap, uint2* leaves, int leaf_cap, int& nleaf, WorkCount& wc,
+                               const float4* __restrict__ leaf_rect = nullptr, float fx = 0.f, float fy = 0.f)
 {
     nleaf = 0;
     int sp = 1;
@@ -129,6 +133,12 @@ __device__ bool collect_leaves(const float4* __restrict__ nodes, const RayL& r, 
                 if (dis > 0.0f)
                 {
                     ++accepted;
+                    if (CULL)
+                    {
+                        const float4 R = __ldg(&leaf_rect[ch]);
+                        if (COUNT) wc.rect++;
+                        if (fx < R.x || fx > R.z || fy < R.y || fy > R.w) continue;
+                    }
                     if (nleaf >= leaf_cap) return false;
                     int k = nleaf;  // stable insertion from the back: ties and later arrivals go after existing entries
                     while (k > 0 && dis < __uint_as_float(leaves[k - 1].y))
@@ -168,13 +178,16 @@ __device__ __forceinline__ void scan_ray_leaves(const DevScene& sc, int lane, in
         if (COUNT && lane == src) wc.scanned++;
         float bt = kMaxFloat;
         uint32_t bpos = 0xffffffffu, bface = 0xffffffffu;
-        const float4* blk = sc.tris + (size_t)(first >> 5) * 96 + lane;
-        for (uint32_t base = 0; base < cnt; base += 32, blk += 96)
+        const uint32_t padded = (cnt + 7u) & ~7u;  // slots of this leaf (packets of 8)
+        for (uint32_t base = 0; base < cnt; base += 32)
         {
-            const float4 A = __ldg(blk);
-            const float4 AB = __ldg(blk + 32);
-            const float4 AC = __ldg(blk + 64);
-            const bool real = base + lane < cnt;
+            // 32 consecutive slots = 4 packets; lane → packet (lane >> 3), slot in packet (lane & 7)
+            const uint32_t slot = first + base + lane;
+            const bool in_leaf = base + lane < padded;
+            const float4* rec = sc.tris + (size_t)(slot >> 3) * 24 + (slot & 7);
+            float4 A = make_float4(0.f, 0.f, 0.f, __uint_as_float(0xffffffffu)), AB = make_float4(0.f, 0.f, 0.f, 0.f), AC = AB;
+            if (in_leaf) { A = __ldg(rec); AB = __ldg(rec + 8); AC = __ldg(rec + 16); }
+            const bool real = __float_as_uint(A.w) != 0xffffffffu;
             // get_triangle_ray_intersection_culled, model.h:75-103 (ab, ac precomputed with the same f32 subtraction)
             const float px = F::crs(dy, AC.z, dz, AC.y), py = F::crs(dz, AC.x, dx, AC.z), pz = F::crs(dx, AC.y, dy, AC.x);
             const float det = F::dot(AB.x, AB.y, AB.z, px, py, pz);
@@ -196,7 +209,7 @@ __device__ __forceinline__ void scan_ray_leaves(const DevScene& sc, int lane, in
             if (alive && t < bt && t > kTol)  // caller's accept: distance < closest && distance > tolerance
             {
                 bt = t;
-                bpos = base + lane;
+                bpos = __float_as_uint(AB.w);  // position in the reference's leaf order (records are Morton-sorted)
                 bface = __float_as_uint(A.w);
             }
         }
@@ -243,7 +256,7 @@ __device__ __forceinline__ void trace_warp(const DevScene& sc, const DevScratch&
                 nleaf = 1;
             }
             else
-                overflow = !collect_leaves<COUNT>(sc.nodes, ray, ix, iy, iz, stack, kStackCap, leaves, kLeafCap, nleaf, wc);
+                overflow = !collect_leaves<COUNT, false>(sc.nodes, ray, ix, iy, iz, stack, kStackCap, leaves, kLeafCap, nleaf, wc);
             if (overflow) nleaf = 0;
         }
     }
@@ -269,7 +282,7 @@ __device__ __forceinline__ void trace_warp(const DevScene& sc, const DevScratch&
             WorkCount dummy;
             dummy.clear();
             // the aborted first attempt already counted a partial walk; the redo is not counted again
-            collect_leaves<false>(sc.nodes, ray, ix, iy, iz, gs, (int)scratch.stack_cap, gl, (int)scratch.leaf_cap, gn, dummy);
+            collect_leaves<false, false>(sc.nodes, ray, ix, iy, iz, gs, (int)scratch.stack_cap, gl, (int)scratch.leaf_cap, gn, dummy);
         }
         __syncwarp();
         scan_ray_leaves<STRICT, COUNT>(sc, lane, src, ray, gl, gn, t_out, face_out, wc);
@@ -331,12 +344,13 @@ __device__ __forceinline__ void flush_counters(DevCounters* c, const WorkCount& 
         return (unsigned long long)v;
     };
     const unsigned long long r = red(rays), b = red(wc.box), t = red(wc.tri), d = red(wc.pdet), u = red(wc.pu), v = red(wc.pv),
-                             l = red(wc.listed), s = red(wc.scanned), o = red(wc.ovf);
+                             l = red(wc.listed), s = red(wc.scanned), o = red(wc.ovf), rc = red(wc.rect), ts = red(wc.tsky),
+                             tb = red(wc.tbusy);
     if ((threadIdx.x & 31) == 0)
     {
         atomicAdd(&c->rays, r); atomicAdd(&c->box_tests, b); atomicAdd(&c->tri_tests, t); atomicAdd(&c->pass_det, d);
         atomicAdd(&c->pass_u, u); atomicAdd(&c->pass_v, v); atomicAdd(&c->leaves_listed, l); atomicAdd(&c->leaves_scanned, s);
-        atomicAdd(&c->overflow_rays, o);
+        atomicAdd(&c->overflow_rays, o); atomicAdd(&c->rect_tests, rc); atomicAdd(&c->tiles_sky, ts); atomicAdd(&c->tiles_busy, tb);
     }
 }
 
@@ -407,6 +421,335 @@ __global__ void __launch_bounds__(kBlock) k_render(DevScene sc, DevCamera cm, De
             const float n = (float)cm.spp;
             const size_t idx = (size_t)y * (size_t)cm.W + (size_t)x;
             if (out.bgrx) out.bgrx[idx] = pack_bgrx(__fdiv_rn(cr, n), __fdiv_rn(cg, n), __fdiv_rn(cb, n));  // :358-365
+            if (out.t) out.t[idx] = t;
+            if (out.prim) out.prim[idx] = face;
+        }
+    }
+    if (COUNT) flush_counters(counters, wc, rays_done);
+}
+
+// ---- per-frame film-space bounds (view_bounds.h): one warp per leaf -------------------------------------------------
+__device__ __forceinline__ float4 rect_union_xor(float4 r, int off)
+{
+    r.x = fminf(r.x, __shfl_xor_sync(FULL_MASK, r.x, off)); r.y = fminf(r.y, __shfl_xor_sync(FULL_MASK, r.y, off));
+    r.z = fmaxf(r.z, __shfl_xor_sync(FULL_MASK, r.z, off)); r.w = fmaxf(r.w, __shfl_xor_sync(FULL_MASK, r.w, off));
+    return r;
+}
+
+__global__ void __launch_bounds__(kBlock) k_view_bounds(DevScene sc, ViewParams vp, DevView view)
+{
+    const int lane = threadIdx.x & 31;
+    const uint32_t node = (blockIdx.x * kBlock + threadIdx.x) >> 5;
+    if (node >= sc.n_nodes) return;
+    const float4 n0 = __ldg(&sc.nodes[2 * node]);
+    if (__float_as_int(n0.w) > 0) return;  // inner node
+    const uint32_t first = ~(uint32_t)__float_as_int(n0.w);
+    const uint32_t cnt = (uint32_t)__float_as_int(__ldg(&sc.nodes[2 * node + 1]).w);
+    const uint32_t padded = (cnt + 7u) & ~7u;
+    const int n_tiles = vp.tiles_x * vp.tiles_y;
+    float4 acc = make_float4(INFINITY, INFINITY, -INFINITY, -INFINITY);
+    for (uint32_t base = 0; base < padded; base += 32)
+    {
+        const uint32_t slot = first + base + lane;
+        const bool in_leaf = base + lane < padded;
+        float4 r = make_float4(INFINITY, INFINITY, -INFINITY, -INFINITY);
+        int tx0 = 0, tx1 = -1, ty0 = 0, ty1 = -1;
+        bool big = false;
+        if (in_leaf)
+        {
+            const float4* rec = sc.tris + (size_t)(slot >> 3) * 24 + (slot & 7);
+            const float4 A = __ldg(rec), AB = __ldg(rec + 8), AC = __ldg(rec + 16);
+            if (__float_as_uint(A.w) != 0xffffffffu)
+            {
+                const FilmRect fr = tri_film_rect(vp, &A.x, &AB.x, &AC.x);
+                r = make_float4(fr.xlo, fr.ylo, fr.xhi, fr.yhi);
+                bool all = false;
+                if (film_rect_tiles(vp, fr, tx0, tx1, ty0, ty1, all))
+                {
+                    const int nt = (tx1 - tx0 + 1) * (ty1 - ty0 + 1);
+                    if (all || 2 * nt >= n_tiles) { *view.all_flag = vp.frame_id; tx1 = tx0 - 1; }
+                    else if (nt > 48) big = true;
+                    else
+                    {
+                        for (int ty = ty0; ty <= ty1; ++ty)
+                            for (int tx = tx0; tx <= tx1; ++tx) view.stamps[ty * vp.tiles_x + tx] = vp.frame_id;
+                    }
+                }
+            }
+            view.tri_rect[slot] = r;
+        }
+        // large rectangles: the whole warp stamps the tiles of one triangle at a time
+        unsigned bm = __ballot_sync(FULL_MASK, big);
+        while (bm)
+        {
+            const int src = __ffs(bm) - 1;
+            bm &= bm - 1;
+            const int ax0 = __shfl_sync(FULL_MASK, tx0, src), ax1 = __shfl_sync(FULL_MASK, tx1, src);
+            const int ay0 = __shfl_sync(FULL_MASK, ty0, src), ay1 = __shfl_sync(FULL_MASK, ty1, src);
+            const int w = ax1 - ax0 + 1, n = w * (ay1 - ay0 + 1);
+            for (int i = lane; i < n; i += 32) view.stamps[(ay0 + i / w) * vp.tiles_x + ax0 + i % w] = vp.frame_id;
+        }
+        float4 p = r;
+        p = rect_union_xor(p, 4); p = rect_union_xor(p, 2); p = rect_union_xor(p, 1);
+        if (in_leaf && (lane & 7) == 0) view.pkt_rect[slot >> 3] = p;
+        acc.x = fminf(acc.x, r.x); acc.y = fminf(acc.y, r.y); acc.z = fmaxf(acc.z, r.z); acc.w = fmaxf(acc.w, r.w);
+    }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) acc = rect_union_xor(acc, off);
+    if (lane == 0) view.leaf_rect[node] = acc;
+}
+
+// ---- culled phase 2: the warp walks the k-th listed leaf of each of its rays; rays that share the leaf form a group.
+// Candidate records are found hierarchically (packet rectangle, then triangle rectangle, against the tile's film
+// rectangle); each candidate is broadcast and every ray of the group whose film point lies inside the triangle's
+// rectangle runs the reference triangle test on it. A ray's result is the lexicographic minimum (t, position in the
+// reference's leaf order) over the accepted records of its first leaf that has any (kd_tree.cpp:437-462).
+__device__ __forceinline__ bool rect_overlap(const float4 R, const float4 T)
+{
+    return !(R.x > T.z || R.z < T.x || R.y > T.w || R.w < T.y);
+}
+
+template <bool STRICT, bool COUNT>
+__device__ __forceinline__ void scan_tile_leaves(const DevScene& sc, const DevView& vw, int lane, const RayL& ray, float fx, float fy,
+                                                 const float4 trect, const uint2* list, int nleaf, float& t_out,
+                                                 uint32_t& face_out, WorkCount& wc)
+{
+    typedef Fp<STRICT> F;
+    bool done = nleaf <= 0;
+    int k = 0;
+    float bt = kMaxFloat;
+    uint32_t bpos = 0xffffffffu, bface = 0xffffffffu;
+    while (__any_sync(FULL_MASK, !done))
+    {
+        const uint32_t myleaf = done ? 0xffffffffu : list[k].x;
+        unsigned pending = __ballot_sync(FULL_MASK, !done);
+        while (pending)
+        {
+            const int leader = __ffs(pending) - 1;
+            const uint32_t id = __shfl_sync(FULL_MASK, myleaf, leader);
+            const bool ingrp = myleaf == id;
+            pending &= ~__ballot_sync(FULL_MASK, ingrp);
+            if (COUNT && ingrp) wc.scanned++;
+            const uint32_t first = ~(uint32_t)__float_as_int(__ldg(&sc.nodes[2 * id]).w);
+            const uint32_t cnt = (uint32_t)__float_as_int(__ldg(&sc.nodes[2 * id + 1]).w);
+            const uint32_t npk = (cnt + 7u) >> 3, pk0 = first >> 3;
+            for (uint32_t pb = 0; pb < npk; pb += 32)
+            {
+                bool pov = false;
+                if (pb + lane < npk)
+                {
+                    pov = rect_overlap(__ldg(&vw.pkt_rect[pk0 + pb + lane]), trect);
+                    if (COUNT) wc.rect++;
+                }
+                unsigned pmask = __ballot_sync(FULL_MASK, pov);
+                while (pmask)
+                {
+                    // the next (up to) four overlapping packets, one per group of 8 lanes
+                    int sel = -1;
+                    {
+                        unsigned m = pmask;
+                        const int j = lane >> 3;
+#pragma unroll
+                        for (int q = 0; q < 4; ++q)
+                        {
+                            const int b = m ? __ffs(m) - 1 : -1;
+                            if (q == j) sel = b;
+                            m &= m - 1;  // m == 0 stays 0
+                        }
+                        pmask = m;
+                    }
+                    bool cov = false;
+                    uint32_t myslot = 0;
+                    if (sel >= 0)
+                    {
+                        myslot = ((pk0 + pb + (uint32_t)sel) << 3) + (lane & 7);
+                        cov = rect_overlap(__ldg(&vw.tri_rect[myslot]), trect);
+                        if (COUNT) wc.rect++;
+                    }
+                    unsigned cmask = __ballot_sync(FULL_MASK, cov);
+                    while (cmask)
+                    {
+                        const int b = __ffs(cmask) - 1;
+                        cmask &= cmask - 1;
+                        const uint32_t s = __shfl_sync(FULL_MASK, myslot, b);
+                        const float4 R = __ldg(&vw.tri_rect[s]);
+                        bool alive = ingrp && !(fx < R.x || fx > R.z || fy < R.y || fy > R.w);
+                        if (!__any_sync(FULL_MASK, alive)) continue;
+                        const float4* rec = sc.tris + (size_t)(s >> 3) * 24 + (s & 7);
+                        const float4 A = __ldg(rec), AB = __ldg(rec + 8), AC = __ldg(rec + 16);
+                        // get_triangle_ray_intersection_culled, model.h:75-103, this lane's own ray
+                        const float px = F::crs(ray.dy, AC.z, ray.dz, AC.y), py = F::crs(ray.dz, AC.x, ray.dx, AC.z),
+                                    pz = F::crs(ray.dx, AC.y, ray.dy, AC.x);
+                        const float det = F::dot(AB.x, AB.y, AB.z, px, py, pz);
+                        if (COUNT) wc.tri += alive ? 1u : 0u;
+                        alive = alive && !(det < kTol);
+                        if (COUNT) wc.pdet += alive ? 1u : 0u;
+                        if (!__any_sync(FULL_MASK, alive)) continue;
+                        const float det_inv = __frcp_rn(det);
+                        const float tx = F::sub(ray.ox, A.x), ty = F::sub(ray.oy, A.y), tz = F::sub(ray.oz, A.z);
+                        const float u = F::mul(F::dot(tx, ty, tz, px, py, pz), det_inv);
+                        alive = alive && !(u < 0.0f || u > 1.0f);
+                        if (COUNT) wc.pu += alive ? 1u : 0u;
+                        if (!__any_sync(FULL_MASK, alive)) continue;
+                        const float qx = F::crs(ty, AB.z, tz, AB.y), qy = F::crs(tz, AB.x, tx, AB.z), qz = F::crs(tx, AB.y, ty, AB.x);
+                        const float v = F::mul(F::dot(ray.dx, ray.dy, ray.dz, qx, qy, qz), det_inv);
+                        alive = alive && !(v < 0.0f || F::add(u, v) > 1.0f);
+                        if (COUNT) wc.pv += alive ? 1u : 0u;
+                        if (!__any_sync(FULL_MASK, alive)) continue;
+                        const float t = F::mul(F::dot(qx, qy, qz, AC.x, AC.y, AC.z), det_inv);
+                        const uint32_t pos = __float_as_uint(AB.w);
+                        if (alive && t > kTol && (t < bt || (t == bt && pos < bpos)))
+                        {
+                            bt = t;
+                            bpos = pos;
+                            bface = __float_as_uint(A.w);
+                        }
+                    }
+                }
+            }
+        }
+        if (!done)
+        {
+            if (bt < kMaxFloat) done = true;  // first leaf with a hit ends the ray (kd_tree.cpp:457-460)
+            else if (++k >= nleaf) done = true;
+        }
+    }
+    t_out = bt;
+    face_out = bface;
+}
+
+// ---- one warp, one 8x4 tile, culled: phase 1 per lane with the leaf-rectangle filter, phase 2 per tile --------------
+template <bool STRICT, bool COUNT>
+__device__ __forceinline__ void trace_tile_culled(const DevScene& sc, const DevScratch& scratch, const DevView& vw, int warp_slot,
+                                                  int lane, bool active, const RayL& ray, float fx, float fy, float& t_out,
+                                                  uint32_t& face_out, WorkCount& wc)
+{
+    uint2 leaves[kLeafCap];
+    uint32_t stack[kStackCap];
+    int nleaf = 0;
+    bool overflow = false;
+    const float ix = __frcp_rn(ray.dx), iy = __frcp_rn(ray.dy), iz = __frcp_rn(ray.dz);
+    if (active)
+    {
+        const float4 lo = __ldg(&sc.nodes[0]);
+        const float4 hi = __ldg(&sc.nodes[1]);
+        if (COUNT) wc.box++;
+        if (box_check(ray, ix, iy, iz, lo, hi))
+        {
+            if (sc.root_is_leaf)
+            {
+                const float4 R = __ldg(&vw.leaf_rect[0]);
+                if (!(fx < R.x || fx > R.z || fy < R.y || fy > R.w)) { leaves[0] = make_uint2(0u, 0u); nleaf = 1; }
+            }
+            else
+                overflow = !collect_leaves<COUNT, true>(sc.nodes, ray, ix, iy, iz, stack, kStackCap, leaves, kLeafCap, nleaf, wc,
+                                                        vw.leaf_rect, fx, fy);
+        }
+    }
+    if (__any_sync(FULL_MASK, overflow))
+    {
+        // a list or stack outgrew the per-lane arrays: this tile takes the unculled path with its global spill area
+        trace_warp<STRICT, COUNT>(sc, scratch, warp_slot, lane, active, ray, t_out, face_out, wc);
+        return;
+    }
+    t_out = kMaxFloat;
+    face_out = 0xffffffffu;
+    if (!__any_sync(FULL_MASK, nleaf > 0)) return;
+    // film rectangle of the rays of this tile that have work
+    float4 tr = nleaf > 0 ? make_float4(fx, fy, fx, fy) : make_float4(INFINITY, INFINITY, -INFINITY, -INFINITY);
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) tr = rect_union_xor(tr, off);
+    scan_tile_leaves<STRICT, COUNT>(sc, vw, lane, ray, fx, fy, tr, leaves, nleaf, t_out, face_out, wc);
+}
+
+// ---- K1c: fused primary-ray render with film-space culling ----------------------------------------------------------
+template <bool STRICT, bool COUNT>
+__global__ void __launch_bounds__(kBlock) k_render_culled(DevScene sc, DevCamera cm, DevPartition part, DevOut out, DevScratch scratch,
+                                                          DevView vw, unsigned int* tile_counter, DevCounters* counters,
+                                                          unsigned long long jitter_seed)
+{
+    const int lane = threadIdx.x & 31;
+    const int warp_slot = (blockIdx.x * kBlock + threadIdx.x) >> 5;
+    const int tiles_x = (cm.W + 7) >> 3;
+    const int rows_per_band = part.band_rows >> 2;
+    const int n_bands = (cm.H + part.band_rows - 1) / part.band_rows;
+    const int my_bands = part.rank < n_bands ? (n_bands - part.rank + part.world - 1) / part.world : 0;
+    const unsigned int tiles_per_band = (unsigned int)(tiles_x * rows_per_band);
+    const unsigned int n_tiles = (unsigned int)my_bands * tiles_per_band;
+    const bool all_busy = __ldg(vw.all_flag) == vw.frame_id;
+    WorkCount wc;
+    wc.clear();
+    unsigned int rays_done = 0;
+    // sky pixel: cast_ray with no hit adds materials[0].emission per sample (renderer.cpp:226, 353-358)
+    float sr = 0.0f, sg = 0.0f, sb = 0.0f;
+    for (uint32_t s = 0; s < cm.spp; ++s) { sr = addr(sr, sc.sky[0]); sg = addr(sg, sc.sky[1]); sb = addr(sb, sc.sky[2]); }
+    const float nspp = (float)cm.spp;
+    const uint32_t sky_px = pack_bgrx(__fdiv_rn(sr, nspp), __fdiv_rn(sg, nspp), __fdiv_rn(sb, nspp));
+    for (;;)
+    {
+        unsigned int tile = 0;
+        if (lane == 0) tile = atomicAdd(tile_counter, 1u);
+        tile = __shfl_sync(FULL_MASK, tile, 0);
+        if (tile >= n_tiles) break;
+        const unsigned int lb = tile / tiles_per_band, rem = tile - lb * tiles_per_band;
+        const int trow = (int)(rem / (unsigned int)tiles_x), tcol = (int)(rem - (unsigned int)trow * (unsigned int)tiles_x);
+        const int x = tcol * 8 + (lane & 7);
+        const int y0 = ((int)lb * part.world + part.rank) * part.band_rows + trow * 4;
+        const int y = y0 + (lane >> 3);
+        const bool active = x < cm.W && y < cm.H;
+        const size_t idx = (size_t)y * (size_t)cm.W + (size_t)x;
+        if (y0 >= cm.H) continue;  // tile rows past the image in the last band
+        const bool busy = all_busy || __ldg(&vw.stamps[(y0 >> 2) * vw.tiles_x + tcol]) == vw.frame_id;
+        if (!busy)
+        {
+            if (active)
+            {
+                if (out.bgrx) out.bgrx[idx] = sky_px;
+                if (out.t) out.t[idx] = kMaxFloat;
+                if (out.prim) out.prim[idx] = 0xffffffffu;
+                rays_done += cm.spp;
+            }
+            if (COUNT && lane == 0) wc.tsky++;
+            continue;
+        }
+        if (COUNT && lane == 0) wc.tbusy++;
+        const float film_y = film_coord(y, cm.H);
+        const float film_x = mulr(mulr(film_coord(x, cm.W), cm.h_fov), cm.aspect);
+        float t = kMaxFloat;
+        uint32_t face = 0xffffffffu;
+        float cr = 0.0f, cg = 0.0f, cb = 0.0f;
+        if (!cm.aa)
+        {
+            const RayL ray = camera_ray(cm, film_x, film_y);
+            trace_tile_culled<STRICT, COUNT>(sc, scratch, vw, warp_slot, lane, active, ray, film_x, film_y, t, face, wc);
+            const bool hit = face != 0xffffffffu;
+            const float er = hit ? sc.mdl[0] : sc.sky[0], eg = hit ? sc.mdl[1] : sc.sky[1], eb = hit ? sc.mdl[2] : sc.sky[2];
+            for (uint32_t s = 0; s < cm.spp; ++s) { cr = addr(cr, er); cg = addr(cg, eg); cb = addr(cb, eb); }
+            if (active) rays_done += 1;
+        }
+        else
+        {
+            const unsigned long long p = (unsigned long long)y * (unsigned long long)cm.W + (unsigned long long)x;
+            Pcg rng;
+            rng.state = splitmix64(jitter_seed ^ p);
+            rng.stream = 2ULL * p + 1ULL;
+            for (uint32_t s = 0; s < cm.spp; ++s)
+            {
+                const float x_off = addr(mulr(pcg_bi(rng), cm.hpw), film_x);
+                const float y_off = addr(mulr(pcg_bi(rng), cm.hph), film_y);
+                const RayL ray = camera_ray(cm, x_off, y_off);
+                trace_tile_culled<STRICT, COUNT>(sc, scratch, vw, warp_slot, lane, active, ray, x_off, y_off, t, face, wc);
+                const bool hit = face != 0xffffffffu;
+                if (hit) { pcg_bi(rng); pcg_bi(rng); pcg_bi(rng); }
+                cr = addr(cr, hit ? sc.mdl[0] : sc.sky[0]);
+                cg = addr(cg, hit ? sc.mdl[1] : sc.sky[1]);
+                cb = addr(cb, hit ? sc.mdl[2] : sc.sky[2]);
+                if (active) rays_done += 1;
+            }
+        }
+        if (active)
+        {
+            if (out.bgrx) out.bgrx[idx] = pack_bgrx(__fdiv_rn(cr, nspp), __fdiv_rn(cg, nspp), __fdiv_rn(cb, nspp));
             if (out.t) out.t[idx] = t;
             if (out.prim) out.prim[idx] = face;
         }
@@ -508,6 +851,34 @@ cudaError_t launch_render(const DevScene& sc, const DevCamera& cam, const DevPar
     {
         if (fp_fast) k_render<false, false><<<cfg.grid, cfg.block, 0, stream>>>(sc, cam, part, out, scratch, tile_counter, counters, jitter_seed);
         else k_render<true, false><<<cfg.grid, cfg.block, 0, stream>>>(sc, cam, part, out, scratch, tile_counter, counters, jitter_seed);
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t launch_view_bounds(const DevScene& sc, const ViewParams& vp, const DevView& view, cudaStream_t stream)
+{
+    const int warps_per_cta = kBlock / 32;
+    const int grid = (int)((sc.n_nodes + warps_per_cta - 1) / warps_per_cta);
+    k_view_bounds<<<grid, kBlock, 0, stream>>>(sc, vp, view);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_render_culled(const DevScene& sc, const DevCamera& cam, const DevPartition& part, const DevOut& out,
+                                 const DevScratch& scratch, const DevView& view, unsigned int* tile_counter,
+                                 DevCounters* counters, int fp_fast, unsigned long long jitter_seed, LaunchCfg cfg,
+                                 cudaStream_t stream)
+{
+    cudaError_t e = cudaMemsetAsync(tile_counter, 0, sizeof(unsigned int), stream);
+    if (e != cudaSuccess) return e;
+    if (counters)
+    {
+        if (fp_fast) k_render_culled<false, true><<<cfg.grid, cfg.block, 0, stream>>>(sc, cam, part, out, scratch, view, tile_counter, counters, jitter_seed);
+        else k_render_culled<true, true><<<cfg.grid, cfg.block, 0, stream>>>(sc, cam, part, out, scratch, view, tile_counter, counters, jitter_seed);
+    }
+    else
+    {
+        if (fp_fast) k_render_culled<false, false><<<cfg.grid, cfg.block, 0, stream>>>(sc, cam, part, out, scratch, view, tile_counter, counters, jitter_seed);
+        else k_render_culled<true, false><<<cfg.grid, cfg.block, 0, stream>>>(sc, cam, part, out, scratch, view, tile_counter, counters, jitter_seed);
     }
     return cudaGetLastError();
 }

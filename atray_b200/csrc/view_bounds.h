@@ -1,0 +1,207 @@
+// View-dependent conservative film-space bounds of one triangle slot ("film rect"), shared by the per-frame CUDA
+// pre-pass (render.cu: k_view_bounds) and the host (capi.cpp: atray_debug_film_rects, used by the CPU soundness tests).
+//
+// Purpose. Every camera ray of a frame starts at the eye and is identified by its film coordinates (fx, fy)
+// (renderer.cpp:317,329,340-341,350-351: pixel_pos = frame_center + camera_x*fx + camera_y*fy). The reference accepts a
+// triangle for a ray only if its float Möller–Trumbore test (model.h:75-103) passes. This file computes, per triangle
+// and per frame, a rectangle R in film space such that
+//
+//        reference accepts the triangle for the ray with film coordinates (fx, fy)   ==>   (fx, fy) lies in R.
+//
+// Rays outside R can skip the triangle without changing any result bit. The implication is proved for the float
+// arithmetic of the reference (not for exact geometry) by the error analysis below; DESIGN.md §4b restates it.
+//
+// Error analysis (u = 2^-24, all quantities real unless hatted; a, ab, ac = the float record values, N = ac x ab,
+// S = |ab||ac|, T = |eye - a|, tau = 1e-4f). With the standard model fl(x∘y) = (x∘y)(1+δ), |δ| <= u:
+//   |pvec^ - pvec| <= 2.42u|d||ac|;  |det^ - det| <= 5.43u S|d|;  |Nu^ - Nu| <= 6.43u T|d||ac|;  |Nv^ - Nv| <= 6.43u T|d||ab|
+//   u^ = Nu^/det^ (1+2δ), v^ = Nv^/det^ (1+2δ), accepted  =>  det^ >= tau, 0 <= u^, 0 <= v^, u^+v^ <= 1+u.
+// All constants are rounded up to 8u. Let c = 8u(1+1e-6)/max(tau, det_lo). Then the barycentric errors satisfy
+//   Eu <= (c|ac|(T+|ab|) + 3u)/(1 - cS - 3u),  Ev <= (c|ab|(T+|ac|) + 3u)/(1 - cS - 3u)
+// and the true line/plane intersection P* = a + u* ab + v* ac lies within
+//   m = [cS(2T + |ab| + |ac|) + 3u(|ab| + |ac|)]/(1 - cS - 3u) + u max(|ab|,|ac|)
+// of the triangle. Hence an accepted ray passes within m of the triangle. det_lo is a lower bound of det^ over all
+// rays from the eye that pass within m of the triangle: det = d.N = ((a-eye).N + δ.N)/s with |δ| <= m and
+// s <= (Tmax + m)(1+2u), so det^ >= ((a-eye).N - m|N|)/((Tmax+m)(1+1e-6)) - 8uS. m is first computed with det_lo = tau
+// (valid for every accepted ray), then refined twice (each step is valid given the previous one). A triangle with
+// (a-eye).N + m|N| <= 0 has det^ <= 8uS < tau for every such ray and is never accepted (back-facing for this eye).
+// The float ray generation (camera_ray in render.cu = renderer.cpp:350-351 + SetRay) deviates from the ideal line
+// through the film point by an angle <= ang (ViewParams.ang, bounded on the host); this adds ang*(Tmax+m) to m.
+// The inflated triangle (vertex balls of radius m) is projected to film space with interval arithmetic in double and
+// rounded outward to float. Triangles that cannot be bounded (non-finite input, huge coordinates, a vertex ball that
+// reaches the eye plane, cS >= 0.5) get the infinite rectangle.
+#pragma once
+#include <cmath>
+#include <cstdint>
+
+#if defined(__CUDACC__)
+#define ATRAY_HD __host__ __device__ __forceinline__
+#else
+#define ATRAY_HD inline
+#endif
+
+namespace atray {
+
+struct ViewParams
+{
+    double eye[3];
+    double minv[3][3];   // (alpha, beta, gamma) = minv * (x - eye); film point of x = (alpha/gamma, beta/gamma)
+    double row[3];       // Euclidean norms of the rows of minv, rounded up
+    double ang;          // angular deviation bound of the float ray generation from the ideal line (radians)
+    double kx;           // h_fov * aspect: film_x(x) = (-1 + 2x/W) * kx   (renderer.cpp:329)
+    double px_slack_x, px_slack_y;  // pixel slack for the tile stamps (rounding of film_x/film_y, + half a pixel with AA)
+    int32_t W, H;
+    int32_t tiles_x, tiles_y;      // 8x4-pixel tiles
+    int32_t valid;                 // 0: camera not usable for culling (singular basis / non-finite) → unculled kernel
+    uint32_t frame_id;             // stamp value of this frame
+};
+
+struct FilmRect { float xlo, ylo, xhi, yhi; };
+
+ATRAY_HD FilmRect film_rect_empty()
+{
+    FilmRect r; r.xlo = INFINITY; r.ylo = INFINITY; r.xhi = -INFINITY; r.yhi = -INFINITY; return r;
+}
+ATRAY_HD FilmRect film_rect_all()
+{
+    FilmRect r; r.xlo = -INFINITY; r.ylo = -INFINITY; r.xhi = INFINITY; r.yhi = INFINITY; return r;
+}
+ATRAY_HD bool film_rect_is_empty(const FilmRect& r) { return r.xlo > r.xhi || r.ylo > r.yhi; }
+ATRAY_HD FilmRect film_rect_union(const FilmRect& a, const FilmRect& b)
+{
+    FilmRect r;
+    r.xlo = a.xlo < b.xlo ? a.xlo : b.xlo; r.ylo = a.ylo < b.ylo ? a.ylo : b.ylo;
+    r.xhi = a.xhi > b.xhi ? a.xhi : b.xhi; r.yhi = a.yhi > b.yhi ? a.yhi : b.yhi;
+    return r;
+}
+
+ATRAY_HD float round_down_f(double x)
+{
+#if defined(__CUDA_ARCH__)
+    return __double2float_rd(x);
+#else
+    float f = (float)x;
+    if ((double)f > x) f = nextafterf(f, -INFINITY);
+    return f;
+#endif
+}
+ATRAY_HD float round_up_f(double x)
+{
+#if defined(__CUDA_ARCH__)
+    return __double2float_ru(x);
+#else
+    float f = (float)x;
+    if ((double)f < x) f = nextafterf(f, INFINITY);
+    return f;
+#endif
+}
+
+// Film rectangle of one triangle record {a, ab, ac} (float values widened to double) for the view `vp`.
+ATRAY_HD FilmRect tri_film_rect(const ViewParams& vp, const float* a_f, const float* ab_f, const float* ac_f)
+{
+    const double U = 5.9604644775390625e-8;   // 2^-24
+    const double TAU = 9.9999e-5;             // just below (double)1e-4f = 9.99999974738e-05
+    const double BIG = 1073741824.0;          // 2^30: beyond this the products of the test may overflow → no bound
+    double a[3], ab[3], ac[3], w[3][3];
+    bool ok = true;
+    for (int i = 0; i < 3; ++i)
+    {
+        a[i] = (double)a_f[i]; ab[i] = (double)ab_f[i]; ac[i] = (double)ac_f[i];
+        ok = ok && fabs(a[i]) < BIG && fabs(ab[i]) < BIG && fabs(ac[i]) < BIG;   // false for NaN/Inf too
+    }
+    if (!ok) return film_rect_all();
+    for (int i = 0; i < 3; ++i)
+    {
+        w[0][i] = a[i] - vp.eye[i];            // vertex a, b' = a + ab, c' = a + ac relative to the eye
+        w[1][i] = w[0][i] + ab[i];
+        w[2][i] = w[0][i] + ac[i];
+    }
+    const double lab = sqrt(ab[0] * ab[0] + ab[1] * ab[1] + ab[2] * ab[2]);
+    const double lac = sqrt(ac[0] * ac[0] + ac[1] * ac[1] + ac[2] * ac[2]);
+    const double S = lab * lac * (1.0 + 1e-12);
+    const double L = lab > lac ? lab : lac;
+    // det = ab.(d x ac) = d.(ac x ab)  (model.h:81-82)  →  N = ac x ab
+    const double N[3] = {ac[1] * ab[2] - ac[2] * ab[1], ac[2] * ab[0] - ac[0] * ab[2], ac[0] * ab[1] - ac[1] * ab[0]};
+    const double lN = sqrt(N[0] * N[0] + N[1] * N[1] + N[2] * N[2]) * (1.0 + 1e-12);
+    const double g = w[0][0] * N[0] + w[0][1] * N[1] + w[0][2] * N[2];   // (a - eye).N
+    double T[3], Tmax = 0.0;
+    for (int k = 0; k < 3; ++k)
+    {
+        T[k] = sqrt(w[k][0] * w[k][0] + w[k][1] * w[k][1] + w[k][2] * w[k][2]) * (1.0 + 1e-12);
+        if (T[k] > Tmax) Tmax = T[k];
+    }
+    if (!(Tmax < 4.0 * BIG)) return film_rect_all();
+    const double err_det = 8.0 * U * S * (1.0 + 1e-6);
+    // margin of the float test as a function of the lower bound `den` of det^ among accepted rays
+    double m = 0.0, den = TAU;
+    for (int it = 0; it < 3; ++it)
+    {
+        const double c = 8.0 * U * (1.0 + 1e-6) / den;
+        const double cS = c * S;
+        if (!(cS < 0.5)) return film_rect_all();
+        m = (cS * (2.0 * T[0] + lab + lac) + 3.0 * U * (lab + lac)) / (1.0 - cS - 3.0 * U) + U * L + 1e-25;
+        m *= (1.0 + 1e-9);
+        if (it == 0)
+        {
+            // never accepted from this eye: det^ <= det + 8uS with det <= ((a-eye).N + m|N|)/s
+            if (err_det < TAU)
+            {
+                const double top = g + m * lN;
+                if (top <= 0.0) return film_rect_empty();
+                const double smin = (fabs(g) / lN - m) * (1.0 - 1e-6);   // distance eye → plane, minus the margin
+                if (smin > 0.0 && top / smin + err_det < TAU) return film_rect_empty();
+            }
+        }
+        const double lo = (g - m * lN) / ((Tmax + m) * (1.0 + 1e-6)) - err_det;
+        if (!(lo > den)) break;   // no improvement (also NaN-safe)
+        den = lo;
+    }
+    // total radius of the vertex balls: float-test margin + deviation of the float ray from the ideal line
+    const double rad = (m + vp.ang * (Tmax + m)) * (1.0 + 1e-9);
+    double xlo = INFINITY, xhi = -INFINITY, ylo = INFINITY, yhi = -INFINITY;
+    for (int k = 0; k < 3; ++k)
+    {
+        const double al = vp.minv[0][0] * w[k][0] + vp.minv[0][1] * w[k][1] + vp.minv[0][2] * w[k][2];
+        const double be = vp.minv[1][0] * w[k][0] + vp.minv[1][1] * w[k][1] + vp.minv[1][2] * w[k][2];
+        const double ga = vp.minv[2][0] * w[k][0] + vp.minv[2][1] * w[k][1] + vp.minv[2][2] * w[k][2];
+        // rounding of the three dot products above (double): 4 ulp of the largest term
+        const double e = 1e-15 * (fabs(w[k][0]) + fabs(w[k][1]) + fabs(w[k][2])) * (vp.row[0] + vp.row[1] + vp.row[2]);
+        const double ra = vp.row[0] * rad + e, rb = vp.row[1] * rad + e, rg = vp.row[2] * rad + e;
+        const double g0 = ga - rg, g1 = ga + rg;
+        if (!(g0 > 1e-9 * (1.0 + fabs(al) + fabs(be)))) return film_rect_all();   // ball reaches the eye plane
+        const double a0 = al - ra, a1 = al + ra, b0 = be - rb, b1 = be + rb;
+        const double x0 = a0 / (a0 < 0.0 ? g0 : g1), x1 = a1 / (a1 < 0.0 ? g1 : g0);
+        const double y0 = b0 / (b0 < 0.0 ? g0 : g1), y1 = b1 / (b1 < 0.0 ? g1 : g0);
+        if (x0 < xlo) xlo = x0;
+        if (x1 > xhi) xhi = x1;
+        if (y0 < ylo) ylo = y0;
+        if (y1 > yhi) yhi = y1;
+    }
+    if (!(xlo <= xhi && ylo <= yhi)) return film_rect_all();   // NaN somewhere
+    FilmRect r;
+    r.xlo = round_down_f(xlo - 1e-12 * (1.0 + fabs(xlo))); r.ylo = round_down_f(ylo - 1e-12 * (1.0 + fabs(ylo)));
+    r.xhi = round_up_f(xhi + 1e-12 * (1.0 + fabs(xhi))); r.yhi = round_up_f(yhi + 1e-12 * (1.0 + fabs(yhi)));
+    return r;
+}
+
+// Pixel-tile range (8x4 tiles) that can contain a ray whose film point lies in `r`:
+// film_x(x) = (-1 + 2(x/W))*h_fov*aspect, film_y(y) = -1 + 2(y/H) (renderer.cpp:317,329), inverted with slack.
+// Returns false when no tile is touched; `all` is set when the range cannot be bounded.
+ATRAY_HD bool film_rect_tiles(const ViewParams& vp, const FilmRect& r, int& tx0, int& tx1, int& ty0, int& ty1, bool& all)
+{
+    all = false;
+    if (film_rect_is_empty(r)) return false;
+    const double W = (double)vp.W, H = (double)vp.H;
+    double xa = ((double)r.xlo / vp.kx + 1.0) * 0.5 * W, xb = ((double)r.xhi / vp.kx + 1.0) * 0.5 * W;
+    if (xa > xb) { const double t = xa; xa = xb; xb = t; }
+    const double ya = ((double)r.ylo + 1.0) * 0.5 * H, yb = ((double)r.yhi + 1.0) * 0.5 * H;
+    if (!(xa == xa && xb == xb && ya == ya && yb == yb)) { all = true; return true; }   // NaN (kx = 0, inf/inf …)
+    xa -= vp.px_slack_x; xb += vp.px_slack_x;
+    const double yl = ya - vp.px_slack_y, yh = yb + vp.px_slack_y;
+    if (xb < 0.0 || xa > W - 1.0 || yh < 0.0 || yl > H - 1.0) return false;
+    const double cx0 = xa < 0.0 ? 0.0 : floor(xa), cx1 = xb > W - 1.0 ? W - 1.0 : ceil(xb);
+    const double cy0 = yl < 0.0 ? 0.0 : floor(yl), cy1 = yh > H - 1.0 ? H - 1.0 : ceil(yh);
+    tx0 = (int)cx0 >> 3; tx1 = (int)cx1 >> 3; ty0 = (int)cy0 >> 2; ty1 = (int)cy1 >> 2;
+    return true;
+}
+
+}  // namespace atray

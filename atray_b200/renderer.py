@@ -51,8 +51,10 @@ class Context:
 
     # -- frames -----------------------------------------------------------------------------------------------------
     @staticmethod
-    def opts(fp_mode=api.FP_STRICT, count_work=False, seed=api.DEFAULT_SEED, rank=0, world=1, band_rows=8):
-        return api.RenderOpts(fp_mode, 1 if count_work else 0, seed, api.Partition(rank, world, band_rows))
+    def opts(fp_mode=api.FP_STRICT, count_work=False, seed=api.DEFAULT_SEED, rank=0, world=1, band_rows=8, cull=True):
+        """cull=False selects the unculled kernel (every listed leaf scanned completely, as the reference does)."""
+        return api.RenderOpts(fp_mode, 1 if count_work else 0, seed, api.Partition(rank, world, band_rows),
+                              0 if cull else api.RENDER_NO_CULL)
 
     def render_begin(self, cam, opts, bgrx=None, t=None, prim=None):
         fr = api.Frame(_p(bgrx) if bgrx is not None else None, _p(t) if t is not None else None,

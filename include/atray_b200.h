@@ -34,6 +34,10 @@ extern "C" {
 #define ATRAY_FP_STRICT 0 /* reference arithmetic: no FMA contraction, IEEE division — bit-exact parity mode */
 #define ATRAY_FP_FAST 1   /* FMA contraction allowed; ids/t inside north_star tolerances, not bit-exact */
 
+/* AtrayRenderOpts.flags. Default (0): per-frame film-space culling — identical results, far less work.
+ * NO_CULL renders with the unculled kernel that scans every listed leaf completely, as the reference does. */
+#define ATRAY_RENDER_NO_CULL 1u
+
 typedef struct atray_model atray_model; /* host: ModelData + Model + KD_Tree (model.h:30-71, kd_tree.h:38-47) */
 typedef struct atray_ctx atray_ctx;     /* one GPU: uploaded scene, streams, frame buffers */
 
@@ -65,6 +69,7 @@ typedef struct AtrayRenderOpts
     int32_t count_work;     /* non-zero: accumulate AtrayCounters (slower instrumented kernel) */
     uint64_t jitter_seed;   /* anti_aliasing: pixel p uses RNG_Stream{splitmix64(seed ^ p), 2p+1} */
     AtrayPartition part;
+    uint32_t flags;         /* ATRAY_RENDER_* */
 } AtrayRenderOpts;
 
 /* Host frame the renderer fills (replaces Texture/BitmapBuffer, engine/tools/texture.h:10-23, plus the two
@@ -81,6 +86,9 @@ typedef struct AtrayFrame
 typedef struct AtrayCounters
 {
     uint64_t rays, box_tests, tri_tests, pass_det, pass_u, pass_v, leaves_listed, leaves_scanned, overflow_rays;
+    uint64_t rect_tests;  /* culled kernel: film-rectangle tests (leaf, packet, triangle level) */
+    uint64_t tiles_sky;   /* culled kernel: 8x4 tiles no triangle rectangle can touch (written as sky without tracing) */
+    uint64_t tiles_busy;  /* culled kernel: tiles that were traced */
 } AtrayCounters;
 
 const char* atray_last_error(void);
@@ -111,9 +119,18 @@ int atray_model_dump(const atray_model* m, float* vertices, float* normals, floa
  * primitive arrays), tri9 refs×9 (a,b,c), face_index refs */
 int atray_model_tree_dump(const atray_model* m, float* boxes, int32_t* children_start, uint32_t* prim_count,
                           uint32_t* prim_first, float* tri9, uint32_t* face_index);
-/* sizes and contents of the flattened GPU form: nodes = n_nodes×2 float4, tris = n_slots/32 blocks of
- * 3×32 float4 {a.xyz,face}{ab.xyz,0}{ac.xyz,0}. Either output pointer may be NULL to query sizes only. */
+/* sizes and contents of the flattened GPU form: nodes = n_nodes×2 float4, tris = n_slots/8 packets of
+ * 3×8 float4 {a.xyz,face}{ab.xyz,position in the reference's leaf order}{ac.xyz,0}, Morton-ordered inside each leaf.
+ * Either output pointer may be NULL to query sizes only. */
 int atray_model_flatten(const atray_model* m, uint32_t* n_nodes, uint32_t* n_slots, float* nodes, float* tris);
+
+/* Host evaluation of the per-frame film-space bounds the culled kernel uses (atray_b200/csrc/view_bounds.h), for
+ * verification without a GPU: rects = n_slots×4 {xlo,ylo,xhi,yhi} per triangle slot of the flat form, slot_leaf /
+ * slot_pos = owning leaf node and position in the reference's leaf order (0xffffffff for padding slots), tile_busy =
+ * one byte per 8x4-pixel tile (row-major, ceil(W/8) per row). Any output may be NULL. Returns ATRAY_ESTATE when the
+ * camera cannot be used for culling (the renderer then takes the unculled kernel). */
+int atray_debug_film_rects(const atray_model* m, const AtrayCamera* cam, float* rects, uint32_t* slot_leaf,
+                           uint32_t* slot_pos, uint8_t* tile_busy);
 
 /* set_camera(Camera&, eye, facing, RenderSettings&, h_fov) — engine/renderer/camera.h:23-45 */
 int atray_camera_set(AtrayCamera* cam, int32_t width, int32_t height, int32_t anti_aliasing, uint32_t samples_per_pixel,

@@ -696,6 +696,75 @@ void or_trace_primary(void* h, int W, int H, const float* eye, const float* faci
     or_trace_primary_ex(h, W, H, eye, facing, hfov, threads, face, t, uv, bgrx, 0);
 }
 
+/* Verification aid for the product's film-space culling (tests/test_view_bounds.py): every (pixel, leaf, position in
+ * the leaf) whose triangle test is ACCEPTED (model.h:75-103 returns t, and t > tolerance, t < MAX_FLOAT) in ANY leaf the
+ * traversal lists for the pixel's ray (kd_tree.cpp:363-435) — without the early exit of :457-460, so it is a superset
+ * of what the reference's scan can ever accept. */
+typedef struct { const or_scene* s; or_camera_t cm; long long cap; long long* count; unsigned* pixel; unsigned* node; unsigned* pos; } or_acc_arg;
+static void or_accepted_rows(void* a_, int y0, int y1, or_scratch* sc, or_counters* ct)
+{
+    (void)ct;
+    or_acc_arg* a = a_;
+    const or_camera_t* cm = &a->cm;
+    const or_node* N = a->s->nodes.p;
+    for (int y = y0; y < y1; y++)
+    {
+        float film_y = -1.0f + 2.0f * ((float)y / (float)cm->H);
+        for (int x = 0; x < cm->W; x++)
+        {
+            float film_x = (-1.0f + 2.0f * ((float)x / (float)cm->W)) * cm->h_fov * cm->aspect;
+            or_ray r;
+            r.o = cm->eye; r.d = or_pixel_dir(cm, film_x, film_y);
+            or_ray_prepare(&r);
+            if (!or_check_box(&r, &N[0].box)) continue;
+            int nleaf = 0;
+            if (N[0].children_start == 0) { sc->leaves[0].node = 0; nleaf = 1; }
+            else
+            {
+                int nstack = 1;
+                sc->hit_stack[0] = 0;
+                while (nstack > 0)
+                {
+                    uint32_t cur = sc->hit_stack[--nstack];
+                    uint32_t c0 = (uint32_t)N[cur].children_start;
+                    int nodes_hit = 0;
+                    for (int i = 0; i < 8 && nodes_hit <= 4; i++)
+                    {
+                        const or_node* ch = &N[c0 + i];
+                        if (ch->children_start) { if (or_check_box(&r, &ch->box)) { nodes_hit++; sc->hit_stack[nstack++] = c0 + i; } }
+                        else if (or_entry_dist(&r, &ch->box) > 0.0f) { nodes_hit++; sc->leaves[nleaf++].node = c0 + i; }
+                    }
+                }
+            }
+            for (int j = 0; j < nleaf; j++)
+            {
+                const or_node* n = &N[sc->leaves[j].node];
+                for (uint32_t i = 0; i < n->count; i++)
+                {
+                    float u = 0, v = 0;
+                    float d = or_tri_hit(&r, &n->prims[i].tri, &u, &v);
+                    if (d < OR_MAX_FLOAT && d > OR_TOL)
+                    {
+                        long long k = __sync_fetch_and_add(a->count, 1);
+                        if (k < a->cap) { a->pixel[k] = (unsigned)((size_t)y * cm->W + x); a->node[k] = sc->leaves[j].node; a->pos[k] = i; }
+                    }
+                }
+            }
+        }
+    }
+}
+long long or_accepted_hits(void* h, int W, int H, const float* eye, const float* facing, float hfov, int threads, long long cap,
+                           unsigned* pixel, unsigned* node, unsigned* pos)
+{
+    or_acc_arg a;
+    long long count = 0;
+    a.s = h; a.cap = cap; a.count = &count; a.pixel = pixel; a.node = node; a.pos = pos;
+    v3 e = { eye[0], eye[1], eye[2] }, f = { facing[0], facing[1], facing[2] };
+    or_set_camera(&a.cm, W, H, e, f, hfov);
+    or_parallel(a.s, H, threads, or_accepted_rows, &a);
+    return count;
+}
+
 typedef struct { const or_scene* s; const float* rays; long long n; unsigned* face; float* t; } or_rays_arg;
 static void or_rays_blocks(void* a_, int b0, int b1, or_scratch* sc, or_counters* ct)
 {

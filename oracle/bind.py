@@ -55,6 +55,10 @@ class Backend:
         else:
             self.trace_primary_ex = g("trace_primary_ex")
             self.trace_primary_ex.argtypes = self.trace_primary.argtypes + [C.c_void_p]
+            self.accepted_hits = g("accepted_hits")
+            self.accepted_hits.restype = C.c_longlong
+            self.accepted_hits.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_float, C.c_int,
+                                           C.c_longlong, C.c_void_p, C.c_void_p, C.c_void_p]
 
 
 _backends = {}
@@ -151,6 +155,15 @@ class Scene:
         self.b.trace_primary_ex(self.h, W, H, _p(e), _p(f), hfov, threads, None, None, None, None, _p(ct))
         names = ["box_tests", "tri_tests", "pass_det", "pass_u", "pass_v", "inner_pops", "leaves_listed", "leaves_scanned"]
         return dict(zip(names, [int(x) for x in ct]))
+
+    def accepted_hits(self, W, H, threads=1, eye=DEFAULT_EYE, facing=DEFAULT_FACING, hfov=DEFAULT_HFOV, cap=None):
+        """port() only: every (pixel, leaf node, position in leaf) the triangle test accepts in any listed leaf."""
+        cap = cap or 8 * W * H
+        px, node, pos = np.zeros(cap, np.uint32), np.zeros(cap, np.uint32), np.zeros(cap, np.uint32)
+        e, f = _f3(eye), _f3(facing)
+        n = self.b.accepted_hits(self.h, W, H, _p(e), _p(f), hfov, threads, cap, _p(px), _p(node), _p(pos))
+        assert n <= cap, "accepted_hits: capacity too small (%d > %d)" % (n, cap)
+        return px[:n], node[:n], pos[:n]
 
     def trace_rays(self, rays, threads=1):
         rays = np.ascontiguousarray(rays, dtype=np.float32).reshape(-1, 6)

@@ -96,13 +96,21 @@ def test_c4_standin_4k_full_size(A, port, standin):
     o = B.Scene(port, standin, rescale=0.0)
     W, H = 3840, 2160
     cam = A.set_camera(W, H)
-    out = sc.ctx.render(cam, sc.ctx.opts(count_work=True))
-    ctr = sc.ctx.counters()
     face, t, img = o.trace_primary(W, H, threads=NTHREADS)
+    # unculled kernel: same work as the reference, counter for counter
+    out = sc.ctx.render(cam, sc.ctx.opts(count_work=True, cull=False))
+    ctr = sc.ctx.counters()
     assert (out["prim"] == face).all() and same_bits(out["t"], t) and (out["bgrx"] == img).all()
     oc = o.primary_counters(W, H, threads=NTHREADS)
     assert ctr["rays"] == W * H and ctr["box_tests"] == oc["box_tests"] and ctr["tri_tests"] == oc["tri_tests"]
     assert ctr["leaves_listed"] == oc["leaves_listed"] and ctr["leaves_scanned"] == oc["leaves_scanned"]
+    # default (film-space culling): same bits, a fraction of the work
+    out = sc.ctx.render(cam, sc.ctx.opts(count_work=True))
+    cc = sc.ctx.counters()
+    assert (out["prim"] == face).all() and same_bits(out["t"], t) and (out["bgrx"] == img).all()
+    assert cc["rays"] == W * H and cc["tiles_sky"] + cc["tiles_busy"] == (W // 8) * (H // 4)
+    assert cc["tiles_sky"] > 0.8 * (W // 8) * (H // 4) and cc["tri_tests"] < 0.02 * ctr["tri_tests"]
+    assert cc["pass_v"] >= int((face != B.MISS).sum())
     fast = sc.ctx.render(cam, sc.ctx.opts(fp_mode=A.FP_FAST))
     mism = int((fast["prim"] != face).sum())
     assert mism <= 1e-5 * W * H, mism
@@ -115,6 +123,45 @@ def test_c4_standin_4k_full_size(A, port, standin):
     # idempotence: same frame twice → same bits; partition union == whole frame
     again = sc.ctx.render(cam)
     assert (again["prim"] == out["prim"]).all() and same_bits(again["t"], out["t"])
+    o.close()
+
+
+CAMS = [dict(), dict(eye=(3.0, -4.0, 9.0), facing=(-0.2, -0.4, -1.0), h_fov=0.7),
+        dict(eye=(0.0, -15.0, -38.0), facing=(0.3, 0.1, -1.0), h_fov=1.3),        # eye inside the model's box
+        dict(eye=(40.0, 5.0, -38.0), facing=(-1.0, -0.4, 0.02), h_fov=0.5),
+        dict(eye=(0.1, 2.0, 0.0), facing=(0.1, 0.5, 1.0)),                         # model behind the camera
+        dict(eye=(1000.0, 500.0, 2000.0), facing=(-1000.0, -515.0, -2038.0), h_fov=0.02),
+        dict(eye=(2.0, -14.0, -36.5), facing=(-1.0, -0.3, -0.7), h_fov=2.5)]       # wide angle from between the coils
+
+
+@pytest.mark.parametrize("name,method,cap", [("knot_mid", 1, 300), ("knot_mid", 0, 32), ("Monkey", 1, 300), ("Deer", 1, 64), ("Cube", 1, 300)])
+def test_culled_equals_unculled_and_oracle(name, method, cap, A, port, meshes):
+    """Film-space culling (default) never changes a bit: against the unculled kernel and the oracle, for cameras outside,
+    inside and facing away from the model, plain and jittered."""
+    from oracle import bind as B
+    if name not in meshes:
+        pytest.skip("mesh not staged")
+    path, rescale = meshes[name]
+    sc = gpu_scene(A, path, rescale, method, cap)
+    o = B.Scene(port, path, rescale=rescale, method=method, cap=cap)
+    for i, kw in enumerate(CAMS):
+        W, H = (801, 453) if i % 2 else (640, 360)
+        cam = A.set_camera(W, H, **kw)
+        a = sc.ctx.render(cam)
+        b = sc.ctx.render(cam, sc.ctx.opts(cull=False))
+        assert (a["prim"] == b["prim"]).all() and same_bits(a["t"], b["t"]) and (a["bgrx"] == b["bgrx"]).all()
+        face, t, img = o.trace_primary(W, H, threads=NTHREADS, eye=kw.get("eye", A.api.DEFAULT_EYE),
+                                       facing=kw.get("facing", A.api.DEFAULT_FACING), hfov=kw.get("h_fov", 1.0))
+        assert (a["prim"] == face).all() and same_bits(a["t"], t) and (a["bgrx"] == img).all()
+        camj = A.set_camera(W // 2, H // 2, anti_aliasing=1, samples_per_pixel=4, **kw)
+        aj = sc.ctx.render(camj, sc.ctx.opts(seed=SEED + i))
+        bj = sc.ctx.render(camj, sc.ctx.opts(seed=SEED + i, cull=False))
+        assert (aj["bgrx"] == bj["bgrx"]).all() and (aj["prim"] == bj["prim"]).all() and same_bits(aj["t"], bj["t"])
+    # camera the culling cannot use (facing ∥ up → non-finite basis): falls back to the unculled kernel, same as the oracle
+    cam = A.set_camera(64, 36, facing=(0.0, 1.0, 0.0))
+    a = sc.ctx.render(cam)
+    face, t, img = o.trace_primary(64, 36, threads=2, facing=(0.0, 1.0, 0.0))
+    assert (a["prim"] == face).all() and (a["bgrx"] == img).all()
     o.close()
 
 

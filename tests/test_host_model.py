@@ -63,18 +63,22 @@ def test_flat_layout_is_one_to_one(port, meshes):
     assert (w0[inner] == tree["children_start"][inner]).all() and (w0[inner] > 0).all()
     assert (w0[~inner] < 0).all() and (w1[~inner] == tree["prim_count"][~inner].astype(np.int32)).all()
     first = ~w0[~inner]
-    assert (first % 32 == 0).all()
+    assert (first % 8 == 0).all()
+    # packets of 8: plane 0 = {a, face}, plane 1 = {ab, position in the reference's leaf order}, plane 2 = {ac, 0}
     A_, AB, AC = tris[:, 0].reshape(-1, 4), tris[:, 1].reshape(-1, 4), tris[:, 2].reshape(-1, 4)
     for leaf_i, f0 in zip(np.nonzero(~inner)[0], first):
         cnt, p0 = int(tree["prim_count"][leaf_i]), int(tree["prim_first"][leaf_i])
         tri = tree["tri"][p0:p0 + cnt]
+        pos = AB[f0:f0 + cnt, 3].view(np.uint32)
+        assert sorted(pos.tolist()) == list(range(cnt))          # a permutation of the leaf (Morton order inside the leaf)
+        tri = tri[pos]
         assert same_bits(A_[f0:f0 + cnt, :3], tri[:, 0:3])
         assert same_bits(AB[f0:f0 + cnt, :3], tri[:, 3:6] - tri[:, 0:3])
         assert same_bits(AC[f0:f0 + cnt, :3], tri[:, 6:9] - tri[:, 0:3])
-        assert (A_[f0:f0 + cnt, 3].view(np.uint32) == tree["face"][p0:p0 + cnt]).all()
-        pad = (cnt + 31) // 32 * 32
+        assert (A_[f0:f0 + cnt, 3].view(np.uint32) == tree["face"][p0:p0 + cnt][pos]).all()
+        pad = (cnt + 7) // 8 * 8
         assert (A_[f0 + cnt:f0 + pad, 3].view(np.uint32) == 0xFFFFFFFF).all()
-        assert (AB[f0 + cnt:f0 + pad] == 0).all() and (AC[f0 + cnt:f0 + pad] == 0).all()
+        assert (AB[f0 + cnt:f0 + pad, :3] == 0).all() and (AC[f0 + cnt:f0 + pad] == 0).all()
 
 
 def test_camera_matches_reference_kat(built):

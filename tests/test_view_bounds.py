@@ -1,0 +1,100 @@
+"""CPU: soundness of the per-frame film-space culling (atray_b200/csrc/view_bounds.h) against the oracle.
+
+For every pixel of a frame the oracle lists every (leaf, triangle) its float triangle test ACCEPTS in any listed leaf
+(a superset of what the reference's leaf scan can accept). The product's host evaluation of the film rectangles
+(atray_debug_film_rects, the same code the CUDA pre-pass runs) must contain that pixel's film point in the triangle's
+rectangle, and the pixel's 8x4 tile must be stamped busy. The test also checks that the bounds actually cull."""
+import os
+
+import numpy as np
+import pytest
+
+NT = min(16, os.cpu_count() or 1)
+
+CAMERAS = [
+    dict(),                                                                   # app.cpp:88
+    dict(eye=(3.0, -4.0, 9.0), facing=(-0.2, -0.4, -1.0), h_fov=0.7),
+    dict(eye=(0.0, -15.0, -38.0), facing=(0.3, 0.1, -1.0), h_fov=1.3),        # eye at the model centre
+    dict(eye=(40.0, 5.0, -38.0), facing=(-1.0, -0.4, 0.02), h_fov=0.5),       # from the side
+    dict(eye=(0.1, 2.0, 0.0), facing=(0.1, 0.5, 1.0), h_fov=1.0),             # model behind the camera
+    dict(eye=(1000.0, 500.0, 2000.0), facing=(-1000.0, -515.0, -2038.0), h_fov=0.02),  # far away, narrow
+]
+
+
+def film_coords(cam, W, H):
+    """renderer.cpp:317,329 in float32, as the kernel and the oracle evaluate them."""
+    f = np.float32
+    y = np.arange(H, dtype=np.float32)
+    x = np.arange(W, dtype=np.float32)
+    fy = f(-1.0) + f(2.0) * (y / f(H))
+    fx = ((f(-1.0) + f(2.0) * (x / f(W))) * f(cam.h_fov)) * f(cam.aspect_ratio)
+    return fx.astype(np.float32), fy.astype(np.float32)
+
+
+def check(A, B, port, path, rescale, method, cap, W, H, camkw):
+    m = A.load_model_data(path, 2)
+    A.place_default(m, rescale)
+    A.build_KD_tree(m, method, cap)
+    o = B.Scene(port, path, rescale=rescale, method=method, cap=cap)
+    cam = A.set_camera(W, H, **camkw)
+    rects, leaf, pos, busy = m.film_rects(cam)
+    okw = dict(eye=camkw.get("eye", A.api.DEFAULT_EYE), facing=camkw.get("facing", A.api.DEFAULT_FACING),
+               hfov=camkw.get("h_fov", 1.0))
+    px, node, ppos = o.accepted_hits(W, H, threads=NT, **okw)
+    o.close()
+    # slot of (leaf node, position in the reference's leaf order)
+    real = pos != 0xFFFFFFFF
+    key = leaf[real].astype(np.uint64) << np.uint64(32) | pos[real].astype(np.uint64)
+    slots = np.nonzero(real)[0]
+    order = np.argsort(key)
+    key, slots = key[order], slots[order]
+    q = node.astype(np.uint64) << np.uint64(32) | ppos.astype(np.uint64)
+    at = np.searchsorted(key, q)
+    assert (key[at] == q).all(), "flat form lost a leaf record"
+    s = slots[at]
+    fx, fy = film_coords(cam, W, H)
+    x, y = px % W, px // W
+    r = rects[s]
+    inside = (fx[x] >= r[:, 0]) & (fx[x] <= r[:, 2]) & (fy[y] >= r[:, 1]) & (fy[y] <= r[:, 3])
+    assert inside.all(), "%d accepted hits outside their film rectangle" % int((~inside).sum())
+    assert busy[y // 4, x // 8].all(), "accepted hit in a tile stamped as sky"
+    return px.size, rects, busy
+
+
+@pytest.mark.parametrize("camkw", CAMERAS)
+@pytest.mark.parametrize("name,method,cap", [("knot_mid", 1, 300), ("knot_small", 0, 64), ("Monkey", 1, 300), ("Deer", 1, 32),
+                                             ("Cube", 1, 300)])
+def test_accepted_hits_lie_in_their_film_rectangles(name, method, cap, camkw, built, port, meshes):
+    import atray_b200 as A
+    from oracle import bind as B
+    if name not in meshes:
+        pytest.skip("mesh not staged")
+    path, rescale = meshes[name]
+    check(A, B, port, path, rescale, method, cap, 480, 270, camkw)
+
+
+def test_bounds_are_tight_on_the_default_view(built, port, meshes):
+    """The rectangles must cull: on the default view most tiles are sky and the average rectangle is small."""
+    import atray_b200 as A
+    from oracle import bind as B
+    path, rescale = meshes["knot_mid"]
+    n, rects, busy = check(A, B, port, path, rescale, 1, 300, 960, 540, {})
+    assert n > 10000
+    assert busy.mean() < 0.5
+    fin = np.isfinite(rects).all(axis=1)
+    assert fin.sum() > 0.3 * rects.shape[0]            # front-facing triangles have finite rectangles
+    empty = rects[:, 0] > rects[:, 2]
+    assert empty.sum() > 0.3 * rects.shape[0]          # back-facing ones are removed for this eye
+    w = (rects[fin, 2] - rects[fin, 0]) / (2 * 1.7778 / 960)
+    assert np.median(w) < 40                           # pixels
+
+
+def test_degenerate_camera_disables_culling(built, meshes):
+    import atray_b200 as A
+    path, rescale = meshes["knot_small"]
+    m = A.load_model_data(path, 1)
+    A.place_default(m, rescale)
+    A.build_KD_tree(m)
+    cam = A.set_camera(64, 36, facing=(0.0, 1.0, 0.0))     # facing ∥ up: camera_x = normalize(0) is not finite
+    with pytest.raises(A.AtrayError):
+        m.film_rects(cam)
