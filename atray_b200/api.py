@@ -11,7 +11,7 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libatray_b200.so")
+LIB_PATH = os.environ.get("ATRAY_B200_LIB") or os.path.join(HERE, "libatray_b200.so")  # override: A/B builds of the same ABI
 
 MISS = 0xFFFFFFFF
 MAX_FLOAT = np.float32(3.402823466e+38)

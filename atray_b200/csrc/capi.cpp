@@ -24,6 +24,8 @@ struct atray_ctx
     LaunchCfg cfg{};
     float4* d_nodes = nullptr;
     float4* d_tris = nullptr;
+    uint32_t* d_inner_order = nullptr;
+    uint32_t* d_level_start = nullptr;
     DevScene scene{};
     bool has_scene = false;
     DevScratch scratch{};
@@ -244,8 +246,10 @@ int atray_ctx_create(int device, atray_ctx** out)
 static void free_scene(atray_ctx* c)
 {
     cudaFree(c->d_nodes); cudaFree(c->d_tris); cudaFree(c->scratch.leaves); cudaFree(c->scratch.stack);
-    cudaFree(c->view.tri_rect); cudaFree(c->view.pkt_rect); cudaFree(c->view.leaf_rect);
-    c->view.tri_rect = c->view.pkt_rect = c->view.leaf_rect = nullptr;
+    cudaFree(c->view.tri_rect); cudaFree(c->view.pkt_rect); cudaFree(c->view.node_rect);
+    cudaFree(c->d_inner_order); cudaFree(c->d_level_start);
+    c->view.tri_rect = c->view.pkt_rect = c->view.node_rect = nullptr;
+    c->d_inner_order = c->d_level_start = nullptr;
     c->d_nodes = c->d_tris = nullptr;
     c->scratch = DevScratch{};
     c->has_scene = false;
@@ -258,7 +262,7 @@ void atray_ctx_destroy(atray_ctx* c)
     if (c->stream) cudaStreamSynchronize(c->stream);
     free_scene(c);
     cudaFree(c->d_tile_counter); cudaFree(c->d_counters);
-    cudaFree(c->view.stamps); cudaFree(c->view.all_flag);
+    cudaFree(c->view.stamps); cudaFree(c->view.all_flag); cudaFree(c->view.busy_list); cudaFree(c->view.busy_count);
     cudaFree(c->d_bgrx); cudaFree(c->d_t); cudaFree(c->d_prim);
     cudaFreeHost(c->h_bgrx); cudaFreeHost(c->h_t); cudaFreeHost(c->h_prim);
     cudaFree(c->d_rays); cudaFree(c->d_rprim); cudaFree(c->d_rt);
@@ -290,7 +294,15 @@ int atray_scene_upload(atray_ctx* c, const atray_model* m, const AtrayMaterial* 
     CU(cudaMalloc(&c->scratch.stack, size_t(warps) * c->scratch.stack_cap * sizeof(uint32_t)));
     CU(cudaMalloc(&c->view.tri_rect, size_t(f.n_slots ? f.n_slots : 1) * sizeof(float4)));
     CU(cudaMalloc(&c->view.pkt_rect, size_t(f.n_slots / 8 + 1) * sizeof(float4)));
-    CU(cudaMalloc(&c->view.leaf_rect, size_t(f.n_nodes) * sizeof(float4)));
+    CU(cudaMalloc(&c->view.node_rect, size_t(f.n_nodes) * sizeof(float4)));
+    CU(cudaMalloc(&c->d_inner_order, (f.inner_order.size() + 1) * sizeof(uint32_t)));
+    CU(cudaMalloc(&c->d_level_start, f.level_start.size() * sizeof(uint32_t)));
+    if (!f.inner_order.empty())
+        CU(cudaMemcpy(c->d_inner_order, f.inner_order.data(), f.inner_order.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(c->d_level_start, f.level_start.data(), f.level_start.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+    c->scene.inner_order = c->d_inner_order;
+    c->scene.level_start = c->d_level_start;
+    c->scene.n_levels = uint32_t(f.level_start.size() - 1);
     c->scene.nodes = c->d_nodes;
     c->scene.tris = c->d_tris;
     c->scene.n_nodes = f.n_nodes;
@@ -405,12 +417,18 @@ static int enqueue_render(atray_ctx* c, const AtrayCamera* cam, const AtrayRende
         {
             if (tiles > c->stamp_cap)
             {
-                cudaFree(c->view.stamps);
-                c->view.stamps = nullptr; c->stamp_cap = 0;
+                cudaFree(c->view.stamps); cudaFree(c->view.busy_list);
+                c->view.stamps = nullptr; c->view.busy_list = nullptr; c->stamp_cap = 0;
                 CU(cudaMalloc(&c->view.stamps, tiles * sizeof(uint32_t)));
+                CU(cudaMalloc(&c->view.busy_list, tiles * sizeof(uint32_t)));
                 c->stamp_cap = tiles;
             }
             if (!c->view.all_flag) CU(cudaMalloc(&c->view.all_flag, sizeof(uint32_t)));
+            if (!c->view.busy_count)
+            {
+                CU(cudaMalloc(&c->view.busy_count, 4 * sizeof(uint32_t)));
+                CU(cudaMemsetAsync(c->view.busy_count, 0, 4 * sizeof(uint32_t), c->stream));
+            }
             CU(cudaMemsetAsync(c->view.stamps, 0, c->stamp_cap * sizeof(uint32_t), c->stream));
             CU(cudaMemsetAsync(c->view.all_flag, 0, sizeof(uint32_t), c->stream));
             c->frame_seq = 0;
@@ -423,9 +441,9 @@ static int enqueue_render(atray_ctx* c, const AtrayCamera* cam, const AtrayRende
     if (cull)
     {
         // the film rectangles depend on the camera: recomputed every frame, inside the timed region
-        CU(launch_view_bounds(c->scene, vp, c->view, c->stream));
-        CU(launch_render_culled(c->scene, to_dev(cam), p, out, c->scratch, c->view, c->d_tile_counter, ctr,
-                                o->fp_mode == ATRAY_FP_FAST, o->jitter_seed, c->cfg, c->stream));
+        CU(launch_view_bounds(c->scene, vp, c->view, to_dev(cam), p, c->stream));
+        CU(launch_render_culled(c->scene, to_dev(cam), p, out, c->scratch, c->view, ctr, o->fp_mode == ATRAY_FP_FAST,
+                                o->jitter_seed, c->cfg, c->stream));
     }
     else
         CU(launch_render(c->scene, to_dev(cam), p, out, c->scratch, c->d_tile_counter, ctr, o->fp_mode == ATRAY_FP_FAST,

@@ -11,6 +11,9 @@ struct DevScene
 {
     const float4* nodes;   // 2 float4 per node
     const float4* tris;    // packets of 8 slots: 8×{a,face} | 8×{ab,pos} | 8×{ac,0}
+    const uint32_t* inner_order;   // inner nodes, deepest level first (FlatScene::inner_order)
+    const uint32_t* level_start;   // n_levels + 1 offsets into inner_order
+    uint32_t n_levels;
     uint32_t n_nodes;
     uint32_t n_slots;
     uint32_t root_is_leaf;
@@ -42,9 +45,11 @@ struct DevView
 {
     float4* tri_rect;      // n_slots   {xlo, ylo, xhi, yhi}
     float4* pkt_rect;      // n_slots/8 union over the packet's slots
-    float4* leaf_rect;     // n_nodes   union over the leaf's packets (inner nodes: unused)
+    float4* node_rect;     // n_nodes   leaf: union over its packets; inner node: union over its children
     uint32_t* stamps;      // one per 8x4-pixel tile: == frame_id ⇔ some triangle rectangle may touch the tile
     uint32_t* all_flag;    // == frame_id ⇔ an unbounded rectangle exists: every tile is busy
+    uint32_t* busy_list;   // tiles of this rank's bands that must be traced (local tile numbering of the render kernel)
+    uint32_t* busy_count;  // [0] = entries in busy_list, [1] = finished-block ticket of k_view_finish
     uint32_t frame_id;
     int32_t tiles_x;
 };
@@ -64,11 +69,13 @@ cudaError_t launch_render(const DevScene& sc, const DevCamera& cam, const DevPar
                           const DevScratch& scratch, unsigned int* tile_counter, DevCounters* counters, int fp_fast,
                           unsigned long long jitter_seed, LaunchCfg cfg, cudaStream_t stream);
 // culled frame = k_view_bounds (per-frame film rectangles + tile stamps) followed by k_render_culled
-cudaError_t launch_view_bounds(const DevScene& sc, const ViewParams& vp, const DevView& view, cudaStream_t stream);
+// k_view_bounds (per-slot rectangles, packet unions, tile stamps) + k_view_finish (leaf and inner-node unions,
+// compact list of this rank's busy tiles)
+cudaError_t launch_view_bounds(const DevScene& sc, const ViewParams& vp, const DevView& view, const DevCamera& cam,
+                               const DevPartition& part, cudaStream_t stream);
 cudaError_t launch_render_culled(const DevScene& sc, const DevCamera& cam, const DevPartition& part, const DevOut& out,
-                                 const DevScratch& scratch, const DevView& view, unsigned int* tile_counter,
-                                 DevCounters* counters, int fp_fast, unsigned long long jitter_seed, LaunchCfg cfg,
-                                 cudaStream_t stream);
+                                 const DevScratch& scratch, const DevView& view, DevCounters* counters, int fp_fast,
+                                 unsigned long long jitter_seed, LaunchCfg cfg, cudaStream_t stream);
 cudaError_t launch_trace(const DevScene& sc, const float* rays, unsigned long long n, uint32_t* prim, float* t,
                          const DevScratch& scratch, unsigned int* tile_counter, DevCounters* counters, int fp_fast,
                          LaunchCfg cfg, cudaStream_t stream);

@@ -456,6 +456,22 @@ void flatten(const HostModel& m, FlatScene& out)
         }
         cursor += padded;
     }
+    // depth of every node (children always follow their parent in the array), inner nodes bucketed deepest first
+    std::vector<uint32_t> depth(out.n_nodes, 0u);
+    uint32_t max_depth = 0;
+    for (uint32_t i = 0; i < out.n_nodes; ++i)
+        if (m.tree[i].children_start != 0)
+        {
+            for (uint32_t c = 0; c < 8; ++c) depth[uint32_t(m.tree[i].children_start) + c] = depth[i] + 1;
+            if (depth[i] > max_depth) max_depth = depth[i];
+        }
+    out.level_start.assign(1, 0u);
+    for (int d = int(max_depth); d >= 0; --d)
+    {
+        for (uint32_t i = 0; i < out.n_nodes; ++i)
+            if (m.tree[i].children_start != 0 && depth[i] == uint32_t(d)) out.inner_order.push_back(i);
+        out.level_start.push_back(uint32_t(out.inner_order.size()));
+    }
 }
 
 // camera basis (camera.h:23-45); normalize = v * (1/sqrt(|v|²)) with |v|² = (x² + y²) + z² (PL_math.h:377-392)

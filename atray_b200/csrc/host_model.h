@@ -40,6 +40,9 @@ struct FlatScene
     // | 8×{ac.xyz, 0}; within a leaf the slots are in Morton order of the triangle centroids
     std::vector<float> tris;         // n_slots/8 * 24 * 4
     std::vector<uint32_t> packet_leaf;  // n_slots/8: node index of the leaf that owns the packet
+    // inner nodes grouped by depth, deepest level first (bottom-up union of the per-frame film rectangles):
+    // level l = inner_order[level_start[l] .. level_start[l+1])
+    std::vector<uint32_t> inner_order, level_start;
     uint32_t n_nodes = 0, n_slots = 0, n_leaves = 0, max_leaf_prims = 0;
 };
 

@@ -95,13 +95,9 @@ __device__ __forceinline__ float box_entry(const RayL& r, float ix, float iy, fl
 }
 
 // ---- phase 1: collect the sorted leaf list of one ray (kd_tree.cpp:363-435). Returns false on capacity overflow.
-// CULL: a leaf whose film rectangle (k_view_bounds) does not contain the ray's film point cannot yield an accepted
-// triangle (view_bounds.h); it still counts as an accepted child for the ≤5 cut but is left out of the list. The stable
-// insertion keeps the relative order of the remaining leaves, so the scan order of the reference is preserved.
-template <bool COUNT, bool CULL>
+template <bool COUNT>
 __device__ bool collect_leaves(const float4* __restrict__ nodes, const RayL& r, float ix, float iy, float iz, uint32_t* stack,
-                               int stack_cap, uint2* leaves, int leaf_cap, int& nleaf, WorkCount& wc,
-                               const float4* __restrict__ leaf_rect = nullptr, float fx = 0.f, float fy = 0.f)
+                               int stack_cap, uint2* leaves, int leaf_cap, int& nleaf, WorkCount& wc)
 {
     nleaf = 0;
     int sp = 1;
@@ -133,12 +129,6 @@ __device__ bool collect_leaves(const float4* __restrict__ nodes, const RayL& r, 
                 if (dis > 0.0f)
                 {
                     ++accepted;
-                    if (CULL)
-                    {
-                        const float4 R = __ldg(&leaf_rect[ch]);
-                        if (COUNT) wc.rect++;
-                        if (fx < R.x || fx > R.z || fy < R.y || fy > R.w) continue;
-                    }
                     if (nleaf >= leaf_cap) return false;
                     int k = nleaf;  // stable insertion from the back: ties and later arrivals go after existing entries
                     while (k > 0 && dis < __uint_as_float(leaves[k - 1].y))
@@ -233,10 +223,9 @@ __device__ __forceinline__ void scan_ray_leaves(const DevScene& sc, int lane, in
 // ---- one warp traces up to 32 rays (one per lane). Result: t (MAX_FLOAT on miss) and face (MISS) per lane.
 template <bool STRICT, bool COUNT>
 __device__ __forceinline__ void trace_warp(const DevScene& sc, const DevScratch& scratch, int warp_slot, int lane, bool active,
-                                           const RayL& ray, float& t_out, uint32_t& face_out, WorkCount& wc)
+                                           const RayL& ray, uint2* leaves, uint32_t* stack, float& t_out, uint32_t& face_out,
+                                           WorkCount& wc)
 {
-    uint2 leaves[kLeafCap];
-    uint32_t stack[kStackCap];
     t_out = kMaxFloat;
     face_out = 0xffffffffu;
     int nleaf = 0;
@@ -256,7 +245,7 @@ __device__ __forceinline__ void trace_warp(const DevScene& sc, const DevScratch&
                 nleaf = 1;
             }
             else
-                overflow = !collect_leaves<COUNT, false>(sc.nodes, ray, ix, iy, iz, stack, kStackCap, leaves, kLeafCap, nleaf, wc);
+                overflow = !collect_leaves<COUNT>(sc.nodes, ray, ix, iy, iz, stack, kStackCap, leaves, kLeafCap, nleaf, wc);
             if (overflow) nleaf = 0;
         }
     }
@@ -282,7 +271,7 @@ __device__ __forceinline__ void trace_warp(const DevScene& sc, const DevScratch&
             WorkCount dummy;
             dummy.clear();
             // the aborted first attempt already counted a partial walk; the redo is not counted again
-            collect_leaves<false, false>(sc.nodes, ray, ix, iy, iz, gs, (int)scratch.stack_cap, gl, (int)scratch.leaf_cap, gn, dummy);
+            collect_leaves<false>(sc.nodes, ray, ix, iy, iz, gs, (int)scratch.stack_cap, gl, (int)scratch.leaf_cap, gn, dummy);
         }
         __syncwarp();
         scan_ray_leaves<STRICT, COUNT>(sc, lane, src, ray, gl, gn, t_out, face_out, wc);
@@ -370,6 +359,8 @@ __global__ void __launch_bounds__(kBlock) k_render(DevScene sc, DevCamera cm, De
     const unsigned int n_tiles = (unsigned int)my_bands * tiles_per_band;
     WorkCount wc;
     wc.clear();
+    uint2 leaves[kLeafCap];    // per-lane sorted leaf list (local memory)
+    uint32_t stack[kStackCap]; // per-lane inner-node stack of the unculled traversal
     unsigned int rays_done = 0;
     for (;;)
     {
@@ -390,7 +381,7 @@ __global__ void __launch_bounds__(kBlock) k_render(DevScene sc, DevCamera cm, De
         if (!cm.aa)
         {
             const RayL ray = camera_ray(cm, film_x, film_y);  // renderer.cpp:350-351
-            trace_warp<STRICT, COUNT>(sc, scratch, warp_slot, lane, active, ray, t, face, wc);
+            trace_warp<STRICT, COUNT>(sc, scratch, warp_slot, lane, active, ray, leaves, stack, t, face, wc);
             const bool hit = face != 0xffffffffu;
             const float er = hit ? sc.mdl[0] : sc.sky[0], eg = hit ? sc.mdl[1] : sc.sky[1], eb = hit ? sc.mdl[2] : sc.sky[2];
             for (uint32_t s = 0; s < cm.spp; ++s) { cr = addr(cr, er); cg = addr(cg, eg); cb = addr(cb, eb); }  // :353-356
@@ -407,7 +398,7 @@ __global__ void __launch_bounds__(kBlock) k_render(DevScene sc, DevCamera cm, De
                 const float x_off = addr(mulr(pcg_bi(rng), cm.hpw), film_x);
                 const float y_off = addr(mulr(pcg_bi(rng), cm.hph), film_y);
                 const RayL ray = camera_ray(cm, x_off, y_off);
-                trace_warp<STRICT, COUNT>(sc, scratch, warp_slot, lane, active, ray, t, face, wc);
+                trace_warp<STRICT, COUNT>(sc, scratch, warp_slot, lane, active, ray, leaves, stack, t, face, wc);
                 const bool hit = face != 0xffffffffu;
                 if (hit) { pcg_bi(rng); pcg_bi(rng); pcg_bi(rng); }  // cast_ray's random bounce draws (renderer.cpp:246)
                 cr = addr(cr, hit ? sc.mdl[0] : sc.sky[0]);
@@ -428,7 +419,7 @@ __global__ void __launch_bounds__(kBlock) k_render(DevScene sc, DevCamera cm, De
     if (COUNT) flush_counters(counters, wc, rays_done);
 }
 
-// ---- per-frame film-space bounds (view_bounds.h): one warp per leaf -------------------------------------------------
+// ---- per-frame film-space bounds (view_bounds.h) ----------------------------------------------------------------------
 __device__ __forceinline__ float4 rect_union_xor(float4 r, int off)
 {
     r.x = fminf(r.x, __shfl_xor_sync(FULL_MASK, r.x, off)); r.y = fminf(r.y, __shfl_xor_sync(FULL_MASK, r.y, off));
@@ -436,67 +427,140 @@ __device__ __forceinline__ float4 rect_union_xor(float4 r, int off)
     return r;
 }
 
+// One thread per triangle slot: film rectangle, union per packet (8 lanes), tile stamps.
 __global__ void __launch_bounds__(kBlock) k_view_bounds(DevScene sc, ViewParams vp, DevView view)
 {
     const int lane = threadIdx.x & 31;
-    const uint32_t node = (blockIdx.x * kBlock + threadIdx.x) >> 5;
-    if (node >= sc.n_nodes) return;
-    const float4 n0 = __ldg(&sc.nodes[2 * node]);
-    if (__float_as_int(n0.w) > 0) return;  // inner node
-    const uint32_t first = ~(uint32_t)__float_as_int(n0.w);
-    const uint32_t cnt = (uint32_t)__float_as_int(__ldg(&sc.nodes[2 * node + 1]).w);
-    const uint32_t padded = (cnt + 7u) & ~7u;
+    const uint32_t slot = blockIdx.x * kBlock + threadIdx.x;
+    const uint32_t slots_up = (sc.n_slots + 31u) & ~31u;
+    if (slot == 0) { view.busy_count[0] = 0u; view.busy_count[2] = 0u; }  // busy-list length and its consumer cursor
+    if (slot >= slots_up) return;  // whole warps only beyond this point
+    const bool in_range = slot < sc.n_slots;
     const int n_tiles = vp.tiles_x * vp.tiles_y;
-    float4 acc = make_float4(INFINITY, INFINITY, -INFINITY, -INFINITY);
-    for (uint32_t base = 0; base < padded; base += 32)
+    float4 r = make_float4(INFINITY, INFINITY, -INFINITY, -INFINITY);
+    int tx0 = 0, tx1 = -1, ty0 = 0, ty1 = -1;
+    bool big = false;
+    if (in_range)
     {
-        const uint32_t slot = first + base + lane;
-        const bool in_leaf = base + lane < padded;
-        float4 r = make_float4(INFINITY, INFINITY, -INFINITY, -INFINITY);
-        int tx0 = 0, tx1 = -1, ty0 = 0, ty1 = -1;
-        bool big = false;
-        if (in_leaf)
+        const float4* rec = sc.tris + (size_t)(slot >> 3) * 24 + (slot & 7);
+        const float4 A = __ldg(rec), AB = __ldg(rec + 8), AC = __ldg(rec + 16);
+        if (__float_as_uint(A.w) != 0xffffffffu)
         {
-            const float4* rec = sc.tris + (size_t)(slot >> 3) * 24 + (slot & 7);
-            const float4 A = __ldg(rec), AB = __ldg(rec + 8), AC = __ldg(rec + 16);
-            if (__float_as_uint(A.w) != 0xffffffffu)
+            const FilmRect fr = tri_film_rect(vp, &A.x, &AB.x, &AC.x);
+            r = make_float4(fr.xlo, fr.ylo, fr.xhi, fr.yhi);
+            bool all = false;
+            if (film_rect_tiles(vp, fr, tx0, tx1, ty0, ty1, all))
             {
-                const FilmRect fr = tri_film_rect(vp, &A.x, &AB.x, &AC.x);
-                r = make_float4(fr.xlo, fr.ylo, fr.xhi, fr.yhi);
-                bool all = false;
-                if (film_rect_tiles(vp, fr, tx0, tx1, ty0, ty1, all))
+                const int nt = (tx1 - tx0 + 1) * (ty1 - ty0 + 1);
+                if (all || 2 * nt >= n_tiles) { *view.all_flag = vp.frame_id; tx1 = tx0 - 1; }
+                else if (nt > 48) big = true;
+                else
                 {
-                    const int nt = (tx1 - tx0 + 1) * (ty1 - ty0 + 1);
-                    if (all || 2 * nt >= n_tiles) { *view.all_flag = vp.frame_id; tx1 = tx0 - 1; }
-                    else if (nt > 48) big = true;
-                    else
-                    {
-                        for (int ty = ty0; ty <= ty1; ++ty)
-                            for (int tx = tx0; tx <= tx1; ++tx) view.stamps[ty * vp.tiles_x + tx] = vp.frame_id;
-                    }
+                    for (int ty = ty0; ty <= ty1; ++ty)
+                        for (int tx = tx0; tx <= tx1; ++tx) view.stamps[ty * vp.tiles_x + tx] = vp.frame_id;
                 }
             }
-            view.tri_rect[slot] = r;
         }
-        // large rectangles: the whole warp stamps the tiles of one triangle at a time
-        unsigned bm = __ballot_sync(FULL_MASK, big);
-        while (bm)
-        {
-            const int src = __ffs(bm) - 1;
-            bm &= bm - 1;
-            const int ax0 = __shfl_sync(FULL_MASK, tx0, src), ax1 = __shfl_sync(FULL_MASK, tx1, src);
-            const int ay0 = __shfl_sync(FULL_MASK, ty0, src), ay1 = __shfl_sync(FULL_MASK, ty1, src);
-            const int w = ax1 - ax0 + 1, n = w * (ay1 - ay0 + 1);
-            for (int i = lane; i < n; i += 32) view.stamps[(ay0 + i / w) * vp.tiles_x + ax0 + i % w] = vp.frame_id;
-        }
-        float4 p = r;
-        p = rect_union_xor(p, 4); p = rect_union_xor(p, 2); p = rect_union_xor(p, 1);
-        if (in_leaf && (lane & 7) == 0) view.pkt_rect[slot >> 3] = p;
-        acc.x = fminf(acc.x, r.x); acc.y = fminf(acc.y, r.y); acc.z = fmaxf(acc.z, r.z); acc.w = fmaxf(acc.w, r.w);
+        view.tri_rect[slot] = r;
     }
+    // large rectangles: the whole warp stamps the tiles of one triangle at a time
+    unsigned bm = __ballot_sync(FULL_MASK, big);
+    while (bm)
+    {
+        const int src = __ffs(bm) - 1;
+        bm &= bm - 1;
+        const int ax0 = __shfl_sync(FULL_MASK, tx0, src), ax1 = __shfl_sync(FULL_MASK, tx1, src);
+        const int ay0 = __shfl_sync(FULL_MASK, ty0, src), ay1 = __shfl_sync(FULL_MASK, ty1, src);
+        const int w = ax1 - ax0 + 1, n = w * (ay1 - ay0 + 1);
+        for (int i = lane; i < n; i += 32) view.stamps[(ay0 + i / w) * vp.tiles_x + ax0 + i % w] = vp.frame_id;
+    }
+    float4 p = r;
+    p = rect_union_xor(p, 4); p = rect_union_xor(p, 2); p = rect_union_xor(p, 1);
+    if (in_range && (lane & 7) == 0) view.pkt_rect[slot >> 3] = p;
+}
+
+// Second pass: (1) one warp per leaf unions its packet rectangles, (2) the stamps of this rank's tiles are compacted
+// into the busy list, (3) the last block to finish unions the children of every inner node, deepest level first.
+__global__ void __launch_bounds__(kBlock) k_view_finish(DevScene sc, DevView view, DevCamera cm, DevPartition part)
+{
+    const int lane = threadIdx.x & 31;
+    const uint32_t warp = (blockIdx.x * kBlock + threadIdx.x) >> 5;
+    const uint32_t n_warps = (gridDim.x * kBlock) >> 5;
+    for (uint32_t node = warp; node < sc.n_nodes; node += n_warps)
+    {
+        const float4 n0 = __ldg(&sc.nodes[2 * node]);
+        if (__float_as_int(n0.w) > 0) continue;
+        const uint32_t first = ~(uint32_t)__float_as_int(n0.w);
+        const uint32_t cnt = (uint32_t)__float_as_int(__ldg(&sc.nodes[2 * node + 1]).w);
+        const uint32_t npk = (cnt + 7u) >> 3, pk0 = first >> 3;
+        float4 acc = make_float4(INFINITY, INFINITY, -INFINITY, -INFINITY);
+        for (uint32_t k = lane; k < npk; k += 32)
+        {
+            const float4 q = view.pkt_rect[pk0 + k];
+            acc.x = fminf(acc.x, q.x); acc.y = fminf(acc.y, q.y); acc.z = fmaxf(acc.z, q.z); acc.w = fmaxf(acc.w, q.w);
+        }
 #pragma unroll
-    for (int off = 16; off > 0; off >>= 1) acc = rect_union_xor(acc, off);
-    if (lane == 0) view.leaf_rect[node] = acc;
+        for (int off = 16; off > 0; off >>= 1) acc = rect_union_xor(acc, off);
+        if (lane == 0) view.node_rect[node] = acc;
+    }
+    // busy tiles of this rank, in the render kernel's local numbering (band-major, then tile row, then tile column)
+    {
+        const int tiles_x = (cm.W + 7) >> 3;
+        const int rows_per_band = part.band_rows >> 2;
+        const int n_bands = (cm.H + part.band_rows - 1) / part.band_rows;
+        const int my_bands = part.rank < n_bands ? (n_bands - part.rank + part.world - 1) / part.world : 0;
+        const unsigned int tiles_per_band = (unsigned int)(tiles_x * rows_per_band);
+        const unsigned int n_tiles = (unsigned int)my_bands * tiles_per_band;
+        const bool all_busy = *((volatile uint32_t*)view.all_flag) == view.frame_id;
+        for (unsigned int base = warp * 32u; base < n_tiles; base += n_warps * 32u)
+        {
+            const unsigned int tile = base + lane;
+            bool busy = false;
+            if (tile < n_tiles)
+            {
+                const unsigned int lb = tile / tiles_per_band, rem = tile - lb * tiles_per_band;
+                const int trow = (int)(rem / (unsigned int)tiles_x), tcol = (int)(rem - (unsigned int)trow * (unsigned int)tiles_x);
+                const int y0 = ((int)lb * part.world + part.rank) * part.band_rows + trow * 4;
+                busy = y0 < cm.H && (all_busy || view.stamps[(y0 >> 2) * view.tiles_x + tcol] == view.frame_id);
+            }
+            const unsigned m = __ballot_sync(FULL_MASK, busy);
+            if (m)
+            {
+                unsigned int at = 0;
+                if (lane == 0) at = atomicAdd(&view.busy_count[0], (unsigned int)__popc(m));
+                at = __shfl_sync(FULL_MASK, at, 0);
+                if (busy) view.busy_list[at + __popc(m & ((1u << lane) - 1u))] = tile;
+            }
+        }
+    }
+    // last block: inner-node rectangles, bottom-up
+    __shared__ bool is_last;
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) is_last = atomicAdd(&view.busy_count[1], 1u) == gridDim.x - 1;
+    __syncthreads();
+    if (!is_last) return;
+    __threadfence();
+    for (uint32_t l = 0; l < sc.n_levels; ++l)
+    {
+        const uint32_t b = __ldg(&sc.level_start[l]), e = __ldg(&sc.level_start[l + 1]);
+        for (uint32_t k = b + threadIdx.x; k < e; k += kBlock)
+        {
+            const uint32_t node = __ldg(&sc.inner_order[k]);
+            const uint32_t c0 = (uint32_t)__float_as_int(__ldg(&sc.nodes[2 * node]).w);
+            float4 acc = make_float4(INFINITY, INFINITY, -INFINITY, -INFINITY);
+#pragma unroll
+            for (int c = 0; c < 8; ++c)
+            {
+                const float4 q = __ldcg(&view.node_rect[c0 + c]);
+                acc.x = fminf(acc.x, q.x); acc.y = fminf(acc.y, q.y); acc.z = fmaxf(acc.z, q.z); acc.w = fmaxf(acc.w, q.w);
+            }
+            view.node_rect[node] = acc;
+        }
+        __threadfence();
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) view.busy_count[1] = 0u;  // ticket for the next frame
 }
 
 // ---- culled phase 2: the warp walks the k-th listed leaf of each of its rays; rays that share the leaf form a group.
@@ -509,16 +573,86 @@ __device__ __forceinline__ bool rect_overlap(const float4 R, const float4 T)
     return !(R.x > T.z || R.z < T.x || R.y > T.w || R.w < T.y);
 }
 
+// Per-warp shared scratch of the culled phase 2: queue of (ray lane, slot) pairs whose film point lies inside the
+// triangle's rectangle, and the per-ray running minimum of (t bits, position in the reference's leaf order).
+static constexpr int kPairCap = 128;
+struct WarpPairs
+{
+    unsigned long long key[32];
+    uint32_t face[32];
+    uint32_t pair_slot[kPairCap];
+    unsigned char pair_lane[kPairCap];
+};
+
+// The reference triangle test (model.h:75-103) for one ray and one record; true iff the caller would accept the
+// distance (t > tolerance && t < MAX_FLOAT, renderer.cpp:52 / kd_tree.cpp:446).
 template <bool STRICT, bool COUNT>
-__device__ __forceinline__ void scan_tile_leaves(const DevScene& sc, const DevView& vw, int lane, const RayL& ray, float fx, float fy,
-                                                 const float4 trect, const uint2* list, int nleaf, float& t_out,
-                                                 uint32_t& face_out, WorkCount& wc)
+__device__ __forceinline__ bool tri_accept(const float4* __restrict__ rec, float ox, float oy, float oz, float dx, float dy, float dz,
+                                           float& t_out, uint32_t& pos_out, uint32_t& face_out, WorkCount& wc)
 {
     typedef Fp<STRICT> F;
+    const float4 AB = __ldg(rec + 8), AC = __ldg(rec + 16);
+    const float px = F::crs(dy, AC.z, dz, AC.y), py = F::crs(dz, AC.x, dx, AC.z), pz = F::crs(dx, AC.y, dy, AC.x);
+    const float det = F::dot(AB.x, AB.y, AB.z, px, py, pz);
+    if (COUNT) wc.tri++;
+    if (det < kTol) return false;
+    if (COUNT) wc.pdet++;
+    const float4 A = __ldg(rec);
+    const float det_inv = __frcp_rn(det);
+    const float tx = F::sub(ox, A.x), ty = F::sub(oy, A.y), tz = F::sub(oz, A.z);
+    const float u = F::mul(F::dot(tx, ty, tz, px, py, pz), det_inv);
+    if (u < 0.0f || u > 1.0f) return false;
+    if (COUNT) wc.pu++;
+    const float qx = F::crs(ty, AB.z, tz, AB.y), qy = F::crs(tz, AB.x, tx, AB.z), qz = F::crs(tx, AB.y, ty, AB.x);
+    const float v = F::mul(F::dot(dx, dy, dz, qx, qy, qz), det_inv);
+    if (v < 0.0f || F::add(u, v) > 1.0f) return false;
+    if (COUNT) wc.pv++;
+    const float t = F::mul(F::dot(qx, qy, qz, AC.x, AC.y, AC.z), det_inv);
+    t_out = t;
+    pos_out = __float_as_uint(AB.w);
+    face_out = __float_as_uint(A.w);
+    return t > kTol && t < kMaxFloat;
+}
+
+// Runs the triangle test on every queued pair, 32 pairs per step: each lane takes one pair, fetches the ray from its
+// owner lane by shuffle and gathers the record. Accepted hits lower key[ray] = (t bits, position) — t > 0, so the float
+// bits order like the values, and the lexicographic minimum equals the reference's sequential strict-< scan.
+template <bool STRICT, bool COUNT>
+__device__ __forceinline__ void drain_pairs(const DevScene& sc, WarpPairs& wp, int lane, int& qn, const RayL& ray, WorkCount& wc)
+{
+    __syncwarp();
+    for (int base = 0; base < qn; base += 32)
+    {
+        const bool have = base + lane < qn;
+        const int src = have ? (int)wp.pair_lane[base + lane] : lane;
+        const uint32_t s = have ? wp.pair_slot[base + lane] : 0u;
+        const float ox = __shfl_sync(FULL_MASK, ray.ox, src), oy = __shfl_sync(FULL_MASK, ray.oy, src), oz = __shfl_sync(FULL_MASK, ray.oz, src);
+        const float dx = __shfl_sync(FULL_MASK, ray.dx, src), dy = __shfl_sync(FULL_MASK, ray.dy, src), dz = __shfl_sync(FULL_MASK, ray.dz, src);
+        float t = 0.f;
+        uint32_t pos = 0u, face = 0u;
+        bool acc = false;
+        if (have) acc = tri_accept<STRICT, COUNT>(sc.tris + (size_t)(s >> 3) * 24 + (s & 7), ox, oy, oz, dx, dy, dz, t, pos, face, wc);
+        const unsigned long long mk = ((unsigned long long)__float_as_uint(t) << 32) | (unsigned long long)pos;
+        if (acc) atomicMin(&wp.key[src], mk);
+        __syncwarp();
+        if (acc && wp.key[src] == mk) wp.face[src] = face;  // (t, pos) is unique per ray and leaf: exactly one writer
+        __syncwarp();
+    }
+    qn = 0;
+}
+
+template <bool STRICT, bool COUNT>
+__device__ __forceinline__ void scan_tile_leaves(const DevScene& sc, const DevView& vw, WarpPairs& wp, int lane, const RayL& ray,
+                                                 float fx, float fy, const float4 trect, const uint2* list, int nleaf,
+                                                 float& t_out, uint32_t& face_out, WorkCount& wc)
+{
     bool done = nleaf <= 0;
     int k = 0;
+    int qn = 0;
     float bt = kMaxFloat;
-    uint32_t bpos = 0xffffffffu, bface = 0xffffffffu;
+    uint32_t bface = 0xffffffffu;
+    wp.key[lane] = ~0ull;
+    __syncwarp();
     while (__any_sync(FULL_MASK, !done))
     {
         const uint32_t myleaf = done ? 0xffffffffu : list[k].x;
@@ -560,10 +694,12 @@ __device__ __forceinline__ void scan_tile_leaves(const DevScene& sc, const DevVi
                     }
                     bool cov = false;
                     uint32_t myslot = 0;
+                    float4 myrect = make_float4(0.f, 0.f, 0.f, 0.f);
                     if (sel >= 0)
                     {
                         myslot = ((pk0 + pb + (uint32_t)sel) << 3) + (lane & 7);
-                        cov = rect_overlap(__ldg(&vw.tri_rect[myslot]), trect);
+                        myrect = __ldg(&vw.tri_rect[myslot]);
+                        cov = rect_overlap(myrect, trect);
                         if (COUNT) wc.rect++;
                     }
                     unsigned cmask = __ballot_sync(FULL_MASK, cov);
@@ -572,45 +708,33 @@ __device__ __forceinline__ void scan_tile_leaves(const DevScene& sc, const DevVi
                         const int b = __ffs(cmask) - 1;
                         cmask &= cmask - 1;
                         const uint32_t s = __shfl_sync(FULL_MASK, myslot, b);
-                        const float4 R = __ldg(&vw.tri_rect[s]);
-                        bool alive = ingrp && !(fx < R.x || fx > R.z || fy < R.y || fy > R.w);
-                        if (!__any_sync(FULL_MASK, alive)) continue;
-                        const float4* rec = sc.tris + (size_t)(s >> 3) * 24 + (s & 7);
-                        const float4 A = __ldg(rec), AB = __ldg(rec + 8), AC = __ldg(rec + 16);
-                        // get_triangle_ray_intersection_culled, model.h:75-103, this lane's own ray
-                        const float px = F::crs(ray.dy, AC.z, ray.dz, AC.y), py = F::crs(ray.dz, AC.x, ray.dx, AC.z),
-                                    pz = F::crs(ray.dx, AC.y, ray.dy, AC.x);
-                        const float det = F::dot(AB.x, AB.y, AB.z, px, py, pz);
-                        if (COUNT) wc.tri += alive ? 1u : 0u;
-                        alive = alive && !(det < kTol);
-                        if (COUNT) wc.pdet += alive ? 1u : 0u;
-                        if (!__any_sync(FULL_MASK, alive)) continue;
-                        const float det_inv = __frcp_rn(det);
-                        const float tx = F::sub(ray.ox, A.x), ty = F::sub(ray.oy, A.y), tz = F::sub(ray.oz, A.z);
-                        const float u = F::mul(F::dot(tx, ty, tz, px, py, pz), det_inv);
-                        alive = alive && !(u < 0.0f || u > 1.0f);
-                        if (COUNT) wc.pu += alive ? 1u : 0u;
-                        if (!__any_sync(FULL_MASK, alive)) continue;
-                        const float qx = F::crs(ty, AB.z, tz, AB.y), qy = F::crs(tz, AB.x, tx, AB.z), qz = F::crs(tx, AB.y, ty, AB.x);
-                        const float v = F::mul(F::dot(ray.dx, ray.dy, ray.dz, qx, qy, qz), det_inv);
-                        alive = alive && !(v < 0.0f || F::add(u, v) > 1.0f);
-                        if (COUNT) wc.pv += alive ? 1u : 0u;
-                        if (!__any_sync(FULL_MASK, alive)) continue;
-                        const float t = F::mul(F::dot(qx, qy, qz, AC.x, AC.y, AC.z), det_inv);
-                        const uint32_t pos = __float_as_uint(AB.w);
-                        if (alive && t > kTol && (t < bt || (t == bt && pos < bpos)))
+                        const float rx0 = __shfl_sync(FULL_MASK, myrect.x, b), ry0 = __shfl_sync(FULL_MASK, myrect.y, b);
+                        const float rx1 = __shfl_sync(FULL_MASK, myrect.z, b), ry1 = __shfl_sync(FULL_MASK, myrect.w, b);
+                        const bool in = ingrp && !(fx < rx0 || fx > rx1 || fy < ry0 || fy > ry1);
+                        const unsigned m = __ballot_sync(FULL_MASK, in);
+                        if (!m) continue;
+                        if (in)
                         {
-                            bt = t;
-                            bpos = pos;
-                            bface = __float_as_uint(A.w);
+                            const int at = qn + __popc(m & ((1u << lane) - 1u));
+                            wp.pair_slot[at] = s;
+                            wp.pair_lane[at] = (unsigned char)lane;
                         }
+                        qn += __popc(m);
+                        if (qn > kPairCap - 32) drain_pairs<STRICT, COUNT>(sc, wp, lane, qn, ray, wc);
                     }
                 }
             }
         }
+        drain_pairs<STRICT, COUNT>(sc, wp, lane, qn, ray, wc);
         if (!done)
         {
-            if (bt < kMaxFloat) done = true;  // first leaf with a hit ends the ray (kd_tree.cpp:457-460)
+            const unsigned long long kk = wp.key[lane];
+            if (kk != ~0ull)  // first leaf with a hit ends the ray (kd_tree.cpp:457-460)
+            {
+                bt = __uint_as_float((uint32_t)(kk >> 32));
+                bface = wp.face[lane];
+                done = true;
+            }
             else if (++k >= nleaf) done = true;
         }
     }
@@ -618,58 +742,190 @@ __device__ __forceinline__ void scan_tile_leaves(const DevScene& sc, const DevVi
     face_out = bface;
 }
 
-// ---- one warp, one 8x4 tile, culled: phase 1 per lane with the leaf-rectangle filter, phase 2 per tile --------------
-template <bool STRICT, bool COUNT>
-__device__ __forceinline__ void trace_tile_culled(const DevScene& sc, const DevScratch& scratch, const DevView& vw, int warp_slot,
-                                                  int lane, bool active, const RayL& ray, float fx, float fy, float& t_out,
-                                                  uint32_t& face_out, WorkCount& wc)
+// ---- culled phase 1: ONE traversal per tile. The warp walks the union of the subtrees its 32 rays need, in the
+// reference's own order (children pushed in index order, last pushed popped first, kd_tree.cpp:368-435), each stack
+// entry carrying the mask of lanes that reach the node. Per child:
+//  * pruning: a lane whose film point lies outside node_rect[child] cannot be accepted by any triangle below it
+//    (view_bounds.h) and drops out of that subtree;
+//  * inner children are not box-tested: for a ray with finite origin, direction and reciprocals every slab value is a
+//    monotone function of the plane it is computed from, the child boxes nest (kd_tree.cpp:120-148), hence a leaf that
+//    passes its own slab test passes the test of every ancestor — the leaf test alone decides. Tiles with a ray that
+//    is not finite in that sense take the unculled path;
+//  * leaves: the reference's entry distance (aabb.h:29-63) > 0, then the stable insertion of kd_tree.cpp:389-409. The
+//    union walk visits a lane's leaves in the same relative order as the lane's own walk would (a depth-first order
+//    restricted to an ancestor-closed subset), so ties keep the reference's order;
+//  * the "at most 5 accepted children" cut (kd_tree.cpp:374): child i >= 5 is processed by a lane iff at most 4 of the
+//    children 0..i-1 pass the reference's acceptance test for that lane; those are evaluated lazily, most distant
+//    octant first, until i-4 rejections are known. A lane that is cut leaves the node.
+// Returns false when the warp stack or a lane's list overflows (the tile then takes the unculled path).
+struct TileStack { uint32_t node[kStackCap]; uint32_t mask[kStackCap]; };
+
+template <bool COUNT>
+__device__ __forceinline__ bool collect_tile_leaves(const float4* __restrict__ nodes, const float4* __restrict__ node_rect,
+                                                    TileStack& ts, int lane, unsigned root_mask, const RayL& r, float ix, float iy,
+                                                    float iz, float fx, float fy, const float4 trect, uint2* leaves, int& nleaf,
+                                                    WorkCount& wc)
 {
-    uint2 leaves[kLeafCap];
-    uint32_t stack[kStackCap];
-    int nleaf = 0;
+    nleaf = 0;
     bool overflow = false;
-    const float ix = __frcp_rn(ray.dx), iy = __frcp_rn(ray.dy), iz = __frcp_rn(ray.dz);
-    if (active)
+    int sp = 0;
+    if (root_mask)
     {
-        const float4 lo = __ldg(&sc.nodes[0]);
-        const float4 hi = __ldg(&sc.nodes[1]);
-        if (COUNT) wc.box++;
-        if (box_check(ray, ix, iy, iz, lo, hi))
+        if (lane == 0) { ts.node[0] = 0u; ts.mask[0] = root_mask; }
+        sp = 1;
+    }
+    __syncwarp();
+    while (sp > 0)
+    {
+        --sp;
+        const uint32_t cur = ts.node[sp];
+        const bool here = (ts.mask[sp] >> lane) & 1u;
+        __syncwarp();
+        const uint32_t c0 = (uint32_t)__float_as_int(__ldg(&nodes[2 * cur]).w);
+        // children whose rectangle overlaps the tile's film rectangle (lanes 0..7, one child each)
+        const float4 myR = __ldg(&node_rect[c0 + (lane & 7)]);
+        if (COUNT && lane < 8) wc.rect++;
+        unsigned cm = __ballot_sync(FULL_MASK, rect_overlap(myR, trect)) & 0xffu;
+        unsigned ev = 0u, am = 0u;  // this lane: children of `cur` whose acceptance is known / that were accepted
+        bool alive = here;          // false once the lane is cut at this node
+        while (cm)
         {
-            if (sc.root_is_leaf)
+            const int i = __ffs(cm) - 1;
+            cm &= cm - 1;
+            const float rx0 = __shfl_sync(FULL_MASK, myR.x, i), ry0 = __shfl_sync(FULL_MASK, myR.y, i);
+            const float rx1 = __shfl_sync(FULL_MASK, myR.z, i), ry1 = __shfl_sync(FULL_MASK, myR.w, i);
+            bool want = alive && !(fx < rx0 || fx > rx1 || fy < ry0 || fy > ry1);
+            if (!__any_sync(FULL_MASK, want)) continue;
+            if (i >= 5)
             {
-                const float4 R = __ldg(&vw.leaf_rect[0]);
-                if (!(fx < R.x || fx > R.z || fy < R.y || fy > R.w)) { leaves[0] = make_uint2(0u, 0u); nleaf = 1; }
+                const unsigned below = (1u << i) - 1u;
+                int nrej = __popc(ev & ~am & below);
+                const unsigned ord = i == 5 ? 0x41302u : (i == 6 ? 0x425301u : 0x6534210u);
+                for (int q = 0; q < i; ++q)
+                {
+                    const int j = (int)((ord >> (4 * q)) & 7u);
+                    const bool need = want && nrej < i - 4 && !((ev >> j) & 1u);
+                    if (!__any_sync(FULL_MASK, need)) continue;
+                    const float4 lo = __ldg(&nodes[2 * (c0 + j)]);
+                    const float4 hi = __ldg(&nodes[2 * (c0 + j) + 1]);
+                    const bool a = __float_as_int(lo.w) > 0 ? box_check(r, ix, iy, iz, lo, hi) : box_entry(r, ix, iy, iz, lo, hi) > 0.0f;
+                    if (need)
+                    {
+                        if (COUNT) wc.box++;
+                        ev |= 1u << j;
+                        if (a) am |= 1u << j; else ++nrej;
+                    }
+                }
+                if (want && nrej < i - 4) { alive = false; want = false; }  // five earlier children accepted: cut
+                if (!__any_sync(FULL_MASK, want)) continue;
+            }
+            const uint32_t ch = c0 + (uint32_t)i;
+            const float4 lo = __ldg(&nodes[2 * ch]);
+            if (__float_as_int(lo.w) > 0)  // inner child: descend with the lanes that want it
+            {
+                const unsigned pm = __ballot_sync(FULL_MASK, want);
+                if (sp >= kStackCap) { overflow = true; break; }
+                if (lane == 0) { ts.node[sp] = ch; ts.mask[sp] = pm; }
+                ++sp;
             }
             else
-                overflow = !collect_leaves<COUNT, true>(sc.nodes, ray, ix, iy, iz, stack, kStackCap, leaves, kLeafCap, nleaf, wc,
-                                                        vw.leaf_rect, fx, fy);
+            {
+                const float4 hi = __ldg(&nodes[2 * ch + 1]);
+                const float dis = box_entry(r, ix, iy, iz, lo, hi);
+                if (want)
+                {
+                    if (COUNT) wc.box++;
+                    ev |= 1u << i;
+                    if (dis > 0.0f)
+                    {
+                        am |= 1u << i;
+                        if (nleaf >= kLeafCap) overflow = true;
+                        else
+                        {
+                            int k = nleaf;
+                            while (k > 0 && dis < __uint_as_float(leaves[k - 1].y))
+                            {
+                                leaves[k] = leaves[k - 1];
+                                --k;
+                            }
+                            leaves[k] = make_uint2(ch, __float_as_uint(dis));
+                            ++nleaf;
+                            if (COUNT) wc.listed++;
+                        }
+                    }
+                }
+            }
         }
+        __syncwarp();
+        if (__any_sync(FULL_MASK, overflow)) return false;
     }
-    if (__any_sync(FULL_MASK, overflow))
-    {
-        // a list or stack outgrew the per-lane arrays: this tile takes the unculled path with its global spill area
-        trace_warp<STRICT, COUNT>(sc, scratch, warp_slot, lane, active, ray, t_out, face_out, wc);
-        return;
-    }
+    return true;
+}
+
+// ---- one warp, one 8x4 tile, culled ------------------------------------------------------------------------------------
+struct WarpScratch { WarpPairs pairs; TileStack ts; };
+
+template <bool STRICT, bool COUNT>
+__device__ __forceinline__ void trace_tile_culled(const DevScene& sc, const DevScratch& scratch, const DevView& vw, WarpScratch& ws,
+                                                  int warp_slot, int lane, bool active, const RayL& ray, float fx, float fy,
+                                                  uint2* leaves, uint32_t* stack, float& t_out, uint32_t& face_out, WorkCount& wc)
+{
+    const float ix = __frcp_rn(ray.dx), iy = __frcp_rn(ray.dy), iz = __frcp_rn(ray.dz);
+    // finite origin, direction and reciprocals (no 0*inf, inf-inf or NaN in any slab product): see collect_tile_leaves
+    const float chk = (ray.ox - ray.ox) + (ray.oy - ray.oy) + (ray.oz - ray.oz) + (ix - ix) + (iy - iy) + (iz - iz) +
+                      (ray.dx - ray.dx) + (ray.dy - ray.dy) + (ray.dz - ray.dz);
+    const bool regular = chk == 0.0f;  // any NaN/Inf operand makes the sum NaN
+    bool fallback = __any_sync(FULL_MASK, active && !regular);
+    int nleaf = 0;
     t_out = kMaxFloat;
     face_out = 0xffffffffu;
-    if (!__any_sync(FULL_MASK, nleaf > 0)) return;
-    // film rectangle of the rays of this tile that have work
-    float4 tr = nleaf > 0 ? make_float4(fx, fy, fx, fy) : make_float4(INFINITY, INFINITY, -INFINITY, -INFINITY);
+    float4 tr = make_float4(INFINITY, INFINITY, -INFINITY, -INFINITY);
+    if (!fallback)
+    {
+        bool in_root = false;
+        if (active)
+        {
+            const float4 lo = __ldg(&sc.nodes[0]);
+            const float4 hi = __ldg(&sc.nodes[1]);
+            if (COUNT) wc.box++;
+            const float4 R = __ldg(&vw.node_rect[0]);
+            in_root = box_check(ray, ix, iy, iz, lo, hi) && !(fx < R.x || fx > R.z || fy < R.y || fy > R.w);  // kd_tree.cpp:339
+        }
+        const unsigned root_mask = __ballot_sync(FULL_MASK, in_root);
+        if (!root_mask) return;
+        // film rectangle of the rays of this tile that can have work
+        if (in_root) tr = make_float4(fx, fy, fx, fy);
 #pragma unroll
-    for (int off = 16; off > 0; off >>= 1) tr = rect_union_xor(tr, off);
-    scan_tile_leaves<STRICT, COUNT>(sc, vw, lane, ray, fx, fy, tr, leaves, nleaf, t_out, face_out, wc);
+        for (int off = 16; off > 0; off >>= 1) tr = rect_union_xor(tr, off);
+        if (sc.root_is_leaf)  // kd_tree.cpp:344-361: the root's primitives are scanned without an entry-distance filter
+        {
+            if (in_root) { leaves[0] = make_uint2(0u, 0u); nleaf = 1; }
+        }
+        else
+            fallback = !collect_tile_leaves<COUNT>(sc.nodes, vw.node_rect, ws.ts, lane, root_mask, ray, ix, iy, iz, fx, fy, tr, leaves,
+                                                   nleaf, wc);
+    }
+    if (fallback)
+    {
+        // irregular ray, or a list / the warp stack outgrew its array: this tile takes the unculled path (global spill area)
+        trace_warp<STRICT, COUNT>(sc, scratch, warp_slot, lane, active, ray, leaves, stack, t_out, face_out, wc);
+        return;
+    }
+    if (!__any_sync(FULL_MASK, nleaf > 0)) return;
+    scan_tile_leaves<STRICT, COUNT>(sc, vw, ws.pairs, lane, ray, fx, fy, tr, leaves, nleaf, t_out, face_out, wc);
 }
 
 // ---- K1c: fused primary-ray render with film-space culling ----------------------------------------------------------
+// Phase A: every warp takes a static, interleaved share of this rank's tiles and writes the sky result into those no
+// triangle rectangle can touch (≈90 % of a typical frame: a pure store stream). Phase B: the busy tiles listed by
+// k_view_finish are pulled one at a time from an atomic cursor (dynamic balance where the work is).
 template <bool STRICT, bool COUNT>
 __global__ void __launch_bounds__(kBlock) k_render_culled(DevScene sc, DevCamera cm, DevPartition part, DevOut out, DevScratch scratch,
-                                                          DevView vw, unsigned int* tile_counter, DevCounters* counters,
-                                                          unsigned long long jitter_seed)
+                                                          DevView vw, DevCounters* counters, unsigned long long jitter_seed)
 {
     const int lane = threadIdx.x & 31;
     const int warp_slot = (blockIdx.x * kBlock + threadIdx.x) >> 5;
+    const unsigned int n_warps = (gridDim.x * kBlock) >> 5;
     const int tiles_x = (cm.W + 7) >> 3;
     const int rows_per_band = part.band_rows >> 2;
     const int n_bands = (cm.H + part.band_rows - 1) / part.band_rows;
@@ -677,41 +933,55 @@ __global__ void __launch_bounds__(kBlock) k_render_culled(DevScene sc, DevCamera
     const unsigned int tiles_per_band = (unsigned int)(tiles_x * rows_per_band);
     const unsigned int n_tiles = (unsigned int)my_bands * tiles_per_band;
     const bool all_busy = __ldg(vw.all_flag) == vw.frame_id;
+    __shared__ WarpScratch wscr[kBlock / 32];
     WorkCount wc;
     wc.clear();
+    uint2 leaves[kLeafCap];    // per-lane sorted leaf list (local memory)
+    uint32_t stack[kStackCap]; // per-lane inner-node stack of the unculled traversal
     unsigned int rays_done = 0;
     // sky pixel: cast_ray with no hit adds materials[0].emission per sample (renderer.cpp:226, 353-358)
     float sr = 0.0f, sg = 0.0f, sb = 0.0f;
     for (uint32_t s = 0; s < cm.spp; ++s) { sr = addr(sr, sc.sky[0]); sg = addr(sg, sc.sky[1]); sb = addr(sb, sc.sky[2]); }
     const float nspp = (float)cm.spp;
     const uint32_t sky_px = pack_bgrx(__fdiv_rn(sr, nspp), __fdiv_rn(sg, nspp), __fdiv_rn(sb, nspp));
-    for (;;)
+
+    // ---- phase A: sky tiles ------------------------------------------------------------------------------------------
+    if (!all_busy)
     {
-        unsigned int tile = 0;
-        if (lane == 0) tile = atomicAdd(tile_counter, 1u);
-        tile = __shfl_sync(FULL_MASK, tile, 0);
-        if (tile >= n_tiles) break;
-        const unsigned int lb = tile / tiles_per_band, rem = tile - lb * tiles_per_band;
-        const int trow = (int)(rem / (unsigned int)tiles_x), tcol = (int)(rem - (unsigned int)trow * (unsigned int)tiles_x);
-        const int x = tcol * 8 + (lane & 7);
-        const int y0 = ((int)lb * part.world + part.rank) * part.band_rows + trow * 4;
-        const int y = y0 + (lane >> 3);
-        const bool active = x < cm.W && y < cm.H;
-        const size_t idx = (size_t)y * (size_t)cm.W + (size_t)x;
-        if (y0 >= cm.H) continue;  // tile rows past the image in the last band
-        const bool busy = all_busy || __ldg(&vw.stamps[(y0 >> 2) * vw.tiles_x + tcol]) == vw.frame_id;
-        if (!busy)
+        for (unsigned int tile = (unsigned int)warp_slot; tile < n_tiles; tile += n_warps)
         {
-            if (active)
+            const unsigned int lb = tile / tiles_per_band, rem = tile - lb * tiles_per_band;
+            const int trow = (int)(rem / (unsigned int)tiles_x), tcol = (int)(rem - (unsigned int)trow * (unsigned int)tiles_x);
+            const int y0 = ((int)lb * part.world + part.rank) * part.band_rows + trow * 4;
+            if (y0 >= cm.H) continue;  // tile rows past the image in the last band
+            if (__ldg(&vw.stamps[(y0 >> 2) * vw.tiles_x + tcol]) == vw.frame_id) continue;  // busy: phase B
+            const int x = tcol * 8 + (lane & 7), y = y0 + (lane >> 3);
+            if (x < cm.W && y < cm.H)
             {
+                const size_t idx = (size_t)y * (size_t)cm.W + (size_t)x;
                 if (out.bgrx) out.bgrx[idx] = sky_px;
                 if (out.t) out.t[idx] = kMaxFloat;
                 if (out.prim) out.prim[idx] = 0xffffffffu;
                 rays_done += cm.spp;
             }
             if (COUNT && lane == 0) wc.tsky++;
-            continue;
         }
+    }
+    // ---- phase B: busy tiles -----------------------------------------------------------------------------------------
+    const unsigned int n_busy = __ldg(&vw.busy_count[0]);
+    for (;;)
+    {
+        unsigned int bi = 0;
+        if (lane == 0) bi = atomicAdd(&vw.busy_count[2], 1u);
+        bi = __shfl_sync(FULL_MASK, bi, 0);
+        if (bi >= n_busy) break;
+        const unsigned int tile = __ldg(&vw.busy_list[bi]);
+        const unsigned int lb = tile / tiles_per_band, rem = tile - lb * tiles_per_band;
+        const int trow = (int)(rem / (unsigned int)tiles_x), tcol = (int)(rem - (unsigned int)trow * (unsigned int)tiles_x);
+        const int x = tcol * 8 + (lane & 7);
+        const int y = ((int)lb * part.world + part.rank) * part.band_rows + trow * 4 + (lane >> 3);
+        const bool active = x < cm.W && y < cm.H;
+        const size_t idx = (size_t)y * (size_t)cm.W + (size_t)x;
         if (COUNT && lane == 0) wc.tbusy++;
         const float film_y = film_coord(y, cm.H);
         const float film_x = mulr(mulr(film_coord(x, cm.W), cm.h_fov), cm.aspect);
@@ -721,7 +991,7 @@ __global__ void __launch_bounds__(kBlock) k_render_culled(DevScene sc, DevCamera
         if (!cm.aa)
         {
             const RayL ray = camera_ray(cm, film_x, film_y);
-            trace_tile_culled<STRICT, COUNT>(sc, scratch, vw, warp_slot, lane, active, ray, film_x, film_y, t, face, wc);
+            trace_tile_culled<STRICT, COUNT>(sc, scratch, vw, wscr[threadIdx.x >> 5], warp_slot, lane, active, ray, film_x, film_y, leaves, stack, t, face, wc);
             const bool hit = face != 0xffffffffu;
             const float er = hit ? sc.mdl[0] : sc.sky[0], eg = hit ? sc.mdl[1] : sc.sky[1], eb = hit ? sc.mdl[2] : sc.sky[2];
             for (uint32_t s = 0; s < cm.spp; ++s) { cr = addr(cr, er); cg = addr(cg, eg); cb = addr(cb, eb); }
@@ -738,7 +1008,7 @@ __global__ void __launch_bounds__(kBlock) k_render_culled(DevScene sc, DevCamera
                 const float x_off = addr(mulr(pcg_bi(rng), cm.hpw), film_x);
                 const float y_off = addr(mulr(pcg_bi(rng), cm.hph), film_y);
                 const RayL ray = camera_ray(cm, x_off, y_off);
-                trace_tile_culled<STRICT, COUNT>(sc, scratch, vw, warp_slot, lane, active, ray, x_off, y_off, t, face, wc);
+                trace_tile_culled<STRICT, COUNT>(sc, scratch, vw, wscr[threadIdx.x >> 5], warp_slot, lane, active, ray, x_off, y_off, leaves, stack, t, face, wc);
                 const bool hit = face != 0xffffffffu;
                 if (hit) { pcg_bi(rng); pcg_bi(rng); pcg_bi(rng); }
                 cr = addr(cr, hit ? sc.mdl[0] : sc.sky[0]);
@@ -767,6 +1037,8 @@ __global__ void __launch_bounds__(kBlock) k_trace(DevScene sc, const float* __re
     const unsigned long long n_groups = (n + 31ULL) >> 5;
     WorkCount wc;
     wc.clear();
+    uint2 leaves[kLeafCap];    // per-lane sorted leaf list (local memory)
+    uint32_t stack[kStackCap]; // per-lane inner-node stack of the unculled traversal
     unsigned int rays_done = 0;
     for (;;)
     {
@@ -785,7 +1057,7 @@ __global__ void __launch_bounds__(kBlock) k_trace(DevScene sc, const float* __re
         }
         float t;
         uint32_t face;
-        trace_warp<STRICT, COUNT>(sc, scratch, warp_slot, lane, active, ray, t, face, wc);
+        trace_warp<STRICT, COUNT>(sc, scratch, warp_slot, lane, active, ray, leaves, stack, t, face, wc);
         if (active)
         {
             prim[i] = face;
@@ -855,30 +1127,30 @@ cudaError_t launch_render(const DevScene& sc, const DevCamera& cam, const DevPar
     return cudaGetLastError();
 }
 
-cudaError_t launch_view_bounds(const DevScene& sc, const ViewParams& vp, const DevView& view, cudaStream_t stream)
+cudaError_t launch_view_bounds(const DevScene& sc, const ViewParams& vp, const DevView& view, const DevCamera& cam,
+                               const DevPartition& part, cudaStream_t stream)
 {
-    const int warps_per_cta = kBlock / 32;
-    const int grid = (int)((sc.n_nodes + warps_per_cta - 1) / warps_per_cta);
-    k_view_bounds<<<grid, kBlock, 0, stream>>>(sc, vp, view);
+    const int grid = (int)((sc.n_slots + kBlock - 1) / kBlock);
+    k_view_bounds<<<grid < 1 ? 1 : grid, kBlock, 0, stream>>>(sc, vp, view);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    k_view_finish<<<296, kBlock, 0, stream>>>(sc, view, cam, part);
     return cudaGetLastError();
 }
 
 cudaError_t launch_render_culled(const DevScene& sc, const DevCamera& cam, const DevPartition& part, const DevOut& out,
-                                 const DevScratch& scratch, const DevView& view, unsigned int* tile_counter,
-                                 DevCounters* counters, int fp_fast, unsigned long long jitter_seed, LaunchCfg cfg,
-                                 cudaStream_t stream)
+                                 const DevScratch& scratch, const DevView& view, DevCounters* counters, int fp_fast,
+                                 unsigned long long jitter_seed, LaunchCfg cfg, cudaStream_t stream)
 {
-    cudaError_t e = cudaMemsetAsync(tile_counter, 0, sizeof(unsigned int), stream);
-    if (e != cudaSuccess) return e;
     if (counters)
     {
-        if (fp_fast) k_render_culled<false, true><<<cfg.grid, cfg.block, 0, stream>>>(sc, cam, part, out, scratch, view, tile_counter, counters, jitter_seed);
-        else k_render_culled<true, true><<<cfg.grid, cfg.block, 0, stream>>>(sc, cam, part, out, scratch, view, tile_counter, counters, jitter_seed);
+        if (fp_fast) k_render_culled<false, true><<<cfg.grid, cfg.block, 0, stream>>>(sc, cam, part, out, scratch, view, counters, jitter_seed);
+        else k_render_culled<true, true><<<cfg.grid, cfg.block, 0, stream>>>(sc, cam, part, out, scratch, view, counters, jitter_seed);
     }
     else
     {
-        if (fp_fast) k_render_culled<false, false><<<cfg.grid, cfg.block, 0, stream>>>(sc, cam, part, out, scratch, view, tile_counter, counters, jitter_seed);
-        else k_render_culled<true, false><<<cfg.grid, cfg.block, 0, stream>>>(sc, cam, part, out, scratch, view, tile_counter, counters, jitter_seed);
+        if (fp_fast) k_render_culled<false, false><<<cfg.grid, cfg.block, 0, stream>>>(sc, cam, part, out, scratch, view, counters, jitter_seed);
+        else k_render_culled<true, false><<<cfg.grid, cfg.block, 0, stream>>>(sc, cam, part, out, scratch, view, counters, jitter_seed);
     }
     return cudaGetLastError();
 }
