@@ -51,7 +51,8 @@ inline void prep_scene(Scene& scene, uint32& kd_tree_max_nodes)
 }
 
 // renderer.cpp:403-455: returns immediately. twq.jobs is filled with one band-shaped job per 8 scanlines (inclusive
-// rectangles as the reference's tiles) so callers that draw "Tiles k/n" keep working; jobs_done jumps to n on completion.
+// rectangles as the reference's tiles) so callers that draw "Tiles k/n" keep working; jobs_done follows the scanlines
+// that have landed in camera_tex (large frames are copied out slab by slab while the kernel is still tracing).
 inline void start_render_from_camera(RenderInfo& info, ThreadPool& tpool)
 {
     (void)tpool;
@@ -81,7 +82,12 @@ inline b32 wait_for_render_from_camera_to_finish(RenderInfo& info, ThreadPool& t
     (void)tpool;
     if (info.last_error != ATRAY_OK || !info.scene->gpu) return FALSE;
     int r = atray_render_poll(info.scene->gpu, ms_to_wait_for);
-    if (r == 1) return TRUE;
+    if (r == 1)
+    {
+        int32_t rows = 0, total = 0;
+        if (atray_render_progress(info.scene->gpu, &rows, &total) == ATRAY_OK) info.twq.jobs_done = rows / 8;
+        return TRUE;
+    }
     if (r < 0) { info.last_error = r; return FALSE; }
     info.twq.jobs_done = info.twq.jobs.size;
     if (info.hit_prim && info.camera->render_settings.samples_per_pixel == 1)

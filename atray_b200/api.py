@@ -92,6 +92,7 @@ _SIGS = {
     "atray_scene_upload": [_vp, _vp, C.POINTER(Material), C.POINTER(Material)],
     "atray_render_begin": [_vp, C.POINTER(CameraStruct), C.POINTER(RenderOpts), C.POINTER(Frame)],
     "atray_render_poll": [_vp, _u],
+    "atray_render_progress": [_vp, C.POINTER(_i), C.POINTER(_i)],
     "atray_render_cancel": [_vp],
     "atray_render_device": [_vp, C.POINTER(CameraStruct), C.POINTER(RenderOpts), C.POINTER(Frame)],
     "atray_ctx_sync": [_vp],

@@ -7,6 +7,7 @@
 #include <chrono>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <thread>
@@ -47,6 +48,16 @@ struct atray_ctx
     bool in_flight = false;
     cudaEvent_t ev_k0 = nullptr, ev_k1 = nullptr, ev_done = nullptr;
     bool have_kernel_time = false;
+    // slab-pipelined copy-out (atray_render_begin): the copy stream waits on the render kernel's per-slab counters
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t ev_reset = nullptr;              // recorded after k_view_bounds cleared the counters of the previous frame
+    cudaEvent_t ev_slab[kMaxSlabs] = {};         // slab s has landed in the host frame
+    int slabs_in_flight = 0;                     // slabs of the frame in flight (0 = unpipelined frame)
+    int32_t slab_row_end[kMaxSlabs] = {};        // first scanline after slab s (host rows landed once ev_slab[s] fired)
+    int32_t pending_rows = 0;                    // height of the frame in flight
+    int slab_copy = 8;                           // slabs per pipelined frame (ATRAY_SLABS overrides; 1 = off)
+    typedef int (*WaitValue32)(cudaStream_t, unsigned long long, uint32_t, unsigned int);
+    WaitValue32 wait_value32 = nullptr;          // cuStreamWaitValue32 through cudaGetDriverEntryPoint
     // ray-list buffers (atray_trace_rays)
     float* d_rays = nullptr; uint32_t* d_rprim = nullptr; float* d_rt = nullptr;
     size_t ray_cap = 0;
@@ -238,7 +249,25 @@ int atray_ctx_create(int device, atray_ctx** out)
     if (e == cudaSuccess) e = cudaEventCreate(&c->ev_k0);
     if (e == cudaSuccess) e = cudaEventCreate(&c->ev_k1);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_done, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_reset, cudaEventDisableTiming);
+    for (int k = 0; k < kMaxSlabs && e == cudaSuccess; ++k) e = cudaEventCreateWithFlags(&c->ev_slab[k], cudaEventDisableTiming);
     if (e != cudaSuccess) { delete c; return cuda_fail(e, "context setup"); }
+    {
+        // stream memory operations (driver API) without linking libcuda: the copy stream waits on device counters
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult qr;
+        if (cudaGetDriverEntryPoint("cuStreamWaitValue32", &fn, cudaEnableDefault, &qr) == cudaSuccess &&
+            qr == cudaDriverEntryPointSuccess && fn)
+            c->wait_value32 = reinterpret_cast<atray_ctx::WaitValue32>(fn);
+        else
+            cudaGetLastError();
+        if (const char* env = std::getenv("ATRAY_SLABS"))
+        {
+            const int v = std::atoi(env);
+            c->slab_copy = v < 1 ? 1 : (v > kMaxSlabs ? kMaxSlabs : v);
+        }
+    }
     *out = c;
     return ATRAY_OK;
 }
@@ -269,6 +298,10 @@ void atray_ctx_destroy(atray_ctx* c)
     if (c->ev_k0) cudaEventDestroy(c->ev_k0);
     if (c->ev_k1) cudaEventDestroy(c->ev_k1);
     if (c->ev_done) cudaEventDestroy(c->ev_done);
+    if (c->ev_reset) cudaEventDestroy(c->ev_reset);
+    for (int k = 0; k < kMaxSlabs; ++k)
+        if (c->ev_slab[k]) cudaEventDestroy(c->ev_slab[k]);
+    if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -398,8 +431,12 @@ static ViewParams make_view_params(const AtrayCamera* cam)
     return vp;
 }
 
-static int enqueue_render(atray_ctx* c, const AtrayCamera* cam, const AtrayRenderOpts* o, const DevOut& out)
+// Queues one frame on the context stream. `want_slabs` > 1 asks for a slab table (culled kernel only); *slabs_out tells
+// the caller what it got (n = 0: unculled kernel, no per-slab counters).
+static int enqueue_render(atray_ctx* c, const AtrayCamera* cam, const AtrayRenderOpts* o, const DevOut& out, int want_slabs = 1,
+                          DevSlabs* slabs_out = nullptr)
 {
+    if (slabs_out) slabs_out->n = 0;
     DevCounters* ctr = nullptr;
     if (o->count_work)
     {
@@ -426,8 +463,8 @@ static int enqueue_render(atray_ctx* c, const AtrayCamera* cam, const AtrayRende
             if (!c->view.all_flag) CU(cudaMalloc(&c->view.all_flag, sizeof(uint32_t)));
             if (!c->view.busy_count)
             {
-                CU(cudaMalloc(&c->view.busy_count, 4 * sizeof(uint32_t)));
-                CU(cudaMemsetAsync(c->view.busy_count, 0, 4 * sizeof(uint32_t), c->stream));
+                CU(cudaMalloc(&c->view.busy_count, kCtlWords * sizeof(uint32_t)));
+                CU(cudaMemsetAsync(c->view.busy_count, 0, kCtlWords * sizeof(uint32_t), c->stream));
             }
             CU(cudaMemsetAsync(c->view.stamps, 0, c->stamp_cap * sizeof(uint32_t), c->stream));
             CU(cudaMemsetAsync(c->view.all_flag, 0, sizeof(uint32_t), c->stream));
@@ -441,9 +478,11 @@ static int enqueue_render(atray_ctx* c, const AtrayCamera* cam, const AtrayRende
     if (cull)
     {
         // the film rectangles depend on the camera: recomputed every frame, inside the timed region
-        CU(launch_view_bounds(c->scene, vp, c->view, to_dev(cam), p, c->stream));
-        CU(launch_render_culled(c->scene, to_dev(cam), p, out, c->scratch, c->view, ctr, o->fp_mode == ATRAY_FP_FAST,
+        const DevSlabs slabs = make_slabs(to_dev(cam), p, want_slabs);
+        CU(launch_view_bounds(c->scene, vp, c->view, to_dev(cam), p, slabs, c->stream, want_slabs > 1 ? c->ev_reset : nullptr));
+        CU(launch_render_culled(c->scene, to_dev(cam), p, out, c->scratch, c->view, slabs, ctr, o->fp_mode == ATRAY_FP_FAST,
                                 o->jitter_seed, c->cfg, c->stream));
+        if (slabs_out) *slabs_out = slabs;
     }
     else
         CU(launch_render(c->scene, to_dev(cam), p, out, c->scratch, c->d_tile_counter, ctr, o->fp_mode == ATRAY_FP_FAST,
@@ -494,16 +533,53 @@ int atray_render_begin(atray_ctx* c, const AtrayCamera* cam, const AtrayRenderOp
         c->stage_cap_px = px;
     }
     DevOut out{host->bgrx ? c->d_bgrx : nullptr, host->t ? c->d_t : nullptr, host->prim ? c->d_prim : nullptr};
-    rc = enqueue_render(c, cam, o, out);
+    // Whole image on this context and a frame large enough to matter: render slab by slab and copy each slab's scanlines
+    // out while the kernel is still tracing the later ones (the copy stream waits on the kernel's per-slab counters).
+    const bool pipelined = o->part.world == 1 && c->wait_value32 && c->slab_copy > 1 && px >= (size_t(1) << 20);
+    DevSlabs slabs{};
+    rc = enqueue_render(c, cam, o, out, pipelined ? c->slab_copy : 1, &slabs);
     if (rc) return rc;
-    // With a partition (world > 1) only this rank's bands are defined on the device; whole planes are still copied and the
-    // caller merges bands (host layer) — single-process multi-GPU gathers on the device instead (atray_render_device).
-    if (host->bgrx) CU(cudaMemcpyAsync(c->stage_bgrx ? c->h_bgrx : host->bgrx, c->d_bgrx, px * 4, cudaMemcpyDeviceToHost, c->stream));
-    if (host->t) CU(cudaMemcpyAsync(c->stage_t ? c->h_t : host->t, c->d_t, px * 4, cudaMemcpyDeviceToHost, c->stream));
-    if (host->prim) CU(cudaMemcpyAsync(c->stage_prim ? c->h_prim : host->prim, c->d_prim, px * 4, cudaMemcpyDeviceToHost, c->stream));
-    CU(cudaEventRecord(c->ev_done, c->stream));
+    uint32_t* hb = c->stage_bgrx ? c->h_bgrx : host->bgrx;
+    float* ht = c->stage_t ? c->h_t : host->t;
+    uint32_t* hp = c->stage_prim ? c->h_prim : host->prim;
+    c->slabs_in_flight = 0;
+    if (pipelined && slabs.n > 1)
+    {
+        CU(launch_slabs_final(c->view, slabs, c->stream));   // safety net: after the kernel every slab is final
+        CU(cudaStreamWaitEvent(c->copy_stream, c->ev_reset, 0));
+        const uint32_t tiles_per_band = uint32_t(((cam->width + 7) >> 3) * (o->part.band_rows >> 2));
+        for (int s = 0; s < slabs.n; ++s)
+        {
+            const size_t y0 = size_t(slabs.tile_begin[s] / tiles_per_band) * size_t(o->part.band_rows);
+            size_t y1 = size_t(slabs.tile_begin[s + 1] / tiles_per_band) * size_t(o->part.band_rows);
+            if (y1 > size_t(cam->height)) y1 = size_t(cam->height);
+            const size_t off = y0 * size_t(cam->width), cnt = (y1 - y0) * size_t(cam->width) * 4;
+            const unsigned long long addr = (unsigned long long)(uintptr_t)(c->view.busy_count + kCtlDone + s);
+            if (c->wait_value32(c->copy_stream, addr, slabs.live_tiles[s], 0u /* CU_STREAM_WAIT_VALUE_GEQ */) != 0)
+                return fail(ATRAY_ECUDA, "cuStreamWaitValue32 failed");
+            if (hb) CU(cudaMemcpyAsync(hb + off, c->d_bgrx + off, cnt, cudaMemcpyDeviceToHost, c->copy_stream));
+            if (ht) CU(cudaMemcpyAsync(ht + off, c->d_t + off, cnt, cudaMemcpyDeviceToHost, c->copy_stream));
+            if (hp) CU(cudaMemcpyAsync(hp + off, c->d_prim + off, cnt, cudaMemcpyDeviceToHost, c->copy_stream));
+            CU(cudaEventRecord(c->ev_slab[s], c->copy_stream));
+            c->slab_row_end[s] = int32_t(y1);
+        }
+        CU(cudaStreamWaitEvent(c->copy_stream, c->ev_k1, 0));   // the frame is done only when the kernel has retired too
+        CU(cudaEventRecord(c->ev_done, c->copy_stream));
+        CU(cudaStreamWaitEvent(c->stream, c->ev_done, 0));      // later work on the context stream must not overtake the copies
+        c->slabs_in_flight = slabs.n;
+    }
+    else
+    {
+        // With a partition (world > 1) only this rank's bands are defined on the device; whole planes are still copied and
+        // the caller merges bands (host layer) — single-process multi-GPU gathers on the device (atray_render_device).
+        if (hb) CU(cudaMemcpyAsync(hb, c->d_bgrx, px * 4, cudaMemcpyDeviceToHost, c->stream));
+        if (ht) CU(cudaMemcpyAsync(ht, c->d_t, px * 4, cudaMemcpyDeviceToHost, c->stream));
+        if (hp) CU(cudaMemcpyAsync(hp, c->d_prim, px * 4, cudaMemcpyDeviceToHost, c->stream));
+        CU(cudaEventRecord(c->ev_done, c->stream));
+    }
     c->pending_user = *host;
     c->pending_px = px;
+    c->pending_rows = cam->height;
     c->in_flight = true;
     return ATRAY_OK;
 }
@@ -530,12 +606,31 @@ int atray_render_poll(atray_ctx* c, uint32_t timeout_ms)
     return 0;
 }
 
+int atray_render_progress(atray_ctx* c, int32_t* rows_done, int32_t* rows_total)
+{
+    if (!c || !rows_done || !rows_total) return fail(ATRAY_EINVAL, "null argument");
+    CU(cudaSetDevice(c->device));
+    *rows_total = c->pending_rows;
+    if (!c->in_flight) { *rows_done = c->pending_rows; return ATRAY_OK; }
+    int32_t rows = 0;
+    for (int s = 0; s < c->slabs_in_flight; ++s)   // slabs land in order (one copy stream)
+    {
+        cudaError_t e = cudaEventQuery(c->ev_slab[s]);
+        if (e == cudaErrorNotReady) break;
+        if (e != cudaSuccess) return cuda_fail(e, "render");
+        rows = c->slab_row_end[s];
+    }
+    *rows_done = rows;
+    return ATRAY_OK;
+}
+
 int atray_render_cancel(atray_ctx* c)
 {
     if (!c) return fail(ATRAY_EINVAL, "null context");
-    // A frame is one sub-millisecond kernel: cancelling = draining the stream and dropping the pending host copy-out.
+    // A frame is one sub-millisecond kernel: cancelling = draining both streams and dropping the pending host copy-out.
     CU(cudaSetDevice(c->device));
     CU(cudaStreamSynchronize(c->stream));
+    CU(cudaStreamSynchronize(c->copy_stream));
     c->in_flight = false;
     return ATRAY_OK;
 }

@@ -49,9 +49,25 @@ struct DevView
     uint32_t* stamps;      // one per 8x4-pixel tile: == frame_id ⇔ some triangle rectangle may touch the tile
     uint32_t* all_flag;    // == frame_id ⇔ an unbounded rectangle exists: every tile is busy
     uint32_t* busy_list;   // tiles of this rank's bands that must be traced (local tile numbering of the render kernel)
-    uint32_t* busy_count;  // [0] = entries in busy_list, [1] = finished-block ticket of k_view_finish
+    uint32_t* busy_count;  // control words, see kCtl* below (per-slab list lengths, cursors, finished-tile counters, ticket)
     uint32_t frame_id;
     int32_t tiles_x;
+};
+
+// Slabs: the rank's tiles (band-major local numbering) split into up to kMaxSlabs contiguous ranges of whole bands. The
+// render kernel finishes slab after slab and publishes a finished-tile counter per slab, so the host side can start the
+// device→host copy of a slab's scanlines while later slabs are still being traced (capi.cpp: atray_render_begin).
+static constexpr int kMaxSlabs = 16;
+static constexpr int kCtlCount = 0;                 // [s] entries in slab s's segment of busy_list
+static constexpr int kCtlCursor = kMaxSlabs;        // [s] consumer cursor of slab s
+static constexpr int kCtlDone = 2 * kMaxSlabs;      // [s] tiles of slab s whose stores are complete (sky + traced)
+static constexpr int kCtlTicket = 3 * kMaxSlabs;    // finished-block ticket of k_view_finish
+static constexpr int kCtlWords = 3 * kMaxSlabs + 4;
+struct DevSlabs
+{
+    int32_t n;                              // 1 … kMaxSlabs
+    uint32_t tile_begin[kMaxSlabs + 1];     // local tile index range of slab s = [tile_begin[s], tile_begin[s+1])
+    uint32_t live_tiles[kMaxSlabs];         // tiles of slab s that lie inside the image = final value of ctl[kCtlDone + s]
 };
 
 // Per-warp spill area for rays whose leaf list / inner-node stack outgrow the per-lane arrays.
@@ -72,10 +88,13 @@ cudaError_t launch_render(const DevScene& sc, const DevCamera& cam, const DevPar
 // k_view_bounds (per-slot rectangles, packet unions, tile stamps) + k_view_finish (leaf and inner-node unions,
 // compact list of this rank's busy tiles)
 cudaError_t launch_view_bounds(const DevScene& sc, const ViewParams& vp, const DevView& view, const DevCamera& cam,
-                               const DevPartition& part, cudaStream_t stream);
+                               const DevPartition& part, const DevSlabs& slabs, cudaStream_t stream, cudaEvent_t after_reset);
 cudaError_t launch_render_culled(const DevScene& sc, const DevCamera& cam, const DevPartition& part, const DevOut& out,
-                                 const DevScratch& scratch, const DevView& view, DevCounters* counters, int fp_fast,
-                                 unsigned long long jitter_seed, LaunchCfg cfg, cudaStream_t stream);
+                                 const DevScratch& scratch, const DevView& view, const DevSlabs& slabs, DevCounters* counters,
+                                 int fp_fast, unsigned long long jitter_seed, LaunchCfg cfg, cudaStream_t stream);
+// local tile count of a rank and the slab table for `n_slabs` (clamped to the number of local bands)
+DevSlabs make_slabs(const DevCamera& cam, const DevPartition& part, int n_slabs);
+cudaError_t launch_slabs_final(const DevView& view, const DevSlabs& slabs, cudaStream_t stream);
 cudaError_t launch_trace(const DevScene& sc, const float* rays, unsigned long long n, uint32_t* prim, float* t,
                          const DevScratch& scratch, unsigned int* tile_counter, DevCounters* counters, int fp_fast,
                          LaunchCfg cfg, cudaStream_t stream);

@@ -433,7 +433,7 @@ __global__ void __launch_bounds__(kBlock) k_view_bounds(DevScene sc, ViewParams 
     const int lane = threadIdx.x & 31;
     const uint32_t slot = blockIdx.x * kBlock + threadIdx.x;
     const uint32_t slots_up = (sc.n_slots + 31u) & ~31u;
-    if (slot == 0) { view.busy_count[0] = 0u; view.busy_count[2] = 0u; }  // busy-list length and its consumer cursor
+    if (slot < (uint32_t)kCtlTicket) view.busy_count[slot] = 0u;  // per-slab list lengths, cursors and finished-tile counters
     if (slot >= slots_up) return;  // whole warps only beyond this point
     const bool in_range = slot < sc.n_slots;
     const int n_tiles = vp.tiles_x * vp.tiles_y;
@@ -481,7 +481,7 @@ __global__ void __launch_bounds__(kBlock) k_view_bounds(DevScene sc, ViewParams 
 
 // Second pass: (1) one warp per leaf unions its packet rectangles, (2) the stamps of this rank's tiles are compacted
 // into the busy list, (3) the last block to finish unions the children of every inner node, deepest level first.
-__global__ void __launch_bounds__(kBlock) k_view_finish(DevScene sc, DevView view, DevCamera cm, DevPartition part)
+__global__ void __launch_bounds__(kBlock) k_view_finish(DevScene sc, DevView view, DevCamera cm, DevPartition part, DevSlabs slabs)
 {
     const int lane = threadIdx.x & 31;
     const uint32_t warp = (blockIdx.x * kBlock + threadIdx.x) >> 5;
@@ -523,13 +523,20 @@ __global__ void __launch_bounds__(kBlock) k_view_finish(DevScene sc, DevView vie
                 const int y0 = ((int)lb * part.world + part.rank) * part.band_rows + trow * 4;
                 busy = y0 < cm.H && (all_busy || view.stamps[(y0 >> 2) * view.tiles_x + tcol] == view.frame_id);
             }
-            const unsigned m = __ballot_sync(FULL_MASK, busy);
-            if (m)
+            // append to the segment of the tile's slab (segment s starts at busy_list[tile_begin[s]]: room for every tile)
+            int slab = 0;
+            while (slab + 1 < slabs.n && tile >= slabs.tile_begin[slab + 1]) ++slab;
+            unsigned todo = __ballot_sync(FULL_MASK, busy);
+            while (todo)
             {
+                const int leader = __ffs(todo) - 1;
+                const int ls = __shfl_sync(FULL_MASK, slab, leader);
+                const unsigned m = __ballot_sync(FULL_MASK, busy && slab == ls);
+                todo &= ~m;
                 unsigned int at = 0;
-                if (lane == 0) at = atomicAdd(&view.busy_count[0], (unsigned int)__popc(m));
-                at = __shfl_sync(FULL_MASK, at, 0);
-                if (busy) view.busy_list[at + __popc(m & ((1u << lane) - 1u))] = tile;
+                if (lane == leader) at = atomicAdd(&view.busy_count[kCtlCount + ls], (unsigned int)__popc(m));
+                at = __shfl_sync(FULL_MASK, at, leader);
+                if (busy && slab == ls) view.busy_list[slabs.tile_begin[ls] + at + __popc(m & ((1u << lane) - 1u))] = tile;
             }
         }
     }
@@ -537,7 +544,7 @@ __global__ void __launch_bounds__(kBlock) k_view_finish(DevScene sc, DevView vie
     __shared__ bool is_last;
     __threadfence();
     __syncthreads();
-    if (threadIdx.x == 0) is_last = atomicAdd(&view.busy_count[1], 1u) == gridDim.x - 1;
+    if (threadIdx.x == 0) is_last = atomicAdd(&view.busy_count[kCtlTicket], 1u) == gridDim.x - 1;
     __syncthreads();
     if (!is_last) return;
     __threadfence();
@@ -560,7 +567,7 @@ __global__ void __launch_bounds__(kBlock) k_view_finish(DevScene sc, DevView vie
         __threadfence();
         __syncthreads();
     }
-    if (threadIdx.x == 0) view.busy_count[1] = 0u;  // ticket for the next frame
+    if (threadIdx.x == 0) view.busy_count[kCtlTicket] = 0u;  // ticket for the next frame
 }
 
 // ---- culled phase 2: the warp walks the k-th listed leaf of each of its rays; rays that share the leaf form a group.
@@ -916,12 +923,17 @@ __device__ __forceinline__ void trace_tile_culled(const DevScene& sc, const DevS
 }
 
 // ---- K1c: fused primary-ray render with film-space culling ----------------------------------------------------------
-// Phase A: every warp takes a static, interleaved share of this rank's tiles and writes the sky result into those no
-// triangle rectangle can touch (≈90 % of a typical frame: a pure store stream). Phase B: the busy tiles listed by
-// k_view_finish are pulled one at a time from an atomic cursor (dynamic balance where the work is).
+// The rank's tiles are processed slab by slab (DevSlabs: contiguous ranges of whole bands, bottom of the image first).
+// Phase A of a slab: every warp takes a static, interleaved share of the slab's tiles and writes the sky result into
+// those no triangle rectangle can touch (≈90 % of a typical frame: a pure store stream). Phase B: the slab's busy tiles
+// listed by k_view_finish are pulled one at a time from an atomic cursor (dynamic balance where the work is). A warp
+// that runs out of work in a slab publishes the number of tiles it completed there (stores fenced first) and moves on:
+// ctl[kCtlDone + s] == tiles of slab s ⇔ every scanline of the slab is final — the host side's copy stream waits for
+// exactly that value (stream memory operation) and copies the slab out while later slabs are still being traced.
 template <bool STRICT, bool COUNT>
 __global__ void __launch_bounds__(kBlock) k_render_culled(DevScene sc, DevCamera cm, DevPartition part, DevOut out, DevScratch scratch,
-                                                          DevView vw, DevCounters* counters, unsigned long long jitter_seed)
+                                                          DevView vw, DevSlabs slabs, DevCounters* counters,
+                                                          unsigned long long jitter_seed)
 {
     const int lane = threadIdx.x & 31;
     const int warp_slot = (blockIdx.x * kBlock + threadIdx.x) >> 5;
@@ -945,15 +957,19 @@ __global__ void __launch_bounds__(kBlock) k_render_culled(DevScene sc, DevCamera
     const float nspp = (float)cm.spp;
     const uint32_t sky_px = pack_bgrx(__fdiv_rn(sr, nspp), __fdiv_rn(sg, nspp), __fdiv_rn(sb, nspp));
 
+  for (int slab = 0; slab < slabs.n; ++slab)
+  {
+    const unsigned int tile_lo = slabs.tile_begin[slab], tile_hi = min(slabs.tile_begin[slab + 1], n_tiles);
+    unsigned int finished = 0;  // tiles of this slab completed by this warp
     // ---- phase A: sky tiles ------------------------------------------------------------------------------------------
     if (!all_busy)
     {
-        for (unsigned int tile = (unsigned int)warp_slot; tile < n_tiles; tile += n_warps)
+        for (unsigned int tile = tile_lo + (unsigned int)warp_slot; tile < tile_hi; tile += n_warps)
         {
             const unsigned int lb = tile / tiles_per_band, rem = tile - lb * tiles_per_band;
             const int trow = (int)(rem / (unsigned int)tiles_x), tcol = (int)(rem - (unsigned int)trow * (unsigned int)tiles_x);
             const int y0 = ((int)lb * part.world + part.rank) * part.band_rows + trow * 4;
-            if (y0 >= cm.H) continue;  // tile rows past the image in the last band
+            if (y0 >= cm.H) continue;  // tile rows past the image in the last band (not counted in live_tiles either)
             if (__ldg(&vw.stamps[(y0 >> 2) * vw.tiles_x + tcol]) == vw.frame_id) continue;  // busy: phase B
             const int x = tcol * 8 + (lane & 7), y = y0 + (lane >> 3);
             if (x < cm.W && y < cm.H)
@@ -964,18 +980,20 @@ __global__ void __launch_bounds__(kBlock) k_render_culled(DevScene sc, DevCamera
                 if (out.prim) out.prim[idx] = 0xffffffffu;
                 rays_done += cm.spp;
             }
+            ++finished;
             if (COUNT && lane == 0) wc.tsky++;
         }
     }
     // ---- phase B: busy tiles -----------------------------------------------------------------------------------------
-    const unsigned int n_busy = __ldg(&vw.busy_count[0]);
+    const unsigned int n_busy = __ldg(&vw.busy_count[kCtlCount + slab]);
     for (;;)
     {
         unsigned int bi = 0;
-        if (lane == 0) bi = atomicAdd(&vw.busy_count[2], 1u);
+        if (lane == 0) bi = atomicAdd(&vw.busy_count[kCtlCursor + slab], 1u);
         bi = __shfl_sync(FULL_MASK, bi, 0);
         if (bi >= n_busy) break;
-        const unsigned int tile = __ldg(&vw.busy_list[bi]);
+        const unsigned int tile = __ldg(&vw.busy_list[tile_lo + bi]);
+        ++finished;
         const unsigned int lb = tile / tiles_per_band, rem = tile - lb * tiles_per_band;
         const int trow = (int)(rem / (unsigned int)tiles_x), tcol = (int)(rem - (unsigned int)trow * (unsigned int)tiles_x);
         const int x = tcol * 8 + (lane & 7);
@@ -1024,6 +1042,14 @@ __global__ void __launch_bounds__(kBlock) k_render_culled(DevScene sc, DevCamera
             if (out.prim) out.prim[idx] = face;
         }
     }
+    // publish this warp's share of the slab: every lane fences its own stores, then one counter update per warp
+    if (__any_sync(FULL_MASK, finished != 0u))
+    {
+        __threadfence();
+        __syncwarp();
+        if (lane == 0) atomicAdd(&vw.busy_count[kCtlDone + slab], finished);
+    }
+  }
     if (COUNT) flush_counters(counters, wc, rays_done);
 }
 
@@ -1127,32 +1153,97 @@ cudaError_t launch_render(const DevScene& sc, const DevCamera& cam, const DevPar
     return cudaGetLastError();
 }
 
+DevSlabs make_slabs(const DevCamera& cam, const DevPartition& part, int n_slabs)
+{
+    DevSlabs s{};
+    const int tiles_x = (cam.W + 7) >> 3;
+    const int n_bands = (cam.H + part.band_rows - 1) / part.band_rows;
+    const int my_bands = part.rank < n_bands ? (n_bands - part.rank + part.world - 1) / part.world : 0;
+    const uint32_t tiles_per_band = (uint32_t)(tiles_x * (part.band_rows >> 2));
+    int n = n_slabs < 1 ? 1 : (n_slabs > kMaxSlabs ? kMaxSlabs : n_slabs);
+    if (n > my_bands) n = my_bands < 1 ? 1 : my_bands;
+    s.n = n;
+    int band_of[kMaxSlabs + 1];
+    for (int k = 0; k <= kMaxSlabs; ++k)
+    {
+        band_of[k] = k >= n ? my_bands : (int)((long long)k * my_bands / n);
+        s.tile_begin[k] = (uint32_t)band_of[k] * tiles_per_band;
+    }
+    for (int k = 0; k < kMaxSlabs; ++k)
+    {
+        uint32_t live = 0;
+        for (int lb = band_of[k]; lb < band_of[k + 1]; ++lb)
+        {
+            const int y0 = (lb * part.world + part.rank) * part.band_rows;
+            int rows = cam.H - y0;
+            if (rows > part.band_rows) rows = part.band_rows;
+            if (rows > 0) live += (uint32_t)(((rows + 3) >> 2) * tiles_x);
+        }
+        s.live_tiles[k] = live;
+    }
+    return s;
+}
+
+// Safety net behind the per-slab counters: once the render kernel has finished, every slab is final by definition.
+__global__ void k_slabs_final(uint32_t* ctl, DevSlabs slabs)
+{
+    if (threadIdx.x < (unsigned)slabs.n) ctl[kCtlDone + threadIdx.x] = slabs.live_tiles[threadIdx.x];
+}
+cudaError_t launch_slabs_final(const DevView& view, const DevSlabs& slabs, cudaStream_t stream)
+{
+    k_slabs_final<<<1, 32, 0, stream>>>(view.busy_count, slabs);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_view_bounds(const DevScene& sc, const ViewParams& vp, const DevView& view, const DevCamera& cam,
-                               const DevPartition& part, cudaStream_t stream)
+                               const DevPartition& part, const DevSlabs& slabs, cudaStream_t stream, cudaEvent_t after_reset)
 {
     const int grid = (int)((sc.n_slots + kBlock - 1) / kBlock);
     k_view_bounds<<<grid < 1 ? 1 : grid, kBlock, 0, stream>>>(sc, vp, view);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;
-    k_view_finish<<<296, kBlock, 0, stream>>>(sc, view, cam, part);
+    if (after_reset)  // the per-slab counters of the previous frame are gone from here on
+    {
+        e = cudaEventRecord(after_reset, stream);
+        if (e != cudaSuccess) return e;
+    }
+    k_view_finish<<<296, kBlock, 0, stream>>>(sc, view, cam, part, slabs);
+    return cudaGetLastError();
+}
+
+// The culled kernel is persistent: its grid is exactly what is resident at once (a slab completes only when every warp
+// has done its static sky share, so no CTA may wait for an SM).
+template <bool STRICT, bool COUNT>
+static cudaError_t launch_culled_t(const DevScene& sc, const DevCamera& cam, const DevPartition& part, const DevOut& out,
+                                   const DevScratch& scratch, const DevView& view, const DevSlabs& slabs, DevCounters* counters,
+                                   unsigned long long jitter_seed, LaunchCfg cfg, cudaStream_t stream)
+{
+    static int per_sm = 0;
+    if (per_sm == 0)
+    {
+        int n = 0;
+        cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_render_culled<STRICT, COUNT>, kBlock, 0);
+        if (e != cudaSuccess) return e;
+        per_sm = n < 1 ? 1 : n;
+    }
+    const int sms = cfg.grid / 4;  // render_launch_cfg: 4 CTAs per SM is the upper bound the scratch areas are sized for
+    int grid = sms * per_sm;
+    if (grid > cfg.grid) grid = cfg.grid;
+    k_render_culled<STRICT, COUNT><<<grid, cfg.block, 0, stream>>>(sc, cam, part, out, scratch, view, slabs, counters, jitter_seed);
     return cudaGetLastError();
 }
 
 cudaError_t launch_render_culled(const DevScene& sc, const DevCamera& cam, const DevPartition& part, const DevOut& out,
-                                 const DevScratch& scratch, const DevView& view, DevCounters* counters, int fp_fast,
-                                 unsigned long long jitter_seed, LaunchCfg cfg, cudaStream_t stream)
+                                 const DevScratch& scratch, const DevView& view, const DevSlabs& slabs, DevCounters* counters,
+                                 int fp_fast, unsigned long long jitter_seed, LaunchCfg cfg, cudaStream_t stream)
 {
     if (counters)
     {
-        if (fp_fast) k_render_culled<false, true><<<cfg.grid, cfg.block, 0, stream>>>(sc, cam, part, out, scratch, view, counters, jitter_seed);
-        else k_render_culled<true, true><<<cfg.grid, cfg.block, 0, stream>>>(sc, cam, part, out, scratch, view, counters, jitter_seed);
+        if (fp_fast) return launch_culled_t<false, true>(sc, cam, part, out, scratch, view, slabs, counters, jitter_seed, cfg, stream);
+        return launch_culled_t<true, true>(sc, cam, part, out, scratch, view, slabs, counters, jitter_seed, cfg, stream);
     }
-    else
-    {
-        if (fp_fast) k_render_culled<false, false><<<cfg.grid, cfg.block, 0, stream>>>(sc, cam, part, out, scratch, view, counters, jitter_seed);
-        else k_render_culled<true, false><<<cfg.grid, cfg.block, 0, stream>>>(sc, cam, part, out, scratch, view, counters, jitter_seed);
-    }
-    return cudaGetLastError();
+    if (fp_fast) return launch_culled_t<false, false>(sc, cam, part, out, scratch, view, slabs, counters, jitter_seed, cfg, stream);
+    return launch_culled_t<true, false>(sc, cam, part, out, scratch, view, slabs, counters, jitter_seed, cfg, stream);
 }
 
 cudaError_t launch_trace(const DevScene& sc, const float* rays, unsigned long long n, uint32_t* prim, float* t,

@@ -65,6 +65,12 @@ class Context:
     def render_poll(self, timeout_ms=0xFFFFFFFF):
         return _ck(_L.atray_render_poll(self.h, timeout_ms))
 
+    def render_progress(self):
+        """(rows_done, rows_total): scanlines [0, rows_done) of the host frame are final (twq.jobs_done analogue)."""
+        a, b = C.c_int32(0), C.c_int32(0)
+        _ck(_L.atray_render_progress(self.h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
     def render(self, cam, opts=None, want=("bgrx", "t", "prim")):
         """Synchronous convenience: one frame into fresh numpy arrays (row 0 = bottom scanline)."""
         opts = opts or self.opts()
@@ -184,13 +190,16 @@ def start_render_from_camera(info, tpool=None):
     """start_render_from_camera(RenderInfo&, ThreadPool&) — renderer.cpp:403-455. Returns immediately; `tpool` is
     accepted for signature parity and ignored (the tile thread pool is replaced by the kernel)."""
     opts = info.opts or Context.opts()
-    info.jobs_size, info.jobs_done = 1, 0
+    # jobs = bands of 8 scanlines (the reference lists square tiles, renderer.cpp:420-445; callers only show k/n)
+    info.jobs_size, info.jobs_done = (info.camera.height + 7) // 8, 0
     info.scene.ctx.render_begin(info.camera, opts, info.camera_tex, info.t, info.prim)
 
 
 def wait_for_render_from_camera_to_finish(info, tpool=None, ms_to_wait_for=33):
     """renderer.cpp:457-471: TRUE (1) while still running, FALSE (0) when finished."""
     running = info.scene.ctx.render_poll(ms_to_wait_for)
+    if running:
+        info.jobs_done = info.scene.ctx.render_progress()[0] // 8   # bands whose scanlines have landed in camera_tex
     if not running:
         info.jobs_done = info.jobs_size
         # ray_casts counts non-sky bounce iterations (renderer.cpp:222-231,260): at bounce 1 = samples that hit geometry

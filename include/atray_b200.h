@@ -150,6 +150,11 @@ int atray_render_begin(atray_ctx* ctx, const AtrayCamera* cam, const AtrayRender
 /* wait_for_render_from_camera_to_finish(RenderInfo&, ThreadPool&, ms) — renderer.cpp:457-471:
  * returns 1 while still running (timed out), 0 when finished, negative on error. */
 int atray_render_poll(atray_ctx* ctx, uint32_t timeout_ms);
+/* info.twq.jobs_done / info.twq.jobs.size as app.cpp:176-185 polls them for "Tiles k/n" and the live blit: scanlines
+ * [0, rows_done) of the host frame are final. Large frames are rendered slab by slab (bottom first) and each slab is
+ * copied out while later slabs are still being traced, so rows_done advances during the frame; small or partitioned
+ * frames jump from 0 to rows_total on completion. */
+int atray_render_progress(atray_ctx* ctx, int32_t* rows_done, int32_t* rows_total);
 /* info.twq.clear() cancel path — app.cpp:165-172 */
 int atray_render_cancel(atray_ctx* ctx);
 /* Same frame, outputs left resident in device memory (planes are device pointers, may live on a peer GPU);

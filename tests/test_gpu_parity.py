@@ -290,7 +290,7 @@ def test_reference_call_sequence(A, port, meshes):
     polls = 0
     while A.wait_for_render_from_camera_to_finish(info, None, 33):
         polls += 1
-    assert info.jobs_done == info.jobs_size == 1
+    assert info.jobs_done == info.jobs_size == 720 // 8
     o = B.Scene(port, path, rescale=0.0)
     face, t, img = o.trace_primary(1280, 720, threads=NTHREADS)
     assert (tex.array == img).all() and (prim == face).all()
@@ -300,6 +300,37 @@ def test_reference_call_sequence(A, port, meshes):
         scene.ctx.render(A.set_camera(64, 64, bounce_limit=5))
     tex.free()
     o.close()
+
+
+def test_pipelined_copy_out_equals_whole_frame(A, meshes, monkeypatch):
+    """Frames of ≥ 1 Mpx through atray_render_begin are rendered slab by slab and copied out while later slabs are
+    still being traced (copy stream waiting on the kernel's per-slab counters). The host frame must equal the
+    device-resident frame of atray_render_device and the unpipelined copy-out (ATRAY_SLABS=1) bit for bit; progress
+    is monotone and ends at the frame height; repeated frames reuse the counters correctly."""
+    path, rescale = meshes["knot_mid"]
+    W, H = 1920, 1084   # height not a multiple of the band height: the last band is partial
+    cam = A.set_camera(W, H)
+    ref_sc = gpu_scene(A, path, rescale)
+    whole = ref_sc.ctx.render(cam)   # synchronous convenience call = begin + poll on pageable arrays (staged)
+    for slabs in ("1", "3", "8", "16"):
+        monkeypatch.setenv("ATRAY_SLABS", slabs)
+        sc = gpu_scene(A, path, rescale)
+        tex, tt, tp = A.PinnedArray((H, W), np.uint32), A.PinnedArray((H, W), np.float32), A.PinnedArray((H, W), np.uint32)
+        for rep in range(3):
+            tex.array[:] = 0xdeadbeef
+            tp.array[:] = 7
+            info = A.RenderInfo(cam, sc, tex.array, t=tt.array, prim=tp.array)
+            A.start_render_from_camera(info)
+            seen = [0]
+            while A.wait_for_render_from_camera_to_finish(info, None, 0):
+                seen.append(sc.ctx.render_progress()[0])
+            assert all(b >= a for a, b in zip(seen, seen[1:])), seen
+            assert sc.ctx.render_progress() == (H, H)
+            assert info.jobs_done == info.jobs_size == (H + 7) // 8
+            assert (tex.array == whole["bgrx"]).all() and (tp.array == whole["prim"]).all()
+            assert same_bits(tt.array, whole["t"])
+        for a in (tex, tt, tp):
+            a.free()
 
 
 def test_errors_on_device_side(A, meshes):
