@@ -481,7 +481,8 @@ __global__ void __launch_bounds__(kBlock) k_view_bounds(DevScene sc, ViewParams 
 
 // Second pass: (1) one warp per leaf unions its packet rectangles, (2) the stamps of this rank's tiles are compacted
 // into the busy list, (3) the last block to finish unions the children of every inner node, deepest level first.
-__global__ void __launch_bounds__(kBlock) k_view_finish(DevScene sc, DevView view, DevCamera cm, DevPartition part, DevSlabs slabs)
+__global__ void __launch_bounds__(kBlock) k_view_finish(DevScene sc, DevView view, DevCamera cm, DevPartition part, DevSlabs slabs,
+                                                        uint32_t smem_nodes)
 {
     const int lane = threadIdx.x & 31;
     const uint32_t warp = (blockIdx.x * kBlock + threadIdx.x) >> 5;
@@ -548,6 +549,44 @@ __global__ void __launch_bounds__(kBlock) k_view_finish(DevScene sc, DevView vie
     __syncthreads();
     if (!is_last) return;
     __threadfence();
+    if (smem_nodes >= sc.n_nodes)
+    {
+        // whole rectangle table in shared memory: one coalesced load, then the levels cost a __syncthreads each
+        extern __shared__ float4 s_rect[];
+        const uint32_t n_inner = __ldg(&sc.level_start[sc.n_levels]);
+        uint32_t* s_node = reinterpret_cast<uint32_t*>(s_rect + sc.n_nodes);
+        uint32_t* s_c0 = s_node + n_inner;
+        for (uint32_t i = threadIdx.x; i < sc.n_nodes; i += kBlock) s_rect[i] = __ldcg(&view.node_rect[i]);  // leaves are final
+        for (uint32_t k = threadIdx.x; k < n_inner; k += kBlock)
+        {
+            const uint32_t node = __ldg(&sc.inner_order[k]);
+            s_node[k] = node;
+            s_c0[k] = (uint32_t)__float_as_int(__ldg(&sc.nodes[2 * node]).w);
+        }
+        __syncthreads();
+        uint32_t b = 0;
+        for (uint32_t l = 0; l < sc.n_levels; ++l)
+        {
+            const uint32_t e = __ldg(&sc.level_start[l + 1]);
+            for (uint32_t k = b + threadIdx.x; k < e; k += kBlock)
+            {
+                const uint32_t c0 = s_c0[k];
+                float4 acc = make_float4(INFINITY, INFINITY, -INFINITY, -INFINITY);
+#pragma unroll
+                for (int c = 0; c < 8; ++c)
+                {
+                    const float4 q = s_rect[c0 + c];
+                    acc.x = fminf(acc.x, q.x); acc.y = fminf(acc.y, q.y); acc.z = fmaxf(acc.z, q.z); acc.w = fmaxf(acc.w, q.w);
+                }
+                s_rect[s_node[k]] = acc;
+                view.node_rect[s_node[k]] = acc;
+            }
+            __syncthreads();
+            b = e;
+        }
+        if (threadIdx.x == 0) view.busy_count[kCtlTicket] = 0u;  // ticket for the next frame
+        return;
+    }
     for (uint32_t l = 0; l < sc.n_levels; ++l)
     {
         const uint32_t b = __ldg(&sc.level_start[l]), e = __ldg(&sc.level_start[l + 1]);
@@ -795,6 +834,16 @@ __device__ __forceinline__ bool collect_tile_leaves(const float4* __restrict__ n
         unsigned cm = __ballot_sync(FULL_MASK, rect_overlap(myR, trect)) & 0xffu;
         unsigned ev = 0u, am = 0u;  // this lane: children of `cur` whose acceptance is known / that were accepted
         bool alive = here;          // false once the lane is cut at this node
+        // Can the cut trigger at this node at all? The children are the 8 octants around the split point s = hi corner of
+        // child 0 (kd_tree.cpp:120-148) and every child's slab interval per axis is [t(lo), t(s)] or [t(s), t(hi)] with the
+        // SAME float t(s) = (s - o)*inv on both sides. If the three split-plane parameters are pairwise different, every
+        // ray parameter lies in the closed intervals of at most 4 octant triples in total, so at most 4 children can pass
+        // the slab test (leaf acceptance is stricter still) and the "accepted <= 4" guard never stops the loop. Only lanes
+        // with a tie (ray through a split edge, up to rounding) need the lazy sibling evaluation below.
+        const float4 sp4 = __ldg(&nodes[2 * c0 + 1]);
+        const float tsx = mulr(subr(sp4.x, r.ox), ix), tsy = mulr(subr(sp4.y, r.oy), iy), tsz = mulr(subr(sp4.z, r.oz), iz);
+        const bool risky = here && (tsx == tsy || tsy == tsz || tsx == tsz);
+        const bool any_risky = __any_sync(FULL_MASK, risky);
         while (cm)
         {
             const int i = __ffs(cm) - 1;
@@ -803,7 +852,7 @@ __device__ __forceinline__ bool collect_tile_leaves(const float4* __restrict__ n
             const float rx1 = __shfl_sync(FULL_MASK, myR.z, i), ry1 = __shfl_sync(FULL_MASK, myR.w, i);
             bool want = alive && !(fx < rx0 || fx > rx1 || fy < ry0 || fy > ry1);
             if (!__any_sync(FULL_MASK, want)) continue;
-            if (i >= 5)
+            if (i >= 5 && any_risky)
             {
                 const unsigned below = (1u << i) - 1u;
                 int nrej = __popc(ev & ~am & below);
@@ -811,7 +860,7 @@ __device__ __forceinline__ bool collect_tile_leaves(const float4* __restrict__ n
                 for (int q = 0; q < i; ++q)
                 {
                     const int j = (int)((ord >> (4 * q)) & 7u);
-                    const bool need = want && nrej < i - 4 && !((ev >> j) & 1u);
+                    const bool need = want && risky && nrej < i - 4 && !((ev >> j) & 1u);
                     if (!__any_sync(FULL_MASK, need)) continue;
                     const float4 lo = __ldg(&nodes[2 * (c0 + j)]);
                     const float4 hi = __ldg(&nodes[2 * (c0 + j) + 1]);
@@ -823,7 +872,7 @@ __device__ __forceinline__ bool collect_tile_leaves(const float4* __restrict__ n
                         if (a) am |= 1u << j; else ++nrej;
                     }
                 }
-                if (want && nrej < i - 4) { alive = false; want = false; }  // five earlier children accepted: cut
+                if (want && risky && nrej < i - 4) { alive = false; want = false; }  // five earlier children accepted: cut
                 if (!__any_sync(FULL_MASK, want)) continue;
             }
             const uint32_t ch = c0 + (uint32_t)i;
@@ -956,13 +1005,57 @@ __global__ void __launch_bounds__(kBlock) k_render_culled(DevScene sc, DevCamera
     for (uint32_t s = 0; s < cm.spp; ++s) { sr = addr(sr, sc.sky[0]); sg = addr(sg, sc.sky[1]); sb = addr(sb, sc.sky[2]); }
     const float nspp = (float)cm.spp;
     const uint32_t sky_px = pack_bgrx(__fdiv_rn(sr, nspp), __fdiv_rn(sg, nspp), __fdiv_rn(sb, nspp));
+    // 16-byte row segments need W % 4 == 0 and 16-byte aligned planes (caller-provided device pointers may be anything)
+    const bool vec_ok = (cm.W & 3) == 0 &&
+                        (((size_t)out.bgrx | (size_t)out.t | (size_t)out.prim) & 15) == 0;
 
   for (int slab = 0; slab < slabs.n; ++slab)
   {
     const unsigned int tile_lo = slabs.tile_begin[slab], tile_hi = min(slabs.tile_begin[slab + 1], n_tiles);
     unsigned int finished = 0;  // tiles of this slab completed by this warp
     // ---- phase A: sky tiles ------------------------------------------------------------------------------------------
-    if (!all_busy)
+    // One strip of 32 consecutive tiles (256×4 pixels) per step: one coalesced stamp load, then 512-byte row segments.
+    if (!all_busy && vec_ok)
+    {
+        const unsigned int strips_x = (unsigned int)(tiles_x + 31) >> 5;
+        const unsigned int trow_lo = tile_lo / (unsigned int)tiles_x, trow_hi = tile_hi / (unsigned int)tiles_x;
+        const unsigned int n_strips = (trow_hi - trow_lo) * strips_x;
+        const uint4 px4 = make_uint4(sky_px, sky_px, sky_px, sky_px);
+        const uint4 t4 = make_uint4(__float_as_uint(kMaxFloat), __float_as_uint(kMaxFloat), __float_as_uint(kMaxFloat), __float_as_uint(kMaxFloat));
+        const uint4 m4 = make_uint4(0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu);
+        for (unsigned int st = (unsigned int)warp_slot; st < n_strips; st += n_warps)
+        {
+            const unsigned int sr = st / strips_x, scol = st - sr * strips_x;
+            const unsigned int ltr = trow_lo + sr;                                   // local tile row
+            const unsigned int lb = ltr / (unsigned int)rows_per_band, trow = ltr - lb * (unsigned int)rows_per_band;
+            const int y0 = ((int)lb * part.world + part.rank) * part.band_rows + (int)trow * 4;
+            if (y0 >= cm.H) continue;  // tile rows past the image in the last band (not counted in live_tiles either)
+            const int tcol = (int)scol * 32 + lane;
+            const bool sky = tcol < tiles_x && __ldg(&vw.stamps[(y0 >> 2) * vw.tiles_x + tcol]) != vw.frame_id;
+            const unsigned skym = __ballot_sync(FULL_MASK, sky);
+            if (!skym) continue;
+            finished += (unsigned int)__popc(skym);
+            if (COUNT && lane == 0) wc.tsky += (unsigned int)__popc(skym);
+#pragma unroll
+            for (int h = 0; h < 2; ++h)
+            {
+                const int x = (int)scol * 256 + h * 128 + lane * 4;                  // 4 pixels = half a tile row
+                if (!((skym >> (h * 16 + (lane >> 1))) & 1u) || x >= cm.W) continue;
+#pragma unroll
+                for (int r = 0; r < 4; ++r)
+                {
+                    const int y = y0 + r;
+                    if (y >= cm.H) break;
+                    const size_t idx = (size_t)y * (size_t)cm.W + (size_t)x;
+                    if (out.bgrx) *reinterpret_cast<uint4*>(out.bgrx + idx) = px4;
+                    if (out.t) *reinterpret_cast<uint4*>(out.t + idx) = t4;
+                    if (out.prim) *reinterpret_cast<uint4*>(out.prim + idx) = m4;
+                    rays_done += 4u * cm.spp;
+                }
+            }
+        }
+    }
+    else if (!all_busy)
     {
         for (unsigned int tile = tile_lo + (unsigned int)warp_slot; tile < tile_hi; tile += n_warps)
         {
@@ -1207,7 +1300,21 @@ cudaError_t launch_view_bounds(const DevScene& sc, const ViewParams& vp, const D
         e = cudaEventRecord(after_reset, stream);
         if (e != cudaSuccess) return e;
     }
-    k_view_finish<<<296, kBlock, 0, stream>>>(sc, view, cam, part, slabs);
+    // inner-node unions run in shared memory when the table fits: 16 B per node + 8 B per inner node
+    static bool attr_set[64] = {};  // per device (function attributes belong to the device's context)
+    const size_t kSmemMax = 200 * 1024;
+    int dev = 0;
+    e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= 64 || !attr_set[dev])
+    {
+        e = cudaFuncSetAttribute(k_view_finish, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemMax);
+        if (e != cudaSuccess) return e;
+        if (dev >= 0 && dev < 64) attr_set[dev] = true;
+    }
+    const size_t need = (size_t)sc.n_nodes * 16 + ((size_t)sc.n_nodes / 8 + 1) * 8;
+    const bool fits = need <= kSmemMax;
+    k_view_finish<<<296, kBlock, fits ? need : 0, stream>>>(sc, view, cam, part, slabs, fits ? sc.n_nodes : 0u);
     return cudaGetLastError();
 }
 

@@ -165,6 +165,38 @@ def test_culled_equals_unculled_and_oracle(name, method, cap, A, port, meshes):
     o.close()
 
 
+@pytest.mark.parametrize("cap", [12, 6])
+def test_cut_rule_on_split_edges(cap, A, port, tmp_path):
+    """The "at most 5 accepted children" cut (kd_tree.cpp:374) only triggers for rays through a split edge. Eight cubes
+    mirrored around the origin with CENTER splits put the split planes at exactly 0 / ±2; an eye at (-3,-3,10) looking
+    down -z makes every diagonal pixel's ray cross x = 0 and y = 0 at the same parameter (bit-equal slab values), inside
+    the tree. The culled kernel decides per node whether the cut can trigger (pairwise different split parameters ⇒
+    ≤ 4 children pass); these rays take its exact sibling evaluation. Culled = unculled = oracle, bit for bit."""
+    from oracle import bind as B
+    v0, f0 = cube_mesh(1.0)
+    vs, fs = [], []
+    for k, c in enumerate([(x, y, z) for x in (-2, 2) for y in (-2, 2) for z in (-2, 2)]):
+        vs.append(v0 + np.array(c, np.float32))
+        fs.append(f0 + 8 * k)
+    path = write_obj(str(tmp_path / "cubes8.obj"), np.concatenate(vs), np.concatenate(fs))
+    m = A.load_model_data(path, 1)
+    A.place_default(m, 0.0, translate=(0.0, 0.0, 0.0))
+    sc = A.Scene(m, division_method=A.DIV_CENTER, max_no_faces_per_node=cap)
+    A.prep_scene(sc)
+    tree = m.tree()
+    assert (tree["boxes"][tree["children_start"][0], 3:] == 0.0).all()   # root split point = hi corner of child 0 = origin
+    o = B.Scene(port, path, rescale=0.0, translate=(0.0, 0.0, 0.0), method=0, cap=cap)
+    for eye in ((-3.0, -3.0, 10.0), (-3.0, -3.0, 2.5), (0.0, 0.0, 10.0), (1.0, 1.0, 0.5)):
+        cam = A.set_camera(256, 256, eye=eye, facing=(0.0, 0.0, -1.0))
+        a = sc.ctx.render(cam)
+        b = sc.ctx.render(cam, sc.ctx.opts(cull=False))
+        face, t, img = o.trace_primary(256, 256, threads=NTHREADS, eye=eye, facing=(0.0, 0.0, -1.0))
+        assert (a["prim"] == face).all() and same_bits(a["t"], t) and (a["bgrx"] == img).all()
+        assert (b["prim"] == face).all() and same_bits(b["t"], t)
+        assert (face != B.MISS).any()
+    o.close()
+
+
 def test_c5_incoherent_rays(A, port, standin):
     """BASELINE.json configs[4] (sub-sample): random-direction rays through the ray-list entry point."""
     from oracle import bind as B
