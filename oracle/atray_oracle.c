@@ -150,7 +150,14 @@ typedef struct
     or_box aabb;
     OR_VEC(or_node) nodes;
     v3 sky_emission, model_emission; /* app.cpp:91,96 */
+    /* full materials + analytic primitives for the multi-bounce path (material.h:4-9, sphere.h:5-10, plane.h:5-10) */
+    struct or_material { v3 emission, reflection; float scatter; } sky_mat, model_mat;
+    OR_VEC(struct or_sphere { v3 center; float radius; struct or_material m; }) spheres;
+    OR_VEC(struct or_plane { v3 normal; float distance; struct or_material m; }) planes;
 } or_scene;
+typedef struct or_material or_material;
+typedef struct or_sphere or_sphere;
+typedef struct or_plane or_plane;
 
 /* OBJ loader: parse_chunks (OBJ_loader.cpp:32-176) applied to the whole file; chunks are newline-aligned and
  * joined in order (190-227), so one sequential pass yields the same arrays. A '\n' sentinel is written just
@@ -591,6 +598,9 @@ void* or_scene_create(const char* obj_path, int loader_threads, float rescale, f
     or_translate_to(s, c);                          /* app.cpp:72 */
     v3 sky = { 0.3f, 0.4f, 0.5f }, mdl = { 0.4f, 0.2f, 0.2f };
     s->sky_emission = sky; s->model_emission = mdl;
+    v3 sky_r = { 0.2f, 0.3f, 0.4f }, mdl_r = { 0.92f, 0.5f, 0.0f };   /* app.cpp:91,96 */
+    s->sky_mat.emission = sky; s->sky_mat.reflection = sky_r; s->sky_mat.scatter = 0.3f;
+    s->model_mat.emission = mdl; s->model_mat.reflection = mdl_r; s->model_mat.scatter = 0.3f;
     if (or_build_tree(s, method, cap) != 0) { return 0; }
     return s;
 }
@@ -599,7 +609,8 @@ void or_scene_destroy(void* h)
 {
     or_scene* s = h;
     for (size_t i = 0; i < s->nodes.n; i++) free(s->nodes.p[i].prims);
-    free(s->nodes.p); free(s->vertices.p); free(s->normals.p); free(s->tex.p); free(s->faces.p); free(s);
+    free(s->nodes.p); free(s->vertices.p); free(s->normals.p); free(s->tex.p); free(s->faces.p);
+    free(s->spheres.p); free(s->planes.p); free(s);
 }
 
 void or_counts(void* h, unsigned* c)
@@ -838,6 +849,201 @@ void or_render_jitter(void* h, int W, int H, unsigned spp, int bounce, unsigned 
     v3 e = { eye[0], eye[1], eye[2] }, f = { facing[0], facing[1], facing[2] };
     or_set_camera(&a.cm, W, H, e, f, hfov);
     or_parallel(a.s, H, threads, or_jitter_rows, &a);
+}
+
+/* ---- multi-bounce path: get_intersection_data (renderer.cpp:34-160) with spheres and planes, cast_ray (213-262) ---- */
+static or_material or_mat7(const float* m7)
+{
+    or_material m;
+    m.emission.x = m7[0]; m.emission.y = m7[1]; m.emission.z = m7[2];
+    m.reflection.x = m7[3]; m.reflection.y = m7[4]; m.reflection.z = m7[5];
+    m.scatter = m7[6];
+    return m;
+}
+int or_scene_add_sphere(void* h, const float* center, float radius, const float* m7)
+{
+    or_scene* s = h;
+    or_sphere sp;
+    sp.center.x = center[0]; sp.center.y = center[1]; sp.center.z = center[2];
+    sp.radius = radius; sp.m = or_mat7(m7);
+    OR_PUSH(s->spheres, sp);
+    return 0;
+}
+int or_scene_add_plane(void* h, const float* normal, float distance, const float* m7)
+{
+    or_scene* s = h;
+    or_plane pl;
+    v3 n = { normal[0], normal[1], normal[2] };
+    pl.normal = v3_normalize(n);               /* prep_scene, renderer.cpp:267-270 */
+    pl.distance = distance; pl.m = or_mat7(m7);
+    OR_PUSH(s->planes, pl);
+    return 0;
+}
+
+static inline float or_sphere_hit(v3 o, v3 d, const or_sphere* sp) /* get_sphere_ray_intersection, sphere.h:12-39 */
+{
+    v3 p_to_c = v3_sub(o, sp->center);
+    float p_to_c_sqr = v3_mag2(p_to_c);
+    float b = 2 * v3_dot(d, p_to_c);
+    float b_sqr = b * b;
+    float c = p_to_c_sqr - sp->radius * sp->radius;
+    float dmt = b_sqr - (4 * c);
+    if (dmt < 0) return 0;
+    float ta = (-b + sqrtf(dmt)) * 0.5f;        /* sqroot = _mm_sqrt_ss, PL_math.h:352-356: IEEE */
+    float tb = (-b - sqrtf(dmt)) * 0.5f;
+    if (ta <= 0 && tb <= 0) return 0;
+    if (tb > 0) return tb;
+    return ta;
+}
+static inline float or_plane_hit(v3 o, v3 d, const or_plane* pl) /* get_plane_ray_intersection, plane.h:12-22 */
+{
+    float denom = v3_dot(pl->normal, d);
+    if (denom > -OR_TOL && denom < OR_TOL) return 0;
+    return (pl->distance - v3_dot(o, pl->normal)) / denom;
+}
+
+/* kinds: 0 sky, 1 triangle, 2 sphere, 3 plane (ObjectType, renderer.cpp:12-15) */
+typedef struct { int kind; float t; v3 normal; const or_material* mat; uint32_t face; } or_hit;
+
+static void or_intersect_full(const or_scene* s, v3 o, v3 d, or_scratch* sc, or_hit* out, or_counters* ct)
+{
+    float dist = OR_MAX_FLOAT;
+    const or_sphere* near_sphere = 0; const or_plane* near_plane = 0; int near_model = 0;
+    uint32_t face = OR_MISS; float u = 0, v = 0;
+    {
+        or_ray r; r.o = o; r.d = d; or_ray_prepare(&r);
+        uint32_t f = OR_MISS; float bu = 0, bv = 0;
+        float t = or_traverse(s, &r, sc, &f, &bu, &bv, ct);
+        if (t > OR_TOL && t < dist) { dist = t; face = f; u = bu; v = bv; near_model = 1; }      /* :52-57 */
+    }
+    for (size_t i = 0; i < s->spheres.n; i++)                                                     /* :86-96 */
+    {
+        float t = or_sphere_hit(o, d, &s->spheres.p[i]);
+        if (t > OR_TOL && t < dist) { dist = t; near_sphere = &s->spheres.p[i]; }
+    }
+    for (size_t i = 0; i < s->planes.n; i++)                                                      /* :97-107 */
+    {
+        float t = or_plane_hit(o, d, &s->planes.p[i]);
+        if (t > OR_TOL && t < dist) { near_plane = &s->planes.p[i]; dist = t; }
+    }
+    out->t = dist; out->face = OR_MISS;
+    v3 zero = { 0, 0, 0 };
+    out->normal = zero;
+    if (near_plane) { out->kind = 3; out->normal = near_plane->normal; out->mat = &near_plane->m; }             /* :111-116 */
+    else if (near_sphere)                                                                                     /* :117-122 */
+    {
+        out->kind = 2;
+        out->normal = v3_sub(v3_add(o, v3_mul(d, dist)), near_sphere->center);   /* ray.at(t) - center, ray.h:11-14 */
+        out->mat = &near_sphere->m;
+    }
+    else if (near_model)                                                                                      /* :124-148 */
+    {
+        out->kind = 1; out->face = face;
+        const or_face* fc = &s->faces.p[face];
+        if (s->normals.n > 0)
+        {
+            v3 na = s->normals.p[fc->vn[0]], nb = s->normals.p[fc->vn[1]], nc = s->normals.p[fc->vn[2]];
+            out->normal = v3_add(v3_add(v3_mul(na, 1 - u - v), v3_mul(nb, u)), v3_mul(nc, v));
+        }
+        else
+        {
+            v3 ab = v3_sub(s->vertices.p[fc->v[0]], s->vertices.p[fc->v[1]]);
+            v3 ac = v3_sub(s->vertices.p[fc->v[0]], s->vertices.p[fc->v[2]]);
+            out->normal = v3_cross(ab, ac);
+        }
+        out->mat = &s->model_mat;
+    }
+    else { out->kind = 0; out->mat = &s->sky_mat; }                                                           /* :149-155 */
+    out->normal = v3_normalize(out->normal);                                                                  /* :157 */
+}
+
+static inline v3 v3_had(v3 a, v3 b) { v3 r = { a.x * b.x, a.y * b.y, a.z * b.z }; return r; } /* PL_math.h:419 */
+
+static v3 or_cast_ray(const or_scene* s, v3 o, v3 d, int bounce_limit, long long* casts, or_rng* rng, or_scratch* sc, or_counters* ct)
+{
+    v3 color = { 0, 0, 0 }, weight = { 1.0f, 1.0f, 1.0f };
+    int i;
+    for (i = 0; i < bounce_limit; i++)
+    {
+        or_hit id;
+        or_intersect_full(s, o, d, sc, &id, ct);
+        if (id.kind == 0) { color = v3_add(color, v3_had(weight, id.mat->emission)); break; }   /* :224-228 */
+        float attenuation = v3_dot(v3_neg(d), id.normal);
+        if (attenuation < 0) { id.normal = v3_neg(id.normal); attenuation = 0; }
+        v3 pure = v3_sub(d, v3_mul(id.normal, 2 * v3_dot(d, id.normal)));                       /* :238-243 */
+        pure = v3_normalize(pure);
+        v3 rb;
+        rb.x = or_rand_bi(rng); rb.y = or_rand_bi(rng); rb.z = or_rand_bi(rng);                /* :246, braces: left to right */
+        rb = v3_add(rb, id.normal);
+        rb = v3_normalize(rb);
+        o = v3_add(o, v3_mul(d, id.t));                                                         /* :251 */
+        d = v3_add(v3_mul(v3_sub(pure, rb), id.mat->scatter), rb);                              /* lerp, PL_math.h:439-442 */
+        d = v3_normalize(d);
+        color = v3_add(color, v3_had(weight, id.mat->emission));                                /* :257-258 */
+        weight = v3_had(weight, v3_mul(id.mat->reflection, attenuation));
+    }
+    *casts += i;
+    return color;
+}
+
+typedef struct { const or_scene* s; or_camera_t cm; unsigned spp; int aa, bounce; uint64_t seed; unsigned* bgrx; float* t;
+                 unsigned* prim; unsigned* kind; long long casts; pthread_mutex_t mu; } or_path_arg;
+static void or_path_rows(void* a_, int y0, int y1, or_scratch* sc, or_counters* ct)
+{
+    or_path_arg* a = a_;
+    const or_camera_t* cm = &a->cm;
+    long long casts = 0;
+    for (int y = y0; y < y1; y++)
+    {
+        float film_y = -1.0f + 2.0f * ((float)y / (float)cm->H);
+        for (int x = 0; x < cm->W; x++)
+        {
+            uint64_t p = (uint64_t)y * cm->W + x;
+            or_rng rng = { or_splitmix64(a->seed ^ p), 2 * p + 1 };
+            float film_x = (-1.0f + 2.0f * ((float)x / (float)cm->W)) * cm->h_fov * cm->aspect;
+            v3 col = { 0, 0, 0 };
+            v3 d = { 0, 0, 0 };
+            if (a->aa)
+                for (unsigned i = 0; i < a->spp; i++)                                           /* renderer.cpp:336-347 */
+                {
+                    float x_off = or_rand_bi(&rng) * cm->hpw + film_x;
+                    float y_off = or_rand_bi(&rng) * cm->hph + film_y;
+                    d = or_pixel_dir(cm, x_off, y_off);
+                    col = v3_add(col, or_cast_ray(a->s, cm->eye, d, a->bounce, &casts, &rng, sc, ct));
+                }
+            else
+            {
+                d = or_pixel_dir(cm, film_x, film_y);                                          /* :349-356 */
+                for (unsigned i = 0; i < a->spp; i++) col = v3_add(col, or_cast_ray(a->s, cm->eye, d, a->bounce, &casts, &rng, sc, ct));
+            }
+            col = v3_div(col, (float)a->spp);
+            a->bgrx[p] = or_pack(col);
+            if (a->t || a->prim || a->kind)
+            {
+                or_hit id;
+                or_intersect_full(a->s, cm->eye, d, sc, &id, ct);
+                if (a->t) a->t[p] = id.t;
+                if (a->prim) a->prim[p] = id.kind == 1 ? id.face : OR_MISS;
+                if (a->kind) a->kind[p] = (unsigned)id.kind;
+            }
+        }
+    }
+    pthread_mutex_lock(&a->mu);
+    a->casts += casts;
+    pthread_mutex_unlock(&a->mu);
+}
+void or_render_path(void* h, int W, int H, unsigned spp, int aa, int bounce, unsigned long long seed, const float* eye,
+                    const float* facing, float hfov, int threads, unsigned* bgrx, float* t, unsigned* prim, unsigned* kind,
+                    long long* casts_out)
+{
+    or_path_arg a;
+    memset(&a, 0, sizeof a);
+    a.s = h; a.spp = spp; a.aa = aa; a.bounce = bounce; a.seed = seed; a.bgrx = bgrx; a.t = t; a.prim = prim; a.kind = kind;
+    pthread_mutex_init(&a.mu, 0);
+    v3 e = { eye[0], eye[1], eye[2] }, f = { facing[0], facing[1], facing[2] };
+    or_set_camera(&a.cm, W, H, e, f, hfov);
+    or_parallel(a.s, H, threads, or_path_rows, &a);
+    if (casts_out) *casts_out = a.casts;
 }
 
 void or_pcg32(unsigned long long state, unsigned long long stream, int n, unsigned* out)

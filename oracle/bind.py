@@ -45,6 +45,14 @@ class Backend:
         self.render_jitter.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_uint, C.c_int, C.c_ulonglong, C.c_void_p,
                                        C.c_void_p, C.c_float, C.c_int, C.c_void_p, C.c_void_p]
         self.pcg32 = g("pcg32"); self.pcg32.argtypes = [C.c_ulonglong, C.c_ulonglong, C.c_int, C.c_void_p]
+        self.scene_add_sphere = g("scene_add_sphere")
+        self.scene_add_sphere.argtypes = [C.c_void_p, C.c_void_p, C.c_float, C.c_void_p]
+        self.scene_add_plane = g("scene_add_plane")
+        self.scene_add_plane.argtypes = [C.c_void_p, C.c_void_p, C.c_float, C.c_void_p]
+        self.render_path = g("render_path")
+        self.render_path.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_uint, C.c_int, C.c_int, C.c_ulonglong, C.c_void_p,
+                                     C.c_void_p, C.c_float, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                     C.c_void_p]
         self.render = None
         self.trace_primary_ex = None
         if prefix == "ref_":
@@ -179,6 +187,33 @@ class Scene:
         e, f = _f3(eye), _f3(facing)
         self.b.render_jitter(self.h, W, H, spp, bounce, seed, _p(e), _p(f), hfov, threads, _p(img), _p(hits))
         return img, hits
+
+
+    # ---- multi-bounce path: spheres, planes, cast_ray at any bounce_limit -------------------
+    def add_sphere(self, center, radius, material):
+        """material = (emission rgb, reflection rgb, scatter) as material.h:4-9."""
+        c = _f3(center)
+        m = np.array([*material[0], *material[1], material[2]], np.float32)
+        assert self.b.scene_add_sphere(self.h, _p(c), radius, _p(m)) == 0
+
+    def add_plane(self, normal, distance, material):
+        n = _f3(normal)
+        m = np.array([*material[0], *material[1], material[2]], np.float32)
+        assert self.b.scene_add_plane(self.h, _p(n), distance, _p(m)) == 0
+
+    def render_path(self, W, H, spp, bounce, seed, aa=0, threads=1, eye=DEFAULT_EYE, facing=DEFAULT_FACING, hfov=DEFAULT_HFOV):
+        """Pixel loop + cast_ray with the per-pixel stream {splitmix64(seed ^ p), 2p+1}. Returns bgrx, t, prim, kind
+        (nearest hit of the last sample's primary ray; kind 0 sky / 1 triangle / 2 sphere / 3 plane) and the total
+        ray_casts (sum of bounce iterations, renderer.cpp:260)."""
+        img = np.zeros((H, W), np.uint32)
+        t = np.zeros((H, W), np.float32)
+        prim = np.zeros((H, W), np.uint32)
+        kind = np.zeros((H, W), np.uint32)
+        casts = C.c_longlong(0)
+        e, f = _f3(eye), _f3(facing)
+        self.b.render_path(self.h, W, H, spp, aa, bounce, seed, _p(e), _p(f), hfov, threads, _p(img), _p(t), _p(prim),
+                           _p(kind), C.byref(casts))
+        return img, t, prim, kind, casts.value
 
 
 def camera(backend, W, H, eye=DEFAULT_EYE, facing=DEFAULT_FACING, hfov=DEFAULT_HFOV):

@@ -29,6 +29,10 @@ struct RefScene
 	std::vector<FaceVertices> faces_vertices;
 	std::vector<FaceData> faces_data;
 	AABB model_aabb;
+	// materials of spheres/planes live here (Sphere::material / Plane::material are plain pointers, sphere.h:5-10,
+	// plane.h:5-10); scene.materials must not grow after model.data.material was taken (DBuffer reallocates)
+	Material extra_materials[256];
+	int n_extra = 0;
 };
 
 static void make_pool(ThreadPool& tp, int n)
@@ -348,6 +352,102 @@ void ref_render_jitter(void* h, int W, int H, unsigned spp, int bounce, unsigned
 			}
 		}
 	});
+}
+
+// Scene primitives as app.cpp:111-129 constructs them (the adds are commented out upstream, app.cpp:139-142).
+// m7 = emission rgb, reflection rgb, scatter (material.h:4-9). Plane normals are normalised as prep_scene does
+// (renderer.cpp:267-270).
+int ref_scene_add_sphere(void* h, const float* center, float radius, const float* m7)
+{
+	RefScene* rs = (RefScene*)h;
+	if (rs->n_extra >= 256) return -1;
+	Material* m = &rs->extra_materials[rs->n_extra++];
+	*m = { {m7[0],m7[1],m7[2]}, {m7[3],m7[4],m7[5]}, m7[6] };
+	Sphere sp;
+	sp.center = { center[0], center[1], center[2] };
+	sp.radius = radius;
+	sp.material = m;
+	rs->scene.spheres.add(sp);
+	return 0;
+}
+int ref_scene_add_plane(void* h, const float* normal, float distance, const float* m7)
+{
+	RefScene* rs = (RefScene*)h;
+	if (rs->n_extra >= 256) return -1;
+	Material* m = &rs->extra_materials[rs->n_extra++];
+	*m = { {m7[0],m7[1],m7[2]}, {m7[3],m7[4],m7[5]}, m7[6] };
+	Plane pl;
+	pl.normal = { normal[0], normal[1], normal[2] };
+	normalize(pl.normal);
+	pl.distance = distance;
+	pl.material = m;
+	rs->scene.planes.add(pl);
+	return 0;
+}
+
+// The reference's pixel loop (renderer.cpp:314-365) with its own cast_ray (213-262) at any bounce_limit, AA on or
+// off, and the harness-defined per-pixel stream of ref_render_jitter (the reference seeds per thread from rdtsc).
+// AA off: one SetRay, cast_ray repeated spp times on the same ray (349-356); the stream keeps running across samples.
+// t_out / kind_out / prim_out describe the nearest hit of the LAST sample's primary ray (get_intersection_data on it
+// once more; it draws no random numbers): kind 0 = sky, 1 = triangle, 2 = sphere, 3 = plane.
+void ref_render_path(void* h, int W, int H, unsigned spp, int aa, int bounce, unsigned long long seed, const float* eye,
+                     const float* facing, float hfov, int threads, unsigned* bgrx_out, float* t_out, unsigned* prim_out,
+                     unsigned* kind_out, long long* casts_out)
+{
+	RefScene* rs = (RefScene*)h;
+	Camera cm;
+	fill_camera(cm, W, H, aa, spp, bounce, eye, facing, hfov);
+	std::vector<long long> casts_per_thread(threads < 1 ? 1 : threads, 0);
+	parallel_rows(H, threads, [&](int y0, int y1, int tid) {
+		TraceScratch sc(rs->max_nodes);
+		for (int32 y = y0; y < y1; y++)
+		{
+			f32 film_y = -1.0f + 2.0f * ((f32)y / (f32)cm.render_settings.resolution.y);
+			for (int32 x = 0; x < W; x++)
+			{
+				uint64 p = (uint64)y * W + x;
+				sc.rng.state = splitmix64(seed ^ p);
+				sc.rng.stream = 2 * p + 1;
+				f32 film_x = (-1.0f + 2.0f * ((f32)x / (f32)cm.render_settings.resolution.x)) * cm.h_fov * cm.aspect_ratio;
+				vec3f flt_pixel_color;
+				Ray ray = {};
+				int64 casts = 0;
+				if (aa)
+				{
+					for (uint32 i = 0; i < spp; i++)
+					{
+						f32 x_off = rand_bi(sc.tools.rng_stream) * cm.half_pixel_width + film_x;
+						f32 y_off = rand_bi(sc.tools.rng_stream) * cm.half_pixel_height + film_y;
+						vec3f pixel_pos = cm.frame_center + (cm.camera_x * x_off) + (cm.camera_y * y_off);
+						SetRay(ray, cm.eye, pixel_pos);
+						flt_pixel_color += cast_ray(ray, rs->scene, bounce, casts, sc.tools);
+					}
+				}
+				else
+				{
+					vec3f pixel_pos = cm.frame_center + (cm.camera_x * film_x) + (cm.camera_y * film_y);
+					SetRay(ray, cm.eye, pixel_pos);
+					for (uint32 i = 0; i < spp; i++)
+						flt_pixel_color += cast_ray(ray, rs->scene, bounce, casts, sc.tools);
+				}
+				casts_per_thread[tid] += casts;
+				flt_pixel_color = flt_pixel_color / (f32)spp;
+				bgrx_out[p] = pack_bgrx(flt_pixel_color);
+				if (t_out || prim_out || kind_out)
+				{
+					IntersectionData id;
+					get_intersection_data(ray, rs->scene, id, sc.tools);
+					unsigned kind = id.type == ObjectType::TRIANGLE ? 1u : id.type == ObjectType::SPHERE ? 2u : id.type == ObjectType::PLANE ? 3u : 0u;
+					if (t_out) t_out[p] = id.distance_at_intersection;
+					if (prim_out) prim_out[p] = kind == 1u ? id.tid.face_index : REF_MISS;
+					if (kind_out) kind_out[p] = kind;
+				}
+			}
+		}
+	});
+	long long total = 0;
+	for (long long c : casts_per_thread) total += c;
+	if (casts_out) *casts_out = total;
 }
 
 // PCG32 known-answer helper: draws n values of random_u32 (PL_math.h:506-516).
