@@ -47,7 +47,28 @@ inline void prep_scene(Scene& scene, uint32& kd_tree_max_nodes)
     static_assert(sizeof(Material) == sizeof(AtrayMaterial), "Material layout");
     std::memcpy(&sky, &scene.materials[0], sizeof sky);
     std::memcpy(&mat, m.data.material ? m.data.material : &scene.materials[0], sizeof mat);
-    atray_scene_upload(scene.gpu, m.data.handle, &sky, &mat);
+    if (atray_scene_upload(scene.gpu, m.data.handle, &sky, &mat) != ATRAY_OK) return;
+    // spheres and planes (scene.h:13-24; prep_scene normalises the plane normals, renderer.cpp:267-270 — done by the library)
+    if (scene.spheres.length > 0 || scene.planes.length > 0)
+    {
+        AtraySphere* sp = (AtraySphere*)std::calloc(scene.spheres.length > 0 ? scene.spheres.length : 1, sizeof(AtraySphere));
+        AtrayPlane* pl = (AtrayPlane*)std::calloc(scene.planes.length > 0 ? scene.planes.length : 1, sizeof(AtrayPlane));
+        for (int32 i = 0; i < scene.spheres.length; i++)
+        {
+            std::memcpy(sp[i].center, &scene.spheres[i].center, 12);
+            sp[i].radius = scene.spheres[i].radius;
+            std::memcpy(&sp[i].material, scene.spheres[i].material ? scene.spheres[i].material : &scene.materials[0], sizeof(AtrayMaterial));
+        }
+        for (int32 i = 0; i < scene.planes.length; i++)
+        {
+            std::memcpy(pl[i].normal, &scene.planes[i].normal, 12);
+            pl[i].distance = scene.planes[i].distance;
+            std::memcpy(&pl[i].material, scene.planes[i].material ? scene.planes[i].material : &scene.materials[0], sizeof(AtrayMaterial));
+        }
+        atray_scene_set_primitives(scene.gpu, sp, (uint32_t)scene.spheres.length, pl, (uint32_t)scene.planes.length);
+        std::free(sp);
+        std::free(pl);
+    }
 }
 
 // renderer.cpp:403-455: returns immediately. twq.jobs is filled with one band-shaped job per 8 scanlines (inclusive
@@ -90,7 +111,12 @@ inline b32 wait_for_render_from_camera_to_finish(RenderInfo& info, ThreadPool& t
     }
     if (r < 0) { info.last_error = r; return FALSE; }
     info.twq.jobs_done = info.twq.jobs.size;
-    if (info.hit_prim && info.camera->render_settings.samples_per_pixel == 1)
+    if (info.camera->render_settings.bounce_limit != 1 || info.scene->spheres.length > 0 || info.scene->planes.length > 0)
+    {
+        uint64_t casts = 0;   // sum of cast_ray's bounce iterations (renderer.cpp:260, 467-470)
+        if (atray_last_ray_casts(info.scene->gpu, &casts) == ATRAY_OK) info.total_ray_casts += (int64)casts;
+    }
+    else if (info.hit_prim && info.camera->render_settings.samples_per_pixel == 1)
     {
         // ray_casts = bounce iterations that hit geometry (renderer.cpp:222-231,260), per band
         const int32 W = info.camera_tex->bmb.width;

@@ -36,6 +36,14 @@ class Material(C.Structure):
     _fields_ = [("emission_color", C.c_float * 3), ("reflection_color", C.c_float * 3), ("scatter", C.c_float)]
 
 
+class Sphere(C.Structure):   # AtraySphere (sphere.h:5-10 with the material by value)
+    _fields_ = [("center", C.c_float * 3), ("radius", C.c_float), ("material", Material)]
+
+
+class Plane(C.Structure):    # AtrayPlane (plane.h:5-10)
+    _fields_ = [("normal", C.c_float * 3), ("distance", C.c_float), ("material", Material)]
+
+
 class CameraStruct(C.Structure):
     _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("anti_aliasing", C.c_int32),
                 ("samples_per_pixel", C.c_uint32), ("bounce_limit", C.c_int32), ("aspect_ratio", C.c_float),
@@ -90,6 +98,8 @@ _SIGS = {
     "atray_device_count": [C.POINTER(_i)],
     "atray_ctx_create": [_i, C.POINTER(_vp)],
     "atray_scene_upload": [_vp, _vp, C.POINTER(Material), C.POINTER(Material)],
+    "atray_scene_set_primitives": [_vp, _vp, _u, _vp, _u],
+    "atray_last_ray_casts": [_vp, C.POINTER(_u64)],
     "atray_render_begin": [_vp, C.POINTER(CameraStruct), C.POINTER(RenderOpts), C.POINTER(Frame)],
     "atray_render_poll": [_vp, _u],
     "atray_render_progress": [_vp, C.POINTER(_i), C.POINTER(_i)],

@@ -33,6 +33,11 @@ struct atray_ctx
     DevView view{};              // per-frame film rectangles + tile stamps (k_view_bounds)
     size_t stamp_cap = 0;        // tiles the stamp buffer holds
     uint32_t frame_seq = 0;      // stamp value of the last frame (0 = buffer freshly cleared)
+    float4* d_fnorm = nullptr;       // per-face normal sources of the multi-bounce path
+    float4* d_spheres = nullptr;     // analytic primitives (atray_scene_set_primitives)
+    float4* d_planes = nullptr;
+    unsigned long long* d_casts = nullptr;   // ray_casts of the last path frame (renderer.cpp:260)
+    bool casts_valid = false;
     unsigned int* d_tile_counter = nullptr;
     DevCounters* d_counters = nullptr;
     bool counters_valid = false;
@@ -246,6 +251,7 @@ int atray_ctx_create(int device, atray_ctx** out)
     cudaError_t e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaMalloc(&c->d_tile_counter, sizeof(unsigned int));
     if (e == cudaSuccess) e = cudaMalloc(&c->d_counters, sizeof(DevCounters));
+    if (e == cudaSuccess) e = cudaMalloc(&c->d_casts, sizeof(unsigned long long));
     if (e == cudaSuccess) e = cudaEventCreate(&c->ev_k0);
     if (e == cudaSuccess) e = cudaEventCreate(&c->ev_k1);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_done, cudaEventDisableTiming);
@@ -280,7 +286,10 @@ static void free_scene(atray_ctx* c)
     c->view.tri_rect = c->view.pkt_rect = c->view.node_rect = nullptr;
     c->d_inner_order = c->d_level_start = nullptr;
     c->d_nodes = c->d_tris = nullptr;
+    cudaFree(c->d_fnorm); cudaFree(c->d_spheres); cudaFree(c->d_planes);
+    c->d_fnorm = c->d_spheres = c->d_planes = nullptr;
     c->scratch = DevScratch{};
+    c->scene = DevScene{};
     c->has_scene = false;
 }
 
@@ -290,7 +299,7 @@ void atray_ctx_destroy(atray_ctx* c)
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     free_scene(c);
-    cudaFree(c->d_tile_counter); cudaFree(c->d_counters);
+    cudaFree(c->d_tile_counter); cudaFree(c->d_counters); cudaFree(c->d_casts);
     cudaFree(c->view.stamps); cudaFree(c->view.all_flag); cudaFree(c->view.busy_list); cudaFree(c->view.busy_count);
     cudaFree(c->d_bgrx); cudaFree(c->d_t); cudaFree(c->d_prim);
     cudaFreeHost(c->h_bgrx); cudaFreeHost(c->h_t); cudaFreeHost(c->h_prim);
@@ -343,7 +352,94 @@ int atray_scene_upload(atray_ctx* c, const atray_model* m, const AtrayMaterial* 
     c->scene.root_is_leaf = m->m.tree[0].children_start == 0 ? 1u : 0u;
     std::memcpy(c->scene.sky, sky->emission_color, 12);
     std::memcpy(c->scene.mdl, mat->emission_color, 12);
+    std::memcpy(c->scene.mdl_refl, mat->reflection_color, 12);
+    c->scene.mdl_scatter = mat->scatter;
+    {
+        // normal sources of get_intersection_data (renderer.cpp:124-148). With vertex normals: the face's three normals
+        // (interpolated per hit). Without: cross(v0 - v1, v0 - v2), the same f32 operations the reference runs per hit.
+        const HostModel& hm = m->m;
+        const bool smooth = !hm.normals.empty();
+        std::vector<float> fn(size_t(hm.faces.size()) * (smooth ? 12 : 4) + 4, 0.f);
+        for (size_t i = 0; i < hm.faces.size(); ++i)
+        {
+            const Face& f = hm.faces[i];
+            if (smooth)
+                for (int k = 0; k < 3; ++k)
+                {
+                    const int32_t ni = f.vn[k];
+                    if (ni < 0 || size_t(ni) >= hm.normals.size()) continue;   // the reference would read out of bounds
+                    float* q = &fn[(3 * i + k) * 4];
+                    q[0] = hm.normals[ni].x; q[1] = hm.normals[ni].y; q[2] = hm.normals[ni].z;
+                }
+            else
+            {
+                const Vec3 a = hm.vertices[f.v[0]], b = hm.vertices[f.v[1]], cc = hm.vertices[f.v[2]];
+                const Vec3 ab = {a.x - b.x, a.y - b.y, a.z - b.z}, ac = {a.x - cc.x, a.y - cc.y, a.z - cc.z};
+                float* q = &fn[i * 4];
+                q[0] = ab.y * ac.z - ab.z * ac.y; q[1] = ab.z * ac.x - ab.x * ac.z; q[2] = ab.x * ac.y - ab.y * ac.x;
+            }
+        }
+        CU(cudaMalloc(&c->d_fnorm, fn.size() * 4));
+        CU(cudaMemcpy(c->d_fnorm, fn.data(), fn.size() * 4, cudaMemcpyHostToDevice));
+        c->scene.fnorm = c->d_fnorm;
+        c->scene.smooth = smooth ? 1u : 0u;
+    }
     c->has_scene = true;
+    return ATRAY_OK;
+}
+
+int atray_scene_set_primitives(atray_ctx* c, const AtraySphere* spheres, uint32_t n_spheres, const AtrayPlane* planes,
+                               uint32_t n_planes)
+{
+    if (!c || (n_spheres && !spheres) || (n_planes && !planes)) return fail(ATRAY_EINVAL, "null argument");
+    if (!c->has_scene) return fail(ATRAY_ESTATE, "set_primitives before scene_upload");
+    if (c->in_flight) return fail(ATRAY_ESTATE, "render in flight");
+    CU(cudaSetDevice(c->device));
+    CU(cudaStreamSynchronize(c->stream));
+    cudaFree(c->d_spheres); cudaFree(c->d_planes);
+    c->d_spheres = c->d_planes = nullptr;
+    c->scene.spheres = c->scene.planes = nullptr;
+    c->scene.n_spheres = c->scene.n_planes = 0;
+    auto pack = [](std::vector<float>& v, const float* head3, float w, const AtrayMaterial& m) {
+        const float rec[12] = {head3[0], head3[1], head3[2], w, m.emission_color[0], m.emission_color[1], m.emission_color[2],
+                               m.scatter, m.reflection_color[0], m.reflection_color[1], m.reflection_color[2], 0.f};
+        v.insert(v.end(), rec, rec + 12);
+    };
+    if (n_spheres)
+    {
+        std::vector<float> v;
+        for (uint32_t i = 0; i < n_spheres; ++i) pack(v, spheres[i].center, spheres[i].radius, spheres[i].material);
+        CU(cudaMalloc(&c->d_spheres, v.size() * 4));
+        CU(cudaMemcpy(c->d_spheres, v.data(), v.size() * 4, cudaMemcpyHostToDevice));
+    }
+    if (n_planes)
+    {
+        std::vector<float> v;
+        for (uint32_t i = 0; i < n_planes; ++i)
+        {
+            // prep_scene normalises every plane normal (renderer.cpp:267-270): n * (1/sqrt((x*x + y*y) + z*z))
+            const float* n = planes[i].normal;
+            const float inv = 1.0f / std::sqrt((n[0] * n[0]) + (n[1] * n[1]) + (n[2] * n[2]));
+            const float nn[3] = {n[0] * inv, n[1] * inv, n[2] * inv};
+            pack(v, nn, planes[i].distance, planes[i].material);
+        }
+        CU(cudaMalloc(&c->d_planes, v.size() * 4));
+        CU(cudaMemcpy(c->d_planes, v.data(), v.size() * 4, cudaMemcpyHostToDevice));
+    }
+    c->scene.spheres = c->d_spheres; c->scene.planes = c->d_planes;
+    c->scene.n_spheres = n_spheres; c->scene.n_planes = n_planes;
+    return ATRAY_OK;
+}
+
+int atray_last_ray_casts(atray_ctx* c, uint64_t* ray_casts)
+{
+    if (!c || !ray_casts) return fail(ATRAY_EINVAL, "null argument");
+    if (!c->casts_valid) return fail(ATRAY_ESTATE, "no multi-bounce frame has been rendered");
+    CU(cudaSetDevice(c->device));
+    unsigned long long v = 0;
+    CU(cudaMemcpyAsync(&v, c->d_casts, sizeof v, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    *ray_casts = v;
     return ATRAY_OK;
 }
 
@@ -352,7 +448,7 @@ static int check_render_args(atray_ctx* c, const AtrayCamera* cam, const AtrayRe
     if (!c || !cam || !o || !out) return fail(ATRAY_EINVAL, "null argument");
     if (!c->has_scene) return fail(ATRAY_ESTATE, "render before scene_upload");
     if (cam->width <= 0 || cam->height <= 0 || cam->samples_per_pixel == 0) return fail(ATRAY_EINVAL, "bad camera");
-    if (cam->bounce_limit != 1) return fail(ATRAY_EINVAL, "this path implements bounce_limit = 1 (primary rays)");
+    if (cam->bounce_limit < 1 || cam->bounce_limit > 64) return fail(ATRAY_EINVAL, "bounce_limit must be in 1..64");
     if (o->part.world < 1 || o->part.rank < 0 || o->part.rank >= o->part.world) return fail(ATRAY_EINVAL, "bad partition");
     if (o->part.band_rows < 4 || (o->part.band_rows & 3)) return fail(ATRAY_EINVAL, "band_rows must be a positive multiple of 4");
     return ATRAY_OK;
@@ -365,6 +461,7 @@ static DevCamera to_dev(const AtrayCamera* cam)
     d.aspect = cam->aspect_ratio; d.h_fov = cam->h_fov; d.hpw = cam->half_pixel_width; d.hph = cam->half_pixel_height;
     std::memcpy(d.eye, cam->eye, 12); std::memcpy(d.fc, cam->frame_center, 12);
     std::memcpy(d.cx, cam->camera_x, 12); std::memcpy(d.cy, cam->camera_y, 12);
+    d.bounce = cam->bounce_limit;
     return d;
 }
 
@@ -445,6 +542,17 @@ static int enqueue_render(atray_ctx* c, const AtrayCamera* cam, const AtrayRende
         c->counters_valid = true;
     }
     DevPartition p{o->part.rank, o->part.world, o->part.band_rows};
+    if (cam->bounce_limit != 1 || c->scene.n_spheres || c->scene.n_planes)
+    {
+        // multi-bounce / analytic primitives: the full get_intersection_data + cast_ray kernel
+        CU(cudaEventRecord(c->ev_k0, c->stream));
+        CU(launch_path(c->scene, to_dev(cam), p, out, c->scratch, c->d_tile_counter, c->d_casts, o->fp_mode == ATRAY_FP_FAST,
+                       o->jitter_seed, c->cfg, c->stream));
+        CU(cudaEventRecord(c->ev_k1, c->stream));
+        c->have_kernel_time = true;
+        c->casts_valid = true;
+        return ATRAY_OK;
+    }
     ViewParams vp = make_view_params(cam);
     const bool cull = !(o->flags & ATRAY_RENDER_NO_CULL) && vp.valid;
     if (cull)

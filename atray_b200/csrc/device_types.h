@@ -19,6 +19,14 @@ struct DevScene
     uint32_t root_is_leaf;
     float sky[3];          // materials[0].emission_color (renderer.cpp:152, 226)
     float mdl[3];          // model material emission_color (renderer.cpp:258)
+    // ---- multi-bounce path (k_path): full materials, per-face normal sources, analytic primitives -----------------
+    float mdl_refl[3];     // model material reflection_color / scatter (material.h:4-9)
+    float mdl_scatter;
+    const float4* fnorm;   // smooth: 3 float4 per face = the face's vertex normals (renderer.cpp:128-137);
+    uint32_t smooth;       // flat: 1 float4 per face = cross(v0 - v1, v0 - v2) precomputed in f32 (renderer.cpp:141-146)
+    const float4* spheres; // 3 float4 per sphere: {center, radius} {emission, scatter} {reflection, 0}  (sphere.h:5-10)
+    const float4* planes;  // 3 float4 per plane : {normal, distance} {emission, scatter} {reflection, 0} (plane.h:5-10)
+    uint32_t n_spheres, n_planes;
 };
 
 struct DevCamera
@@ -28,6 +36,7 @@ struct DevCamera
     uint32_t spp;
     float aspect, h_fov, hpw, hph;
     float eye[3], fc[3], cx[3], cy[3];
+    int32_t bounce;        // RenderSettings.bounce_limit (settings.h:4-10)
 };
 
 struct DevPartition { int32_t rank, world, band_rows; };
@@ -95,6 +104,10 @@ cudaError_t launch_render_culled(const DevScene& sc, const DevCamera& cam, const
 // local tile count of a rank and the slab table for `n_slabs` (clamped to the number of local bands)
 DevSlabs make_slabs(const DevCamera& cam, const DevPartition& part, int n_slabs);
 cudaError_t launch_slabs_final(const DevView& view, const DevSlabs& slabs, cudaStream_t stream);
+// K3: pixel loop + cast_ray at any bounce_limit with spheres/planes (renderer.cpp:34-160, 213-262, 314-365)
+cudaError_t launch_path(const DevScene& sc, const DevCamera& cam, const DevPartition& part, const DevOut& out,
+                        const DevScratch& scratch, unsigned int* tile_counter, unsigned long long* casts, int fp_fast,
+                        unsigned long long seed, LaunchCfg cfg, cudaStream_t stream);
 cudaError_t launch_trace(const DevScene& sc, const float* rays, unsigned long long n, uint32_t* prim, float* t,
                          const DevScratch& scratch, unsigned int* tile_counter, DevCounters* counters, int fp_fast,
                          LaunchCfg cfg, cudaStream_t stream);

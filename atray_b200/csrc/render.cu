@@ -148,9 +148,10 @@ __device__ bool collect_leaves(const float4* __restrict__ nodes, const RayL& r, 
 
 // ---- phase 2: warp-cooperative scan of ONE ray's leaf list (kd_tree.cpp:437-462). All 32 lanes call this with the
 // same `src` lane; the ray and the list entries are broadcast from that lane. Lane `src` receives the result.
-template <bool STRICT, bool COUNT>
+template <bool STRICT, bool COUNT, bool UV = false>
 __device__ __forceinline__ void scan_ray_leaves(const DevScene& sc, int lane, int src, const RayL& mine, const uint2* my_list,
-                                                int my_nleaf, float& out_t, uint32_t& out_face, WorkCount& wc)
+                                                int my_nleaf, float& out_t, uint32_t& out_face, WorkCount& wc,
+                                                float* out_u = nullptr, float* out_v = nullptr)
 {
     typedef Fp<STRICT> F;
     const float ox = __shfl_sync(FULL_MASK, mine.ox, src), oy = __shfl_sync(FULL_MASK, mine.oy, src),
@@ -167,6 +168,7 @@ __device__ __forceinline__ void scan_ray_leaves(const DevScene& sc, int lane, in
         const uint32_t cnt = (uint32_t)__float_as_int(__ldg(&sc.nodes[2 * node + 1]).w);
         if (COUNT && lane == src) wc.scanned++;
         float bt = kMaxFloat;
+        float bu = 0.0f, bv = 0.0f;  // barycentrics of the best hit (TriangleIntersectionData.u/v), UV only
         uint32_t bpos = 0xffffffffu, bface = 0xffffffffu;
         const uint32_t padded = (cnt + 7u) & ~7u;  // slots of this leaf (packets of 8)
         for (uint32_t base = 0; base < cnt; base += 32)
@@ -201,6 +203,7 @@ __device__ __forceinline__ void scan_ray_leaves(const DevScene& sc, int lane, in
                 bt = t;
                 bpos = __float_as_uint(AB.w);  // position in the reference's leaf order (records are Morton-sorted)
                 bface = __float_as_uint(A.w);
+                if (UV) { bu = u; bv = v; }
             }
         }
         // sequential strict-< scan ≡ lexicographic arg-min over (t, slot)
@@ -210,21 +213,23 @@ __device__ __forceinline__ void scan_ray_leaves(const DevScene& sc, int lane, in
             const float ot = __shfl_xor_sync(FULL_MASK, bt, off);
             const uint32_t op = __shfl_xor_sync(FULL_MASK, bpos, off);
             const uint32_t of = __shfl_xor_sync(FULL_MASK, bface, off);
-            if (ot < bt || (ot == bt && op < bpos)) { bt = ot; bpos = op; bface = of; }
+            float ou = 0.0f, ov = 0.0f;
+            if (UV) { ou = __shfl_xor_sync(FULL_MASK, bu, off); ov = __shfl_xor_sync(FULL_MASK, bv, off); }
+            if (ot < bt || (ot == bt && op < bpos)) { bt = ot; bpos = op; bface = of; if (UV) { bu = ou; bv = ov; } }
         }
         if (bt < kMaxFloat)  // this leaf produced a hit → stop (kd_tree.cpp:457-460)
         {
-            if (lane == src) { out_t = bt; out_face = bface; }
+            if (lane == src) { out_t = bt; out_face = bface; if (UV) { *out_u = bu; *out_v = bv; } }
             break;
         }
     }
 }
 
 // ---- one warp traces up to 32 rays (one per lane). Result: t (MAX_FLOAT on miss) and face (MISS) per lane.
-template <bool STRICT, bool COUNT>
+template <bool STRICT, bool COUNT, bool UV = false>
 __device__ __forceinline__ void trace_warp(const DevScene& sc, const DevScratch& scratch, int warp_slot, int lane, bool active,
                                            const RayL& ray, uint2* leaves, uint32_t* stack, float& t_out, uint32_t& face_out,
-                                           WorkCount& wc)
+                                           WorkCount& wc, float* u_out = nullptr, float* v_out = nullptr)
 {
     t_out = kMaxFloat;
     face_out = 0xffffffffu;
@@ -254,7 +259,7 @@ __device__ __forceinline__ void trace_warp(const DevScene& sc, const DevScratch&
     {
         const int src = __ffs(todo) - 1;
         todo &= todo - 1;
-        scan_ray_leaves<STRICT, COUNT>(sc, lane, src, ray, leaves, nleaf, t_out, face_out, wc);
+        scan_ray_leaves<STRICT, COUNT, UV>(sc, lane, src, ray, leaves, nleaf, t_out, face_out, wc, u_out, v_out);
     }
     // rare: list or stack outgrew the per-lane arrays → redo that ray with the warp's spill area in global memory
     unsigned spill = __ballot_sync(FULL_MASK, overflow);
@@ -274,7 +279,7 @@ __device__ __forceinline__ void trace_warp(const DevScene& sc, const DevScratch&
             collect_leaves<false>(sc.nodes, ray, ix, iy, iz, gs, (int)scratch.stack_cap, gl, (int)scratch.leaf_cap, gn, dummy);
         }
         __syncwarp();
-        scan_ray_leaves<STRICT, COUNT>(sc, lane, src, ray, gl, gn, t_out, face_out, wc);
+        scan_ray_leaves<STRICT, COUNT, UV>(sc, lane, src, ray, gl, gn, t_out, face_out, wc, u_out, v_out);
         __syncwarp();
     }
 }
@@ -1187,6 +1192,216 @@ __global__ void __launch_bounds__(kBlock) k_trace(DevScene sc, const float* __re
     if (COUNT) flush_counters(counters, wc, rays_done);
 }
 
+// ---- K3: multi-bounce path ------------------------------------------------------------------------
+// get_intersection_data in full (renderer.cpp:34-160: model through the tree, then spheres, then planes, hit-type
+// priority plane > sphere > model > sky, smooth or flat triangle normal) and cast_ray at any bounce_limit
+// (renderer.cpp:213-262). All shading arithmetic is explicit round-to-nearest in the reference's operation order, so the
+// frame is bit-identical to the CPU path given the same per-pixel RNG stream. The tree part of every bounce runs on the
+// warp-cooperative unculled core (secondary rays are incoherent; the film-space bounds only hold for camera rays).
+struct V3 { float x, y, z; };
+__device__ __forceinline__ V3 v3(float x, float y, float z) { V3 r; r.x = x; r.y = y; r.z = z; return r; }
+__device__ __forceinline__ V3 v3add(V3 a, V3 b) { return v3(addr(a.x, b.x), addr(a.y, b.y), addr(a.z, b.z)); }
+__device__ __forceinline__ V3 v3sub(V3 a, V3 b) { return v3(subr(a.x, b.x), subr(a.y, b.y), subr(a.z, b.z)); }
+__device__ __forceinline__ V3 v3mul(V3 a, float k) { return v3(mulr(a.x, k), mulr(a.y, k), mulr(a.z, k)); }
+__device__ __forceinline__ V3 v3had(V3 a, V3 b) { return v3(mulr(a.x, b.x), mulr(a.y, b.y), mulr(a.z, b.z)); }
+__device__ __forceinline__ V3 v3neg(V3 a) { return v3(-a.x, -a.y, -a.z); }
+__device__ __forceinline__ float v3dot(V3 a, V3 b) { return addr(addr(mulr(a.x, b.x), mulr(a.y, b.y)), mulr(a.z, b.z)); }  // PL_math.h:416
+__device__ __forceinline__ V3 v3cross(V3 a, V3 b)                                                                         // PL_math.h:422
+{
+    return v3(subr(mulr(a.y, b.z), mulr(a.z, b.y)), subr(mulr(a.z, b.x), mulr(a.x, b.z)), subr(mulr(a.x, b.y), mulr(a.y, b.x)));
+}
+__device__ __forceinline__ V3 v3norm(V3 a)  // normalize, PL_math.h:387-392 with invsqrt := 1/sqrtf
+{
+    const float inv = __fdiv_rn(1.0f, __fsqrt_rn(v3dot(a, a)));
+    return v3mul(a, inv);
+}
+__device__ __forceinline__ V3 f4v(float4 q) { return v3(q.x, q.y, q.z); }
+
+struct HitFull
+{
+    int kind;        // 0 sky, 1 triangle, 2 sphere, 3 plane (ObjectType, renderer.cpp:12-15)
+    float t;         // distance_at_intersection (MAX_FLOAT for the sky)
+    V3 n;            // normalised normal
+    V3 em, refl;     // hit material
+    float scatter;
+    uint32_t face;
+};
+
+// get_sphere_ray_intersection, sphere.h:12-39
+__device__ __forceinline__ float sphere_hit(V3 o, V3 d, float4 cr)
+{
+    const V3 pc = v3sub(o, f4v(cr));
+    const float pc2 = v3dot(pc, pc);
+    const float b = mulr(2.0f, v3dot(d, pc));
+    const float b2 = mulr(b, b);
+    const float c = subr(pc2, mulr(cr.w, cr.w));
+    const float dmt = subr(b2, mulr(4.0f, c));
+    if (dmt < 0.0f) return 0.0f;
+    const float sq = __fsqrt_rn(dmt);
+    const float ta = mulr(addr(-b, sq), 0.5f);
+    const float tb = mulr(subr(-b, sq), 0.5f);
+    if (ta <= 0.0f && tb <= 0.0f) return 0.0f;
+    if (tb > 0.0f) return tb;
+    return ta;
+}
+// get_plane_ray_intersection, plane.h:12-22
+__device__ __forceinline__ float plane_hit(V3 o, V3 d, float4 nd)
+{
+    const float denom = v3dot(f4v(nd), d);
+    if (denom > -kTol && denom < kTol) return 0.0f;
+    return __fdiv_rn(subr(nd.w, v3dot(o, f4v(nd))), denom);
+}
+
+// Everything of get_intersection_data after the tree query: t_tri/face/u/v come from trace_warp (MISS when no triangle).
+__device__ __forceinline__ void resolve_hit(const DevScene& sc, V3 o, V3 d, float t_tri, uint32_t face, float u, float v, HitFull& h)
+{
+    float dist = kMaxFloat;
+    int near_sphere = -1, near_plane = -1;
+    const bool near_model = face != 0xffffffffu && t_tri > kTol && t_tri < dist;                // renderer.cpp:52-57
+    if (near_model) dist = t_tri;
+    for (uint32_t i = 0; i < sc.n_spheres; ++i)                                                  // :86-96
+    {
+        const float t = sphere_hit(o, d, __ldg(&sc.spheres[3 * i]));
+        if (t > kTol && t < dist) { dist = t; near_sphere = (int)i; }
+    }
+    for (uint32_t i = 0; i < sc.n_planes; ++i)                                                   // :97-107
+    {
+        const float t = plane_hit(o, d, __ldg(&sc.planes[3 * i]));
+        if (t > kTol && t < dist) { near_plane = (int)i; dist = t; }
+    }
+    h.t = dist;
+    h.face = 0xffffffffu;
+    h.n = v3(0.f, 0.f, 0.f);
+    if (near_plane >= 0)                                                                         // :111-116
+    {
+        const float4 a = __ldg(&sc.planes[3 * near_plane]), b = __ldg(&sc.planes[3 * near_plane + 1]), c = __ldg(&sc.planes[3 * near_plane + 2]);
+        h.kind = 3; h.n = f4v(a); h.em = f4v(b); h.scatter = b.w; h.refl = f4v(c);
+    }
+    else if (near_sphere >= 0)                                                                   // :117-122
+    {
+        const float4 a = __ldg(&sc.spheres[3 * near_sphere]), b = __ldg(&sc.spheres[3 * near_sphere + 1]), c = __ldg(&sc.spheres[3 * near_sphere + 2]);
+        h.kind = 2; h.n = v3sub(v3add(o, v3mul(d, dist)), f4v(a)); h.em = f4v(b); h.scatter = b.w; h.refl = f4v(c);
+    }
+    else if (near_model)                                                                         // :124-148
+    {
+        h.kind = 1; h.face = face;
+        if (sc.smooth)
+        {
+            const V3 na = f4v(__ldg(&sc.fnorm[3 * (size_t)face])), nb = f4v(__ldg(&sc.fnorm[3 * (size_t)face + 1])),
+                     nc = f4v(__ldg(&sc.fnorm[3 * (size_t)face + 2]));
+            const float w = subr(subr(1.0f, u), v);
+            h.n = v3add(v3add(v3mul(na, w), v3mul(nb, u)), v3mul(nc, v));
+        }
+        else
+            h.n = f4v(__ldg(&sc.fnorm[face]));
+        h.em = v3(sc.mdl[0], sc.mdl[1], sc.mdl[2]); h.refl = v3(sc.mdl_refl[0], sc.mdl_refl[1], sc.mdl_refl[2]); h.scatter = sc.mdl_scatter;
+    }
+    else                                                                                         // :149-155
+    {
+        h.kind = 0; h.em = v3(sc.sky[0], sc.sky[1], sc.sky[2]); h.refl = v3(0.f, 0.f, 0.f); h.scatter = 0.f;
+    }
+    h.n = v3norm(h.n);                                                                           // :157
+}
+
+template <bool STRICT>
+__global__ void __launch_bounds__(kBlock) k_path(DevScene sc, DevCamera cm, DevPartition part, DevOut out, DevScratch scratch,
+                                                 unsigned int* tile_counter, unsigned long long* casts_total, unsigned long long seed)
+{
+    const int lane = threadIdx.x & 31;
+    const int warp_slot = (blockIdx.x * kBlock + threadIdx.x) >> 5;
+    const int tiles_x = (cm.W + 7) >> 3;
+    const int rows_per_band = part.band_rows >> 2;
+    const int n_bands = (cm.H + part.band_rows - 1) / part.band_rows;
+    const int my_bands = part.rank < n_bands ? (n_bands - part.rank + part.world - 1) / part.world : 0;
+    const unsigned int tiles_per_band = (unsigned int)(tiles_x * rows_per_band);
+    const unsigned int n_tiles = (unsigned int)my_bands * tiles_per_band;
+    WorkCount wc;
+    wc.clear();
+    uint2 leaves[kLeafCap];
+    uint32_t stack[kStackCap];
+    unsigned long long casts = 0;  // ray_casts: bounce iterations that did not end in the sky (renderer.cpp:260)
+    for (;;)
+    {
+        unsigned int tile = 0;
+        if (lane == 0) tile = atomicAdd(tile_counter, 1u);
+        tile = __shfl_sync(FULL_MASK, tile, 0);
+        if (tile >= n_tiles) break;
+        const unsigned int lb = tile / tiles_per_band, rem = tile - lb * tiles_per_band;
+        const int trow = (int)(rem / (unsigned int)tiles_x), tcol = (int)(rem - (unsigned int)trow * (unsigned int)tiles_x);
+        const int x = tcol * 8 + (lane & 7);
+        const int y = ((int)lb * part.world + part.rank) * part.band_rows + trow * 4 + (lane >> 3);
+        const bool active = x < cm.W && y < cm.H;
+        const float film_y = film_coord(y, cm.H);
+        const float film_x = mulr(mulr(film_coord(x, cm.W), cm.h_fov), cm.aspect);
+        const unsigned long long p = (unsigned long long)y * (unsigned long long)cm.W + (unsigned long long)x;
+        Pcg rng;  // harness-defined per-pixel stream (the reference seeds per thread from rdtsc, renderer.cpp:376-378)
+        rng.state = splitmix64(seed ^ p);
+        rng.stream = 2ULL * p + 1ULL;
+        V3 col = v3(0.f, 0.f, 0.f);
+        float t_first = kMaxFloat;
+        uint32_t face_first = 0xffffffffu;
+        for (uint32_t s = 0; s < cm.spp; ++s)  // renderer.cpp:336-356: AA on = a jittered ray per sample, off = the same ray
+        {
+            float fx = film_x, fy = film_y;
+            if (cm.aa)
+            {
+                fx = addr(mulr(pcg_bi(rng), cm.hpw), film_x);
+                fy = addr(mulr(pcg_bi(rng), cm.hph), film_y);
+            }
+            const RayL pr = camera_ray(cm, fx, fy);
+            V3 o = v3(pr.ox, pr.oy, pr.oz), d = v3(pr.dx, pr.dy, pr.dz);
+            V3 color = v3(0.f, 0.f, 0.f), weight = v3(1.0f, 1.0f, 1.0f);
+            bool alive = active;
+            for (int32_t i = 0; i < cm.bounce; ++i)  // cast_ray, renderer.cpp:213-262
+            {
+                if (!__any_sync(FULL_MASK, alive)) break;
+                RayL r;
+                r.ox = o.x; r.oy = o.y; r.oz = o.z; r.dx = d.x; r.dy = d.y; r.dz = d.z;
+                float t_tri, u = 0.0f, v = 0.0f;
+                uint32_t face;
+                trace_warp<STRICT, false, true>(sc, scratch, warp_slot, lane, alive, r, leaves, stack, t_tri, face, wc, &u, &v);
+                if (!alive) continue;
+                HitFull h;
+                resolve_hit(sc, o, d, t_tri, face, u, v, h);
+                if (i == 0) { t_first = h.t; face_first = h.face; }
+                if (h.kind == 0)
+                {
+                    color = v3add(color, v3had(weight, h.em));  // :224-228
+                    alive = false;
+                    continue;
+                }
+                casts += 1;
+                float att = v3dot(v3neg(d), h.n);
+                if (att < 0.0f) { h.n = v3neg(h.n); att = 0.0f; }
+                V3 pure = v3sub(d, v3mul(h.n, mulr(2.0f, v3dot(d, h.n))));  // :238-243
+                pure = v3norm(pure);
+                V3 rb;
+                rb.x = pcg_bi(rng); rb.y = pcg_bi(rng); rb.z = pcg_bi(rng);   // :246
+                rb = v3norm(v3add(rb, h.n));
+                o = v3add(o, v3mul(d, h.t));                                   // :251
+                d = v3norm(v3add(v3mul(v3sub(pure, rb), h.scatter), rb));      // lerp, PL_math.h:439-442
+                color = v3add(color, v3had(weight, h.em));                     // :257-258
+                weight = v3had(weight, v3mul(h.refl, att));
+            }
+            col = v3add(col, color);
+        }
+        if (active)
+        {
+            const float n = (float)cm.spp;
+            const size_t idx = (size_t)p;
+            if (out.bgrx) out.bgrx[idx] = pack_bgrx(__fdiv_rn(col.x, n), __fdiv_rn(col.y, n), __fdiv_rn(col.z, n));
+            if (out.t) out.t[idx] = t_first;
+            if (out.prim) out.prim[idx] = face_first;
+        }
+    }
+    if (casts_total)
+    {
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) casts += __shfl_xor_sync(FULL_MASK, casts, off);
+        if (lane == 0 && casts) atomicAdd(casts_total, casts);
+    }
+}
+
 // ---- K0: microbenchmarks for the roofline denominators ------------------------------------------------------------
 __global__ void k_fp32_issue(float* sink, int iters)
 {
@@ -1351,6 +1566,22 @@ cudaError_t launch_render_culled(const DevScene& sc, const DevCamera& cam, const
     }
     if (fp_fast) return launch_culled_t<false, false>(sc, cam, part, out, scratch, view, slabs, counters, jitter_seed, cfg, stream);
     return launch_culled_t<true, false>(sc, cam, part, out, scratch, view, slabs, counters, jitter_seed, cfg, stream);
+}
+
+cudaError_t launch_path(const DevScene& sc, const DevCamera& cam, const DevPartition& part, const DevOut& out,
+                        const DevScratch& scratch, unsigned int* tile_counter, unsigned long long* casts, int fp_fast,
+                        unsigned long long seed, LaunchCfg cfg, cudaStream_t stream)
+{
+    cudaError_t e = cudaMemsetAsync(tile_counter, 0, sizeof(unsigned int), stream);
+    if (e != cudaSuccess) return e;
+    if (casts)
+    {
+        e = cudaMemsetAsync(casts, 0, sizeof(unsigned long long), stream);
+        if (e != cudaSuccess) return e;
+    }
+    if (fp_fast) k_path<false><<<cfg.grid, cfg.block, 0, stream>>>(sc, cam, part, out, scratch, tile_counter, casts, seed);
+    else k_path<true><<<cfg.grid, cfg.block, 0, stream>>>(sc, cam, part, out, scratch, tile_counter, casts, seed);
+    return cudaGetLastError();
 }
 
 cudaError_t launch_trace(const DevScene& sc, const float* rays, unsigned long long n, uint32_t* prim, float* t,

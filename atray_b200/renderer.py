@@ -49,6 +49,22 @@ class Context:
         s, m = api.make_material(sky), api.make_material(material)
         _ck(_L.atray_scene_upload(self.h, model.h, C.byref(s), C.byref(m)))
 
+    def set_primitives(self, spheres=(), planes=()):
+        """scene.spheres / scene.planes (scene.h:13-24): spheres = [(center, radius, material)], planes = [(normal,
+        distance, material)], material = (emission rgb, reflection rgb, scatter)."""
+        sp = (api.Sphere * max(1, len(spheres)))()
+        for i, (c, r, m) in enumerate(spheres):
+            sp[i] = api.Sphere((C.c_float * 3)(*c), r, api.make_material(m))
+        pl = (api.Plane * max(1, len(planes)))()
+        for i, (n, d, m) in enumerate(planes):
+            pl[i] = api.Plane((C.c_float * 3)(*n), d, api.make_material(m))
+        _ck(_L.atray_scene_set_primitives(self.h, C.cast(sp, C.c_void_p), len(spheres), C.cast(pl, C.c_void_p), len(planes)))
+
+    def last_ray_casts(self):
+        v = C.c_uint64(0)
+        _ck(_L.atray_last_ray_casts(self.h, C.byref(v)))
+        return v.value
+
     # -- frames -----------------------------------------------------------------------------------------------------
     @staticmethod
     def opts(fp_mode=api.FP_STRICT, count_work=False, seed=api.DEFAULT_SEED, rank=0, world=1, band_rows=8, cull=True):
@@ -160,6 +176,7 @@ class Scene:
                  max_no_faces_per_node=300):
         self.model, self.sky, self.material = model, sky, material
         self.division_method, self.max_no_faces_per_node = division_method, max_no_faces_per_node
+        self.spheres, self.planes = [], []   # scene.spheres / scene.planes: (center, radius, material) / (normal, distance, material)
         self.ctx = None
 
 
@@ -183,6 +200,8 @@ def prep_scene(scene, device=0):
     if scene.ctx is None:
         scene.ctx = Context(device)
     scene.ctx.upload(scene.model, scene.sky, scene.material)
+    if scene.spheres or scene.planes:
+        scene.ctx.set_primitives(scene.spheres, scene.planes)
     return n["nodes"]
 
 
@@ -203,6 +222,8 @@ def wait_for_render_from_camera_to_finish(info, tpool=None, ms_to_wait_for=33):
     if not running:
         info.jobs_done = info.jobs_size
         # ray_casts counts non-sky bounce iterations (renderer.cpp:222-231,260): at bounce 1 = samples that hit geometry
-        if info.prim is not None and info.camera.samples_per_pixel == 1:
+        if info.camera.bounce_limit != 1 or info.scene.spheres or info.scene.planes:
+            info.total_ray_casts = info.scene.ctx.last_ray_casts()
+        elif info.prim is not None and info.camera.samples_per_pixel == 1:
             info.total_ray_casts = int((info.prim != api.MISS).sum())
     return running

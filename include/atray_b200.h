@@ -44,6 +44,10 @@ typedef struct atray_ctx atray_ctx;     /* one GPU: uploaded scene, streams, fra
 /* Material, engine/renderer/material.h:4-9 (28 bytes, same layout) */
 typedef struct AtrayMaterial { float emission_color[3]; float reflection_color[3]; float scatter; } AtrayMaterial;
 
+/* Sphere / Plane with their material by value (engine/renderer/sphere.h:5-10, plane.h:5-10 hold a Material*). */
+typedef struct AtraySphere { float center[3]; float radius; AtrayMaterial material; } AtraySphere;
+typedef struct AtrayPlane { float normal[3]; float distance; AtrayMaterial material; } AtrayPlane;
+
 /* Camera + RenderSettings as the kernel consumes them: the values set_camera/update_camera_pos compute
  * (engine/renderer/camera.h:9-45, settings.h:4-10). Filled by atray_camera_set on the host. */
 typedef struct AtrayCamera
@@ -51,7 +55,8 @@ typedef struct AtrayCamera
     int32_t width, height;            /* RenderSettings.resolution */
     int32_t anti_aliasing;            /* RenderSettings.anti_aliasing (b32) */
     uint32_t samples_per_pixel;       /* RenderSettings.samples_per_pixel */
-    int32_t bounce_limit;             /* RenderSettings.bounce_limit; this path implements 1 (SURVEY §8f row 1 = next) */
+    int32_t bounce_limit;             /* RenderSettings.bounce_limit: 1 = primary rays (film-space culled kernel);
+                                         > 1 = cast_ray's bounce loop, renderer.cpp:213-262 (multi-bounce kernel) */
     float aspect_ratio;
     float camera_z[3], camera_x[3], camera_y[3];
     float eye[3], frame_center[3];
@@ -143,6 +148,18 @@ void atray_ctx_destroy(atray_ctx* ctx);
 /* prep_scene(Scene&, uint32&) tail: flatten + upload once — renderer.cpp:264-291. materials[0] = sky
  * (renderer.cpp:152), materials[1] = the model's material (model.data.material). */
 int atray_scene_upload(atray_ctx* ctx, const atray_model* m, const AtrayMaterial* sky, const AtrayMaterial* model_mat);
+
+/* scene.spheres / scene.planes (engine/renderer/scene.h:13-24; app.cpp:111-129,139-142): replaces the current sets
+ * (n = 0 removes them). Plane normals are normalised as prep_scene does (renderer.cpp:267-270). With primitives
+ * present, or bounce_limit > 1, frames run get_intersection_data in full (plane > sphere > model > sky,
+ * renderer.cpp:86-157) and cast_ray's bounce loop; random draws come from the per-pixel stream
+ * RNG_Stream{splitmix64(jitter_seed ^ p), 2p+1} (the reference seeds per thread from rdtsc, renderer.cpp:376-378).
+ * The t / prim planes then describe the nearest hit of the last sample's primary ray (prim = ATRAY_MISS unless it is
+ * a triangle). Call after atray_scene_upload (which clears them). */
+int atray_scene_set_primitives(atray_ctx* ctx, const AtraySphere* spheres, uint32_t n_spheres, const AtrayPlane* planes,
+                               uint32_t n_planes);
+/* info.total_ray_casts of the last multi-bounce frame: bounce iterations that hit an object (renderer.cpp:260) */
+int atray_last_ray_casts(atray_ctx* ctx, uint64_t* ray_casts);
 
 /* start_render_from_camera(RenderInfo&, ThreadPool&) — renderer.cpp:403-455: returns immediately; kernels and the
  * device→host copies of the frame planes are queued on the context's stream. */

@@ -73,6 +73,27 @@ def main():
                 jitter_bgrx=jit, jitter_hits=hits.astype(np.uint8), ray_seed=99, ray_face=rf, ray_t_bits=rt.view(np.uint32))
             print(name, mname, "nodes", s.n_nodes, "refs", s.n_refs, "hit frac", float((face != B.MISS).mean()))
             s.close()
+    # multi-bounce path: the reference's own cast_ray / get_intersection_data with spheres and planes
+    sys.path.insert(0, os.path.dirname(OUT))
+    from helpers import PATH_CONFIGS, PATH_PLANES, PATH_SPHERES, PH, PW
+    for name in ("knot_small", "Deer", "Monkey"):
+        path, rescale = cases[name]
+        out = {"obj_sha256": gen_standin_obj.sha256(path), "rescale": rescale}
+        for prims in (0, 1):
+            s = B.Scene(R, path, loader_threads=1, rescale=rescale)
+            if prims:
+                for c, r, m in PATH_SPHERES:
+                    s.add_sphere(c, r, m)
+                for n, dd, m in PATH_PLANES:
+                    s.add_plane(n, dd, m)
+            for k, (spp, bounce, aa) in enumerate(PATH_CONFIGS):
+                img, t, prim, kind, casts = s.render_path(PW, PH, spp, bounce, SEED + k, aa=aa, threads=4)
+                tag = "p%d_c%d_" % (prims, k)
+                out.update({tag + "bgrx": img, tag + "t_bits": t.view(np.uint32), tag + "prim": prim,
+                            tag + "kind": kind.astype(np.uint8), tag + "casts": casts})
+            s.close()
+        np.savez_compressed(os.path.join(OUT, "path_%s.npz" % name), **out)
+        print("path", name)
     np.savez(os.path.join(OUT, "kat.npz"), pcg32_42_54=B.pcg32(R, 42, 54, 16),
              camera_1280x720=B.camera(R, 1280, 720).view(np.uint32), camera_3840x2160=B.camera(R, 3840, 2160).view(np.uint32),
              camera_custom=B.camera(R, 640, 360, eye=(1.5, -2.0, 3.0), facing=(0.3, 0.2, -1.0), hfov=0.8).view(np.uint32))

@@ -43,7 +43,7 @@ def random_rays(aabb, n, seed):
 def golden_cases():
     out = []
     for f in sorted(os.listdir(GOLDEN)):
-        if f.endswith(".npz") and f != "kat.npz":
+        if f.endswith(".npz") and f != "kat.npz" and not f.startswith("path_"):
             out.append(f[:-4])
     return out
 
@@ -83,3 +83,13 @@ def cube_mesh(size=1.0):
     for a, b, c, d in q:
         f += [(a, b, c), (a, c, d)]
     return np.array(v, np.float32), np.array(f, np.int32)
+
+
+# Scene primitives for the multi-bounce path tests (shapes as app.cpp:111-129 builds them): (center, radius, material)
+# and (normal, distance, material) with material = (emission rgb, reflection rgb, scatter).
+PATH_SPHERES = [((-6.0, -12.0, -30.0), 3.0, ((0.0, 0.0, 0.0), (0.9, 0.9, 0.9), 0.9)),
+                ((8.0, -9.0, -34.0), 4.0, ((0.6, 0.5, 0.1), (0.3, 0.8, 0.3), 0.1))]
+PATH_PLANES = [((0.0, 1.0, 0.05), -20.0, ((0.05, 0.05, 0.05), (0.6, 0.6, 0.7), 0.5))]
+# (spp, bounce_limit, anti_aliasing)
+PATH_CONFIGS = [(1, 1, 0), (2, 5, 0), (3, 4, 1), (1, 8, 1)]
+PW, PH = 160, 90

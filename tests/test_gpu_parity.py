@@ -6,8 +6,8 @@ import os
 import numpy as np
 import pytest
 
-from helpers import (GH, GW, SEED, bits, cube_mesh, golden_cases, load_golden, mesh_for_case, random_rays, same_bits,
-                     write_obj)
+from helpers import (GH, GOLDEN, GW, PATH_CONFIGS, PATH_PLANES, PATH_SPHERES, PH, PW, SEED, bits, cube_mesh, golden_cases,
+                     load_golden, mesh_for_case, random_rays, same_bits, write_obj)
 
 pytestmark = pytest.mark.gpu
 
@@ -329,7 +329,7 @@ def test_reference_call_sequence(A, port, meshes):
     assert info.total_ray_casts == int((face != B.MISS).sum())
     assert A.wait_for_render_from_camera_to_finish(info, None, 0) == 0  # idle → finished
     with pytest.raises(A.AtrayError):
-        scene.ctx.render(A.set_camera(64, 64, bounce_limit=5))
+        scene.ctx.render(A.set_camera(64, 64, bounce_limit=0))
     tex.free()
     o.close()
 
@@ -363,6 +363,67 @@ def test_pipelined_copy_out_equals_whole_frame(A, meshes, monkeypatch):
             assert same_bits(tt.array, whole["t"])
         for a in (tex, tt, tp):
             a.free()
+
+
+@pytest.mark.parametrize("name", ["knot_small", "Deer", "Monkey"])
+def test_multi_bounce_path_matches_reference_golden(name, A, meshes):
+    """cast_ray at bounce_limit > 1, smooth/flat normals, spheres and planes — k_path against the
+    vectors the reference's own code produced (tests/golden/path_*.npz): pixels, t, primitive id, ray_casts bit-exact."""
+    if name not in meshes:
+        pytest.skip("mesh not staged")
+    g = np.load(os.path.join(GOLDEN, "path_%s.npz" % name))
+    path, rescale = meshes[name]
+    for prims in (0, 1):
+        sc = gpu_scene(A, path, rescale)
+        if prims:
+            sc.ctx.set_primitives(PATH_SPHERES, PATH_PLANES)
+        for k, (spp, bounce, aa) in enumerate(PATH_CONFIGS):
+            cam = A.set_camera(PW, PH, anti_aliasing=aa, samples_per_pixel=spp, bounce_limit=bounce)
+            out = sc.ctx.render(cam, sc.ctx.opts(seed=SEED + k))
+            tag = "p%d_c%d_" % (prims, k)
+            assert (out["bgrx"] == g[tag + "bgrx"]).all(), tag
+            assert (bits(out["t"]) == g[tag + "t_bits"]).all() and (out["prim"] == g[tag + "prim"]).all(), tag
+            if bounce != 1 or prims:
+                assert sc.ctx.last_ray_casts() == int(g[tag + "casts"])
+
+
+@pytest.mark.parametrize("name", ["knot_mid", "Cube", "Monkey"])
+def test_multi_bounce_path_equals_oracle(name, A, port, meshes):
+    """Larger frames, other cameras (inside the model, grazing the plane), 5 spp x 5 bounces (the reference's default
+    workload, app.cpp:84-85), through the reference-named entry points with Scene.spheres / Scene.planes."""
+    from oracle import bind as B
+    if name not in meshes:
+        pytest.skip("mesh not staged")
+    path, rescale = meshes[name]
+    m = A.load_model_data(path, 2)
+    A.place_default(m, rescale)
+    scene = A.Scene(m)
+    scene.spheres, scene.planes = list(PATH_SPHERES), list(PATH_PLANES)
+    A.prep_scene(scene)
+    o = B.Scene(port, path, rescale=rescale)
+    for c, r, mm in PATH_SPHERES:
+        o.add_sphere(c, r, mm)
+    for n, d, mm in PATH_PLANES:
+        o.add_plane(n, d, mm)
+    for i, (eye, facing, aa) in enumerate([(B.DEFAULT_EYE, B.DEFAULT_FACING, 0), ((0.0, -14.0, -36.0), (0.2, 0.1, -1.0), 1),
+                                           ((20.0, -19.5, -10.0), (-0.6, 0.0, -1.0), 1)]):
+        W, H = 401, 227
+        cam = A.set_camera(W, H, eye=eye, facing=facing, anti_aliasing=aa, samples_per_pixel=5, bounce_limit=5)
+        tex, tt, tp = np.zeros((H, W), np.uint32), np.zeros((H, W), np.float32), np.zeros((H, W), np.uint32)
+        info = A.RenderInfo(cam, scene, tex, t=tt, prim=tp, opts=scene.ctx.opts(seed=SEED + i))
+        A.start_render_from_camera(info)
+        while A.wait_for_render_from_camera_to_finish(info, None, 33):
+            pass
+        img, t, prim, kind, casts = o.render_path(W, H, 5, 5, SEED + i, aa=aa, threads=NTHREADS, eye=eye, facing=facing)
+        assert (tex == img).all() and same_bits(tt, t) and (tp == prim).all()
+        assert info.total_ray_casts == casts
+        assert len(np.unique(kind)) >= 2
+    # removing the primitives restores the culled primary-ray path
+    scene.ctx.set_primitives()
+    a = scene.ctx.render(A.set_camera(320, 180))
+    face, t, img = B.Scene(port, path, rescale=rescale).trace_primary(320, 180, threads=NTHREADS)
+    assert (a["prim"] == face).all() and (a["bgrx"] == img).all()
+    o.close()
 
 
 def test_errors_on_device_side(A, meshes):
