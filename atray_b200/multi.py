@@ -33,10 +33,19 @@ def exchange_handles(dist, rank, payload):
 class FrameGather:
     """GPU 0 owns the frame planes; other ranks map them. `planes[p]` is a device pointer valid in this process."""
 
-    def __init__(self, ctx, dist, rank, world, width, height, planes=PLANES):
+    def __init__(self, ctx, dist, rank, world, width, height, planes=PLANES, local=()):
+        """`local`: planes that are NOT gathered — every rank keeps its own full-size plane and fills only its bands
+        (the live view needs the BGRX bitmap on GPU 0, north_star; t and primitive ids can stay where they were made,
+        which cuts GPU 0's NVLink ingress from 12 to 4 bytes per pixel)."""
         self.ctx, self.rank, self.world = ctx, rank, world
         self.nbytes = width * height * 4
         self.planes, self._owned, self._opened = {}, [], []
+        self.local = tuple(p for p in local if p in planes) if world > 1 else ()
+        for p in self.local:
+            ptr = ctx.dev_alloc(self.nbytes)
+            self._owned.append(ptr)
+            self.planes[p] = ptr
+        planes = tuple(p for p in planes if p not in self.local)
         handles = None
         if rank == 0:
             handles = {}

@@ -192,7 +192,9 @@ def run_ours(args):
     setup_s = time.perf_counter() - t_setup
     ctx = scene.ctx
     cam = A.set_camera(W, H, samples_per_pixel=SPP)
-    gather = multi.FrameGather(ctx, dist, rank, world, W, H)
+    # GPU 0 gathers the BGRX bitmap (what the live view shows, north_star); t and primitive ids stay on the rank that
+    # traced them: 4 instead of 12 bytes per pixel cross NVLink into GPU 0
+    gather = multi.FrameGather(ctx, dist, rank, world, W, H, local=("t", "prim"))
     opts = ctx.opts(fp_mode=fp_mode, rank=rank, world=world, band_rows=BAND_ROWS)
     my_rays = multi.rays_of_rank(W, H, SPP, BAND_ROWS, rank, world)
     flush_bytes = 256 << 20                            # > 126 MB L2
@@ -235,8 +237,12 @@ def run_ours(args):
         tt = torch.tensor([dev_ms], dtype=torch.float64, device="cuda")
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         dev_ms_max = float(tt.item())
+        allms = [torch.zeros(1, dtype=torch.float64, device="cuda") for _ in range(world)]
+        dist.all_gather(allms, torch.tensor([dev_ms / args.steps], dtype=torch.float64, device="cuda"))
+        per_rank_ms = [float(x.item()) for x in allms]
     else:
         dev_ms_max = dev_ms
+        per_rank_ms = [dev_ms / args.steps]
     total_rays = W * H * SPP * args.steps
     value = total_rays / (dev_ms_max * 1e-3) / 1e6
 
@@ -323,11 +329,11 @@ def run_ours(args):
         line = base_line(args.gpus, args.steps, args.warmup)
         line.update({"impl": "ours", "value": value, "ms_per_step": dev_ms_max / args.steps, "e2e": e2e, "roofline": roofline,
                      "cpu_baseline": cpu_baseline, "clocks": clocks, "gpu_launches": args.steps * world,
-                     "wall_ms_bracket": wall_ms, "per_step_ms_rank0": per_step_ms, "counters": ctr, "setup_s": setup_s})
+                     "wall_ms_bracket": wall_ms, "per_step_ms_rank0": per_step_ms, "ms_per_step_by_rank": per_rank_ms, "counters": ctr, "setup_s": setup_s})
         line["config"].update({"fp_mode": args.fp, "band_rows": BAND_ROWS, "parallelism": "bands%d" % world,
                                "l2": "flushed between timed steps (256 MiB device memset outside the per-step event pair)",
                                "timing": "CUDA events on the library's stream around each frame's launch, summed over K steps, max over ranks",
-                               "gather": "direct peer stores into GPU 0's frame through CUDA IPC" if world > 1 else "none (1 GPU)"})
+                               "gather": "BGRX bitmap: direct peer stores into GPU 0's frame through CUDA IPC; t/prim planes stay on the tracing rank" if world > 1 else "none (1 GPU)"})
     barrier()
     if tex is not None:
         tex.free()
@@ -340,6 +346,8 @@ def run_ours(args):
 
 
 def main():
+    # NCCL writes its version banner to stdout when NCCL_DEBUG is set by the environment; the contract is ONE JSON line there
+    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)

@@ -59,6 +59,13 @@ def _worker(rank, world, port, q):
     g = multi.FrameGather(ctx, dist, rank, world, 64, 32)
     planes = dict(g.planes)
     g.close()
+    n0 = len(ctx.log)
+    g2 = multi.FrameGather(ctx, dist, rank, world, 64, 32, local=("t", "prim"))   # only the bitmap is gathered
+    assert set(g2.planes) == {"bgrx", "t", "prim"} and g2.local == ("t", "prim")
+    kinds = [e[0] for e in ctx.log[n0:]]
+    assert kinds == (["alloc"] * 3 if rank == 0 else ["alloc", "alloc", "open"]), kinds
+    g2.close()
+    del ctx.log[n0:]
     dist.barrier()
     dist.destroy_process_group()
     q.put((rank, planes, ctx.log))
