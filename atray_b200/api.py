@@ -18,6 +18,7 @@ MAX_FLOAT = np.float32(3.402823466e+38)
 DIV_CENTER, DIV_SAH = 0, 1
 FP_STRICT, FP_FAST = 0, 1
 RENDER_NO_CULL = 1
+RENDER_RASTER = 2
 
 # app.cpp:88,91,96
 DEFAULT_EYE = (0.1, 2.0, 0.0)

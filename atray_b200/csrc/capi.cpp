@@ -33,6 +33,13 @@ struct atray_ctx
     DevView view{};              // per-frame film rectangles + tile stamps (k_view_bounds)
     size_t stamp_cap = 0;        // tiles the stamp buffer holds
     uint32_t frame_seq = 0;      // stamp value of the last frame (0 = buffer freshly cleared)
+    // film-space rasteriser (raster.cuh): scene tables, per-frame tables / keys / lists
+    uint32_t* d_packet_leaf = nullptr; uint32_t* d_leaf_seq = nullptr; uint32_t* d_seq_leaf = nullptr;
+    uint32_t* d_parent = nullptr; uint32_t* d_pos_face = nullptr;
+    DevRaster rs{};
+    size_t key_cap_px = 0;           // pixels the key planes hold (all-ones between frames)
+    int tab_w = 0, tab_h = 0;        // capacity of the film tables
+    int use_raster = 0;              // ATRAY_RASTER=1 rasterises every AA-off frame (otherwise per frame: ATRAY_RENDER_RASTER)
     float4* d_fnorm = nullptr;       // per-face normal sources of the multi-bounce path
     float4* d_spheres = nullptr;     // analytic primitives (atray_scene_set_primitives)
     float4* d_planes = nullptr;
@@ -268,6 +275,7 @@ int atray_ctx_create(int device, atray_ctx** out)
             c->wait_value32 = reinterpret_cast<atray_ctx::WaitValue32>(fn);
         else
             cudaGetLastError();
+        if (const char* env = std::getenv("ATRAY_RASTER")) c->use_raster = std::atoi(env) != 0;
         if (const char* env = std::getenv("ATRAY_SLABS"))
         {
             const int v = std::atoi(env);
@@ -288,6 +296,10 @@ static void free_scene(atray_ctx* c)
     c->d_nodes = c->d_tris = nullptr;
     cudaFree(c->d_fnorm); cudaFree(c->d_spheres); cudaFree(c->d_planes);
     c->d_fnorm = c->d_spheres = c->d_planes = nullptr;
+    cudaFree(c->d_packet_leaf); cudaFree(c->d_leaf_seq); cudaFree(c->d_seq_leaf); cudaFree(c->d_parent); cudaFree(c->d_pos_face);
+    c->d_packet_leaf = c->d_leaf_seq = c->d_seq_leaf = c->d_parent = c->d_pos_face = nullptr;
+    cudaFree(c->rs.big);
+    c->rs.big = nullptr; c->rs.big_cap = 0;
     c->scratch = DevScratch{};
     c->scene = DevScene{};
     c->has_scene = false;
@@ -301,6 +313,8 @@ void atray_ctx_destroy(atray_ctx* c)
     free_scene(c);
     cudaFree(c->d_tile_counter); cudaFree(c->d_counters); cudaFree(c->d_casts);
     cudaFree(c->view.stamps); cudaFree(c->view.all_flag); cudaFree(c->view.busy_list); cudaFree(c->view.busy_count);
+    cudaFree(c->rs.tabx); cudaFree(c->rs.taby); cudaFree(c->rs.key1); cudaFree(c->rs.key2); cudaFree(c->rs.hit_a);
+    cudaFree(c->rs.hit_pos); cudaFree(c->rs.ctl);
     cudaFree(c->d_bgrx); cudaFree(c->d_t); cudaFree(c->d_prim);
     cudaFreeHost(c->h_bgrx); cudaFreeHost(c->h_t); cudaFreeHost(c->h_prim);
     cudaFree(c->d_rays); cudaFree(c->d_rprim); cudaFree(c->d_rt);
@@ -342,6 +356,19 @@ int atray_scene_upload(atray_ctx* c, const atray_model* m, const AtrayMaterial* 
     if (!f.inner_order.empty())
         CU(cudaMemcpy(c->d_inner_order, f.inner_order.data(), f.inner_order.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
     CU(cudaMemcpy(c->d_level_start, f.level_start.data(), f.level_start.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+    {
+        auto up = [](uint32_t** dst, const std::vector<uint32_t>& v) -> cudaError_t {
+            cudaError_t e = cudaMalloc(dst, (v.size() + 1) * sizeof(uint32_t));
+            if (e == cudaSuccess && !v.empty()) e = cudaMemcpy(*dst, v.data(), v.size() * sizeof(uint32_t), cudaMemcpyHostToDevice);
+            return e;
+        };
+        CU(up(&c->d_packet_leaf, f.packet_leaf)); CU(up(&c->d_leaf_seq, f.leaf_seq)); CU(up(&c->d_seq_leaf, f.seq_leaf));
+        CU(up(&c->d_parent, f.parent)); CU(up(&c->d_pos_face, f.pos_face));
+        c->scene.packet_leaf = c->d_packet_leaf; c->scene.leaf_seq = c->d_leaf_seq; c->scene.seq_leaf = c->d_seq_leaf;
+        c->scene.parent = c->d_parent; c->scene.pos_face = c->d_pos_face;
+        c->rs.big_cap = f.n_slots ? f.n_slots : 1u;
+        CU(cudaMalloc(&c->rs.big, size_t(c->rs.big_cap) * sizeof(uint2)));
+    }
     c->scene.inner_order = c->d_inner_order;
     c->scene.level_start = c->d_level_start;
     c->scene.n_levels = uint32_t(f.level_start.size() - 1);
@@ -528,6 +555,41 @@ static ViewParams make_view_params(const AtrayCamera* cam)
     return vp;
 }
 
+// Per-frame buffers of the rasteriser: film tables for W and H, two 64-bit key planes (all-ones between frames; k_resolve
+// restores what a frame consumed), the hit list (4 entries per pixel, at least 1 Mi) and three counters.
+static int ensure_raster_buffers(atray_ctx* c, const AtrayCamera* cam)
+{
+    const size_t px = size_t(cam->width) * size_t(cam->height);
+    if (!c->rs.ctl) CU(cudaMalloc(&c->rs.ctl, 4 * sizeof(uint32_t)));
+    if (cam->width > c->tab_w)
+    {
+        cudaFree(c->rs.tabx); c->rs.tabx = nullptr; c->tab_w = 0;
+        CU(cudaMalloc(&c->rs.tabx, size_t(cam->width) * sizeof(float4)));
+        c->tab_w = cam->width;
+    }
+    if (cam->height > c->tab_h)
+    {
+        cudaFree(c->rs.taby); c->rs.taby = nullptr; c->tab_h = 0;
+        CU(cudaMalloc(&c->rs.taby, size_t(cam->height) * sizeof(float4)));
+        c->tab_h = cam->height;
+    }
+    if (px > c->key_cap_px)
+    {
+        cudaFree(c->rs.key1); cudaFree(c->rs.key2); cudaFree(c->rs.hit_a); cudaFree(c->rs.hit_pos);
+        c->rs.key1 = c->rs.key2 = nullptr; c->rs.hit_a = nullptr; c->rs.hit_pos = nullptr; c->key_cap_px = 0;
+        size_t cap = px * 4;
+        if (cap < (size_t(1) << 20)) cap = size_t(1) << 20;
+        if (cap > (size_t(1) << 28)) cap = size_t(1) << 28;
+        if (const char* env = std::getenv("ATRAY_HIT_CAP")) cap = size_t(std::atoll(env)) ? size_t(std::atoll(env)) : cap;   // tests: force the overflow path
+        CU(cudaMalloc(&c->rs.key1, px * 8)); CU(cudaMalloc(&c->rs.key2, px * 8));
+        CU(cudaMalloc(&c->rs.hit_a, cap * sizeof(uint4))); CU(cudaMalloc(&c->rs.hit_pos, cap * sizeof(uint32_t)));
+        CU(cudaMemsetAsync(c->rs.key1, 0xff, px * 8, c->stream)); CU(cudaMemsetAsync(c->rs.key2, 0xff, px * 8, c->stream));
+        c->rs.hit_cap = uint32_t(cap);
+        c->key_cap_px = px;
+    }
+    return ATRAY_OK;
+}
+
 // Queues one frame on the context stream. `want_slabs` > 1 asks for a slab table (culled kernel only); *slabs_out tells
 // the caller what it got (n = 0: unculled kernel, no per-slab counters).
 static int enqueue_render(atray_ctx* c, const AtrayCamera* cam, const AtrayRenderOpts* o, const DevOut& out, int want_slabs = 1,
@@ -582,8 +644,24 @@ static int enqueue_render(atray_ctx* c, const AtrayCamera* cam, const AtrayRende
         c->view.frame_id = vp.frame_id;
         c->view.tiles_x = vp.tiles_x;
     }
+    // opt-in, AA off and a real tree: the frame is rasterised triangle by triangle (raster.cuh) — same bits, no per-tile traversal
+    const bool raster = cull && (c->use_raster || (o->flags & ATRAY_RENDER_RASTER)) && !cam->anti_aliasing && !c->scene.root_is_leaf;
+    if (raster)
+    {
+        int rc = ensure_raster_buffers(c, cam);
+        if (rc) return rc;
+    }
     CU(cudaEventRecord(c->ev_k0, c->stream));
-    if (cull)
+    if (raster)
+    {
+        const DevSlabs slabs = make_slabs(to_dev(cam), p, want_slabs);
+        CU(launch_film_tables(to_dev(cam), c->rs, c->stream));
+        CU(launch_view_bounds(c->scene, vp, c->view, to_dev(cam), p, slabs, c->stream, want_slabs > 1 ? c->ev_reset : nullptr, false));
+        CU(launch_raster(c->scene, vp, to_dev(cam), p, out, c->scratch, c->view, c->rs, slabs, ctr, o->fp_mode == ATRAY_FP_FAST, c->cfg,
+                         c->stream));
+        if (slabs_out) *slabs_out = slabs;
+    }
+    else if (cull)
     {
         // the film rectangles depend on the camera: recomputed every frame, inside the timed region
         const DevSlabs slabs = make_slabs(to_dev(cam), p, want_slabs);

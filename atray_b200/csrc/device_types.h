@@ -27,6 +27,12 @@ struct DevScene
     const float4* spheres; // 3 float4 per sphere: {center, radius} {emission, scatter} {reflection, 0}  (sphere.h:5-10)
     const float4* planes;  // 3 float4 per plane : {normal, distance} {emission, scatter} {reflection, 0} (plane.h:5-10)
     uint32_t n_spheres, n_planes;
+    // ---- film-space rasteriser (k_raster / k_resolve): FlatScene::packet_leaf, leaf_seq, seq_leaf, parent, pos_face ----
+    const uint32_t* packet_leaf;   // n_slots/8: leaf node that owns the packet
+    const uint32_t* leaf_seq;      // n_nodes  : static insertion rank of a leaf (kd_tree.cpp:363-435 with every node visited)
+    const uint32_t* seq_leaf;      // n_leaves : inverse of leaf_seq
+    const uint32_t* parent;        // n_nodes  : parent node, 0xffffffff for the root
+    const uint32_t* pos_face;      // n_slots  : [first_slot + position in the reference's leaf order] → face index
 };
 
 struct DevCamera
@@ -63,6 +69,26 @@ struct DevView
     int32_t tiles_x;
 };
 
+// Per-frame state of the film-space rasteriser (render.cu: k_film_tables, k_raster, k_raster_big, k_hit_filter, k_resolve).
+// key1/key2 hold one 64-bit word per pixel each and are all-ones between frames (k_resolve restores what it consumes):
+//   key1 = (entry distance bits << 32) | leaf_seq   minimum over the (leaf, triangle) pairs the reference would accept for the
+//          pixel's ray = the first leaf of the ray's sorted leaf list that yields a hit (kd_tree.cpp:437-462); 0 = the pixel
+//          must be traced by the exact per-ray walker (irregular ray, possible "at most 5 children" cut, hit list overflow);
+//   key2 = (t bits << 32) | position in the reference's leaf order, minimum over the accepted triangles of that leaf.
+struct DevRaster
+{
+    float4* tabx;                  // W: {frame_center + camera_x*film_x (xyz), film_x}      (renderer.cpp:329,350)
+    float4* taby;                  // H: {camera_y*film_y (xyz), film_y}                      (renderer.cpp:317,350)
+    unsigned long long* key1;
+    unsigned long long* key2;
+    uint4* hit_a;                  // accepted hits that were the best of their pixel when found: {pixel, dis bits, leaf_seq, t bits}
+    uint32_t* hit_pos;             // … and the position of the triangle in the reference's leaf order
+    uint32_t hit_cap;
+    uint2* big;                    // {slot, pixel pairs} of the slots whose rectangle is too large for one warp pass
+    uint32_t big_cap;
+    uint32_t* ctl;                 // [0] hits appended, [1] big-list entries
+};
+
 // Slabs: the rank's tiles (band-major local numbering) split into up to kMaxSlabs contiguous ranges of whole bands. The
 // render kernel finishes slab after slab and publishes a finished-tile counter per slab, so the host side can start the
 // device→host copy of a slab's scanlines while later slabs are still being traced (capi.cpp: atray_render_begin).
@@ -97,7 +123,14 @@ cudaError_t launch_render(const DevScene& sc, const DevCamera& cam, const DevPar
 // k_view_bounds (per-slot rectangles, packet unions, tile stamps) + k_view_finish (leaf and inner-node unions,
 // compact list of this rank's busy tiles)
 cudaError_t launch_view_bounds(const DevScene& sc, const ViewParams& vp, const DevView& view, const DevCamera& cam,
-                               const DevPartition& part, const DevSlabs& slabs, cudaStream_t stream, cudaEvent_t after_reset);
+                               const DevPartition& part, const DevSlabs& slabs, cudaStream_t stream, cudaEvent_t after_reset,
+                               bool finish = true);
+// rasterised frame (AA off, root is an inner node): k_film_tables → [k_view_bounds by the caller] → k_raster → k_raster_big →
+// k_hit_filter → k_resolve (sky fill + per-pixel decode + exact per-ray fallback, slab by slab like the culled kernel)
+cudaError_t launch_film_tables(const DevCamera& cam, const DevRaster& rs, cudaStream_t stream);
+cudaError_t launch_raster(const DevScene& sc, const ViewParams& vp, const DevCamera& cam, const DevPartition& part, const DevOut& out,
+                          const DevScratch& scratch, const DevView& view, const DevRaster& rs, const DevSlabs& slabs,
+                          DevCounters* counters, int fp_fast, LaunchCfg cfg, cudaStream_t stream);
 cudaError_t launch_render_culled(const DevScene& sc, const DevCamera& cam, const DevPartition& part, const DevOut& out,
                                  const DevScratch& scratch, const DevView& view, const DevSlabs& slabs, DevCounters* counters,
                                  int fp_fast, unsigned long long jitter_seed, LaunchCfg cfg, cudaStream_t stream);

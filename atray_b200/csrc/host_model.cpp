@@ -412,6 +412,7 @@ void flatten(const HostModel& m, FlatScene& out)
     out.n_slots = slots;
     out.tris.assign(size_t(slots / 8) * 24 * 4, 0.f);
     out.packet_leaf.assign(slots / 8, 0u);
+    out.pos_face.assign(slots, 0xffffffffu);
     uint32_t cursor = 0;
     std::vector<uint32_t> order;
     for (uint32_t i = 0; i < out.n_nodes; ++i)
@@ -433,6 +434,7 @@ void flatten(const HostModel& m, FlatScene& out)
         if (cnt > out.max_leaf_prims) out.max_leaf_prims = cnt;
         const uint32_t padded = (cnt + 7u) & ~7u;
         morton_order(n.prims, order);
+        for (uint32_t k = 0; k < cnt; ++k) out.pos_face[cursor + k] = n.prims[k].face;
         for (uint32_t k = 0; k < padded; ++k)
         {
             const uint32_t slot = cursor + k;
@@ -465,6 +467,30 @@ void flatten(const HostModel& m, FlatScene& out)
             for (uint32_t c = 0; c < 8; ++c) depth[uint32_t(m.tree[i].children_start) + c] = depth[i] + 1;
             if (depth[i] > max_depth) max_depth = depth[i];
         }
+    // static insertion order of the leaves and the parent links (rasteriser tables)
+    out.leaf_seq.assign(out.n_nodes, 0u);
+    out.parent.assign(out.n_nodes, 0xffffffffu);
+    if (out.n_nodes && m.tree[0].children_start != 0)
+    {
+        std::vector<uint32_t> stack(1, 0u);
+        while (!stack.empty())
+        {
+            const uint32_t cur = stack.back();
+            stack.pop_back();
+            const uint32_t c0 = uint32_t(m.tree[cur].children_start);
+            for (uint32_t c = 0; c < 8; ++c)
+            {
+                const uint32_t ch = c0 + c;
+                out.parent[ch] = cur;
+                if (m.tree[ch].children_start != 0) stack.push_back(ch);
+                else
+                {
+                    out.leaf_seq[ch] = uint32_t(out.seq_leaf.size());
+                    out.seq_leaf.push_back(ch);
+                }
+            }
+        }
+    }
     out.level_start.assign(1, 0u);
     for (int d = int(max_depth); d >= 0; --d)
     {

@@ -43,6 +43,13 @@ struct FlatScene
     // inner nodes grouped by depth, deepest level first (bottom-up union of the per-frame film rectangles):
     // level l = inner_order[level_start[l] .. level_start[l+1])
     std::vector<uint32_t> inner_order, level_start;
+    // tables of the film-space rasteriser (render.cu: k_raster / k_resolve):
+    // leaf_seq[node]  = rank of the leaf in the reference's insertion order when every node is visited (kd_tree.cpp:363-435:
+    //                   LIFO over inner nodes, children examined in index order, leaves inserted when their parent is
+    //                   processed) — a ray's own insertion order is this order restricted to the leaves it lists;
+    // seq_leaf        = inverse of leaf_seq over the leaves; parent[node] = parent node (root: 0xffffffff);
+    // pos_face[first_slot + pos] = face index of the leaf's primitive at position `pos` of the reference's leaf order.
+    std::vector<uint32_t> leaf_seq, seq_leaf, parent, pos_face;
     uint32_t n_nodes = 0, n_slots = 0, n_leaves = 0, max_leaf_prims = 0;
 };
 

@@ -1151,6 +1151,8 @@ __global__ void __launch_bounds__(kBlock) k_render_culled(DevScene sc, DevCamera
     if (COUNT) flush_counters(counters, wc, rays_done);
 }
 
+#include "raster.cuh"
+
 // ---- K2: ray-list trace (get_intersection_data model branch for arbitrary rays) ---------------------------------
 template <bool STRICT, bool COUNT>
 __global__ void __launch_bounds__(kBlock) k_trace(DevScene sc, const float* __restrict__ rays, unsigned long long n, uint32_t* prim,
@@ -1504,7 +1506,8 @@ cudaError_t launch_slabs_final(const DevView& view, const DevSlabs& slabs, cudaS
 }
 
 cudaError_t launch_view_bounds(const DevScene& sc, const ViewParams& vp, const DevView& view, const DevCamera& cam,
-                               const DevPartition& part, const DevSlabs& slabs, cudaStream_t stream, cudaEvent_t after_reset)
+                               const DevPartition& part, const DevSlabs& slabs, cudaStream_t stream, cudaEvent_t after_reset,
+                               bool finish)
 {
     const int grid = (int)((sc.n_slots + kBlock - 1) / kBlock);
     k_view_bounds<<<grid < 1 ? 1 : grid, kBlock, 0, stream>>>(sc, vp, view);
@@ -1515,6 +1518,7 @@ cudaError_t launch_view_bounds(const DevScene& sc, const ViewParams& vp, const D
         e = cudaEventRecord(after_reset, stream);
         if (e != cudaSuccess) return e;
     }
+    if (!finish) return cudaSuccess;  // rasterised frame: no tile lists, no node rectangles
     // inner-node unions run in shared memory when the table fits: 16 B per node + 8 B per inner node
     static bool attr_set[64] = {};  // per device (function attributes belong to the device's context)
     const size_t kSmemMax = 200 * 1024;
@@ -1566,6 +1570,51 @@ cudaError_t launch_render_culled(const DevScene& sc, const DevCamera& cam, const
     }
     if (fp_fast) return launch_culled_t<false, false>(sc, cam, part, out, scratch, view, slabs, counters, jitter_seed, cfg, stream);
     return launch_culled_t<true, false>(sc, cam, part, out, scratch, view, slabs, counters, jitter_seed, cfg, stream);
+}
+
+// ---- rasterised frame (raster.cuh) ---------------------------------------------------------------------------------------
+cudaError_t launch_film_tables(const DevCamera& cam, const DevRaster& rs, cudaStream_t stream)
+{
+    const int n = cam.W + cam.H;
+    k_film_tables<<<(n + kBlock - 1) / kBlock, kBlock, 0, stream>>>(cam, rs);
+    return cudaGetLastError();
+}
+
+template <bool STRICT, bool COUNT>
+static cudaError_t launch_raster_t(const DevScene& sc, const ViewParams& vp, const DevCamera& cam, const DevPartition& part,
+                                   const DevOut& out, const DevScratch& scratch, const DevView& view, const DevRaster& rs,
+                                   const DevSlabs& slabs, DevCounters* counters, LaunchCfg cfg, cudaStream_t stream)
+{
+    static int per_sm = 0;
+    if (per_sm == 0)
+    {
+        int n = 0;
+        cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_resolve<STRICT, COUNT>, kBlock, 0);
+        if (e != cudaSuccess) return e;
+        per_sm = n < 1 ? 1 : n;
+    }
+    const int sms = cfg.grid / 4;
+    const uint32_t groups = (sc.n_slots + 31u) / 32u;
+    k_raster<STRICT, COUNT><<<(groups + 3u) / 4u, 128, 0, stream>>>(sc, vp, cam, part, view, rs, counters);
+    k_raster_big<STRICT, COUNT><<<sms * 4, kBlock, 0, stream>>>(sc, vp, cam, part, view, rs, counters);
+    k_hit_filter<<<sms * 4, kBlock, 0, stream>>>(rs);
+    int grid = sms * per_sm;
+    if (grid > cfg.grid) grid = cfg.grid;  // the spill areas are sized for cfg.grid CTAs
+    k_resolve<STRICT, COUNT><<<grid, kBlock, 0, stream>>>(sc, cam, part, out, scratch, view, rs, slabs, counters);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_raster(const DevScene& sc, const ViewParams& vp, const DevCamera& cam, const DevPartition& part, const DevOut& out,
+                          const DevScratch& scratch, const DevView& view, const DevRaster& rs, const DevSlabs& slabs,
+                          DevCounters* counters, int fp_fast, LaunchCfg cfg, cudaStream_t stream)
+{
+    if (counters)
+    {
+        if (fp_fast) return launch_raster_t<false, true>(sc, vp, cam, part, out, scratch, view, rs, slabs, counters, cfg, stream);
+        return launch_raster_t<true, true>(sc, vp, cam, part, out, scratch, view, rs, slabs, counters, cfg, stream);
+    }
+    if (fp_fast) return launch_raster_t<false, false>(sc, vp, cam, part, out, scratch, view, rs, slabs, counters, cfg, stream);
+    return launch_raster_t<true, false>(sc, vp, cam, part, out, scratch, view, rs, slabs, counters, cfg, stream);
 }
 
 cudaError_t launch_path(const DevScene& sc, const DevCamera& cam, const DevPartition& part, const DevOut& out,

@@ -183,10 +183,10 @@ ATRAY_HD FilmRect tri_film_rect(const ViewParams& vp, const float* a_f, const fl
     return r;
 }
 
-// Pixel-tile range (8x4 tiles) that can contain a ray whose film point lies in `r`:
+// Pixel range that can contain a ray whose film point lies in `r`:
 // film_x(x) = (-1 + 2(x/W))*h_fov*aspect, film_y(y) = -1 + 2(y/H) (renderer.cpp:317,329), inverted with slack.
-// Returns false when no tile is touched; `all` is set when the range cannot be bounded.
-ATRAY_HD bool film_rect_tiles(const ViewParams& vp, const FilmRect& r, int& tx0, int& tx1, int& ty0, int& ty1, bool& all)
+// Returns false when no pixel is touched; `all` is set when the range cannot be bounded.
+ATRAY_HD bool film_rect_pixels(const ViewParams& vp, const FilmRect& r, int& x0, int& x1, int& y0, int& y1, bool& all)
 {
     all = false;
     if (film_rect_is_empty(r)) return false;
@@ -200,7 +200,16 @@ ATRAY_HD bool film_rect_tiles(const ViewParams& vp, const FilmRect& r, int& tx0,
     if (xb < 0.0 || xa > W - 1.0 || yh < 0.0 || yl > H - 1.0) return false;
     const double cx0 = xa < 0.0 ? 0.0 : floor(xa), cx1 = xb > W - 1.0 ? W - 1.0 : ceil(xb);
     const double cy0 = yl < 0.0 ? 0.0 : floor(yl), cy1 = yh > H - 1.0 ? H - 1.0 : ceil(yh);
-    tx0 = (int)cx0 >> 3; tx1 = (int)cx1 >> 3; ty0 = (int)cy0 >> 2; ty1 = (int)cy1 >> 2;
+    x0 = (int)cx0; x1 = (int)cx1; y0 = (int)cy0; y1 = (int)cy1;
+    return true;
+}
+
+// Pixel-tile range (8x4 tiles) of the same pixels.
+ATRAY_HD bool film_rect_tiles(const ViewParams& vp, const FilmRect& r, int& tx0, int& tx1, int& ty0, int& ty1, bool& all)
+{
+    int x0 = 0, x1 = -1, y0 = 0, y1 = -1;
+    if (!film_rect_pixels(vp, r, x0, x1, y0, y1, all)) return false;
+    tx0 = x0 >> 3; tx1 = x1 >> 3; ty0 = y0 >> 2; ty1 = y1 >> 2;
     return true;
 }
 

@@ -67,10 +67,12 @@ class Context:
 
     # -- frames -----------------------------------------------------------------------------------------------------
     @staticmethod
-    def opts(fp_mode=api.FP_STRICT, count_work=False, seed=api.DEFAULT_SEED, rank=0, world=1, band_rows=8, cull=True):
-        """cull=False selects the unculled kernel (every listed leaf scanned completely, as the reference does)."""
+    def opts(fp_mode=api.FP_STRICT, count_work=False, seed=api.DEFAULT_SEED, rank=0, world=1, band_rows=8, cull=True, raster=False):
+        """cull=False selects the unculled kernel (every listed leaf scanned completely, as the reference does);
+        raster=True (frames without anti-aliasing) rasterises the frame triangle by triangle in film space instead of
+        traversing tile by tile (raster.cuh) — same bits."""
         return api.RenderOpts(fp_mode, 1 if count_work else 0, seed, api.Partition(rank, world, band_rows),
-                              0 if cull else api.RENDER_NO_CULL)
+                              (0 if cull else api.RENDER_NO_CULL) | (api.RENDER_RASTER if raster else 0))
 
     def render_begin(self, cam, opts, bgrx=None, t=None, prim=None):
         fr = api.Frame(_p(bgrx) if bgrx is not None else None, _p(t) if t is not None else None,

@@ -37,6 +37,9 @@ extern "C" {
 /* AtrayRenderOpts.flags. Default (0): per-frame film-space culling — identical results, far less work.
  * NO_CULL renders with the unculled kernel that scans every listed leaf completely, as the reference does. */
 #define ATRAY_RENDER_NO_CULL 1u
+/* RASTER (opt-in, frames without anti-aliasing): the frame is rasterised triangle by triangle in film space instead of
+ * traversed tile by tile — identical results again; measured slower on the headline workload. */
+#define ATRAY_RENDER_RASTER 2u
 
 typedef struct atray_model atray_model; /* host: ModelData + Model + KD_Tree (model.h:30-71, kd_tree.h:38-47) */
 typedef struct atray_ctx atray_ctx;     /* one GPU: uploaded scene, streams, frame buffers */

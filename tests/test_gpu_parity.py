@@ -111,6 +111,8 @@ def test_c4_standin_4k_full_size(A, port, standin):
     assert cc["rays"] == W * H and cc["tiles_sky"] + cc["tiles_busy"] == (W // 8) * (H // 4)
     assert cc["tiles_sky"] > 0.8 * (W // 8) * (H // 4) and cc["tri_tests"] < 0.02 * ctr["tri_tests"]
     assert cc["pass_v"] >= int((face != B.MISS).sum())
+    ras = sc.ctx.render(cam, sc.ctx.opts(raster=True))   # film-space rasteriser (opt-in, raster.cuh)
+    assert (ras["prim"] == face).all() and same_bits(ras["t"], t) and (ras["bgrx"] == img).all()
     fast = sc.ctx.render(cam, sc.ctx.opts(fp_mode=A.FP_FAST))
     mism = int((fast["prim"] != face).sum())
     assert mism <= 1e-5 * W * H, mism
@@ -165,6 +167,50 @@ def test_culled_equals_unculled_and_oracle(name, method, cap, A, port, meshes):
     o.close()
 
 
+@pytest.mark.parametrize("name,method,cap", [("knot_mid", 1, 300), ("knot_mid", 0, 32), ("Monkey", 1, 300), ("Deer", 1, 64)])
+def test_rasterised_frame_equals_tile_kernel(name, method, cap, A, meshes, monkeypatch):
+    """raster=True rasterises a frame without anti-aliasing triangle by triangle (raster.cuh) instead of traversing it
+    tile by tile. Same bits for every camera, with a band partition, and when the hit list overflows (those pixels go
+    through the exact per-ray walker inside k_resolve)."""
+    if name not in meshes:
+        pytest.skip("mesh not staged")
+    path, rescale = meshes[name]
+    sc = gpu_scene(A, path, rescale, method, cap)
+    frames = []
+    for i, kw in enumerate(CAMS):
+        W, H = (801, 453) if i % 2 else (640, 360)
+        cam = A.set_camera(W, H, samples_per_pixel=1 + (i % 3), **kw)
+        a = sc.ctx.render(cam, sc.ctx.opts(count_work=True, raster=True))
+        ca = sc.ctx.counters()
+        b = sc.ctx.render(cam)
+        assert (a["prim"] == b["prim"]).all() and same_bits(a["t"], b["t"]) and (a["bgrx"] == b["bgrx"]).all()
+        assert ca["rays"] == W * H * (1 + (i % 3))
+        again = sc.ctx.render(cam, sc.ctx.opts(raster=True))   # the pixel keys were restored: the next frame starts clean
+        assert (again["prim"] == a["prim"]).all() and same_bits(again["t"], a["t"])
+        frames.append((cam, a))
+    # band partition executed rank by rank on this GPU
+    cam, a = frames[1]
+    W, H = cam.width, cam.height
+    ctx = sc.ctx
+    d = [ctx.dev_alloc(W * H * 4) for _ in range(3)]
+    for world, band in ((2, 8), (3, 12)):
+        for rank in range(world):
+            ctx.render_device(cam, ctx.opts(rank=rank, world=world, band_rows=band, raster=True), d[0], d[1], d[2])
+        ctx.sync()
+        assert (ctx.to_host(d[0], np.zeros((H, W), np.uint32)) == a["bgrx"]).all()
+        assert same_bits(ctx.to_host(d[1], np.zeros((H, W), np.float32)), a["t"])
+        assert (ctx.to_host(d[2], np.zeros((H, W), np.uint32)) == a["prim"]).all()
+    for p in d:
+        ctx.dev_free(p)
+    # tiny hit list: nearly every hit pixel is flagged and re-traced exactly
+    monkeypatch.setenv("ATRAY_HIT_CAP", "64")
+    sc2 = gpu_scene(A, path, rescale, method, cap)
+    for cam, a in frames[:3]:
+        c = sc2.ctx.render(cam, sc2.ctx.opts(count_work=True, raster=True))
+        assert (c["prim"] == a["prim"]).all() and same_bits(c["t"], a["t"]) and (c["bgrx"] == a["bgrx"]).all()
+    assert sc2.ctx.counters()["overflow_rays"] > 0
+
+
 @pytest.mark.parametrize("cap", [12, 6])
 def test_cut_rule_on_split_edges(cap, A, port, tmp_path):
     """The "at most 5 accepted children" cut (kd_tree.cpp:374) only triggers for rays through a split edge. Eight cubes
@@ -190,9 +236,11 @@ def test_cut_rule_on_split_edges(cap, A, port, tmp_path):
         cam = A.set_camera(256, 256, eye=eye, facing=(0.0, 0.0, -1.0))
         a = sc.ctx.render(cam)
         b = sc.ctx.render(cam, sc.ctx.opts(cull=False))
+        c = sc.ctx.render(cam, sc.ctx.opts(raster=True))
         face, t, img = o.trace_primary(256, 256, threads=NTHREADS, eye=eye, facing=(0.0, 0.0, -1.0))
         assert (a["prim"] == face).all() and same_bits(a["t"], t) and (a["bgrx"] == img).all()
         assert (b["prim"] == face).all() and same_bits(b["t"], t)
+        assert (c["prim"] == face).all() and same_bits(c["t"], t)
         assert (face != B.MISS).any()
     o.close()
 

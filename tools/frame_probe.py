@@ -1,0 +1,39 @@
+#!/usr/bin/env python3
+"""Renders the C4 frame a few times on one GPU (device planes, no copy-out) and prints the frame's kernel time; under
+`ncu --metrics gpu__time_duration.sum` it gives the per-kernel split of one frame.
+usage: python tools/frame_probe.py [--reps N] [--raster] [--world N]"""
+import argparse
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import atray_b200 as A  # noqa: E402
+from tools import gen_standin_obj  # noqa: E402
+
+ap = argparse.ArgumentParser()
+ap.add_argument("--reps", type=int, default=10)
+ap.add_argument("--raster", action="store_true")
+ap.add_argument("--world", type=int, default=1)
+ap.add_argument("--count", action="store_true")
+args = ap.parse_args()
+W, H = 3840, 2160
+path = gen_standin_obj.ensure(os.path.join(os.environ.get("ATRAY_MESH_CACHE", "/tmp/atray_meshes"), "standin_272x256.obj"))
+m = A.load_model_data(path, 8)
+A.place_default(m, 0.0)
+sc = A.Scene(m)
+A.prep_scene(sc)
+ctx = sc.ctx
+cam = A.set_camera(W, H)
+planes = [ctx.dev_alloc(W * H * 4) for _ in range(3)]
+flush = ctx.dev_alloc(256 << 20)
+opts = ctx.opts(rank=0, world=args.world, band_rows=8, raster=args.raster, count_work=args.count)
+ms = []
+for i in range(args.reps + 2):
+    ctx.dev_memset(flush, 0, 256 << 20)
+    ctx.render_device(cam, opts, *planes)
+    ctx.sync()
+    if i >= 2:
+        ms.append(ctx.last_kernel_ms())
+print("world %d rank 0 raster=%s: %.1f us per frame (min %.1f)" % (args.world, args.raster, 1e3 * sum(ms) / len(ms), 1e3 * min(ms)), flush=True)
+if args.count:
+    print(ctx.counters())
