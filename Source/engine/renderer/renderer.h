@@ -8,7 +8,9 @@
 #include "scene.h"
 #include "camera.h"
 
-#define USE_KD_TREE
+#ifndef ATRAY_NO_KD_TREE
+#define USE_KD_TREE   // renderer.h:8; compile with -DATRAY_NO_KD_TREE for the reference's no-tree branch (renderer.cpp:58-82)
+#endif
 
 struct RenderTile { Tile tile; int64 ray_casts; };
 
@@ -69,6 +71,9 @@ inline void prep_scene(Scene& scene, uint32& kd_tree_max_nodes)
         std::free(sp);
         std::free(pl);
     }
+#if !defined(USE_KD_TREE)
+    atray_scene_use_kd_tree(scene.gpu, 0);   // get_intersection_data's #else branch: model box, then every face
+#endif
 }
 
 // renderer.cpp:403-455: returns immediately. twq.jobs is filled with one band-shaped job per 8 scanlines (inclusive

@@ -24,17 +24,9 @@ inline bool Setup_Texture(Texture& tex, TextureFileType file_type, uint32 width,
 }
 inline void Free_Texture(Texture& tex) { if (tex.bmb.buffer_memory) atray_host_free_pinned(tex.bmb.buffer_memory); tex.bmb.buffer_memory = nullptr; }
 
-// 32-bit BMP v3, bottom-up (texture.cpp:66-115) — debugging aid only.
+// Write_To_File (texture.cpp:66-115, 147-158): byte-identical BMP into "<file_name>_<id>.bmp", first id not yet on disk.
 inline bool Write_To_File(Texture& tex, const char* file_name)
 {
-    FILE* f = std::fopen(file_name, "wb");
-    if (!f) return false;
-    const uint32 img = tex.bmb.size(), off = 54, total = off + img;
-    unsigned char h[54] = {'B', 'M'};
-    auto put32 = [&](int at, uint32 v) { std::memcpy(h + at, &v, 4); };
-    put32(2, total); put32(10, off); put32(14, 40); put32(18, tex.bmb.width); put32(22, tex.bmb.height);
-    h[26] = 1; h[28] = 32; put32(34, img);
-    bool ok = std::fwrite(h, 1, 54, f) == 54 && std::fwrite(tex.bmb.buffer_memory, 1, img, f) == img;
-    std::fclose(f);
-    return ok;
+    if (tex.file_type != TextureFileType::BMP) return false;
+    return atray_write_bmp((const uint32_t*)tex.bmb.buffer_memory, tex.bmb.width, tex.bmb.height, file_name, nullptr, 0) == ATRAY_OK;
 }

@@ -94,12 +94,14 @@ _SIGS = {
     "atray_model_dump": [_vp] * 8,
     "atray_model_tree_dump": [_vp] * 7,
     "atray_model_flatten": [_vp, _vp, _vp, _vp, _vp],
+    "atray_write_bmp": [_vp, C.c_uint32, C.c_uint32, C.c_char_p, C.c_char_p, C.c_size_t],
     "atray_debug_film_rects": [_vp, C.POINTER(CameraStruct), _vp, _vp, _vp, _vp],
     "atray_camera_set": [C.POINTER(CameraStruct), _i, _i, _i, _u, _i, _vp, _vp, _f],
     "atray_device_count": [C.POINTER(_i)],
     "atray_ctx_create": [_i, C.POINTER(_vp)],
     "atray_scene_upload": [_vp, _vp, C.POINTER(Material), C.POINTER(Material)],
     "atray_scene_set_primitives": [_vp, _vp, _u, _vp, _u],
+    "atray_scene_use_kd_tree": [_vp, _i],
     "atray_last_ray_casts": [_vp, C.POINTER(_u64)],
     "atray_render_begin": [_vp, C.POINTER(CameraStruct), C.POINTER(RenderOpts), C.POINTER(Frame)],
     "atray_render_poll": [_vp, _u],
@@ -273,6 +275,16 @@ def place_default(model, rescale=40.0, translate=(0.0, -15.0, -38.0)):
     if rescale and rescale > 0:
         resize_scale(model, rescale)
     translate_to(model, translate)
+
+
+def Write_To_File(bgrx, file_name):
+    """Write_To_File(Texture&, const char*) — texture.cpp:66-115, 147-158: byte-identical BMP of a (H, W) uint32 BGRX bitmap
+    into "<file_name>_<id>.bmp" (first id not on disk yet). Returns the name written."""
+    a = np.ascontiguousarray(bgrx, np.uint32)
+    H, W = a.shape
+    out = C.create_string_buffer(1100)
+    _ck(_L.atray_write_bmp(_p(a), W, H, os.fsencode(file_name), out, 1100))
+    return os.fsdecode(out.value)
 
 
 def device_count():

@@ -4,6 +4,7 @@
 #include "device_types.h"
 #include "host_model.h"
 
+#include <cerrno>
 #include <chrono>
 #include <cmath>
 #include <cstdio>
@@ -40,6 +41,7 @@ struct atray_ctx
     size_t key_cap_px = 0;           // pixels the key planes hold (all-ones between frames)
     int tab_w = 0, tab_h = 0;        // capacity of the film tables
     int use_raster = 0;              // ATRAY_RASTER=1 rasterises every AA-off frame (otherwise per frame: ATRAY_RENDER_RASTER)
+    float4* d_faces = nullptr;       // face table of the no-tree branch (renderer.cpp:58-82)
     float4* d_fnorm = nullptr;       // per-face normal sources of the multi-bounce path
     float4* d_spheres = nullptr;     // analytic primitives (atray_scene_set_primitives)
     float4* d_planes = nullptr;
@@ -300,6 +302,8 @@ static void free_scene(atray_ctx* c)
     c->d_packet_leaf = c->d_leaf_seq = c->d_seq_leaf = c->d_parent = c->d_pos_face = nullptr;
     cudaFree(c->rs.big);
     c->rs.big = nullptr; c->rs.big_cap = 0;
+    cudaFree(c->d_faces);
+    c->d_faces = nullptr;
     c->scratch = DevScratch{};
     c->scene = DevScene{};
     c->has_scene = false;
@@ -411,7 +415,39 @@ int atray_scene_upload(atray_ctx* c, const atray_model* m, const AtrayMaterial* 
         c->scene.fnorm = c->d_fnorm;
         c->scene.smooth = smooth ? 1u : 0u;
     }
+    {
+        // face table of the no-tree branch: the three vertices of face j as {a, b - a, c - a}; the two subtractions are the
+        // first operations of get_triangle_ray_intersection_culled (model.h:78-79), done here once in f32
+        const HostModel& hm = m->m;
+        std::vector<float> ft(size_t(hm.faces.size()) * 12 + 4, 0.f);
+        for (size_t i = 0; i < hm.faces.size(); ++i)
+        {
+            const Face& fc = hm.faces[i];
+            const Vec3 a = hm.vertices[fc.v[0]], b = hm.vertices[fc.v[1]], cc = hm.vertices[fc.v[2]];
+            float* q = &ft[i * 12];
+            q[0] = a.x; q[1] = a.y; q[2] = a.z;
+            q[4] = b.x - a.x; q[5] = b.y - a.y; q[6] = b.z - a.z;
+            q[8] = cc.x - a.x; q[9] = cc.y - a.y; q[10] = cc.z - a.z;
+        }
+        CU(cudaMalloc(&c->d_faces, ft.size() * 4));
+        CU(cudaMemcpy(c->d_faces, ft.data(), ft.size() * 4, cudaMemcpyHostToDevice));
+        c->scene.faces = c->d_faces;
+        c->scene.n_faces = uint32_t(hm.faces.size());
+        c->scene.brute = 0;
+        const Box bb = hm.aabb;
+        c->scene.aabb_lo[0] = bb.lo.x; c->scene.aabb_lo[1] = bb.lo.y; c->scene.aabb_lo[2] = bb.lo.z;
+        c->scene.aabb_hi[0] = bb.hi.x; c->scene.aabb_hi[1] = bb.hi.y; c->scene.aabb_hi[2] = bb.hi.z;
+    }
     c->has_scene = true;
+    return ATRAY_OK;
+}
+
+int atray_scene_use_kd_tree(atray_ctx* c, int use_kd_tree)
+{
+    if (!c) return fail(ATRAY_EINVAL, "null context");
+    if (!c->has_scene) return fail(ATRAY_ESTATE, "use_kd_tree before scene_upload");
+    if (c->in_flight) return fail(ATRAY_ESTATE, "render in flight");
+    c->scene.brute = use_kd_tree ? 0u : 1u;
     return ATRAY_OK;
 }
 
@@ -604,7 +640,7 @@ static int enqueue_render(atray_ctx* c, const AtrayCamera* cam, const AtrayRende
         c->counters_valid = true;
     }
     DevPartition p{o->part.rank, o->part.world, o->part.band_rows};
-    if (cam->bounce_limit != 1 || c->scene.n_spheres || c->scene.n_planes)
+    if (cam->bounce_limit != 1 || c->scene.n_spheres || c->scene.n_planes)   // (the path kernel honours scene.brute too)
     {
         // multi-bounce / analytic primitives: the full get_intersection_data + cast_ray kernel
         CU(cudaEventRecord(c->ev_k0, c->stream));
@@ -616,7 +652,7 @@ static int enqueue_render(atray_ctx* c, const AtrayCamera* cam, const AtrayRende
         return ATRAY_OK;
     }
     ViewParams vp = make_view_params(cam);
-    const bool cull = !(o->flags & ATRAY_RENDER_NO_CULL) && vp.valid;
+    const bool cull = !(o->flags & ATRAY_RENDER_NO_CULL) && vp.valid && !c->scene.brute;   // no tree, no film-space culling
     if (cull)
     {
         const size_t tiles = size_t(vp.tiles_x) * size_t(vp.tiles_y);
@@ -976,6 +1012,39 @@ int atray_dev_memset(atray_ctx* c, void* dev, int value, size_t bytes)
     CU(cudaMemsetAsync(dev, value, bytes, c->stream));
     return ATRAY_OK;
 }
+// ---- bitmap file (texture.cpp:66-115): the one artefact the reference application writes ------------------------------
+int atray_write_bmp(const uint32_t* bgrx, uint32_t width, uint32_t height, const char* file_name, char* written_name, size_t cap)
+{
+    if (!bgrx || !file_name) return fail(ATRAY_EINVAL, "null argument");
+    const size_t len = std::strlen(file_name);
+    if (len + 8 > 1024) return fail(ATRAY_EINVAL, "file name too long (reference buffer: 1024)");
+#pragma pack(push, 1)
+    struct FileHeader { uint8_t type[2]; int32_t total_size; int16_t r1, r2; uint32_t offset_bits; };
+#pragma pack(pop)
+    struct DibHeader
+    {
+        uint32_t size_header, width, height; int16_t planes, bits_per_pixel;
+        uint32_t compression, buffer_size, ppm_x, ppm_y, clr_used, clr_important, red, green, blue, alpha;
+    };
+    static_assert(sizeof(FileHeader) == 14 && sizeof(DibHeader) == 56, "BMP header layout");
+    const uint32_t bytes = 4u * width * height;
+    DibHeader dib{uint32_t(sizeof(DibHeader)), width, height, 1, 32, 3u, bytes, 197u, 39u, 0u, 0u, 0x00FF0000u, 0x0000FF00u, 0x000000FFu, 0u};
+    FileHeader fh{{'B', 'M'}, int32_t(14u + sizeof(DibHeader) + bytes), 0, 0, uint32_t(14u + sizeof(DibHeader))};
+    char name[1024];
+    FILE* f = nullptr;
+    for (uint32_t id = 0; !f; ++id)   // CREATE_NEW semantics: the first "<name>_<id>.bmp" that does not exist yet
+    {
+        std::snprintf(name, len + 8, "%s_%u.bmp", file_name, id);
+        f = std::fopen(name, "wbx");
+        if (!f && errno != EEXIST) return fail(ATRAY_EIO, std::string("cannot create ") + name);
+    }
+    const bool ok = std::fwrite(&fh, 1, 14, f) == 14 && std::fwrite(&dib, 1, sizeof dib, f) == sizeof dib &&
+                    std::fwrite(bgrx, 1, bytes, f) == bytes;
+    std::fclose(f);
+    if (written_name && cap) std::snprintf(written_name, cap, "%s", name);
+    return ok ? ATRAY_OK : fail(ATRAY_EIO, "short write");
+}
+
 int atray_host_alloc_pinned(size_t bytes, void** out)
 {
     if (!out) return fail(ATRAY_EINVAL, "null argument");

@@ -33,6 +33,11 @@ struct DevScene
     const uint32_t* seq_leaf;      // n_leaves : inverse of leaf_seq
     const uint32_t* parent;        // n_nodes  : parent node, 0xffffffff for the root
     const uint32_t* pos_face;      // n_slots  : [first_slot + position in the reference's leaf order] → face index
+    // ---- no-tree path (renderer.cpp:58-82, the #ifndef USE_KD_TREE branch): model box, then every face in file order ----
+    const float4* faces;           // 3 float4 per face: {a, 0} {b - a, 0} {c - a, 0} from the vertex arrays
+    uint32_t n_faces;
+    uint32_t brute;                // per launch: non-zero → the model query is the no-tree branch
+    float aabb_lo[3], aabb_hi[3];  // Model::surrounding_aabb (model.h:41-61 after the transforms)
 };
 
 struct DevCamera

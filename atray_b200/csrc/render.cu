@@ -225,12 +225,56 @@ __device__ __forceinline__ void scan_ray_leaves(const DevScene& sc, int lane, in
     }
 }
 
+// ---- the no-tree model query, renderer.cpp:58-82 (#ifndef USE_KD_TREE): if get_ray_AABB_intersection(model box) is
+// non-zero, every face in file order through the triangle test, accepting t > tolerance && t < best (strict: the first
+// face with the smallest t wins). One ray per lane; the 32 lanes walk the face table together (uniform loads).
+template <bool STRICT, bool UV>
+__device__ __forceinline__ void brute_warp(const DevScene& sc, bool active, const RayL& ray, float& t_out, uint32_t& face_out,
+                                           float* u_out, float* v_out)
+{
+    typedef Fp<STRICT> F;
+    t_out = kMaxFloat;
+    face_out = 0xffffffffu;
+    const float ix = __frcp_rn(ray.dx), iy = __frcp_rn(ray.dy), iz = __frcp_rn(ray.dz);
+    const float4 lo = make_float4(sc.aabb_lo[0], sc.aabb_lo[1], sc.aabb_lo[2], 0.f), hi = make_float4(sc.aabb_hi[0], sc.aabb_hi[1], sc.aabb_hi[2], 0.f);
+    const bool go = active && box_entry(ray, ix, iy, iz, lo, hi) != 0.0f;
+    if (!__any_sync(FULL_MASK, go)) return;
+    float best = kMaxFloat;
+    for (uint32_t j = 0; j < sc.n_faces; ++j)
+    {
+        const float4 A = __ldg(&sc.faces[3 * (size_t)j]), AB = __ldg(&sc.faces[3 * (size_t)j + 1]), AC = __ldg(&sc.faces[3 * (size_t)j + 2]);
+        const float px = F::crs(ray.dy, AC.z, ray.dz, AC.y), py = F::crs(ray.dz, AC.x, ray.dx, AC.z), pz = F::crs(ray.dx, AC.y, ray.dy, AC.x);
+        const float det = F::dot(AB.x, AB.y, AB.z, px, py, pz);
+        if (!go || det < kTol) continue;
+        const float det_inv = __frcp_rn(det);
+        const float tx = F::sub(ray.ox, A.x), ty = F::sub(ray.oy, A.y), tz = F::sub(ray.oz, A.z);
+        const float u = F::mul(F::dot(tx, ty, tz, px, py, pz), det_inv);
+        if (u < 0.0f || u > 1.0f) continue;
+        const float qx = F::crs(ty, AB.z, tz, AB.y), qy = F::crs(tz, AB.x, tx, AB.z), qz = F::crs(tx, AB.y, ty, AB.x);
+        const float v = F::mul(F::dot(ray.dx, ray.dy, ray.dz, qx, qy, qz), det_inv);
+        if (v < 0.0f || F::add(u, v) > 1.0f) continue;
+        const float t = F::mul(F::dot(qx, qy, qz, AC.x, AC.y, AC.z), det_inv);
+        if (t > kTol && t < best)
+        {
+            best = t;
+            face_out = j;
+            if (UV) { *u_out = u; *v_out = v; }
+        }
+    }
+    t_out = best;
+}
+
 // ---- one warp traces up to 32 rays (one per lane). Result: t (MAX_FLOAT on miss) and face (MISS) per lane.
 template <bool STRICT, bool COUNT, bool UV = false>
 __device__ __forceinline__ void trace_warp(const DevScene& sc, const DevScratch& scratch, int warp_slot, int lane, bool active,
                                            const RayL& ray, uint2* leaves, uint32_t* stack, float& t_out, uint32_t& face_out,
                                            WorkCount& wc, float* u_out = nullptr, float* v_out = nullptr)
 {
+    if (sc.brute)  // warp-uniform: the no-tree branch of get_intersection_data
+    {
+        brute_warp<STRICT, UV>(sc, active, ray, t_out, face_out, u_out, v_out);
+        return;
+    }
     t_out = kMaxFloat;
     face_out = 0xffffffffu;
     int nleaf = 0;

@@ -60,6 +60,11 @@ class Context:
             pl[i] = api.Plane((C.c_float * 3)(*n), d, api.make_material(m))
         _ck(_L.atray_scene_set_primitives(self.h, C.cast(sp, C.c_void_p), len(spheres), C.cast(pl, C.c_void_p), len(planes)))
 
+    def use_kd_tree(self, use=True):
+        """renderer.h:8 USE_KD_TREE as a run-time switch: False → every model query is the no-tree branch
+        (renderer.cpp:58-82: model box, then every face in file order)."""
+        _ck(_L.atray_scene_use_kd_tree(self.h, 1 if use else 0))
+
     def last_ray_casts(self):
         v = C.c_uint64(0)
         _ck(_L.atray_last_ray_casts(self.h, C.byref(v)))

@@ -152,6 +152,12 @@ void atray_ctx_destroy(atray_ctx* ctx);
  * (renderer.cpp:152), materials[1] = the model's material (model.data.material). */
 int atray_scene_upload(atray_ctx* ctx, const atray_model* m, const AtrayMaterial* sky, const AtrayMaterial* model_mat);
 
+/* renderer.h:8 `#define USE_KD_TREE` as a run-time switch of the uploaded scene (default 1). With 0 every model query
+ * of frames, paths and ray lists is the reference's no-tree branch (renderer.cpp:58-82): get_ray_AABB_intersection on
+ * Model::surrounding_aabb, then every face in file order, accepting t > tolerance && t < best. O(faces) per ray — a
+ * geometry-exact cross-check for the tree, not a fast path. */
+int atray_scene_use_kd_tree(atray_ctx* ctx, int use_kd_tree);
+
 /* scene.spheres / scene.planes (engine/renderer/scene.h:13-24; app.cpp:111-129,139-142): replaces the current sets
  * (n = 0 removes them). Plane normals are normalised as prep_scene does (renderer.cpp:267-270). With primitives
  * present, or bounce_limit > 1, frames run get_intersection_data in full (plane > sphere > model > sky,
@@ -200,6 +206,10 @@ int atray_dev_copy_to_host(atray_ctx* ctx, void* host, const void* dev, size_t b
 int atray_dev_copy_from_host(atray_ctx* ctx, void* dev, const void* host, size_t bytes);
 /* asynchronous memset on the context stream (bench.py uses it to flush L2 between timed frames) */
 int atray_dev_memset(atray_ctx* ctx, void* dev, int value, size_t bytes);
+/* Write_To_File(Texture&, const char*) — engine/tools/texture.cpp:66-115, 147-158: byte-identical 32-bit BMP (14-byte
+ * file header, 56-byte DIB header with BI_BITFIELDS masks, rows bottom-up as stored) into "<file_name>_<id>.bmp" for the
+ * first id whose file does not exist. `written_name` (optional, `cap` bytes) receives the name used. Host only. */
+int atray_write_bmp(const uint32_t* bgrx, uint32_t width, uint32_t height, const char* file_name, char* written_name, size_t cap);
 int atray_host_alloc_pinned(size_t bytes, void** out);
 int atray_host_free_pinned(void* p);
 /* cross-process gather target (multi-GPU, one process per GPU): export a device allocation of this context and

@@ -12,6 +12,7 @@
  * Build: gcc -O2 -ffp-contract=off (no -ffast-math, no FMA contraction) — see oracle/Makefile.
  * Every function cites the reference file:line (relative to /root/reference/Source) it restates.
  */
+#include <errno.h>
 #include <math.h>
 #include <pthread.h>
 #include <stdint.h>
@@ -154,6 +155,7 @@ typedef struct
     struct or_material { v3 emission, reflection; float scatter; } sky_mat, model_mat;
     OR_VEC(struct or_sphere { v3 center; float radius; struct or_material m; }) spheres;
     OR_VEC(struct or_plane { v3 normal; float distance; struct or_material m; }) planes;
+    int no_tree; /* renderer.h:8: USE_KD_TREE undefined → the brute-force branch of get_intersection_data */
 } or_scene;
 typedef struct or_material or_material;
 typedef struct or_sphere or_sphere;
@@ -491,6 +493,34 @@ static float or_traverse(const or_scene* s, const or_ray* r, or_scratch* sc, uin
 }
 
 /* get_intersection_data, model branch only (renderer.cpp:34-57): returns 1 on a triangle hit */
+/* The #else branch of renderer.cpp:49-82 (USE_KD_TREE undefined): model box first, then every face in file order;
+ * a face is accepted when t > tolerance && t < the best so far (which starts at MAX_FLOAT, renderer.cpp:36). */
+static float or_brute(const or_scene* s, const or_ray* r, uint32_t* face, float* bu, float* bv)
+{
+    float best = OR_MAX_FLOAT;
+    if (or_entry_dist(r, &s->aabb))                                   /* renderer.cpp:59: non-zero float = true */
+    {
+        for (size_t j = 0; j < s->faces.n; j++)                       /* :61-79 */
+        {
+            or_tri tri;
+            tri.a = s->vertices.p[s->faces.p[j].v[0]];
+            tri.b = s->vertices.p[s->faces.p[j].v[1]];
+            tri.c = s->vertices.p[s->faces.p[j].v[2]];
+            float u, v;
+            float t = or_tri_hit(r, &tri, &u, &v);
+            if (t > OR_TOL && t < best) { best = t; *bu = u; *bv = v; *face = (uint32_t)j; }
+        }
+    }
+    return best;
+}
+
+/* model query of get_intersection_data: the tree (USE_KD_TREE, the shipped configuration) or the brute-force branch */
+static inline float or_model_query(const or_scene* s, const or_ray* r, or_scratch* sc, uint32_t* face, float* bu, float* bv,
+                                   or_counters* ct)
+{
+    return s->no_tree ? or_brute(s, r, face, bu, bv) : or_traverse(s, r, sc, face, bu, bv, ct);
+}
+
 static inline int or_intersect(const or_scene* s, v3 o, v3 d, or_scratch* sc, float* t_out, uint32_t* face, float* u,
                                float* v, or_counters* ct)
 {
@@ -498,7 +528,7 @@ static inline int or_intersect(const or_scene* s, v3 o, v3 d, or_scratch* sc, fl
     r.o = o; r.d = d;
     or_ray_prepare(&r);
     uint32_t f = OR_MISS; float bu = 0, bv = 0;
-    float t = or_traverse(s, &r, sc, &f, &bu, &bv, ct);
+    float t = or_model_query(s, &r, sc, &f, &bu, &bv, ct);
     if (t > OR_TOL && t < OR_MAX_FLOAT) { *t_out = t; *face = f; *u = bu; *v = bv; return 1; }
     *t_out = OR_MAX_FLOAT; *face = OR_MISS; *u = 0; *v = 0;
     return 0;
@@ -604,6 +634,9 @@ void* or_scene_create(const char* obj_path, int loader_threads, float rescale, f
     if (or_build_tree(s, method, cap) != 0) { return 0; }
     return s;
 }
+
+/* 0 → every query takes the no-tree branch (the reference compiled without USE_KD_TREE, renderer.h:8) */
+void or_scene_use_kd_tree(void* h, int use) { ((or_scene*)h)->no_tree = !use; }
 
 void or_scene_destroy(void* h)
 {
@@ -913,7 +946,7 @@ static void or_intersect_full(const or_scene* s, v3 o, v3 d, or_scratch* sc, or_
     {
         or_ray r; r.o = o; r.d = d; or_ray_prepare(&r);
         uint32_t f = OR_MISS; float bu = 0, bv = 0;
-        float t = or_traverse(s, &r, sc, &f, &bu, &bv, ct);
+        float t = or_model_query(s, &r, sc, &f, &bu, &bv, ct);
         if (t > OR_TOL && t < dist) { dist = t; face = f; u = bu; v = bv; near_model = 1; }      /* :52-57 */
     }
     for (size_t i = 0; i < s->spheres.n; i++)                                                     /* :86-96 */
@@ -1050,4 +1083,39 @@ void or_pcg32(unsigned long long state, unsigned long long stream, int n, unsign
 {
     or_rng s = { state, stream };
     for (int i = 0; i < n; i++) out[i] = or_random_u32(&s);
+}
+
+/* BMP_FILE_FORMAT::Write_To_File (engine/tools/texture.cpp:66-115) under Write_To_File(Texture&, name) (:147-158):
+ * 14-byte packed file header + 56-byte DIB header (compression 3 = bit fields, ppm 197 x 39, masks R/G/B/0) + the
+ * BGRX rows bottom-up exactly as they sit in the bitmap buffer. The file is "<file_name>_<id>.bmp" for the first id
+ * whose file does not exist yet (pl_create_file = CreateFileA(CREATE_NEW), PL/Win32/pl_utils_win32.cpp:143-158); the
+ * name is formatted into length + 8 characters (texture.cpp:101). Returns 1 like the reference (0 on a bad argument). */
+int or_write_bmp(const unsigned* pixels, unsigned W, unsigned H, const char* file_name)
+{
+    if (!pixels || !file_name) return 0;
+    unsigned char h[70];
+    memset(h, 0, sizeof h);
+    const unsigned size = 4u * W * H;                      /* BitmapBuffer::size(), texture.h:17 */
+    const unsigned total = 14u + 56u + size, off = 14u + 56u, hdr = 56u;
+    const unsigned short planes = 1, bpp = 32;
+    const unsigned comp = 3, ppx = 197, ppy = 39, rm = 0x00FF0000u, gm = 0x0000FF00u, bm = 0x000000FFu;
+    h[0] = 'B'; h[1] = 'M';
+    memcpy(h + 2, &total, 4); memcpy(h + 10, &off, 4);
+    memcpy(h + 14, &hdr, 4); memcpy(h + 18, &W, 4); memcpy(h + 22, &H, 4); memcpy(h + 26, &planes, 2); memcpy(h + 28, &bpp, 2);
+    memcpy(h + 30, &comp, 4); memcpy(h + 34, &size, 4); memcpy(h + 38, &ppx, 4); memcpy(h + 42, &ppy, 4);
+    memcpy(h + 54, &rm, 4); memcpy(h + 58, &gm, 4); memcpy(h + 62, &bm, 4);
+    const size_t len = strlen(file_name);
+    if (len + 8 > 1024) return 0;
+    char name[1024];
+    FILE* f = 0;
+    for (unsigned id = 0; !f; id++)
+    {
+        snprintf(name, len + 8, "%s%c%u%s", file_name, '_', id, ".bmp");
+        f = fopen(name, "wbx");
+        if (!f && errno != EEXIST) return 1;               /* reference: no handle → nothing written, still TRUE */
+    }
+    fwrite(h, 1, 70, f);
+    fwrite(pixels, 1, size, f);
+    fclose(f);
+    return 1;
 }

@@ -21,6 +21,7 @@ DEFAULT_HFOV = 1.0
 
 
 PORT_PATH = os.path.join(HERE, "liboracle.so")
+NOTREE_PATH = os.path.join(HERE, "_ref", "libatray_ref_notree.so")
 
 
 class Backend:
@@ -53,6 +54,8 @@ class Backend:
         self.render_path.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_uint, C.c_int, C.c_int, C.c_ulonglong, C.c_void_p,
                                      C.c_void_p, C.c_float, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                      C.c_void_p]
+        self.write_bmp = g("write_bmp"); self.write_bmp.restype = C.c_int
+        self.write_bmp.argtypes = [C.c_void_p, C.c_uint, C.c_uint, C.c_char_p]
         self.render = None
         self.trace_primary_ex = None
         if prefix == "ref_":
@@ -63,6 +66,7 @@ class Backend:
         else:
             self.trace_primary_ex = g("trace_primary_ex")
             self.trace_primary_ex.argtypes = self.trace_primary.argtypes + [C.c_void_p]
+            self.scene_use_kd_tree = g("scene_use_kd_tree"); self.scene_use_kd_tree.argtypes = [C.c_void_p, C.c_int]
             self.accepted_hits = g("accepted_hits")
             self.accepted_hits.restype = C.c_longlong
             self.accepted_hits.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_float, C.c_int,
@@ -84,6 +88,17 @@ def ref():
     if "ref" not in _backends:
         _backends["ref"] = Backend(LIB_PATH, "ref_")
     return _backends["ref"]
+
+
+def ref_notree():
+    """The reference built without `#define USE_KD_TREE` (renderer.h:8): get_intersection_data's brute-force branch."""
+    if "ref_notree" not in _backends:
+        _backends["ref_notree"] = Backend(NOTREE_PATH, "ref_")
+    return _backends["ref_notree"]
+
+
+def ref_notree_available():
+    return os.path.exists(NOTREE_PATH)
 
 
 def port():
@@ -113,6 +128,10 @@ class Scene:
         self.b.counts(self.h, _p(c))
         (self.n_vertices, self.n_normals, self.n_tex, self.n_faces, self.n_nodes, self.n_refs, self.n_inner,
          self.max_leaf) = [int(x) for x in c]
+
+    def use_kd_tree(self, use):
+        """port() only: 0 → the no-tree branch of get_intersection_data (renderer.cpp:58-82)."""
+        self.b.scene_use_kd_tree(self.h, 1 if use else 0)
 
     def close(self):
         if self.h:
@@ -221,6 +240,12 @@ def camera(backend, W, H, eye=DEFAULT_EYE, facing=DEFAULT_FACING, hfov=DEFAULT_H
     e, f = _f3(eye), _f3(facing)
     backend.camera(W, H, _p(e), _p(f), hfov, _p(out))
     return out
+
+
+def write_bmp(backend, bgrx, file_name):
+    """Write_To_File on a (H, W) uint32 bitmap: "<file_name>_<id>.bmp" (texture.cpp:66-115)."""
+    a = np.ascontiguousarray(bgrx, np.uint32)
+    return backend.write_bmp(_p(a), a.shape[1], a.shape[0], os.fsencode(file_name))
 
 
 def pcg32(backend, state, stream, n):

@@ -27,6 +27,13 @@ PY
 g++ -std=c++17 -O2 -ffp-contract=off -fPIC -shared -fno-semantic-interposition -pthread -w \
     -I "$HERE/overlay" -I "$HERE" -I "$STAGE/Source" \
     "$HERE/ref_harness.cpp" -o "$OUT/libatray_ref.so"
+# second build: the reference compiled WITHOUT `#define USE_KD_TREE` (renderer.h:8) — get_intersection_data's brute-force
+# branch (renderer.cpp:58-82), the oracle of atray_scene_use_kd_tree(ctx, 0)
+sed -i 's|^#define USE_KD_TREE|// #define USE_KD_TREE  (no-tree build)|' "$STAGE/Source/engine/renderer/renderer.h"
+! grep -q '^#define USE_KD_TREE' "$STAGE/Source/engine/renderer/renderer.h"
+g++ -std=c++17 -O2 -ffp-contract=off -fPIC -shared -fno-semantic-interposition -pthread -w \
+    -I "$HERE/overlay" -I "$HERE" -I "$STAGE/Source" \
+    "$HERE/ref_harness.cpp" -o "$OUT/libatray_ref_notree.so"
 # mesh inputs for the parity tests travel beside the .so (data, not source; git-ignored)
 cp "$REF/Assets/Cube.obj" "$REF/Assets/Deer.obj" "$REF/Assets/Monkey.obj" "$REF/Assets/Simple.obj" "$OUT/assets/"
 echo "built $OUT/libatray_ref.so"

@@ -106,7 +106,8 @@ uint64 pl_get_file_size(void* handle)
 	return (uint64)sz;
 }
 b32 pl_load_file_into(void* handle, void* block, uint32 file_size) { return fread(block, 1, file_size, (FILE*)handle) == file_size; }
-b32 pl_create_file(void** file_handle, char* path) { FILE* f = fopen(path, "wb"); *file_handle = f; return f != 0; }
+// CreateFileA(..., CREATE_NEW, ...) (PL/Win32/pl_utils_win32.cpp:143-158): fails when the file already exists
+b32 pl_create_file(void** file_handle, char* path) { FILE* f = fopen(path, "wbx"); *file_handle = f; return f != 0; }
 b32 pl_append_to_file(void* file_handle, void* block, int32 n) { return fwrite(block, 1, n, (FILE*)file_handle) == (size_t)n; }
 b32 pl_close_file_handle(void* file_handle) { return fclose((FILE*)file_handle) == 0; }
 void pl_throw_error_box(const char* error) { fprintf(stderr, "PL error: %s\n", error); }

@@ -457,4 +457,15 @@ void ref_pcg32(unsigned long long state, unsigned long long stream, int n, unsig
 	for (int i = 0; i < n; i++) out[i] = random_u32(&s);
 }
 
+// The reference's BMP writer on a caller-supplied BGRX bitmap (texture.cpp:66-115, 147-158): "<file_name>_<id>.bmp".
+int ref_write_bmp(const unsigned* pixels, unsigned W, unsigned H, const char* file_name)
+{
+	Texture tex;
+	if (!Setup_Texture(tex, TextureFileType::BMP, W, H)) return 0;
+	memcpy(tex.bmb.buffer_memory, pixels, (size_t)W * H * 4);
+	const bool ok = Write_To_File(tex, file_name);
+	pl_buffer_free(tex.bmb.buffer_memory);
+	return ok ? 1 : 0;
+}
+
 } // extern "C"

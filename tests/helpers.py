@@ -93,3 +93,9 @@ PATH_PLANES = [((0.0, 1.0, 0.05), -20.0, ((0.05, 0.05, 0.05), (0.6, 0.6, 0.7), 0
 # (spp, bounce_limit, anti_aliasing)
 PATH_CONFIGS = [(1, 1, 0), (2, 5, 0), (3, 4, 1), (1, 8, 1)]
 PW, PH = 160, 90
+
+
+def bmp_test_bitmap(w=7, h=5):
+    """Deterministic BGRX bitmap (alpha byte 0, as Set_Pixel writes it) for the BMP writer tests."""
+    y, x = np.mgrid[0:h, 0:w].astype(np.uint32)
+    return ((x * 37 + y * 11) & 255) | (((x * 5 + y * 91 + 3) & 255) << 8) | (((x * 17 + y * 29 + 200) & 255) << 16)

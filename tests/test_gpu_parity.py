@@ -474,6 +474,42 @@ def test_multi_bounce_path_equals_oracle(name, A, port, meshes):
     o.close()
 
 
+@pytest.mark.parametrize("name", ["knot_small", "Cube", "Deer", "Monkey"])
+def test_no_tree_branch_matches_reference_golden_and_oracle(name, A, port, meshes):
+    """atray_scene_use_kd_tree(ctx, 0) = the reference compiled without USE_KD_TREE (renderer.cpp:58-82): frames, jittered
+    frames, ray lists and the multi-bounce path against golden vectors made by that reference build, then the tree back."""
+    from oracle import bind as B
+    if name not in meshes:
+        pytest.skip("mesh not staged")
+    g = np.load(os.path.join(GOLDEN, "notree_%s.npz" % name))
+    path, rescale = meshes[name]
+    sc = gpu_scene(A, path, rescale)
+    with_tree = sc.ctx.render(A.set_camera(PW, PH))
+    sc.ctx.use_kd_tree(False)
+    out = sc.ctx.render(A.set_camera(PW, PH))
+    assert (out["prim"] == g["face"]).all() and (bits(out["t"]) == g["t_bits"]).all() and (out["bgrx"] == g["bgrx"]).all()
+    jit = sc.ctx.render(A.set_camera(PW, PH, anti_aliasing=1, samples_per_pixel=4), sc.ctx.opts(seed=SEED))
+    assert (jit["bgrx"] == g["jitter_bgrx"]).all()
+    prim, t = sc.ctx.trace_rays(random_rays(sc.model.dump()["aabb"], 4000, int(g["ray_seed"])))
+    assert (prim == g["ray_face"]).all() and (bits(t) == g["ray_t_bits"]).all()
+    sc.ctx.set_primitives(PATH_SPHERES, PATH_PLANES)
+    p = sc.ctx.render(A.set_camera(PW, PH, anti_aliasing=1, samples_per_pixel=2, bounce_limit=4), sc.ctx.opts(seed=SEED + 1))
+    assert (p["bgrx"] == g["path_bgrx"]).all() and (bits(p["t"]) == g["path_t_bits"]).all() and (p["prim"] == g["path_prim"]).all()
+    assert sc.ctx.last_ray_casts() == int(g["path_casts"])
+    sc.ctx.set_primitives([], [])
+    # other camera and size against the oracle's no-tree branch
+    o = B.Scene(port, path, rescale=rescale)
+    o.use_kd_tree(False)
+    eye, facing = (3.0, -4.0, 9.0), (-0.2, -0.4, -1.0)
+    a = sc.ctx.render(A.set_camera(333, 187, eye=eye, facing=facing, h_fov=0.7))
+    face, tt, img = o.trace_primary(333, 187, threads=NTHREADS, eye=eye, facing=facing, hfov=0.7)
+    assert (a["prim"] == face).all() and same_bits(a["t"], tt) and (a["bgrx"] == img).all()
+    o.close()
+    sc.ctx.use_kd_tree(True)
+    back = sc.ctx.render(A.set_camera(PW, PH))
+    assert (back["prim"] == with_tree["prim"]).all() and same_bits(back["t"], with_tree["t"])
+
+
 def test_errors_on_device_side(A, meshes):
     ctx = A.Context(0)
     with pytest.raises(A.AtrayError):
