@@ -1,7 +1,7 @@
 // Headless replay of the reference's render_app call sequence (engine/app.cpp:59-195) against the drop-in host layer:
 // load → get_AABB → translate_to → set_camera → materials/scene → prep_scene → start_render_from_camera →
 // poll wait_for_render_from_camera_to_finish(33 ms) → stats (+ optional BMP and raw plane dumps).
-//   app_headless <obj> [W H] [rescale] [out.bmp] [out_planes.bin]
+//   app_headless <obj> [W H] [rescale] [bmp_base] [out_planes.bin]
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -11,7 +11,7 @@
 
 int main(int argc, char** argv)
 {
-    if (argc < 2) { std::fprintf(stderr, "usage: %s model.obj [W H] [rescale] [out.bmp] [planes.bin]\n", argv[0]); return 2; }
+    if (argc < 2) { std::fprintf(stderr, "usage: %s model.obj [W H] [rescale] [bmp_base] [planes.bin]\n", argv[0]); return 2; }
     const uint32 W = argc > 3 ? (uint32)std::atoi(argv[2]) : 1280, H = argc > 3 ? (uint32)std::atoi(argv[3]) : 720;
     const f32 rescale = argc > 4 ? (f32)std::atof(argv[4]) : 0.f;
     Texture texture;

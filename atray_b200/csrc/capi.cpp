@@ -61,6 +61,8 @@ struct atray_ctx
     bool stage_bgrx = false, stage_t = false, stage_prim = false;
     bool in_flight = false;
     cudaEvent_t ev_k0 = nullptr, ev_k1 = nullptr, ev_done = nullptr;
+    cudaEvent_t ev_kr = nullptr;     // between the per-frame view pass and the render kernel (atray_last_render_kernel_ms)
+    bool have_split = false;
     bool have_kernel_time = false;
     // slab-pipelined copy-out (atray_render_begin): the copy stream waits on the render kernel's per-slab counters
     cudaStream_t copy_stream = nullptr;
@@ -263,6 +265,7 @@ int atray_ctx_create(int device, atray_ctx** out)
     if (e == cudaSuccess) e = cudaMalloc(&c->d_casts, sizeof(unsigned long long));
     if (e == cudaSuccess) e = cudaEventCreate(&c->ev_k0);
     if (e == cudaSuccess) e = cudaEventCreate(&c->ev_k1);
+    if (e == cudaSuccess) e = cudaEventCreate(&c->ev_kr);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_done, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_reset, cudaEventDisableTiming);
@@ -324,6 +327,7 @@ void atray_ctx_destroy(atray_ctx* c)
     cudaFree(c->d_rays); cudaFree(c->d_rprim); cudaFree(c->d_rt);
     if (c->ev_k0) cudaEventDestroy(c->ev_k0);
     if (c->ev_k1) cudaEventDestroy(c->ev_k1);
+    if (c->ev_kr) cudaEventDestroy(c->ev_kr);
     if (c->ev_done) cudaEventDestroy(c->ev_done);
     if (c->ev_reset) cudaEventDestroy(c->ev_reset);
     for (int k = 0; k < kMaxSlabs; ++k)
@@ -648,6 +652,7 @@ static int enqueue_render(atray_ctx* c, const AtrayCamera* cam, const AtrayRende
                        o->jitter_seed, c->cfg, c->stream));
         CU(cudaEventRecord(c->ev_k1, c->stream));
         c->have_kernel_time = true;
+        c->have_split = false;
         c->casts_valid = true;
         return ATRAY_OK;
     }
@@ -702,6 +707,7 @@ static int enqueue_render(atray_ctx* c, const AtrayCamera* cam, const AtrayRende
         // the film rectangles depend on the camera: recomputed every frame, inside the timed region
         const DevSlabs slabs = make_slabs(to_dev(cam), p, want_slabs);
         CU(launch_view_bounds(c->scene, vp, c->view, to_dev(cam), p, slabs, c->stream, want_slabs > 1 ? c->ev_reset : nullptr));
+        CU(cudaEventRecord(c->ev_kr, c->stream));
         CU(launch_render_culled(c->scene, to_dev(cam), p, out, c->scratch, c->view, slabs, ctr, o->fp_mode == ATRAY_FP_FAST,
                                 o->jitter_seed, c->cfg, c->stream));
         if (slabs_out) *slabs_out = slabs;
@@ -711,6 +717,7 @@ static int enqueue_render(atray_ctx* c, const AtrayCamera* cam, const AtrayRende
                          o->jitter_seed, c->cfg, c->stream));
     CU(cudaEventRecord(c->ev_k1, c->stream));
     c->have_kernel_time = true;
+    c->have_split = cull && !raster;
     return ATRAY_OK;
 }
 
@@ -875,6 +882,16 @@ int atray_last_kernel_ms(atray_ctx* c, float* ms)
     return ATRAY_OK;
 }
 
+int atray_last_render_kernel_ms(atray_ctx* c, float* ms)
+{
+    if (!c || !ms) return fail(ATRAY_EINVAL, "null argument");
+    if (!c->have_kernel_time || !c->have_split) return fail(ATRAY_ESTATE, "the last launch was not a culled frame");
+    CU(cudaSetDevice(c->device));
+    CU(cudaEventSynchronize(c->ev_k1));
+    CU(cudaEventElapsedTime(ms, c->ev_kr, c->ev_k1));
+    return ATRAY_OK;
+}
+
 // ---- ray lists ------------------------------------------------------------------------------------------------------
 int atray_trace_rays_device(atray_ctx* c, const float* rays_dev, uint64_t n, int32_t fp_mode, int32_t count_work,
                             uint32_t* prim_dev, float* t_dev)
@@ -896,6 +913,7 @@ int atray_trace_rays_device(atray_ctx* c, const float* rays_dev, uint64_t n, int
                     c->stream));
     CU(cudaEventRecord(c->ev_k1, c->stream));
     c->have_kernel_time = true;
+    c->have_split = false;
     return ATRAY_OK;
 }
 

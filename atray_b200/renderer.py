@@ -118,6 +118,12 @@ class Context:
         _ck(_L.atray_last_kernel_ms(self.h, C.byref(ms)))
         return ms.value
 
+    def last_render_kernel_ms(self):
+        """Device time of the render kernel alone (k_render_culled) in the last culled frame."""
+        ms = C.c_float(0)
+        _ck(_L.atray_last_render_kernel_ms(self.h, C.byref(ms)))
+        return ms.value
+
     def counters(self):
         c = api.Counters()
         _ck(_L.atray_get_counters(self.h, C.byref(c)))

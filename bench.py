@@ -54,23 +54,62 @@ def measured_peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks/throttle reasons during the timed region (B200_PROFILING.md)."""
+    """SM clock and clock-event (throttle) reasons DURING the timed region (B200_PROFILING.md). A frame takes a third of a
+    millisecond, so the sampler reads NVML directly (≈1 kHz); `nvidia-smi` (≈50 ms per query) is the fallback."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    BITS = {"sw_power_cap": 0x4, "hw_slowdown": 0x8, "sw_thermal_slowdown": 0x20, "hw_thermal_slowdown": 0x40}
 
     def __init__(self, gpu_index):
-        self.idx, self.rows, self.stop_flag, self.th = gpu_index, [], False, None
+        self.idx, self.sm, self.mx, self.reasons, self.stop_flag, self.th, self.source = gpu_index, [], [], set(), False, None, None
+        self.nv, self.h = None, None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv, self.h = pynvml, pynvml.nvmlDeviceGetHandleByIndex(self._nvml_index(pynvml, gpu_index))
+            self.source = "nvml"
+        except Exception:
+            self.nv, self.source = None, "nvidia-smi"
+
+    @staticmethod
+    def _nvml_index(nv, cuda_index):
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        if vis:
+            tok = vis.split(",")[cuda_index].strip()
+            if tok.isdigit():
+                return int(tok)
+            for i in range(nv.nvmlDeviceGetCount()):
+                u = nv.nvmlDeviceGetUUID(nv.nvmlDeviceGetHandleByIndex(i))
+                u = u.decode() if isinstance(u, bytes) else u
+                if u.startswith(tok) or tok in u:
+                    return i
+        return cuda_index
 
     def _loop(self):
         while not self.stop_flag:
             try:
+                if self.nv is not None:
+                    self.sm.append(float(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM)))
+                    self.mx.append(float(self.nv.nvmlDeviceGetMaxClockInfo(self.h, self.nv.NVML_CLOCK_SM)))
+                    try:
+                        m = self.nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                    except Exception:
+                        m = self.nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                    for name, bit in self.BITS.items():
+                        if m & bit:
+                            self.reasons.add(name)
+                    time.sleep(0.0005)
+                    continue
                 out = subprocess.run(["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits"],
                                      stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True, timeout=5).stdout.strip()
-                if out:
-                    self.rows.append([c.strip() for c in out.splitlines()[0].split(",")])
+                r = [c.strip() for c in out.splitlines()[0].split(",")] if out else []
+                if len(r) >= 9:
+                    self.sm.append(float(r[1])); self.mx.append(float(r[2]))
+                    for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[5:9]):
+                        if v.lower().startswith("active"):
+                            self.reasons.add(name)
             except Exception:
-                pass
-            time.sleep(0.05)
+                time.sleep(0.01)
 
     def start(self):
         self.th = threading.Thread(target=self._loop, daemon=True)
@@ -80,16 +119,8 @@ class ClockSampler:
         self.stop_flag = True
         if self.th:
             self.th.join(timeout=6)
-        sm = [float(r[1]) for r in self.rows if len(r) >= 9 and r[1].replace(".", "").isdigit()]
-        mx = [float(r[2]) for r in self.rows if len(r) >= 9 and r[2].replace(".", "").isdigit()]
-        reasons = set()
-        for r in self.rows:
-            if len(r) >= 9:
-                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[5:9]):
-                    if v.lower().startswith("active"):
-                        reasons.add(name)
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+        return {"sm_mhz": float(np.median(self.sm)) if self.sm else None, "sm_max_mhz": max(self.mx) if self.mx else None,
+                "reasons": sorted(self.reasons), "samples": len(self.sm), "source": self.source}
 
 
 # ---- CPU side: the reference's own renderer (oracle/_ref) or, if it could not be built, the C port -----------------
@@ -215,22 +246,23 @@ def run_ours(args):
         ctx.render_device(cam, opts, gather.planes["bgrx"], gather.planes["t"], gather.planes["prim"])
 
     # ---- HBM-resident leg: `value` -------------------------------------------------------------------------------------
+    # clocks are sampled from the first warm-up frame to the last end-to-end frame (a timed leg lasts only milliseconds)
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
     for _ in range(args.warmup):
         flush_l2()
         step_device()
     barrier()
-    sampler = ClockSampler(local_rank)
-    if rank == 0:
-        sampler.start()
     wall0 = time.perf_counter()
-    per_step_ms = []
+    per_step_ms, render_ms = [], []
     for _ in range(args.steps):
         flush_l2()
         step_device()
         per_step_ms.append(ctx.last_kernel_ms())       # waits for this step's stop event (device time on our stream)
+        render_ms.append(ctx.last_render_kernel_ms())  # k_render_culled alone (event after the per-frame view pass)
     barrier()
     wall_ms = 1e3 * (time.perf_counter() - wall0)
-    clocks = sampler.stop() if rank == 0 else None
     dev_ms = float(sum(per_step_ms))
     if dist is not None:
         import torch
@@ -282,6 +314,9 @@ def run_ours(args):
         tt = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         e2e_s = float(tt.item())
+    clocks = sampler.stop() if rank == 0 else None
+    if clocks is not None:
+        clocks["window"] = "warm-up + value leg + e2e leg"
     e2e = {"value": total_rays / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": 136,
            "d2h_bytes_per_step": W * H * 4, "ms_per_step": 1e3 * e2e_s / args.steps,
            "note": "host BGRX bitmap (Texture.bmb.buffer_memory, pinned) is the output; input per step is the camera/settings "
@@ -297,8 +332,9 @@ def run_ours(args):
         ops_ray, bytes_ray = ops_and_bytes_per_ray(ctr)
         k0 = ctx.microbench()
         hbm_peak, peak_src = measured_peaks()
-        # dominant kernel = k_render: one launch per step per rank; per-launch algorithmic bytes = bytes/ray × rays of the launch
-        launch_ms = dev_ms / args.steps
+        # dominant kernel = k_render_culled: one launch per step per rank, timed alone with CUDA events on the library's stream
+        # (after k_view_bounds + k_view_finish); per-launch algorithmic bytes = bytes/ray × rays of the launch
+        launch_ms = float(sum(render_ms)) / args.steps
         launch_rays = my_rays
         achieved_gbs = bytes_ray * launch_rays / (launch_ms * 1e-3) / 1e9
         fp32_achieved = ops_ray * launch_rays / (launch_ms * 1e-3)
@@ -306,7 +342,8 @@ def run_ours(args):
         bound_hbm = hbm_peak * 1e9 / bytes_ray / 1e6
         per_gpu = value / world
         roofline = {"bound": "hbm", "achieved": achieved_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": achieved_gbs / hbm_peak,
-                    "traffic": load_traffic(), "peak_source": peak_src, "kernel": "k_render",
+                    "traffic": load_traffic(), "peak_source": peak_src, "kernel": "k_render_culled<STRICT>" if args.fp == "strict" else "k_render_culled<FAST>",
+                    "kernel_ms_per_launch": launch_ms, "kernel_share_of_step": launch_ms / (dev_ms / args.steps),
                     "algorithmic_bytes_per_ray": bytes_ray, "algorithmic_fp32_ops_per_ray": ops_ray,
                     "fp32": {"achieved_lane_ops_per_s": fp32_achieved, "peak_lane_ops_per_s": k0["fp32_lane_ops_per_s"],
                              "frac": fp32_achieved / k0["fp32_lane_ops_per_s"], "peak_source": "K0 FFMA microbenchmark, this run"},
@@ -328,7 +365,9 @@ def run_ours(args):
                             "seconds": secs}
         line = base_line(args.gpus, args.steps, args.warmup)
         line.update({"impl": "ours", "value": value, "ms_per_step": dev_ms_max / args.steps, "e2e": e2e, "roofline": roofline,
-                     "cpu_baseline": cpu_baseline, "clocks": clocks, "gpu_launches": args.steps * world,
+                     "cpu_baseline": cpu_baseline, "clocks": clocks,
+                     # timed `value` region: k_view_bounds + k_view_finish + k_render_culled per step and rank
+                     "gpu_launches": 3 * args.steps * world,
                      "wall_ms_bracket": wall_ms, "per_step_ms_rank0": per_step_ms, "ms_per_step_by_rank": per_rank_ms, "counters": ctr, "setup_s": setup_s})
         line["config"].update({"fp_mode": args.fp, "band_rows": BAND_ROWS, "parallelism": "bands%d" % world,
                                "l2": "flushed between timed steps (256 MiB device memset outside the per-step event pair)",
@@ -350,7 +389,7 @@ def main():
     os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--fp", choices=["strict", "fast"], default="strict")

@@ -189,6 +189,8 @@ int atray_render_device(atray_ctx* ctx, const AtrayCamera* cam, const AtrayRende
 int atray_ctx_sync(atray_ctx* ctx);
 /* device time of the last completed atray_render_device / atray_render_begin kernel(s), CUDA events, ms */
 int atray_last_kernel_ms(atray_ctx* ctx, float* ms);
+/* Same frame, the render kernel alone (k_render_culled: CUDA events after the per-frame view pass and after the kernel). */
+int atray_last_render_kernel_ms(atray_ctx* ctx, float* ms);
 
 /* get_intersection_data model branch for an arbitrary ray list — renderer.cpp:34-57 + kd_tree.cpp:302-313.
  * rays = n × {ox,oy,oz,dx,dy,dz} (direction used as given). Host pointers; synchronous. */

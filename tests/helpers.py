@@ -43,7 +43,7 @@ def random_rays(aabb, n, seed):
 def golden_cases():
     out = []
     for f in sorted(os.listdir(GOLDEN)):
-        if f.endswith(".npz") and f != "kat.npz" and not f.startswith("path_"):
+        if f.endswith(".npz") and f != "kat.npz" and not f.startswith(("path_", "notree_")):
             out.append(f[:-4])
     return out
 

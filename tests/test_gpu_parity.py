@@ -542,7 +542,7 @@ def test_cpp_host_layer_replays_app_cpp(A, port, meshes, tmp_path):
     assert os.path.exists(exe), "run __graft_entry__.build()"
     path, rescale = meshes["knot_mid"]
     planes = str(tmp_path / "planes.bin")
-    bmp = str(tmp_path / "out.bmp")
+    bmp = str(tmp_path / "resultings")   # Write_To_File appends "_<id>.bmp" (texture.cpp:98-106)
     W, H = 1280, 720
     out = subprocess.run([exe, path, str(W), str(H), "0", bmp, planes], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
     assert out.returncode == 0, out.stdout
@@ -551,6 +551,6 @@ def test_cpp_host_layer_replays_app_cpp(A, port, meshes, tmp_path):
     face, t, img = o.trace_primary(W, H, threads=NTHREADS)
     assert (raw[0] == img).all() and (raw[1] == t.view(np.uint32)).all() and (raw[2] == face).all()
     assert "total_ray_casts %d " % int((face != B.MISS).sum()) in out.stdout
-    b = open(bmp, "rb").read()
-    assert b[:2] == b"BM" and len(b) == 54 + W * H * 4 and np.frombuffer(b[54:], np.uint32).reshape(H, W)[5, 7] == img[5, 7]
+    b = open(bmp + "_0.bmp", "rb").read()
+    assert b[:2] == b"BM" and len(b) == 70 + W * H * 4 and (np.frombuffer(b[70:], np.uint32).reshape(H, W) == img).all()
     o.close()
