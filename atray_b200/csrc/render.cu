@@ -95,18 +95,26 @@ __device__ __forceinline__ float box_entry(const RayL& r, float ix, float iy, fl
 }
 
 // ---- phase 1: collect the sorted leaf list of one ray (kd_tree.cpp:363-435). Returns false on capacity overflow.
+// The reference's list is ascending in the entry distance with ties in insertion order; the insertion order of a ray is
+// the static full-tree order restricted to the leaves it lists (FlatScene::leaf_seq), so the list is "ascending
+// (distance, leaf_seq)" and does not depend on the order in which subtrees are visited. The children of a node are still
+// examined in index order (the "at most 5 accepted" cut counts in that order), but the accepted inner children are
+// pushed far-to-near for this ray's direction signs (child bit 4/2/1 = upper x/y/z half, kd_tree.cpp:120-148): subtrees
+// are then visited front to back, entry distances arrive almost ascending and the insertion rarely has to shift.
 template <bool COUNT>
-__device__ bool collect_leaves(const float4* __restrict__ nodes, const RayL& r, float ix, float iy, float iz, uint32_t* stack,
-                               int stack_cap, uint2* leaves, int leaf_cap, int& nleaf, WorkCount& wc)
+__device__ bool collect_leaves(const float4* __restrict__ nodes, const uint32_t* __restrict__ leaf_seq, const RayL& r, float ix, float iy,
+                               float iz, uint32_t* stack, int stack_cap, uint2* leaves, int leaf_cap, int& nleaf, WorkCount& wc)
 {
     nleaf = 0;
     int sp = 1;
     stack[0] = 0u;
+    const unsigned near_mask = (ix < 0.0f ? 4u : 0u) | (iy < 0.0f ? 2u : 0u) | (iz < 0.0f ? 1u : 0u);
     while (sp > 0)
     {
         const uint32_t cur = stack[--sp];
         const uint32_t c0 = (uint32_t)__float_as_int(__ldg(&nodes[2 * cur]).w);
         int accepted = 0;
+        unsigned inner_acc = 0u;
 #pragma unroll 1
         for (int i = 0; i < 8 && accepted <= 4; ++i)  // at most 5 accepted children (kd_tree.cpp:374)
         {
@@ -119,8 +127,7 @@ __device__ bool collect_leaves(const float4* __restrict__ nodes, const RayL& r, 
                 if (box_check(r, ix, iy, iz, lo, hi))
                 {
                     ++accepted;
-                    if (sp >= stack_cap) return false;
-                    stack[sp++] = ch;
+                    inner_acc |= 1u << i;
                 }
             }
             else  // leaf child (possibly empty)
@@ -130,9 +137,11 @@ __device__ bool collect_leaves(const float4* __restrict__ nodes, const RayL& r, 
                 {
                     ++accepted;
                     if (nleaf >= leaf_cap) return false;
-                    int k = nleaf;  // stable insertion from the back: ties and later arrivals go after existing entries
-                    while (k > 0 && dis < __uint_as_float(leaves[k - 1].y))
+                    int k = nleaf;
+                    while (k > 0)
                     {
+                        const float pd = __uint_as_float(leaves[k - 1].y);
+                        if (!(dis < pd || (dis == pd && __ldg(&leaf_seq[ch]) < __ldg(&leaf_seq[leaves[k - 1].x])))) break;
                         leaves[k] = leaves[k - 1];
                         --k;
                     }
@@ -140,6 +149,16 @@ __device__ bool collect_leaves(const float4* __restrict__ nodes, const RayL& r, 
                     ++nleaf;
                     if (COUNT) wc.listed++;
                 }
+            }
+        }
+        if (inner_acc)
+        {
+            if (sp + __popc(inner_acc) > stack_cap) return false;
+#pragma unroll
+            for (int j = 7; j >= 0; --j)  // farthest octant first → the nearest is popped next
+            {
+                const unsigned i = (unsigned)j ^ near_mask;
+                if ((inner_acc >> i) & 1u) stack[sp++] = c0 + i;
             }
         }
     }
@@ -206,6 +225,7 @@ __device__ __forceinline__ void scan_ray_leaves(const DevScene& sc, int lane, in
                 if (UV) { bu = u; bv = v; }
             }
         }
+        if (!__any_sync(FULL_MASK, bt < kMaxFloat)) continue;  // no triangle of this leaf accepted the ray: next leaf
         // sequential strict-< scan ≡ lexicographic arg-min over (t, slot)
 #pragma unroll
         for (int off = 16; off > 0; off >>= 1)
@@ -294,7 +314,7 @@ __device__ __forceinline__ void trace_warp(const DevScene& sc, const DevScratch&
                 nleaf = 1;
             }
             else
-                overflow = !collect_leaves<COUNT>(sc.nodes, ray, ix, iy, iz, stack, kStackCap, leaves, kLeafCap, nleaf, wc);
+                overflow = !collect_leaves<COUNT>(sc.nodes, sc.leaf_seq, ray, ix, iy, iz, stack, kStackCap, leaves, kLeafCap, nleaf, wc);
             if (overflow) nleaf = 0;
         }
     }
@@ -320,7 +340,7 @@ __device__ __forceinline__ void trace_warp(const DevScene& sc, const DevScratch&
             WorkCount dummy;
             dummy.clear();
             // the aborted first attempt already counted a partial walk; the redo is not counted again
-            collect_leaves<false>(sc.nodes, ray, ix, iy, iz, gs, (int)scratch.stack_cap, gl, (int)scratch.leaf_cap, gn, dummy);
+            collect_leaves<false>(sc.nodes, sc.leaf_seq, ray, ix, iy, iz, gs, (int)scratch.stack_cap, gl, (int)scratch.leaf_cap, gn, dummy);
         }
         __syncwarp();
         scan_ray_leaves<STRICT, COUNT, UV>(sc, lane, src, ray, gl, gn, t_out, face_out, wc, u_out, v_out);
