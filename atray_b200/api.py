@@ -121,6 +121,8 @@ _SIGS = {
     "atray_dev_memset": [_vp, _vp, C.c_int, _sz],
     "atray_host_alloc_pinned": [_sz, C.POINTER(_vp)],
     "atray_host_free_pinned": [_vp],
+    "atray_host_register": [_vp, _sz],
+    "atray_host_unregister": [_vp],
     "atray_ipc_export": [_vp, _vp, _vp],
     "atray_ipc_open": [_vp, _vp, C.POINTER(_vp)],
     "atray_ipc_close": [_vp, _vp],

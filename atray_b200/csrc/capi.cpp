@@ -58,6 +58,8 @@ struct atray_ctx
     size_t stage_cap_px = 0;
     AtrayFrame pending_user{};   // where staged planes still have to be copied on completion
     size_t pending_px = 0;
+    AtrayPartition pending_part{0, 1, 8};
+    int32_t pending_w = 0;
     bool stage_bgrx = false, stage_t = false, stage_prim = false;
     bool in_flight = false;
     cudaEvent_t ev_k0 = nullptr, ev_k1 = nullptr, ev_done = nullptr;
@@ -737,6 +739,31 @@ static bool host_ptr_is_pinned(const void* p)
     return a.type == cudaMemoryTypeHost;
 }
 
+// Device→host copy of the scanlines one rank owns (band b of band_rows scanlines belongs to rank b % world): the whole
+// bands are one strided 2-D copy (pitch = world bands), a clipped last band is one more plain copy.
+static cudaError_t copy_rank_bands(void* dst, const void* src, int W, int H, const AtrayPartition& part, cudaMemcpyKind kind,
+                                   cudaStream_t stream)
+{
+    const size_t band_bytes = size_t(part.band_rows) * size_t(W) * 4;
+    const int n_bands = (H + part.band_rows - 1) / part.band_rows;
+    const int mine = part.rank < n_bands ? (n_bands - part.rank + part.world - 1) / part.world : 0;
+    if (mine == 0) return cudaSuccess;
+    const int last_band = part.rank + (mine - 1) * part.world;
+    const bool last_clipped = (last_band + 1) * part.band_rows > H;
+    const int whole = last_clipped ? mine - 1 : mine;
+    const size_t off = size_t(part.rank) * band_bytes;
+    cudaError_t e = cudaSuccess;
+    if (whole > 0)
+        e = cudaMemcpy2DAsync(static_cast<char*>(dst) + off, size_t(part.world) * band_bytes, static_cast<const char*>(src) + off,
+                              size_t(part.world) * band_bytes, band_bytes, size_t(whole), kind, stream);
+    if (e == cudaSuccess && last_clipped)
+    {
+        const size_t o2 = size_t(last_band) * band_bytes, rows = size_t(H - last_band * part.band_rows);
+        e = cudaMemcpyAsync(static_cast<char*>(dst) + o2, static_cast<const char*>(src) + o2, rows * size_t(W) * 4, kind, stream);
+    }
+    return e;
+}
+
 int atray_render_begin(atray_ctx* c, const AtrayCamera* cam, const AtrayRenderOpts* o, const AtrayFrame* host)
 {
     int rc = check_render_args(c, cam, o, host);
@@ -797,16 +824,26 @@ int atray_render_begin(atray_ctx* c, const AtrayCamera* cam, const AtrayRenderOp
         CU(cudaStreamWaitEvent(c->stream, c->ev_done, 0));      // later work on the context stream must not overtake the copies
         c->slabs_in_flight = slabs.n;
     }
+    else if (o->part.world > 1)
+    {
+        // A partition writes exactly this rank's scanlines of the host frame, as a worker of the reference's tile pool
+        // writes only its tiles (renderer.cpp:294-369): every rank of a multi-GPU job can be handed the SAME host bitmap
+        // (shared pinned memory) and the copies of all ranks run in parallel, each over its own GPU's PCIe link.
+        if (hb) CU(copy_rank_bands(hb, c->d_bgrx, cam->width, cam->height, o->part, cudaMemcpyDeviceToHost, c->stream));
+        if (ht) CU(copy_rank_bands(ht, c->d_t, cam->width, cam->height, o->part, cudaMemcpyDeviceToHost, c->stream));
+        if (hp) CU(copy_rank_bands(hp, c->d_prim, cam->width, cam->height, o->part, cudaMemcpyDeviceToHost, c->stream));
+        CU(cudaEventRecord(c->ev_done, c->stream));
+    }
     else
     {
-        // With a partition (world > 1) only this rank's bands are defined on the device; whole planes are still copied and
-        // the caller merges bands (host layer) — single-process multi-GPU gathers on the device (atray_render_device).
         if (hb) CU(cudaMemcpyAsync(hb, c->d_bgrx, px * 4, cudaMemcpyDeviceToHost, c->stream));
         if (ht) CU(cudaMemcpyAsync(ht, c->d_t, px * 4, cudaMemcpyDeviceToHost, c->stream));
         if (hp) CU(cudaMemcpyAsync(hp, c->d_prim, px * 4, cudaMemcpyDeviceToHost, c->stream));
         CU(cudaEventRecord(c->ev_done, c->stream));
     }
     c->pending_user = *host;
+    c->pending_part = o->part;
+    c->pending_w = cam->width;
     c->pending_px = px;
     c->pending_rows = cam->height;
     c->in_flight = true;
@@ -827,10 +864,20 @@ int atray_render_poll(atray_ctx* c, uint32_t timeout_ms)
         if (timeout_ms != 0xffffffffu && std::chrono::steady_clock::now() >= deadline) return 1;  // still running
         std::this_thread::yield();
     }
-    const size_t bytes = c->pending_px * 4;
-    if (c->stage_bgrx) std::memcpy(c->pending_user.bgrx, c->h_bgrx, bytes);
-    if (c->stage_t) std::memcpy(c->pending_user.t, c->h_t, bytes);
-    if (c->stage_prim) std::memcpy(c->pending_user.prim, c->h_prim, bytes);
+    // staged planes (caller passed pageable memory): whole frame, or this rank's scanlines only when partitioned
+    auto unstage = [&](uint32_t* dst, const uint32_t* src) {
+        const AtrayPartition& pt = c->pending_part;
+        if (pt.world <= 1) { std::memcpy(dst, src, c->pending_px * 4); return; }
+        const size_t row = size_t(c->pending_w);
+        for (int y0 = pt.rank * pt.band_rows; y0 < c->pending_rows; y0 += pt.world * pt.band_rows)
+        {
+            const int y1 = y0 + pt.band_rows < c->pending_rows ? y0 + pt.band_rows : c->pending_rows;
+            std::memcpy(dst + size_t(y0) * row, src + size_t(y0) * row, size_t(y1 - y0) * row * 4);
+        }
+    };
+    if (c->stage_bgrx) unstage(c->pending_user.bgrx, c->h_bgrx);
+    if (c->stage_t) unstage(reinterpret_cast<uint32_t*>(c->pending_user.t), reinterpret_cast<const uint32_t*>(c->h_t));
+    if (c->stage_prim) unstage(c->pending_user.prim, c->h_prim);
     c->in_flight = false;
     return 0;
 }
@@ -1069,6 +1116,20 @@ int atray_host_alloc_pinned(size_t bytes, void** out)
     CU(cudaMallocHost(out, bytes ? bytes : 1));
     return ATRAY_OK;
 }
+int atray_host_register(void* p, size_t bytes)
+{
+    if (!p || !bytes) return fail(ATRAY_EINVAL, "null argument");
+    CU(cudaHostRegister(p, bytes, cudaHostRegisterPortable));
+    return ATRAY_OK;
+}
+
+int atray_host_unregister(void* p)
+{
+    if (!p) return ATRAY_OK;
+    CU(cudaHostUnregister(p));
+    return ATRAY_OK;
+}
+
 int atray_host_free_pinned(void* p)
 {
     CU(cudaFreeHost(p));

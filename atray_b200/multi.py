@@ -4,6 +4,9 @@ a CUDA-IPC mapping (peer stores over NVLink) — there is no collective on the d
 (north_star). torch.distributed is used only to hand the 64-byte IPC handles around and for barriers.
 
 The reference's counterpart is the tile work queue of renderer.cpp:403-445 (tiles pulled by 8 threads)."""
+import ctypes as C
+import os
+
 import numpy as np
 
 PLANES = ("bgrx", "t", "prim")
@@ -69,3 +72,33 @@ class FrameGather:
         for p in self._owned:
             self.ctx.dev_free(p)
         self._opened, self._owned = [], []
+
+
+class SharedBitmap:
+    """The host bitmap (Texture.bmb.buffer_memory) of a multi-process job: a file in /dev/shm mapped by every rank and
+    page-locked in each process (atray_host_register). With a partition, atray_render_begin writes exactly the rank's
+    scanlines, so all ranks render into this one bitmap — the analogue of the reference's pool threads writing their
+    tiles into one texture (renderer.cpp:294-369) — and the N device→host copies run in parallel, each over its own GPU's
+    PCIe link. Rank 0 creates the file (call with create=True first, then a barrier, then the other ranks open it)."""
+
+    def __init__(self, name, shape, dtype=np.uint32, create=False, register=True):
+        from . import api
+        self.path = os.path.join("/dev/shm", name)
+        self.nbytes = int(np.prod(shape)) * np.dtype(dtype).itemsize
+        self.owner = create
+        if create:
+            with open(self.path, "wb") as f:
+                f.truncate(self.nbytes)
+        self.array = np.memmap(self.path, dtype=dtype, mode="r+", shape=tuple(shape))
+        self._api, self._registered = api, False
+        if register:
+            api._ck(api._L.atray_host_register(C.c_void_p(self.array.ctypes.data), self.nbytes))
+            self._registered = True
+
+    def close(self):
+        if self.array is not None:
+            if self._registered:
+                self._api._L.atray_host_unregister(C.c_void_p(self.array.ctypes.data))
+            self.array = None
+            if self.owner and os.path.exists(self.path):
+                os.remove(self.path)

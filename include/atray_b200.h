@@ -214,6 +214,11 @@ int atray_dev_memset(atray_ctx* ctx, void* dev, int value, size_t bytes);
 int atray_write_bmp(const uint32_t* bgrx, uint32_t width, uint32_t height, const char* file_name, char* written_name, size_t cap);
 int atray_host_alloc_pinned(size_t bytes, void** out);
 int atray_host_free_pinned(void* p);
+/* Page-locks memory the caller already owns (e.g. a bitmap in shared memory that several rank processes render into:
+ * with AtrayRenderOpts.part.world > 1, atray_render_begin writes exactly this rank's scanlines of the host frame, so all
+ * ranks can be handed the same bitmap and their copies run in parallel over their own PCIe links). */
+int atray_host_register(void* p, size_t bytes);
+int atray_host_unregister(void* p);
 /* cross-process gather target (multi-GPU, one process per GPU): export a device allocation of this context and
  * open it in a peer process; the opened pointer can be used as AtrayFrame planes of atray_render_device
  * (the kernel stores straight into GPU 0's frame over NVLink). handle64 = 64 bytes. */

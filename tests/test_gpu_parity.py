@@ -294,6 +294,39 @@ def test_partition_union_equals_whole(A, meshes):
         ctx.dev_free(p)
 
 
+def test_partitioned_host_copy_out_writes_only_own_scanlines(A, meshes):
+    """atray_render_begin with a partition writes exactly the rank's scanlines of the host frame (pinned and pageable
+    hosts): the ranks of a multi-GPU job render into ONE host bitmap, as the reference's pool threads do."""
+    path, rescale = meshes["knot_mid"]
+    sc = gpu_scene(A, path, rescale)
+    ctx = sc.ctx
+    for (W, H) in ((500, 301), (1280, 720)):
+        cam = A.set_camera(W, H)
+        whole = ctx.render(cam)
+        for world, band in ((2, 8), (3, 12), (8, 8)):
+            pin = {k: A.PinnedArray((H, W), np.uint32) for k in ("bgrx", "t", "prim")}
+            page = {k: np.full((H, W), 0xDEADBEEF, np.uint32) for k in ("bgrx", "t", "prim")}
+            for a in pin.values():
+                a.array[:] = 0xDEADBEEF
+            for rank in range(world):
+                for host in (pin, page):
+                    arr = {k: (v.array if host is pin else v) for k, v in host.items()}
+                    ctx.render_begin(cam, ctx.opts(rank=rank, world=world, band_rows=band), arr["bgrx"], arr["t"].view(np.float32), arr["prim"])
+                    while ctx.render_poll(1000):
+                        pass
+                if rank == 0:   # after the first rank only its bands are written
+                    rows = np.arange(H)
+                    mine = (rows // band) % world == 0
+                    assert (pin["bgrx"].array[mine] == whole["bgrx"][mine]).all() and (pin["bgrx"].array[~mine] == 0xDEADBEEF).all()
+                    assert (page["prim"][mine] == whole["prim"][mine]).all() and (page["prim"][~mine] == 0xDEADBEEF).all()
+            for host in (pin, page):
+                arr = {k: (v.array if host is pin else v) for k, v in host.items()}
+                assert (arr["bgrx"] == whole["bgrx"]).all() and (arr["prim"] == whole["prim"]).all()
+                assert (arr["t"] == whole["t"].view(np.uint32)).all()
+            for a in pin.values():
+                a.free()
+
+
 def test_spill_path_long_leaf_lists(A, port, meshes):
     """Rays whose leaf list outgrows the per-lane array take the per-warp spill path; results stay bit-exact."""
     from oracle import bind as B

@@ -96,3 +96,52 @@ def test_frame_gather_handle_exchange_gloo_world2(built):
     for k in p0:  # rank 1 mapped exactly the allocations rank 0 exported
         assert p1[k] == p0[k] + 7
     assert [e[0] for e in log1] == ["open"] * 3 + ["close"] * 3
+
+
+def _bitmap_worker(rank, world, port, q):
+    sys.path.insert(0, ROOT)
+    import torch.distributed as dist
+    from atray_b200 import multi
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    H, W, band = 50, 16, 8
+    name = "atray_test_%d" % port
+    bm = multi.SharedBitmap(name, (H, W), np.uint32, create=True, register=False) if rank == 0 else None
+    dist.barrier()
+    if rank != 0:
+        bm = multi.SharedBitmap(name, (H, W), np.uint32, create=False, register=False)
+    rows = multi.rows_of_rank(H, band, rank, world)     # what atray_render_begin writes for this partition
+    bm.array[rows] = (rank + 1) * 1000 + rows[:, None]
+    bm.array.flush()
+    dist.barrier()
+    ok = True
+    if rank == 0:
+        for r in range(world):
+            rr = multi.rows_of_rank(H, band, r, world)
+            ok = ok and bool((np.asarray(bm.array)[rr] == (r + 1) * 1000 + rr[:, None]).all())
+    dist.barrier()
+    path = bm.path
+    bm.close()
+    dist.barrier()
+    dist.destroy_process_group()
+    q.put((rank, ok, os.path.exists(path)))
+
+
+def test_shared_host_bitmap_gloo_world2(built):
+    """Two rank processes map one host bitmap and write their own scanline bands into it (the multi-GPU e2e output path;
+    page-locking is skipped here, there is no CUDA driver on the CPU box)."""
+    import torch.multiprocessing as mp
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_bitmap_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=120) for _ in range(2)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert all(ok for _, ok, _ in res) and not any(left for _, _, left in res)
