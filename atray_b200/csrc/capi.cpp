@@ -739,21 +739,25 @@ static bool host_ptr_is_pinned(const void* p)
     return a.type == cudaMemoryTypeHost;
 }
 
-// Device→host copy of the scanlines one rank owns (band b of band_rows scanlines belongs to rank b % world): the whole
-// bands are one strided 2-D copy (pitch = world bands), a clipped last band is one more plain copy.
-static cudaError_t copy_rank_bands(void* dst, const void* src, int W, int H, const AtrayPartition& part, cudaMemcpyKind kind,
-                                   cudaStream_t stream)
+// Device→host copy of the scanlines of this rank's local bands [lb0, lb1) (local band lb = global band lb*world + rank,
+// band_rows scanlines each): the whole bands are one strided 2-D copy (pitch = world bands; a plain copy when world = 1),
+// a band clipped by the image's top edge is one more plain copy.
+static cudaError_t copy_local_bands(void* dst, const void* src, int W, int H, const AtrayPartition& part, int lb0, int lb1,
+                                    cudaMemcpyKind kind, cudaStream_t stream)
 {
     const size_t band_bytes = size_t(part.band_rows) * size_t(W) * 4;
     const int n_bands = (H + part.band_rows - 1) / part.band_rows;
     const int mine = part.rank < n_bands ? (n_bands - part.rank + part.world - 1) / part.world : 0;
-    if (mine == 0) return cudaSuccess;
-    const int last_band = part.rank + (mine - 1) * part.world;
+    if (lb1 > mine) lb1 = mine;
+    if (lb0 >= lb1) return cudaSuccess;
+    const int last_band = part.rank + (lb1 - 1) * part.world;
     const bool last_clipped = (last_band + 1) * part.band_rows > H;
-    const int whole = last_clipped ? mine - 1 : mine;
-    const size_t off = size_t(part.rank) * band_bytes;
+    const int whole = (last_clipped ? lb1 - 1 : lb1) - lb0;
+    const size_t off = size_t(part.rank + lb0 * part.world) * band_bytes;
     cudaError_t e = cudaSuccess;
-    if (whole > 0)
+    if (whole > 0 && part.world == 1)
+        e = cudaMemcpyAsync(static_cast<char*>(dst) + off, static_cast<const char*>(src) + off, size_t(whole) * band_bytes, kind, stream);
+    else if (whole > 0)
         e = cudaMemcpy2DAsync(static_cast<char*>(dst) + off, size_t(part.world) * band_bytes, static_cast<const char*>(src) + off,
                               size_t(part.world) * band_bytes, band_bytes, size_t(whole), kind, stream);
     if (e == cudaSuccess && last_clipped)
@@ -762,6 +766,11 @@ static cudaError_t copy_rank_bands(void* dst, const void* src, int W, int H, con
         e = cudaMemcpyAsync(static_cast<char*>(dst) + o2, static_cast<const char*>(src) + o2, rows * size_t(W) * 4, kind, stream);
     }
     return e;
+}
+static cudaError_t copy_rank_bands(void* dst, const void* src, int W, int H, const AtrayPartition& part, cudaMemcpyKind kind,
+                                   cudaStream_t stream)
+{
+    return copy_local_bands(dst, src, W, H, part, 0, 0x7fffffff, kind, stream);
 }
 
 int atray_render_begin(atray_ctx* c, const AtrayCamera* cam, const AtrayRenderOpts* o, const AtrayFrame* host)
@@ -791,7 +800,7 @@ int atray_render_begin(atray_ctx* c, const AtrayCamera* cam, const AtrayRenderOp
     DevOut out{host->bgrx ? c->d_bgrx : nullptr, host->t ? c->d_t : nullptr, host->prim ? c->d_prim : nullptr};
     // Whole image on this context and a frame large enough to matter: render slab by slab and copy each slab's scanlines
     // out while the kernel is still tracing the later ones (the copy stream waits on the kernel's per-slab counters).
-    const bool pipelined = o->part.world == 1 && c->wait_value32 && c->slab_copy > 1 && px >= (size_t(1) << 20);
+    const bool pipelined = c->wait_value32 && c->slab_copy > 1 && px >= (size_t(1) << 20);
     DevSlabs slabs{};
     rc = enqueue_render(c, cam, o, out, pipelined ? c->slab_copy : 1, &slabs);
     if (rc) return rc;
@@ -806,18 +815,18 @@ int atray_render_begin(atray_ctx* c, const AtrayCamera* cam, const AtrayRenderOp
         const uint32_t tiles_per_band = uint32_t(((cam->width + 7) >> 3) * (o->part.band_rows >> 2));
         for (int s = 0; s < slabs.n; ++s)
         {
-            const size_t y0 = size_t(slabs.tile_begin[s] / tiles_per_band) * size_t(o->part.band_rows);
-            size_t y1 = size_t(slabs.tile_begin[s + 1] / tiles_per_band) * size_t(o->part.band_rows);
-            if (y1 > size_t(cam->height)) y1 = size_t(cam->height);
-            const size_t off = y0 * size_t(cam->width), cnt = (y1 - y0) * size_t(cam->width) * 4;
+            // local bands of the slab; with a partition they are every world-th band of the image (strided copy)
+            const int lb0 = int(slabs.tile_begin[s] / tiles_per_band), lb1 = int(slabs.tile_begin[s + 1] / tiles_per_band);
+            int y1 = ((lb1 - 1) * o->part.world + o->part.rank + 1) * o->part.band_rows;
+            if (y1 > cam->height) y1 = cam->height;
             const unsigned long long addr = (unsigned long long)(uintptr_t)(c->view.busy_count + kCtlDone + s);
             if (c->wait_value32(c->copy_stream, addr, slabs.live_tiles[s], 0u /* CU_STREAM_WAIT_VALUE_GEQ */) != 0)
                 return fail(ATRAY_ECUDA, "cuStreamWaitValue32 failed");
-            if (hb) CU(cudaMemcpyAsync(hb + off, c->d_bgrx + off, cnt, cudaMemcpyDeviceToHost, c->copy_stream));
-            if (ht) CU(cudaMemcpyAsync(ht + off, c->d_t + off, cnt, cudaMemcpyDeviceToHost, c->copy_stream));
-            if (hp) CU(cudaMemcpyAsync(hp + off, c->d_prim + off, cnt, cudaMemcpyDeviceToHost, c->copy_stream));
+            if (hb) CU(copy_local_bands(hb, c->d_bgrx, cam->width, cam->height, o->part, lb0, lb1, cudaMemcpyDeviceToHost, c->copy_stream));
+            if (ht) CU(copy_local_bands(ht, c->d_t, cam->width, cam->height, o->part, lb0, lb1, cudaMemcpyDeviceToHost, c->copy_stream));
+            if (hp) CU(copy_local_bands(hp, c->d_prim, cam->width, cam->height, o->part, lb0, lb1, cudaMemcpyDeviceToHost, c->copy_stream));
             CU(cudaEventRecord(c->ev_slab[s], c->copy_stream));
-            c->slab_row_end[s] = int32_t(y1);
+            c->slab_row_end[s] = int32_t(y1);   // this rank's scanlines below y1 have landed
         }
         CU(cudaStreamWaitEvent(c->copy_stream, c->ev_k1, 0));   // the frame is done only when the kernel has retired too
         CU(cudaEventRecord(c->ev_done, c->copy_stream));

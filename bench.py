@@ -301,16 +301,18 @@ def run_ours(args):
         # pinned memory (atray_render_begin with a partition): N device→host copies in parallel, one per PCIe link
         name = "atray_bench_%s" % os.environ.get("MASTER_PORT", "0")
         shared = multi.SharedBitmap(name, (H, W), np.uint32, create=True) if rank == 0 else None
+        shm_bar = multi.ShmBarrier(name + "_bar", rank, world, create=True) if rank == 0 else None
         barrier()
         if rank != 0:
             shared = multi.SharedBitmap(name, (H, W), np.uint32, create=False)
+            shm_bar = multi.ShmBarrier(name + "_bar", rank, world, create=False)
         info = A.RenderInfo(cam, scene, shared.array, opts=opts)
 
         def e2e_step():
             A.start_render_from_camera(info)
             while A.wait_for_render_from_camera_to_finish(info, None, 33):
                 pass
-            barrier()                                   # the frame is complete when every rank's scanlines have landed
+            shm_bar.wait()                              # the frame is complete when every rank's scanlines have landed
         for _ in range(2):
             e2e_step()
         t0 = time.perf_counter()
@@ -325,6 +327,7 @@ def run_ours(args):
             e2e_check = bool((np.asarray(shared.array) == tex.array).all())
         barrier()
         shared.close()
+        shm_bar.close()
     if dist is not None:
         import torch
         tt = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")

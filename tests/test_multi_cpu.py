@@ -110,6 +110,15 @@ def _bitmap_worker(rank, world, port, q):
     dist.barrier()
     if rank != 0:
         bm = multi.SharedBitmap(name, (H, W), np.uint32, create=False, register=False)
+    bar = multi.ShmBarrier(name + "_bar", rank, world, create=True) if rank == 0 else None
+    dist.barrier()
+    if rank != 0:
+        bar = multi.ShmBarrier(name + "_bar", rank, world, create=False)
+    for _ in range(200):                                # the shared-memory barrier that brackets the timed e2e frames
+        bar.wait()
+    assert int(bar.slots[:, 0].min()) == 200
+    dist.barrier()
+    bar.close()
     rows = multi.rows_of_rank(H, band, rank, world)     # what atray_render_begin writes for this partition
     bm.array[rows] = (rank + 1) * 1000 + rows[:, None]
     bm.array.flush()
