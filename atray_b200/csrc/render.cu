@@ -899,6 +899,10 @@ __device__ __forceinline__ bool collect_tile_leaves(const float4* __restrict__ n
         const uint32_t c0 = (uint32_t)__float_as_int(__ldg(&nodes[2 * cur]).w);
         // children whose rectangle overlaps the tile's film rectangle (lanes 0..7, one child each)
         const float4 myR = __ldg(&node_rect[c0 + (lane & 7)]);
+        // the 8 child boxes, one per lane of each group of 8, fetched together with the rectangles: the child loop below
+        // reads them by shuffle instead of waiting for a dependent load per child
+        const float4 myLo = __ldg(&nodes[2 * (c0 + (lane & 7))]);
+        const float4 myHi = __ldg(&nodes[2 * (c0 + (lane & 7)) + 1]);
         if (COUNT && lane < 8) wc.rect++;
         unsigned cm = __ballot_sync(FULL_MASK, rect_overlap(myR, trect)) & 0xffu;
         unsigned ev = 0u, am = 0u;  // this lane: children of `cur` whose acceptance is known / that were accepted
@@ -909,7 +913,8 @@ __device__ __forceinline__ bool collect_tile_leaves(const float4* __restrict__ n
         // ray parameter lies in the closed intervals of at most 4 octant triples in total, so at most 4 children can pass
         // the slab test (leaf acceptance is stricter still) and the "accepted <= 4" guard never stops the loop. Only lanes
         // with a tie (ray through a split edge, up to rounding) need the lazy sibling evaluation below.
-        const float4 sp4 = __ldg(&nodes[2 * c0 + 1]);
+        float4 sp4;  // split point = hi corner of child 0
+        sp4.x = __shfl_sync(FULL_MASK, myHi.x, 0); sp4.y = __shfl_sync(FULL_MASK, myHi.y, 0); sp4.z = __shfl_sync(FULL_MASK, myHi.z, 0);
         const float tsx = mulr(subr(sp4.x, r.ox), ix), tsy = mulr(subr(sp4.y, r.oy), iy), tsz = mulr(subr(sp4.z, r.oz), iz);
         const bool risky = here && (tsx == tsy || tsy == tsz || tsx == tsz);
         const bool any_risky = __any_sync(FULL_MASK, risky);
@@ -945,8 +950,8 @@ __device__ __forceinline__ bool collect_tile_leaves(const float4* __restrict__ n
                 if (!__any_sync(FULL_MASK, want)) continue;
             }
             const uint32_t ch = c0 + (uint32_t)i;
-            const float4 lo = __ldg(&nodes[2 * ch]);
-            if (__float_as_int(lo.w) > 0)  // inner child: descend with the lanes that want it
+            const int low = __shfl_sync(FULL_MASK, __float_as_int(myLo.w), i);
+            if (low > 0)  // inner child: descend with the lanes that want it
             {
                 const unsigned pm = __ballot_sync(FULL_MASK, want);
                 if (sp >= kStackCap) { overflow = true; break; }
@@ -955,7 +960,10 @@ __device__ __forceinline__ bool collect_tile_leaves(const float4* __restrict__ n
             }
             else
             {
-                const float4 hi = __ldg(&nodes[2 * ch + 1]);
+                float4 lo, hi;
+                lo.x = __shfl_sync(FULL_MASK, myLo.x, i); lo.y = __shfl_sync(FULL_MASK, myLo.y, i); lo.z = __shfl_sync(FULL_MASK, myLo.z, i);
+                hi.x = __shfl_sync(FULL_MASK, myHi.x, i); hi.y = __shfl_sync(FULL_MASK, myHi.y, i); hi.z = __shfl_sync(FULL_MASK, myHi.z, i);
+                lo.w = hi.w = 0.f;
                 const float dis = box_entry(r, ix, iy, iz, lo, hi);
                 if (want)
                 {
