@@ -576,6 +576,7 @@ static ViewParams make_view_params(const AtrayCamera* cam)
     const double aa_x = cam->anti_aliasing ? std::fabs(double(cam->half_pixel_width)) : 0.0;
     const double aa_y = cam->anti_aliasing ? std::fabs(double(cam->half_pixel_height)) : 0.0;
     const double fx_max = std::fabs(vp.kx) * (1.0 + 1e-6) + aa_x, fy_max = 1.0 + 1e-6 + aa_y;
+    vp.fx_max = fx_max; vp.fy_max = fy_max;
     double e2 = 0.0, eye_inf = 0.0;
     for (int i = 0; i < 3; ++i)
     {
@@ -1008,7 +1009,7 @@ int atray_get_counters(atray_ctx* c, AtrayCounters* out)
 
 // ---- verification aid: the film rectangles of view_bounds.h evaluated on the host ------------------------------------
 int atray_debug_film_rects(const atray_model* m, const AtrayCamera* cam, float* rects, uint32_t* slot_leaf, uint32_t* slot_pos,
-                           uint8_t* tile_busy)
+                           uint8_t* tile_busy, float* hulls)
 {
     if (!m || !cam) return fail(ATRAY_EINVAL, "null argument");
     if (m->m.tree.empty()) return fail(ATRAY_ESTATE, "film_rects before build_tree");
@@ -1028,7 +1029,10 @@ int atray_debug_film_rects(const atray_model* m, const AtrayCamera* cam, float* 
         std::memcpy(&face, A + 3, 4);
         std::memcpy(&pos, AB + 3, 4);
         FilmRect r = film_rect_empty();
-        if (face != 0xffffffffu) r = tri_film_rect(vp, A, AB, AC);
+        FilmHull hl = film_hull_all();
+        if (face != 0xffffffffu) r = tri_film_rect(vp, A, AB, AC, &hl);
+        if (hulls)
+            for (int k = 0; k < 3; ++k) { hulls[9 * size_t(s) + 3 * k] = hl.a[k]; hulls[9 * size_t(s) + 3 * k + 1] = hl.b[k]; hulls[9 * size_t(s) + 3 * k + 2] = hl.c[k]; }
         if (rects) { rects[4 * size_t(s)] = r.xlo; rects[4 * size_t(s) + 1] = r.ylo; rects[4 * size_t(s) + 2] = r.xhi; rects[4 * size_t(s) + 3] = r.yhi; }
         if (slot_leaf) slot_leaf[s] = f.packet_leaf[s / 8];
         if (slot_pos) slot_pos[s] = face != 0xffffffffu ? pos : 0xffffffffu;

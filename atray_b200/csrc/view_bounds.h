@@ -49,6 +49,7 @@ struct ViewParams
     double ang;          // angular deviation bound of the float ray generation from the ideal line (radians)
     double kx;           // h_fov * aspect: film_x(x) = (-1 + 2x/W) * kx   (renderer.cpp:329)
     double px_slack_x, px_slack_y;  // pixel slack for the tile stamps (rounding of film_x/film_y, + half a pixel with AA)
+    double fx_max, fy_max;          // bounds of |film_x|, |film_y| over every ray of the frame (jitter included)
     int32_t W, H;
     int32_t tiles_x, tiles_y;      // 8x4-pixel tiles
     int32_t valid;                 // 0: camera not usable for culling (singular basis / non-finite) → unculled kernel
@@ -56,6 +57,22 @@ struct ViewParams
 };
 
 struct FilmRect { float xlo, ylo, xhi, yhi; };
+// (Groundwork, verified on the CPU by tests/test_view_bounds.py; the kernels do not read it yet — measured this round:
+// testing (slot, ray) pairs against it cuts the triangle tests 4.6x but adds a dependent load in front of every test and
+// the latency-bound render kernel got slower, 269 -> 292 us.)
+// Three half-planes a[k]*fx + b[k]*fy <= c[k] (evaluated in float, any association, with or without FMA) that hold for the
+// film point of every ray the reference accepts for the triangle. The film point lies in the projection of the inflated
+// triangle = convex hull of the three projected vertex balls (a perspective map with gamma > 0 sends segments to
+// segments), each ball lies in its axis-parallel film box, so any half-plane containing the three boxes is sound. One
+// half-plane per edge, oriented away from the third vertex, offset = maximum over the 12 box corners plus a slack for
+// every float rounding on the way (see tri_film_rect). (0, 0, 0) is the trivial half-plane.
+struct FilmHull { float a[3], b[3], c[3]; };
+ATRAY_HD FilmHull film_hull_all()
+{
+    FilmHull h;
+    for (int k = 0; k < 3; ++k) { h.a[k] = 0.f; h.b[k] = 0.f; h.c[k] = 0.f; }
+    return h;
+}
 
 ATRAY_HD FilmRect film_rect_empty()
 {
@@ -96,8 +113,9 @@ ATRAY_HD float round_up_f(double x)
 }
 
 // Film rectangle of one triangle record {a, ab, ac} (float values widened to double) for the view `vp`.
-ATRAY_HD FilmRect tri_film_rect(const ViewParams& vp, const float* a_f, const float* ab_f, const float* ac_f)
+ATRAY_HD FilmRect tri_film_rect(const ViewParams& vp, const float* a_f, const float* ab_f, const float* ac_f, FilmHull* hull = nullptr)
 {
+    if (hull) *hull = film_hull_all();
     const double U = 5.9604644775390625e-8;   // 2^-24
     const double TAU = 9.9999e-5;             // just below (double)1e-4f = 9.99999974738e-05
     const double BIG = 1073741824.0;          // 2^30: beyond this the products of the test may overflow → no bound
@@ -158,6 +176,7 @@ ATRAY_HD FilmRect tri_film_rect(const ViewParams& vp, const float* a_f, const fl
     // total radius of the vertex balls: float-test margin + deviation of the float ray from the ideal line
     const double rad = (m + vp.ang * (Tmax + m)) * (1.0 + 1e-9);
     double xlo = INFINITY, xhi = -INFINITY, ylo = INFINITY, yhi = -INFINITY;
+    double bx0[3], bx1[3], by0[3], by1[3];  // film box of each inflated vertex
     for (int k = 0; k < 3; ++k)
     {
         const double al = vp.minv[0][0] * w[k][0] + vp.minv[0][1] * w[k][1] + vp.minv[0][2] * w[k][2];
@@ -175,8 +194,42 @@ ATRAY_HD FilmRect tri_film_rect(const ViewParams& vp, const float* a_f, const fl
         if (x1 > xhi) xhi = x1;
         if (y0 < ylo) ylo = y0;
         if (y1 > yhi) yhi = y1;
+        bx0[k] = x0 - 1e-12 * (1.0 + fabs(x0)); bx1[k] = x1 + 1e-12 * (1.0 + fabs(x1));
+        by0[k] = y0 - 1e-12 * (1.0 + fabs(y0)); by1[k] = y1 + 1e-12 * (1.0 + fabs(y1));
     }
     if (!(xlo <= xhi && ylo <= yhi)) return film_rect_all();   // NaN somewhere
+    if (hull)
+    {
+        // In float (the FP64 pipe is what bounds the pre-pass): the boxes are rounded outward to float, the edge normal and
+        // the offset are float expressions, and every rounding — of the offset's own evaluation, of its sum with the slack,
+        // and of the kernel's a*fx + b*fy — is below 3u(|a| Mx + |b| My) with Mx, My bounding every coordinate involved
+        // (u = 2^-24); 24u is added.
+        float fx0[3], fx1[3], fy0[3], fy1[3];
+        float Mx = round_up_f(vp.fx_max), My = round_up_f(vp.fy_max);
+        for (int k = 0; k < 3; ++k)
+        {
+            fx0[k] = round_down_f(bx0[k]); fx1[k] = round_up_f(bx1[k]); fy0[k] = round_down_f(by0[k]); fy1[k] = round_up_f(by1[k]);
+            Mx = fmaxf(Mx, fmaxf(fabsf(fx0[k]), fabsf(fx1[k])));
+            My = fmaxf(My, fmaxf(fabsf(fy0[k]), fabsf(fy1[k])));
+        }
+        for (int e = 0; e < 3; ++e)
+        {
+            const int i = e, j = (e + 1) % 3, k = (e + 2) % 3;
+            const float cix = 0.5f * (fx0[i] + fx1[i]), ciy = 0.5f * (fy0[i] + fy1[i]);
+            float nx = 0.5f * (fy0[j] + fy1[j]) - ciy, ny = -(0.5f * (fx0[j] + fx1[j]) - cix);
+            if (!(fabsf(nx) + fabsf(ny) > 0.0f)) continue;       // coincident centres or NaN: trivial half-plane
+            if (nx * (0.5f * (fx0[k] + fx1[k]) - cix) + ny * (0.5f * (fy0[k] + fy1[k]) - ciy) > 0.0f) { nx = -nx; ny = -ny; }
+            float c = -INFINITY;
+            for (int v = 0; v < 3; ++v)
+            {
+                const float px = nx > 0.0f ? fx1[v] : fx0[v], py = ny > 0.0f ? fy1[v] : fy0[v];   // corner maximising nx x + ny y
+                c = fmaxf(c, nx * px + ny * py);
+            }
+            c += 24.0f * 5.9604644775390625e-8f * (fabsf(nx) * Mx + fabsf(ny) * My) + 1e-30f;
+            if (!(c == c) || !(fabsf(c) < 1e30f)) continue;
+            hull->a[e] = nx; hull->b[e] = ny; hull->c[e] = c;
+        }
+    }
     FilmRect r;
     r.xlo = round_down_f(xlo - 1e-12 * (1.0 + fabs(xlo))); r.ylo = round_down_f(ylo - 1e-12 * (1.0 + fabs(ylo)));
     r.xhi = round_up_f(xhi + 1e-12 * (1.0 + fabs(xhi))); r.yhi = round_up_f(yhi + 1e-12 * (1.0 + fabs(yhi)));

@@ -37,7 +37,7 @@ def check(A, B, port, path, rescale, method, cap, W, H, camkw):
     A.build_KD_tree(m, method, cap)
     o = B.Scene(port, path, rescale=rescale, method=method, cap=cap)
     cam = A.set_camera(W, H, **camkw)
-    rects, leaf, pos, busy = m.film_rects(cam)
+    rects, leaf, pos, busy, hulls = m.film_rects(cam, hulls=True)
     okw = dict(eye=camkw.get("eye", A.api.DEFAULT_EYE), facing=camkw.get("facing", A.api.DEFAULT_FACING),
                hfov=camkw.get("h_fov", 1.0))
     px, node, ppos = o.accepted_hits(W, H, threads=NT, **okw)
@@ -58,7 +58,15 @@ def check(A, B, port, path, rescale, method, cap, W, H, camkw):
     inside = (fx[x] >= r[:, 0]) & (fx[x] <= r[:, 2]) & (fy[y] >= r[:, 1]) & (fy[y] <= r[:, 3])
     assert inside.all(), "%d accepted hits outside their film rectangle" % int((~inside).sum())
     assert busy[y // 4, x // 8].all(), "accepted hit in a tile stamped as sky"
-    return px.size, rects, busy
+    # the three half-planes of the slot, evaluated in float32 the way the kernel does (both association orders)
+    hl = hulls[s]
+    for k in range(3):
+        a, b, c = hl[:, k, 0], hl[:, k, 1], hl[:, k, 2]
+        e = (a * fx[x]).astype(np.float32) + (b * fy[y]).astype(np.float32)
+        assert (e.astype(np.float32) <= c).all(), "%d accepted hits outside half-plane %d" % (int((e > c).sum()), k)
+        e64 = a.astype(np.float64) * fx[x] + b.astype(np.float64) * fy[y]      # what an FMA contraction rounds from
+        assert (e64.astype(np.float32) <= c).all()
+    return px.size, rects, busy, hulls, s
 
 
 @pytest.mark.parametrize("camkw", CAMERAS)
@@ -78,7 +86,20 @@ def test_bounds_are_tight_on_the_default_view(built, port, meshes):
     import atray_b200 as A
     from oracle import bind as B
     path, rescale = meshes["knot_mid"]
-    n, rects, busy = check(A, B, port, path, rescale, 1, 300, 960, 540, {})
+    n, rects, busy, hulls, hit_slots = check(A, B, port, path, rescale, 1, 300, 960, 540, {})
+    # the half-planes cull: inside its own rectangle a triangle's hull keeps well under the whole pixel count
+    cam = A.set_camera(960, 540)
+    fx, fy = film_coords(cam, 960, 540)
+    kept = total = 0
+    for sl in np.unique(hit_slots)[:400]:
+        r, h = rects[sl], hulls[sl]
+        xs, ys = fx[(fx >= r[0]) & (fx <= r[2])], fy[(fy >= r[1]) & (fy <= r[3])]
+        gx, gy = np.meshgrid(xs, ys)
+        ok = np.ones(gx.shape, bool)
+        for k in range(3):
+            ok &= (h[k, 0] * gx + h[k, 1] * gy) <= h[k, 2]
+        kept += int(ok.sum()); total += ok.size
+    assert kept < 0.75 * total, (kept, total)
     assert n > 10000
     assert busy.mean() < 0.5
     fin = np.isfinite(rects).all(axis=1)

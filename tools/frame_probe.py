@@ -27,13 +27,17 @@ cam = A.set_camera(W, H)
 planes = [ctx.dev_alloc(W * H * 4) for _ in range(3)]
 flush = ctx.dev_alloc(256 << 20)
 opts = ctx.opts(rank=0, world=args.world, band_rows=8, raster=args.raster, count_work=args.count)
-ms = []
+ms, rms = [], []
 for i in range(args.reps + 2):
     ctx.dev_memset(flush, 0, 256 << 20)
     ctx.render_device(cam, opts, *planes)
     ctx.sync()
     if i >= 2:
         ms.append(ctx.last_kernel_ms())
+        if not args.raster:
+            rms.append(ctx.last_render_kernel_ms())
 print("world %d rank 0 raster=%s: %.1f us per frame (min %.1f)" % (args.world, args.raster, 1e3 * sum(ms) / len(ms), 1e3 * min(ms)), flush=True)
+if rms:
+    print("  render kernel alone %.1f us, view pass %.1f us" % (1e3 * sum(rms) / len(rms), 1e3 * (sum(ms) - sum(rms)) / len(ms)), flush=True)
 if args.count:
     print(ctx.counters())
