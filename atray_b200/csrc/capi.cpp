@@ -68,12 +68,18 @@ struct atray_ctx
     bool have_kernel_time = false;
     // slab-pipelined copy-out (atray_render_begin): the copy stream waits on the render kernel's per-slab counters
     cudaStream_t copy_stream = nullptr;
+    cudaStream_t copy_stream2 = nullptr;         // odd slabs of a pipelined frame when copy_streams == 2
+    int copy_streams = 2;                        // slabs alternate between two copy streams (ATRAY_COPY_STREAMS=1: one)
     cudaEvent_t ev_reset = nullptr;              // recorded after k_view_bounds cleared the counters of the previous frame
     cudaEvent_t ev_slab[kMaxSlabs] = {};         // slab s has landed in the host frame
     int slabs_in_flight = 0;                     // slabs of the frame in flight (0 = unpipelined frame)
     int32_t slab_row_end[kMaxSlabs] = {};        // first scanline after slab s (host rows landed once ev_slab[s] fired)
     int32_t pending_rows = 0;                    // height of the frame in flight
-    int slab_copy = 8;                           // slabs per pipelined frame (ATRAY_SLABS overrides; 1 = off)
+    // Slab plan of a pipelined frame: a short first slab lets the copy-out start right after the view pass (frames bound by
+    // the PCIe copy), a short last slab leaves little to copy once the kernel has retired (frames bound by tracing).
+    // ATRAY_SLABS=n: n equal slabs (1 = no pipelining); ATRAY_SLAB_WEIGHTS="2,6,8,16": relative heights. tools/slab_sweep.sh.
+    int slab_copy = 6;
+    int slab_w[kMaxSlabs] = {2, 6, 8, 8, 6, 2};
     typedef int (*WaitValue32)(cudaStream_t, unsigned long long, uint32_t, unsigned int);
     WaitValue32 wait_value32 = nullptr;          // cuStreamWaitValue32 through cudaGetDriverEntryPoint
     // ray-list buffers (atray_trace_rays)
@@ -270,6 +276,7 @@ int atray_ctx_create(int device, atray_ctx** out)
     if (e == cudaSuccess) e = cudaEventCreate(&c->ev_kr);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_done, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->copy_stream2, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_reset, cudaEventDisableTiming);
     for (int k = 0; k < kMaxSlabs && e == cudaSuccess; ++k) e = cudaEventCreateWithFlags(&c->ev_slab[k], cudaEventDisableTiming);
     if (e != cudaSuccess) { delete c; return cuda_fail(e, "context setup"); }
@@ -287,6 +294,22 @@ int atray_ctx_create(int device, atray_ctx** out)
         {
             const int v = std::atoi(env);
             c->slab_copy = v < 1 ? 1 : (v > kMaxSlabs ? kMaxSlabs : v);
+            for (int k = 0; k < kMaxSlabs; ++k) c->slab_w[k] = 0;
+        }
+        if (const char* env = std::getenv("ATRAY_COPY_STREAMS")) c->copy_streams = std::atoi(env) == 2 ? 2 : 1;
+        if (const char* env = std::getenv("ATRAY_SLAB_WEIGHTS"))
+        {
+            int n = 0;
+            for (int k = 0; k < kMaxSlabs; ++k) c->slab_w[k] = 0;
+            for (const char* p = env; *p && n < kMaxSlabs;)
+            {
+                char* end = nullptr;
+                const long v = std::strtol(p, &end, 10);
+                if (end == p) break;
+                c->slab_w[n++] = v < 1 ? 1 : int(v);
+                p = *end == ',' ? end + 1 : end;
+            }
+            if (n > 0) c->slab_copy = n;
         }
     }
     *out = c;
@@ -335,6 +358,7 @@ void atray_ctx_destroy(atray_ctx* c)
     for (int k = 0; k < kMaxSlabs; ++k)
         if (c->ev_slab[k]) cudaEventDestroy(c->ev_slab[k]);
     if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
+    if (c->copy_stream2) cudaStreamDestroy(c->copy_stream2);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -698,7 +722,7 @@ static int enqueue_render(atray_ctx* c, const AtrayCamera* cam, const AtrayRende
     CU(cudaEventRecord(c->ev_k0, c->stream));
     if (raster)
     {
-        const DevSlabs slabs = make_slabs(to_dev(cam), p, want_slabs);
+        const DevSlabs slabs = make_slabs(to_dev(cam), p, want_slabs, want_slabs > 1 ? c->slab_w : nullptr);
         CU(launch_film_tables(to_dev(cam), c->rs, c->stream));
         CU(launch_view_bounds(c->scene, vp, c->view, to_dev(cam), p, slabs, c->stream, want_slabs > 1 ? c->ev_reset : nullptr, false));
         CU(launch_raster(c->scene, vp, to_dev(cam), p, out, c->scratch, c->view, c->rs, slabs, ctr, o->fp_mode == ATRAY_FP_FAST, c->cfg,
@@ -708,7 +732,7 @@ static int enqueue_render(atray_ctx* c, const AtrayCamera* cam, const AtrayRende
     else if (cull)
     {
         // the film rectangles depend on the camera: recomputed every frame, inside the timed region
-        const DevSlabs slabs = make_slabs(to_dev(cam), p, want_slabs);
+        const DevSlabs slabs = make_slabs(to_dev(cam), p, want_slabs, want_slabs > 1 ? c->slab_w : nullptr);
         CU(launch_view_bounds(c->scene, vp, c->view, to_dev(cam), p, slabs, c->stream, want_slabs > 1 ? c->ev_reset : nullptr));
         CU(cudaEventRecord(c->ev_kr, c->stream));
         CU(launch_render_culled(c->scene, to_dev(cam), p, out, c->scratch, c->view, slabs, ctr, o->fp_mode == ATRAY_FP_FAST,
@@ -813,6 +837,7 @@ int atray_render_begin(atray_ctx* c, const AtrayCamera* cam, const AtrayRenderOp
     {
         CU(launch_slabs_final(c->view, slabs, c->stream));   // safety net: after the kernel every slab is final
         CU(cudaStreamWaitEvent(c->copy_stream, c->ev_reset, 0));
+        if (c->copy_streams == 2) CU(cudaStreamWaitEvent(c->copy_stream2, c->ev_reset, 0));
         const uint32_t tiles_per_band = uint32_t(((cam->width + 7) >> 3) * (o->part.band_rows >> 2));
         for (int s = 0; s < slabs.n; ++s)
         {
@@ -820,15 +845,18 @@ int atray_render_begin(atray_ctx* c, const AtrayCamera* cam, const AtrayRenderOp
             const int lb0 = int(slabs.tile_begin[s] / tiles_per_band), lb1 = int(slabs.tile_begin[s + 1] / tiles_per_band);
             int y1 = ((lb1 - 1) * o->part.world + o->part.rank + 1) * o->part.band_rows;
             if (y1 > cam->height) y1 = cam->height;
+            cudaStream_t cs = (c->copy_streams == 2 && (s & 1)) ? c->copy_stream2 : c->copy_stream;
             const unsigned long long addr = (unsigned long long)(uintptr_t)(c->view.busy_count + kCtlDone + s);
-            if (c->wait_value32(c->copy_stream, addr, slabs.live_tiles[s], 0u /* CU_STREAM_WAIT_VALUE_GEQ */) != 0)
+            if (c->wait_value32(cs, addr, slabs.live_tiles[s], 0u /* CU_STREAM_WAIT_VALUE_GEQ */) != 0)
                 return fail(ATRAY_ECUDA, "cuStreamWaitValue32 failed");
-            if (hb) CU(copy_local_bands(hb, c->d_bgrx, cam->width, cam->height, o->part, lb0, lb1, cudaMemcpyDeviceToHost, c->copy_stream));
-            if (ht) CU(copy_local_bands(ht, c->d_t, cam->width, cam->height, o->part, lb0, lb1, cudaMemcpyDeviceToHost, c->copy_stream));
-            if (hp) CU(copy_local_bands(hp, c->d_prim, cam->width, cam->height, o->part, lb0, lb1, cudaMemcpyDeviceToHost, c->copy_stream));
-            CU(cudaEventRecord(c->ev_slab[s], c->copy_stream));
+            if (hb) CU(copy_local_bands(hb, c->d_bgrx, cam->width, cam->height, o->part, lb0, lb1, cudaMemcpyDeviceToHost, cs));
+            if (ht) CU(copy_local_bands(ht, c->d_t, cam->width, cam->height, o->part, lb0, lb1, cudaMemcpyDeviceToHost, cs));
+            if (hp) CU(copy_local_bands(hp, c->d_prim, cam->width, cam->height, o->part, lb0, lb1, cudaMemcpyDeviceToHost, cs));
+            CU(cudaEventRecord(c->ev_slab[s], cs));
             c->slab_row_end[s] = int32_t(y1);   // this rank's scanlines below y1 have landed
         }
+        if (c->copy_streams == 2 && slabs.n > 1)   // the last odd slab's event orders stream 2 before the frame's end
+            CU(cudaStreamWaitEvent(c->copy_stream, c->ev_slab[((slabs.n - 1) & 1) ? slabs.n - 1 : slabs.n - 2], 0));
         CU(cudaStreamWaitEvent(c->copy_stream, c->ev_k1, 0));   // the frame is done only when the kernel has retired too
         CU(cudaEventRecord(c->ev_done, c->copy_stream));
         CU(cudaStreamWaitEvent(c->stream, c->ev_done, 0));      // later work on the context stream must not overtake the copies
@@ -917,6 +945,7 @@ int atray_render_cancel(atray_ctx* c)
     CU(cudaSetDevice(c->device));
     CU(cudaStreamSynchronize(c->stream));
     CU(cudaStreamSynchronize(c->copy_stream));
+    CU(cudaStreamSynchronize(c->copy_stream2));
     c->in_flight = false;
     return ATRAY_OK;
 }

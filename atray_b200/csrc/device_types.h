@@ -140,7 +140,7 @@ cudaError_t launch_render_culled(const DevScene& sc, const DevCamera& cam, const
                                  const DevScratch& scratch, const DevView& view, const DevSlabs& slabs, DevCounters* counters,
                                  int fp_fast, unsigned long long jitter_seed, LaunchCfg cfg, cudaStream_t stream);
 // local tile count of a rank and the slab table for `n_slabs` (clamped to the number of local bands)
-DevSlabs make_slabs(const DevCamera& cam, const DevPartition& part, int n_slabs);
+DevSlabs make_slabs(const DevCamera& cam, const DevPartition& part, int n_slabs, const int* weights = nullptr);
 cudaError_t launch_slabs_final(const DevView& view, const DevSlabs& slabs, cudaStream_t stream);
 // K3: pixel loop + cast_ray at any bounce_limit with spheres/planes (renderer.cpp:34-160, 213-262, 314-365)
 cudaError_t launch_path(const DevScene& sc, const DevCamera& cam, const DevPartition& part, const DevOut& out,

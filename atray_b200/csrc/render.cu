@@ -1535,7 +1535,7 @@ cudaError_t launch_render(const DevScene& sc, const DevCamera& cam, const DevPar
     return cudaGetLastError();
 }
 
-DevSlabs make_slabs(const DevCamera& cam, const DevPartition& part, int n_slabs)
+DevSlabs make_slabs(const DevCamera& cam, const DevPartition& part, int n_slabs, const int* weights)
 {
     DevSlabs s{};
     const int tiles_x = (cam.W + 7) >> 3;
@@ -1545,12 +1545,21 @@ DevSlabs make_slabs(const DevCamera& cam, const DevPartition& part, int n_slabs)
     int n = n_slabs < 1 ? 1 : (n_slabs > kMaxSlabs ? kMaxSlabs : n_slabs);
     if (n > my_bands) n = my_bands < 1 ? 1 : my_bands;
     s.n = n;
+    // slab k covers the bands [band_of[k], band_of[k+1]): proportional to weights[k] (uniform without), at least one band
     int band_of[kMaxSlabs + 1];
-    for (int k = 0; k <= kMaxSlabs; ++k)
+    long long w_total = 0, w_acc = 0;
+    for (int k = 0; k < n; ++k) w_total += weights && weights[k] > 0 ? weights[k] : 1;
+    band_of[0] = 0;
+    for (int k = 1; k <= kMaxSlabs; ++k)
     {
-        band_of[k] = k >= n ? my_bands : (int)((long long)k * my_bands / n);
-        s.tile_begin[k] = (uint32_t)band_of[k] * tiles_per_band;
+        if (k >= n) { band_of[k] = my_bands; continue; }
+        w_acc += weights && weights[k - 1] > 0 ? weights[k - 1] : 1;
+        int b = (int)(w_acc * my_bands / w_total);
+        if (b <= band_of[k - 1]) b = band_of[k - 1] + 1;
+        if (b > my_bands - (n - k)) b = my_bands - (n - k);   // leave a band for each later slab
+        band_of[k] = b;
     }
+    for (int k = 0; k <= kMaxSlabs; ++k) s.tile_begin[k] = (uint32_t)band_of[k] * tiles_per_band;
     for (int k = 0; k < kMaxSlabs; ++k)
     {
         uint32_t live = 0;

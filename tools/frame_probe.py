@@ -1,10 +1,13 @@
 #!/usr/bin/env python3
 """Renders the C4 frame a few times on one GPU (device planes, no copy-out) and prints the frame's kernel time; under
 `ncu --metrics gpu__time_duration.sum` it gives the per-kernel split of one frame.
-usage: python tools/frame_probe.py [--reps N] [--raster] [--world N]"""
+With --host it times the end-to-end frame instead (pinned host bitmap, slab-pipelined copy-out, wall clock), which is
+what ATRAY_SLABS / ATRAY_SLAB_WEIGHTS tune.
+usage: python tools/frame_probe.py [--reps N] [--raster] [--world N] [--host]"""
 import argparse
 import os
 import sys
+import time
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import atray_b200 as A  # noqa: E402
@@ -15,6 +18,7 @@ ap.add_argument("--reps", type=int, default=10)
 ap.add_argument("--raster", action="store_true")
 ap.add_argument("--world", type=int, default=1)
 ap.add_argument("--count", action="store_true")
+ap.add_argument("--host", action="store_true")
 args = ap.parse_args()
 W, H = 3840, 2160
 path = gen_standin_obj.ensure(os.path.join(os.environ.get("ATRAY_MESH_CACHE", "/tmp/atray_meshes"), "standin_272x256.obj"))
@@ -24,6 +28,24 @@ sc = A.Scene(m)
 A.prep_scene(sc)
 ctx = sc.ctx
 cam = A.set_camera(W, H)
+if args.host:
+    import numpy as np
+    tex = A.PinnedArray((H, W), np.uint32)
+    info = A.RenderInfo(cam, sc, tex.array, opts=ctx.opts(rank=0, world=1, band_rows=8, raster=args.raster))
+    best = 1e9
+    for rep in range(3):
+        for i in range(args.reps + 2):
+            if i == 2:
+                ctx.sync()
+                t0 = time.perf_counter()
+            A.start_render_from_camera(info)
+            while A.wait_for_render_from_camera_to_finish(info, None, 33):
+                pass
+        dt = (time.perf_counter() - t0) / args.reps
+        best = min(best, dt)
+    print("host frame (slabs %s weights %s): %.1f us per frame (best of 3 x %d)" % (
+        os.environ.get("ATRAY_SLABS", "default"), os.environ.get("ATRAY_SLAB_WEIGHTS", "uniform"), 1e6 * best, args.reps), flush=True)
+    sys.exit(0)
 planes = [ctx.dev_alloc(W * H * 4) for _ in range(3)]
 flush = ctx.dev_alloc(256 << 20)
 opts = ctx.opts(rank=0, world=args.world, band_rows=8, raster=args.raster, count_work=args.count)
