@@ -345,6 +345,7 @@ void atray_ctx_destroy(atray_ctx* c)
     free_scene(c);
     cudaFree(c->d_tile_counter); cudaFree(c->d_counters); cudaFree(c->d_casts);
     cudaFree(c->view.stamps); cudaFree(c->view.all_flag); cudaFree(c->view.busy_list); cudaFree(c->view.busy_count);
+    cudaFree(c->view.tile_cost);
     cudaFree(c->rs.tabx); cudaFree(c->rs.taby); cudaFree(c->rs.key1); cudaFree(c->rs.key2); cudaFree(c->rs.hit_a);
     cudaFree(c->rs.hit_pos); cudaFree(c->rs.ctl);
     cudaFree(c->d_bgrx); cudaFree(c->d_t); cudaFree(c->d_prim);
@@ -692,11 +693,16 @@ static int enqueue_render(atray_ctx* c, const AtrayCamera* cam, const AtrayRende
         {
             if (tiles > c->stamp_cap)
             {
-                cudaFree(c->view.stamps); cudaFree(c->view.busy_list);
-                c->view.stamps = nullptr; c->view.busy_list = nullptr; c->stamp_cap = 0;
+                cudaFree(c->view.stamps); cudaFree(c->view.busy_list); cudaFree(c->view.tile_cost);
+                c->view.stamps = nullptr; c->view.busy_list = nullptr; c->view.tile_cost = nullptr; c->stamp_cap = 0;
                 CU(cudaMalloc(&c->view.stamps, tiles * sizeof(uint32_t)));
-                CU(cudaMalloc(&c->view.busy_list, tiles * sizeof(uint32_t)));
+                CU(cudaMalloc(&c->view.tile_cost, tiles * sizeof(uint32_t)));
+                CU(cudaMalloc(&c->view.busy_list, tiles * kCostBuckets * sizeof(uint32_t)));
+                CU(cudaMemsetAsync(c->view.tile_cost, 0, tiles * sizeof(uint32_t), c->stream));
                 c->stamp_cap = tiles;
+                c->view.bucket_stride = uint32_t(tiles);
+                c->view.cost_shift = 0;
+                if (const char* env = std::getenv("ATRAY_COST_SHIFT")) c->view.cost_shift = std::atoi(env);
             }
             if (!c->view.all_flag) CU(cudaMalloc(&c->view.all_flag, sizeof(uint32_t)));
             if (!c->view.busy_count)

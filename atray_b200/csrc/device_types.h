@@ -67,8 +67,12 @@ struct DevView
     float4* pkt_rect;      // n_slots/8 union over the packet's slots
     float4* node_rect;     // n_nodes   leaf: union over its packets; inner node: union over its children
     uint32_t* stamps;      // one per 8x4-pixel tile: == frame_id ⇔ some triangle rectangle may touch the tile
+    uint32_t* tile_cost;   // one per tile: rectangles of every 8th triangle slot that touch it this frame (k_view_finish reads and clears it)
     uint32_t* all_flag;    // == frame_id ⇔ an unbounded rectangle exists: every tile is busy
-    uint32_t* busy_list;   // tiles of this rank's bands that must be traced (local tile numbering of the render kernel)
+    uint32_t* busy_list;   // tiles of this rank's bands that must be traced (local tile numbering of the render kernel):
+                           // kCostBuckets regions of bucket_stride entries, see below
+    uint32_t bucket_stride; // entries per cost class (>= tiles of the frame)
+    int32_t cost_shift;    // class = floor(log2(rectangles)) - cost_shift, clamped to [0, kCostBuckets)
     uint32_t* busy_count;  // control words, see kCtl* below (per-slab list lengths, cursors, finished-tile counters, ticket)
     uint32_t frame_id;
     int32_t tiles_x;
@@ -97,12 +101,16 @@ struct DevRaster
 // Slabs: the rank's tiles (band-major local numbering) split into up to kMaxSlabs contiguous ranges of whole bands. The
 // render kernel finishes slab after slab and publishes a finished-tile counter per slab, so the host side can start the
 // device→host copy of a slab's scanlines while later slabs are still being traced (capi.cpp: atray_render_begin).
+// The busy tiles of a slab are listed per cost class (class = log2 of the number of triangle rectangles touching the tile,
+// see tile_cost_class) and traced most expensive class first: the longest tiles start earliest, which is what bounds the
+// kernel's tail. Region b of busy_list holds class b; inside it the segment of slab s starts at tile_begin[s].
 static constexpr int kMaxSlabs = 16;
-static constexpr int kCtlCount = 0;                 // [s] entries in slab s's segment of busy_list
-static constexpr int kCtlCursor = kMaxSlabs;        // [s] consumer cursor of slab s
-static constexpr int kCtlDone = 2 * kMaxSlabs;      // [s] tiles of slab s whose stores are complete (sky + traced)
-static constexpr int kCtlTicket = 3 * kMaxSlabs;    // finished-block ticket of k_view_finish
-static constexpr int kCtlWords = 3 * kMaxSlabs + 4;
+static constexpr int kCostBuckets = 8;
+static constexpr int kCtlCount = 0;                              // [s * kCostBuckets + b] entries of slab s in class b
+static constexpr int kCtlCursor = kMaxSlabs * kCostBuckets;      // [s] consumer cursor of slab s
+static constexpr int kCtlDone = kCtlCursor + kMaxSlabs;          // [s] tiles of slab s whose stores are complete (sky + traced)
+static constexpr int kCtlTicket = kCtlDone + kMaxSlabs;          // end of the words k_view_bounds clears every frame
+static constexpr int kCtlWords = kCtlTicket + 4;
 struct DevSlabs
 {
     int32_t n;                              // 1 … kMaxSlabs

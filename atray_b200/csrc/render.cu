@@ -496,15 +496,35 @@ __device__ __forceinline__ float4 rect_union_xor(float4 r, int off)
     return r;
 }
 
+// Order-independent float min/max on global memory (the sign decides which integer order matches the float order;
+// -0 is folded into +0 first, NaN never wins as with fminf/fmaxf).
+__device__ __forceinline__ void atomic_min_float(float* p, float v)
+{
+    v += 0.0f;
+    if (v >= 0.0f) atomicMin(reinterpret_cast<int*>(p), __float_as_int(v));
+    else if (v < 0.0f) atomicMax(reinterpret_cast<unsigned int*>(p), __float_as_uint(v));
+}
+__device__ __forceinline__ void atomic_max_float(float* p, float v)
+{
+    v += 0.0f;
+    if (v >= 0.0f) atomicMax(reinterpret_cast<int*>(p), __float_as_int(v));
+    else if (v < 0.0f) atomicMin(reinterpret_cast<unsigned int*>(p), __float_as_uint(v));
+}
+
 // One thread per triangle slot: film rectangle, union per packet (8 lanes), tile stamps.
-__global__ void __launch_bounds__(kBlock) k_view_bounds(DevScene sc, ViewParams vp, DevView view)
+__global__ void __launch_bounds__(kBlock, 4) k_view_bounds(DevScene sc, ViewParams vp, DevView view)
 {
     const int lane = threadIdx.x & 31;
     const uint32_t slot = blockIdx.x * kBlock + threadIdx.x;
     const uint32_t slots_up = (sc.n_slots + 31u) & ~31u;
-    if (slot < (uint32_t)kCtlTicket) view.busy_count[slot] = 0u;  // per-slab list lengths, cursors and finished-tile counters
+    for (uint32_t i = slot; i < (uint32_t)kCtlTicket; i += gridDim.x * kBlock) view.busy_count[i] = 0u;  // list lengths, cursors, finished-tile counters
+    // node rectangles start empty: k_view_finish accumulates every leaf's rectangle into its ancestors with atomics
+    for (uint32_t i = slot; i < sc.n_nodes; i += gridDim.x * kBlock) view.node_rect[i] = make_float4(INFINITY, INFINITY, -INFINITY, -INFINITY);
     if (slot >= slots_up) return;  // whole warps only beyond this point
     const bool in_range = slot < sc.n_slots;
+    // tile cost = rectangles of the first slot of every packet (1 in 8: the lists only need the cost's order of magnitude,
+    // and one atomic per (triangle, tile) pair costs the pre-pass 16 us on the 4K frame)
+    const bool sampled = (slot & 7u) == 0u;
     const int n_tiles = vp.tiles_x * vp.tiles_y;
     float4 r = make_float4(INFINITY, INFINITY, -INFINITY, -INFINITY);
     int tx0 = 0, tx1 = -1, ty0 = 0, ty1 = -1;
@@ -526,7 +546,11 @@ __global__ void __launch_bounds__(kBlock) k_view_bounds(DevScene sc, ViewParams 
                 else
                 {
                     for (int ty = ty0; ty <= ty1; ++ty)
-                        for (int tx = tx0; tx <= tx1; ++tx) view.stamps[ty * vp.tiles_x + tx] = vp.frame_id;
+                        for (int tx = tx0; tx <= tx1; ++tx)
+                        {
+                            view.stamps[ty * vp.tiles_x + tx] = vp.frame_id;
+                            if (sampled) atomicAdd(&view.tile_cost[ty * vp.tiles_x + tx], 1u);
+                        }
                 }
             }
         }
@@ -541,141 +565,171 @@ __global__ void __launch_bounds__(kBlock) k_view_bounds(DevScene sc, ViewParams 
         const int ax0 = __shfl_sync(FULL_MASK, tx0, src), ax1 = __shfl_sync(FULL_MASK, tx1, src);
         const int ay0 = __shfl_sync(FULL_MASK, ty0, src), ay1 = __shfl_sync(FULL_MASK, ty1, src);
         const int w = ax1 - ax0 + 1, n = w * (ay1 - ay0 + 1);
-        for (int i = lane; i < n; i += 32) view.stamps[(ay0 + i / w) * vp.tiles_x + ax0 + i % w] = vp.frame_id;
+        for (int i = lane; i < n; i += 32)
+        {
+            view.stamps[(ay0 + i / w) * vp.tiles_x + ax0 + i % w] = vp.frame_id;
+            if ((src & 7) == 0) atomicAdd(&view.tile_cost[(ay0 + i / w) * vp.tiles_x + ax0 + i % w], 1u);
+        }
     }
     float4 p = r;
     p = rect_union_xor(p, 4); p = rect_union_xor(p, 2); p = rect_union_xor(p, 1);
     if (in_range && (lane & 7) == 0) view.pkt_rect[slot >> 3] = p;
 }
 
-// Second pass: (1) one warp per leaf unions its packet rectangles, (2) the stamps of this rank's tiles are compacted
-// into the busy list, (3) the last block to finish unions the children of every inner node, deepest level first.
+// Second pass, two kinds of blocks running side by side:
+//  * blocks [0, leaf_blocks): one warp per leaf unions its packet rectangles and folds the result into every ancestor's
+//    rectangle (order-independent atomics: no level-by-level pass);
+//  * the other blocks compact the stamps of this rank's tiles into the busy list, kTilesPerThread tiles per thread and ONE
+//    global atomic per block and slab (the warps reserve their places in shared memory first; per-warp global atomics
+//    would serialise on the handful of slab counters).
+static constexpr int kTilesPerThread = 4;
+// floor(log2(cost)) - shift, clamped to the classes. Measured on the 4K frame (tools/cost_sweep.sh): 8 classes from the sampled
+// count (shift 0: 1, 2-3, 4-7, … ≥ 128) take the render kernel from 275 to 257 us; 16 half-octave classes do no better.
+__device__ __forceinline__ int tile_cost_class(uint32_t cost, int shift)
+{
+    const int c = 31 - __clz((int)(cost | 1u)) - shift;
+    return c < 0 ? 0 : (c > kCostBuckets - 1 ? kCostBuckets - 1 : c);
+}
 __global__ void __launch_bounds__(kBlock) k_view_finish(DevScene sc, DevView view, DevCamera cm, DevPartition part, DevSlabs slabs,
-                                                        uint32_t smem_nodes)
+                                                        uint32_t leaf_blocks)
 {
     const int lane = threadIdx.x & 31;
-    const uint32_t warp = (blockIdx.x * kBlock + threadIdx.x) >> 5;
-    const uint32_t n_warps = (gridDim.x * kBlock) >> 5;
-    for (uint32_t node = warp; node < sc.n_nodes; node += n_warps)
+    if (blockIdx.x < leaf_blocks)
     {
-        const float4 n0 = __ldg(&sc.nodes[2 * node]);
-        if (__float_as_int(n0.w) > 0) continue;
-        const uint32_t first = ~(uint32_t)__float_as_int(n0.w);
-        const uint32_t cnt = (uint32_t)__float_as_int(__ldg(&sc.nodes[2 * node + 1]).w);
-        const uint32_t npk = (cnt + 7u) >> 3, pk0 = first >> 3;
-        float4 acc = make_float4(INFINITY, INFINITY, -INFINITY, -INFINITY);
-        for (uint32_t k = lane; k < npk; k += 32)
+        const uint32_t warp = (blockIdx.x * kBlock + threadIdx.x) >> 5;
+        const uint32_t n_warps = (leaf_blocks * kBlock) >> 5;
+        float4 mine = make_float4(INFINITY, INFINITY, -INFINITY, -INFINITY);  // union over the leaves this warp handled (lane 0)
+        for (uint32_t node = warp; node < sc.n_nodes; node += n_warps)
         {
-            const float4 q = view.pkt_rect[pk0 + k];
-            acc.x = fminf(acc.x, q.x); acc.y = fminf(acc.y, q.y); acc.z = fmaxf(acc.z, q.z); acc.w = fmaxf(acc.w, q.w);
-        }
+            const float4 n0 = __ldg(&sc.nodes[2 * node]);
+            if (__float_as_int(n0.w) > 0) continue;
+            const uint32_t first = ~(uint32_t)__float_as_int(n0.w);
+            const uint32_t cnt = (uint32_t)__float_as_int(__ldg(&sc.nodes[2 * node + 1]).w);
+            const uint32_t npk = (cnt + 7u) >> 3, pk0 = first >> 3;
+            float4 acc = make_float4(INFINITY, INFINITY, -INFINITY, -INFINITY);
+            for (uint32_t k = lane; k < npk; k += 32)
+            {
+                const float4 q = view.pkt_rect[pk0 + k];
+                acc.x = fminf(acc.x, q.x); acc.y = fminf(acc.y, q.y); acc.z = fmaxf(acc.z, q.z); acc.w = fmaxf(acc.w, q.w);
+            }
 #pragma unroll
-        for (int off = 16; off > 0; off >>= 1) acc = rect_union_xor(acc, off);
-        if (lane == 0) view.node_rect[node] = acc;
+            for (int off = 16; off > 0; off >>= 1) acc = rect_union_xor(acc, off);
+            if (lane == 0)
+            {
+                view.node_rect[node] = acc;
+                if (acc.x <= acc.z && acc.y <= acc.w)   // an empty rectangle changes no ancestor
+                {
+                    // every ancestor but the root: a few hundred updates per address at most
+                    for (uint32_t p = __ldg(&sc.parent[node]); p != 0xffffffffu && p != 0u; p = __ldg(&sc.parent[p]))
+                    {
+                        float* q = reinterpret_cast<float*>(&view.node_rect[p]);
+                        atomic_min_float(q + 0, acc.x); atomic_min_float(q + 1, acc.y);
+                        atomic_max_float(q + 2, acc.z); atomic_max_float(q + 3, acc.w);
+                    }
+                    mine.x = fminf(mine.x, acc.x); mine.y = fminf(mine.y, acc.y); mine.z = fmaxf(mine.z, acc.z); mine.w = fmaxf(mine.w, acc.w);
+                }
+            }
+        }
+        // the root takes one update per block (every leaf is below it: per-leaf atomics would serialise on one address)
+        __shared__ float4 s_mine[kBlock / 32];
+        if (lane == 0) s_mine[threadIdx.x >> 5] = mine;
+        __syncthreads();
+        if (threadIdx.x == 0 && !sc.root_is_leaf)
+        {
+            float4 m = s_mine[0];
+            for (int w = 1; w < kBlock / 32; ++w)
+            {
+                const float4 q = s_mine[w];
+                m.x = fminf(m.x, q.x); m.y = fminf(m.y, q.y); m.z = fmaxf(m.z, q.z); m.w = fmaxf(m.w, q.w);
+            }
+            if (m.x <= m.z && m.y <= m.w)
+            {
+                float* q = reinterpret_cast<float*>(&view.node_rect[0]);
+                atomic_min_float(q + 0, m.x); atomic_min_float(q + 1, m.y);
+                atomic_max_float(q + 2, m.z); atomic_max_float(q + 3, m.w);
+            }
+        }
+        return;
     }
     // busy tiles of this rank, in the render kernel's local numbering (band-major, then tile row, then tile column)
+    const int tiles_x = (cm.W + 7) >> 3;
+    const int rows_per_band = part.band_rows >> 2;
+    const int n_bands = (cm.H + part.band_rows - 1) / part.band_rows;
+    const int my_bands = part.rank < n_bands ? (n_bands - part.rank + part.world - 1) / part.world : 0;
+    const unsigned int tiles_per_band = (unsigned int)(tiles_x * rows_per_band);
+    const unsigned int n_tiles = (unsigned int)my_bands * tiles_per_band;
+    const bool all_busy = *((volatile uint32_t*)view.all_flag) == view.frame_id;
+    const unsigned int blk = blockIdx.x - leaf_blocks, n_blk = gridDim.x - leaf_blocks;
+    constexpr unsigned int kStep = kBlock * kTilesPerThread;
+    __shared__ unsigned int s_count[kMaxSlabs * kCostBuckets], s_at[kMaxSlabs * kCostBuckets];
+    for (unsigned int base = blk * kStep; base < n_tiles; base += n_blk * kStep)
     {
-        const int tiles_x = (cm.W + 7) >> 3;
-        const int rows_per_band = part.band_rows >> 2;
-        const int n_bands = (cm.H + part.band_rows - 1) / part.band_rows;
-        const int my_bands = part.rank < n_bands ? (n_bands - part.rank + part.world - 1) / part.world : 0;
-        const unsigned int tiles_per_band = (unsigned int)(tiles_x * rows_per_band);
-        const unsigned int n_tiles = (unsigned int)my_bands * tiles_per_band;
-        const bool all_busy = *((volatile uint32_t*)view.all_flag) == view.frame_id;
-        for (unsigned int base = warp * 32u; base < n_tiles; base += n_warps * 32u)
+        if (threadIdx.x < kMaxSlabs * kCostBuckets) s_count[threadIdx.x] = 0u;
+        __syncthreads();
+        bool busy[kTilesPerThread];
+        int slab[kTilesPerThread];
+#pragma unroll
+        for (int k = 0; k < kTilesPerThread; ++k)
         {
-            const unsigned int tile = base + lane;
-            bool busy = false;
+            const unsigned int tile = base + k * kBlock + threadIdx.x;
+            busy[k] = false;
+            int cls = 0;
             if (tile < n_tiles)
             {
                 const unsigned int lb = tile / tiles_per_band, rem = tile - lb * tiles_per_band;
                 const int trow = (int)(rem / (unsigned int)tiles_x), tcol = (int)(rem - (unsigned int)trow * (unsigned int)tiles_x);
                 const int y0 = ((int)lb * part.world + part.rank) * part.band_rows + trow * 4;
-                busy = y0 < cm.H && (all_busy || view.stamps[(y0 >> 2) * view.tiles_x + tcol] == view.frame_id);
+                const int gt = (y0 >> 2) * view.tiles_x + tcol;
+                busy[k] = y0 < cm.H && (all_busy || view.stamps[gt] == view.frame_id);
+                if (busy[k])
+                {
+                    cls = tile_cost_class(view.tile_cost[gt], view.cost_shift);
+                    view.tile_cost[gt] = 0u;   // the next frame counts from zero
+                }
             }
-            // append to the segment of the tile's slab (segment s starts at busy_list[tile_begin[s]]: room for every tile)
-            int slab = 0;
-            while (slab + 1 < slabs.n && tile >= slabs.tile_begin[slab + 1]) ++slab;
-            unsigned todo = __ballot_sync(FULL_MASK, busy);
+            int sl = 0;
+            while (sl + 1 < slabs.n && tile >= slabs.tile_begin[sl + 1]) ++sl;
+            slab[k] = sl * kCostBuckets + cls;   // list key: (slab, cost class)
+        }
+        // pass 1: how many entries does this block add to each slab's segment
+#pragma unroll
+        for (int k = 0; k < kTilesPerThread; ++k)
+        {
+            unsigned todo = __ballot_sync(FULL_MASK, busy[k]);
             while (todo)
             {
                 const int leader = __ffs(todo) - 1;
-                const int ls = __shfl_sync(FULL_MASK, slab, leader);
-                const unsigned m = __ballot_sync(FULL_MASK, busy && slab == ls);
+                const int ls = __shfl_sync(FULL_MASK, slab[k], leader);
+                const unsigned m = __ballot_sync(FULL_MASK, busy[k] && slab[k] == ls);
+                todo &= ~m;
+                if (lane == leader) atomicAdd(&s_count[ls], (unsigned int)__popc(m));
+            }
+        }
+        __syncthreads();
+        if (threadIdx.x < (unsigned)(slabs.n * kCostBuckets) && s_count[threadIdx.x])
+            s_at[threadIdx.x] = atomicAdd(&view.busy_count[kCtlCount + threadIdx.x], s_count[threadIdx.x]);
+        __syncthreads();
+        // pass 2: places inside the block's reservation (segment s starts at busy_list[tile_begin[s]]: room for every tile)
+#pragma unroll
+        for (int k = 0; k < kTilesPerThread; ++k)
+        {
+            unsigned todo = __ballot_sync(FULL_MASK, busy[k]);
+            while (todo)
+            {
+                const int leader = __ffs(todo) - 1;
+                const int ls = __shfl_sync(FULL_MASK, slab[k], leader);
+                const unsigned m = __ballot_sync(FULL_MASK, busy[k] && slab[k] == ls);
                 todo &= ~m;
                 unsigned int at = 0;
-                if (lane == leader) at = atomicAdd(&view.busy_count[kCtlCount + ls], (unsigned int)__popc(m));
+                if (lane == leader) at = atomicAdd(&s_at[ls], (unsigned int)__popc(m));
                 at = __shfl_sync(FULL_MASK, at, leader);
-                if (busy && slab == ls) view.busy_list[slabs.tile_begin[ls] + at + __popc(m & ((1u << lane) - 1u))] = tile;
+                if (busy[k] && slab[k] == ls)
+                    view.busy_list[(unsigned int)(ls % kCostBuckets) * view.bucket_stride + slabs.tile_begin[ls / kCostBuckets] + at +
+                                   __popc(m & ((1u << lane) - 1u))] = base + k * kBlock + threadIdx.x;
             }
-        }
-    }
-    // last block: inner-node rectangles, bottom-up
-    __shared__ bool is_last;
-    __threadfence();
-    __syncthreads();
-    if (threadIdx.x == 0) is_last = atomicAdd(&view.busy_count[kCtlTicket], 1u) == gridDim.x - 1;
-    __syncthreads();
-    if (!is_last) return;
-    __threadfence();
-    if (smem_nodes >= sc.n_nodes)
-    {
-        // whole rectangle table in shared memory: one coalesced load, then the levels cost a __syncthreads each
-        extern __shared__ float4 s_rect[];
-        const uint32_t n_inner = __ldg(&sc.level_start[sc.n_levels]);
-        uint32_t* s_node = reinterpret_cast<uint32_t*>(s_rect + sc.n_nodes);
-        uint32_t* s_c0 = s_node + n_inner;
-        for (uint32_t i = threadIdx.x; i < sc.n_nodes; i += kBlock) s_rect[i] = __ldcg(&view.node_rect[i]);  // leaves are final
-        for (uint32_t k = threadIdx.x; k < n_inner; k += kBlock)
-        {
-            const uint32_t node = __ldg(&sc.inner_order[k]);
-            s_node[k] = node;
-            s_c0[k] = (uint32_t)__float_as_int(__ldg(&sc.nodes[2 * node]).w);
         }
         __syncthreads();
-        uint32_t b = 0;
-        for (uint32_t l = 0; l < sc.n_levels; ++l)
-        {
-            const uint32_t e = __ldg(&sc.level_start[l + 1]);
-            for (uint32_t k = b + threadIdx.x; k < e; k += kBlock)
-            {
-                const uint32_t c0 = s_c0[k];
-                float4 acc = make_float4(INFINITY, INFINITY, -INFINITY, -INFINITY);
-#pragma unroll
-                for (int c = 0; c < 8; ++c)
-                {
-                    const float4 q = s_rect[c0 + c];
-                    acc.x = fminf(acc.x, q.x); acc.y = fminf(acc.y, q.y); acc.z = fmaxf(acc.z, q.z); acc.w = fmaxf(acc.w, q.w);
-                }
-                s_rect[s_node[k]] = acc;
-                view.node_rect[s_node[k]] = acc;
-            }
-            __syncthreads();
-            b = e;
-        }
-        if (threadIdx.x == 0) view.busy_count[kCtlTicket] = 0u;  // ticket for the next frame
-        return;
     }
-    for (uint32_t l = 0; l < sc.n_levels; ++l)
-    {
-        const uint32_t b = __ldg(&sc.level_start[l]), e = __ldg(&sc.level_start[l + 1]);
-        for (uint32_t k = b + threadIdx.x; k < e; k += kBlock)
-        {
-            const uint32_t node = __ldg(&sc.inner_order[k]);
-            const uint32_t c0 = (uint32_t)__float_as_int(__ldg(&sc.nodes[2 * node]).w);
-            float4 acc = make_float4(INFINITY, INFINITY, -INFINITY, -INFINITY);
-#pragma unroll
-            for (int c = 0; c < 8; ++c)
-            {
-                const float4 q = __ldcg(&view.node_rect[c0 + c]);
-                acc.x = fminf(acc.x, q.x); acc.y = fminf(acc.y, q.y); acc.z = fmaxf(acc.z, q.z); acc.w = fmaxf(acc.w, q.w);
-            }
-            view.node_rect[node] = acc;
-        }
-        __threadfence();
-        __syncthreads();
-    }
-    if (threadIdx.x == 0) view.busy_count[kCtlTicket] = 0u;  // ticket for the next frame
 }
 
 // ---- culled phase 2: the warp walks the k-th listed leaf of each of its rays; rays that share the leaf form a group.
@@ -1155,14 +1209,26 @@ __global__ void __launch_bounds__(kBlock) k_render_culled(DevScene sc, DevCamera
         }
     }
     // ---- phase B: busy tiles -----------------------------------------------------------------------------------------
-    const unsigned int n_busy = __ldg(&vw.busy_count[kCtlCount + slab]);
+    // The slab's list is walked most expensive cost class first: lane r < kCostBuckets holds the length of class
+    // kCostBuckets-1-r (re-read per tile: two registers less across the trace) and where it starts in that order.
     for (;;)
     {
         unsigned int bi = 0;
         if (lane == 0) bi = atomicAdd(&vw.busy_count[kCtlCursor + slab], 1u);
         bi = __shfl_sync(FULL_MASK, bi, 0);
-        if (bi >= n_busy) break;
-        const unsigned int tile = __ldg(&vw.busy_list[tile_lo + bi]);
+        const unsigned int cnt = lane < kCostBuckets ? __ldg(&vw.busy_count[kCtlCount + slab * kCostBuckets + (kCostBuckets - 1 - lane)]) : 0u;
+        unsigned int end = cnt;   // inclusive prefix sum over the lanes
+#pragma unroll
+        for (int off = 1; off < kCostBuckets; off <<= 1)
+        {
+            const unsigned int v = __shfl_up_sync(FULL_MASK, end, off);
+            if (lane >= off) end += v;
+        }
+        const unsigned hit = __ballot_sync(FULL_MASK, lane < kCostBuckets && bi < end);
+        if (!hit) break;   // past the slab's last busy tile
+        const int r = __ffs(hit) - 1;
+        const unsigned int start = __shfl_sync(FULL_MASK, end - cnt, r);
+        const unsigned int tile = __ldg(&vw.busy_list[(unsigned int)(kCostBuckets - 1 - r) * vw.bucket_stride + tile_lo + (bi - start)]);
         ++finished;
         const unsigned int lb = tile / tiles_per_band, rem = tile - lb * tiles_per_band;
         const int trow = (int)(rem / (unsigned int)tiles_x), tcol = (int)(rem - (unsigned int)trow * (unsigned int)tiles_x);
@@ -1600,21 +1666,8 @@ cudaError_t launch_view_bounds(const DevScene& sc, const ViewParams& vp, const D
         if (e != cudaSuccess) return e;
     }
     if (!finish) return cudaSuccess;  // rasterised frame: no tile lists, no node rectangles
-    // inner-node unions run in shared memory when the table fits: 16 B per node + 8 B per inner node
-    static bool attr_set[64] = {};  // per device (function attributes belong to the device's context)
-    const size_t kSmemMax = 200 * 1024;
-    int dev = 0;
-    e = cudaGetDevice(&dev);
-    if (e != cudaSuccess) return e;
-    if (dev < 0 || dev >= 64 || !attr_set[dev])
-    {
-        e = cudaFuncSetAttribute(k_view_finish, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemMax);
-        if (e != cudaSuccess) return e;
-        if (dev >= 0 && dev < 64) attr_set[dev] = true;
-    }
-    const size_t need = (size_t)sc.n_nodes * 16 + ((size_t)sc.n_nodes / 8 + 1) * 8;
-    const bool fits = need <= kSmemMax;
-    k_view_finish<<<296, kBlock, fits ? need : 0, stream>>>(sc, view, cam, part, slabs, fits ? sc.n_nodes : 0u);
+    // 296 + 296 blocks of 32 registers: all resident at once (4 per SM); one round of leaves, one of tiles for a 4K frame
+    k_view_finish<<<592, kBlock, 0, stream>>>(sc, view, cam, part, slabs, 296u);
     return cudaGetLastError();
 }
 
