@@ -103,6 +103,7 @@ _SIGS = {
     "atray_scene_set_primitives": [_vp, _vp, _u, _vp, _u],
     "atray_scene_use_kd_tree": [_vp, _i],
     "atray_last_ray_casts": [_vp, C.POINTER(_u64)],
+    "atray_debug_tile_log": [_vp, _vp, C.c_size_t],
     "atray_render_begin": [_vp, C.POINTER(CameraStruct), C.POINTER(RenderOpts), C.POINTER(Frame)],
     "atray_render_poll": [_vp, _u],
     "atray_render_progress": [_vp, C.POINTER(_i), C.POINTER(_i)],

@@ -345,7 +345,7 @@ void atray_ctx_destroy(atray_ctx* c)
     free_scene(c);
     cudaFree(c->d_tile_counter); cudaFree(c->d_counters); cudaFree(c->d_casts);
     cudaFree(c->view.stamps); cudaFree(c->view.all_flag); cudaFree(c->view.busy_list); cudaFree(c->view.busy_count);
-    cudaFree(c->view.tile_cost);
+    cudaFree(c->view.tile_cost); cudaFree(c->view.tile_log);
     cudaFree(c->rs.tabx); cudaFree(c->rs.taby); cudaFree(c->rs.key1); cudaFree(c->rs.key2); cudaFree(c->rs.hit_a);
     cudaFree(c->rs.hit_pos); cudaFree(c->rs.ctl);
     cudaFree(c->d_bgrx); cudaFree(c->d_t); cudaFree(c->d_prim);
@@ -701,6 +701,14 @@ static int enqueue_render(atray_ctx* c, const AtrayCamera* cam, const AtrayRende
                 CU(cudaMemsetAsync(c->view.tile_cost, 0, tiles * sizeof(uint32_t), c->stream));
                 c->stamp_cap = tiles;
                 c->view.bucket_stride = uint32_t(tiles);
+                cudaFree(c->view.tile_log);
+                c->view.tile_log = nullptr;
+                if (const char* env = std::getenv("ATRAY_TILE_LOG"))
+                    if (std::atoi(env) != 0)
+                    {
+                        CU(cudaMalloc(&c->view.tile_log, tiles * sizeof(uint4)));
+                        CU(cudaMemsetAsync(c->view.tile_log, 0, tiles * sizeof(uint4), c->stream));
+                    }
                 c->view.cost_shift = 0;
                 if (const char* env = std::getenv("ATRAY_COST_SHIFT")) c->view.cost_shift = std::atoi(env);
             }
@@ -1084,6 +1092,19 @@ int atray_debug_film_rects(const atray_model* m, const AtrayCamera* cam, float* 
             }
         }
     }
+    return ATRAY_OK;
+}
+
+// Verification aid (ATRAY_TILE_LOG=1 when the context renders its first culled frame): per local tile of the last culled
+// frame {start ns (low word of the global timer), duration ns, sampled cost, cost class}; zeros for sky tiles.
+int atray_debug_tile_log(atray_ctx* c, uint32_t* out, size_t n_tiles)
+{
+    if (!c || !out) return fail(ATRAY_EINVAL, "null argument");
+    if (!c->view.tile_log) return fail(ATRAY_ESTATE, "tile log not enabled (ATRAY_TILE_LOG=1)");
+    if (n_tiles > c->stamp_cap) return fail(ATRAY_EINVAL, "more tiles than the last frame had");
+    CU(cudaSetDevice(c->device));
+    CU(cudaStreamSynchronize(c->stream));
+    CU(cudaMemcpy(out, c->view.tile_log, n_tiles * sizeof(uint4), cudaMemcpyDeviceToHost));
     return ATRAY_OK;
 }
 

@@ -67,11 +67,12 @@ struct DevView
     float4* pkt_rect;      // n_slots/8 union over the packet's slots
     float4* node_rect;     // n_nodes   leaf: union over its packets; inner node: union over its children
     uint32_t* stamps;      // one per 8x4-pixel tile: == frame_id ⇔ some triangle rectangle may touch the tile
-    uint32_t* tile_cost;   // one per tile: rectangles of every 8th triangle slot that touch it this frame (k_view_finish reads and clears it)
+    uint32_t* tile_cost;   // one per tile: packet rectangles that touch it this frame (k_view_finish reads and clears it)
     uint32_t* all_flag;    // == frame_id ⇔ an unbounded rectangle exists: every tile is busy
     uint32_t* busy_list;   // tiles of this rank's bands that must be traced (local tile numbering of the render kernel):
                            // kCostBuckets regions of bucket_stride entries, see below
     uint32_t bucket_stride; // entries per cost class (>= tiles of the frame)
+    uint4* tile_log;       // verification aid (ATRAY_TILE_LOG=1), else null: per local tile {start ns, duration ns, sampled cost, class}
     int32_t cost_shift;    // class = floor(log2(rectangles)) - cost_shift, clamped to [0, kCostBuckets)
     uint32_t* busy_count;  // control words, see kCtl* below (per-slab list lengths, cursors, finished-tile counters, ticket)
     uint32_t frame_id;

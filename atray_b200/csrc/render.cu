@@ -522,9 +522,6 @@ __global__ void __launch_bounds__(kBlock, 4) k_view_bounds(DevScene sc, ViewPara
     for (uint32_t i = slot; i < sc.n_nodes; i += gridDim.x * kBlock) view.node_rect[i] = make_float4(INFINITY, INFINITY, -INFINITY, -INFINITY);
     if (slot >= slots_up) return;  // whole warps only beyond this point
     const bool in_range = slot < sc.n_slots;
-    // tile cost = rectangles of the first slot of every packet (1 in 8: the lists only need the cost's order of magnitude,
-    // and one atomic per (triangle, tile) pair costs the pre-pass 16 us on the 4K frame)
-    const bool sampled = (slot & 7u) == 0u;
     const int n_tiles = vp.tiles_x * vp.tiles_y;
     float4 r = make_float4(INFINITY, INFINITY, -INFINITY, -INFINITY);
     int tx0 = 0, tx1 = -1, ty0 = 0, ty1 = -1;
@@ -549,7 +546,6 @@ __global__ void __launch_bounds__(kBlock, 4) k_view_bounds(DevScene sc, ViewPara
                         for (int tx = tx0; tx <= tx1; ++tx)
                         {
                             view.stamps[ty * vp.tiles_x + tx] = vp.frame_id;
-                            if (sampled) atomicAdd(&view.tile_cost[ty * vp.tiles_x + tx], 1u);
                         }
                 }
             }
@@ -568,12 +564,23 @@ __global__ void __launch_bounds__(kBlock, 4) k_view_bounds(DevScene sc, ViewPara
         for (int i = lane; i < n; i += 32)
         {
             view.stamps[(ay0 + i / w) * vp.tiles_x + ax0 + i % w] = vp.frame_id;
-            if ((src & 7) == 0) atomicAdd(&view.tile_cost[(ay0 + i / w) * vp.tiles_x + ax0 + i % w], 1u);
         }
     }
     float4 p = r;
     p = rect_union_xor(p, 4); p = rect_union_xor(p, 2); p = rect_union_xor(p, 1);
-    if (in_range && (lane & 7) == 0) view.pkt_rect[slot >> 3] = p;
+    if (in_range && (lane & 7) == 0)
+    {
+        view.pkt_rect[slot >> 3] = p;
+        // tile cost = packet rectangles touching the tile: what the leaf scan of the render kernel tests against the tile's
+        // rectangle, and (tools/tile_log_probe.py) the cheapest of the predictors of a tile's duration that were compared —
+        // one atomic per (triangle, tile) pair instead costs the pre-pass 16 us on the 4K frame
+        int px0, px1, py0, py1;
+        bool all = false;
+        if (film_rect_tiles(vp, FilmRect{p.x, p.y, p.z, p.w}, px0, px1, py0, py1, all) && !all &&
+            (px1 - px0 + 1) * (py1 - py0 + 1) <= 64)
+            for (int ty = py0; ty <= py1; ++ty)
+                for (int tx = px0; tx <= px1; ++tx) atomicAdd(&view.tile_cost[ty * vp.tiles_x + tx], 1u);
+    }
 }
 
 // Second pass, two kinds of blocks running side by side:
@@ -583,8 +590,8 @@ __global__ void __launch_bounds__(kBlock, 4) k_view_bounds(DevScene sc, ViewPara
 //    global atomic per block and slab (the warps reserve their places in shared memory first; per-warp global atomics
 //    would serialise on the handful of slab counters).
 static constexpr int kTilesPerThread = 4;
-// floor(log2(cost)) - shift, clamped to the classes. Measured on the 4K frame (tools/cost_sweep.sh): 8 classes from the sampled
-// count (shift 0: 1, 2-3, 4-7, … ≥ 128) take the render kernel from 275 to 257 us; 16 half-octave classes do no better.
+// floor(log2(cost)) - shift, clamped to the classes. Measured on the 4K frame (tools/cost_sweep.sh): 8 classes
+// (shift 0: 1, 2-3, 4-7, … ≥ 128) take the render kernel from 275 to 257 us; 16 half-octave classes do no better.
 __device__ __forceinline__ int tile_cost_class(uint32_t cost, int shift)
 {
     const int c = 31 - __clz((int)(cost | 1u)) - shift;
@@ -683,8 +690,10 @@ __global__ void __launch_bounds__(kBlock) k_view_finish(DevScene sc, DevView vie
                 busy[k] = y0 < cm.H && (all_busy || view.stamps[gt] == view.frame_id);
                 if (busy[k])
                 {
-                    cls = tile_cost_class(view.tile_cost[gt], view.cost_shift);
+                    const uint32_t cost = view.tile_cost[gt];
+                    cls = tile_cost_class(cost, view.cost_shift);
                     view.tile_cost[gt] = 0u;   // the next frame counts from zero
+                    if (view.tile_log) { view.tile_log[tile].z = cost; view.tile_log[tile].w = (uint32_t)cls; }
                 }
             }
             int sl = 0;
@@ -1229,6 +1238,8 @@ __global__ void __launch_bounds__(kBlock) k_render_culled(DevScene sc, DevCamera
         const int r = __ffs(hit) - 1;
         const unsigned int start = __shfl_sync(FULL_MASK, end - cnt, r);
         const unsigned int tile = __ldg(&vw.busy_list[(unsigned int)(kCostBuckets - 1 - r) * vw.bucket_stride + tile_lo + (bi - start)]);
+        unsigned long long log_t0 = 0;
+        if (vw.tile_log) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(log_t0));
         ++finished;
         const unsigned int lb = tile / tiles_per_band, rem = tile - lb * tiles_per_band;
         const int trow = (int)(rem / (unsigned int)tiles_x), tcol = (int)(rem - (unsigned int)trow * (unsigned int)tiles_x);
@@ -1276,6 +1287,13 @@ __global__ void __launch_bounds__(kBlock) k_render_culled(DevScene sc, DevCamera
             if (out.bgrx) out.bgrx[idx] = pack_bgrx(__fdiv_rn(cr, nspp), __fdiv_rn(cg, nspp), __fdiv_rn(cb, nspp));
             if (out.t) out.t[idx] = t;
             if (out.prim) out.prim[idx] = face;
+        }
+        if (vw.tile_log && lane == 0)
+        {
+            unsigned long long log_t1;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(log_t1));
+            vw.tile_log[tile].x = (uint32_t)log_t0;
+            vw.tile_log[tile].y = (uint32_t)(log_t1 - log_t0);
         }
     }
     // publish this warp's share of the slab: every lane fences its own stores, then one counter update per warp

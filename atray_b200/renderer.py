@@ -124,6 +124,12 @@ class Context:
         _ck(_L.atray_last_render_kernel_ms(self.h, C.byref(ms)))
         return ms.value
 
+    def tile_log(self, n_tiles):
+        """(n_tiles, 4) uint32 {start ns, duration ns, sampled cost, class} of the last culled frame (ATRAY_TILE_LOG=1)."""
+        out = np.zeros((n_tiles, 4), np.uint32)
+        _ck(_L.atray_debug_tile_log(self.h, api._p(out), n_tiles))
+        return out
+
     def counters(self):
         c = api.Counters()
         _ck(_L.atray_get_counters(self.h, C.byref(c)))

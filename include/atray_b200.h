@@ -170,6 +170,10 @@ int atray_scene_set_primitives(atray_ctx* ctx, const AtraySphere* spheres, uint3
                                uint32_t n_planes);
 /* info.total_ray_casts of the last multi-bounce frame: bounce iterations that hit an object (renderer.cpp:260) */
 int atray_last_ray_casts(atray_ctx* ctx, uint64_t* ray_casts);
+/* Verification aid, no reference counterpart: with ATRAY_TILE_LOG=1 in the environment the culled render kernel records, per
+ * local 8x4-pixel tile of the last frame, {start ns, duration ns, sampled cost, cost class} (4 x uint32 per tile; sky tiles
+ * stay zero). tools/tile_log_probe.py reads it to check the heaviest-first schedule. */
+int atray_debug_tile_log(atray_ctx* ctx, uint32_t* out, size_t n_tiles);
 
 /* start_render_from_camera(RenderInfo&, ThreadPool&) — renderer.cpp:403-455: returns immediately; kernels and the
  * device→host copies of the frame planes are queued on the context's stream. */
