@@ -568,18 +568,20 @@ __global__ void __launch_bounds__(kBlock, 4) k_view_bounds(DevScene sc, ViewPara
     }
     float4 p = r;
     p = rect_union_xor(p, 4); p = rect_union_xor(p, 2); p = rect_union_xor(p, 1);
-    if (in_range && (lane & 7) == 0)
+    if (in_range && (lane & 7) == 0) view.pkt_rect[slot >> 3] = p;
+    // tile cost = packet rectangles touching the tile: what the leaf scan of the render kernel tests against the tile's
+    // rectangle, and (tools/tile_log_probe.py) the cheapest of the predictors of a tile's duration that were compared —
+    // one atomic per (triangle, tile) pair instead costs the pre-pass 16 us on the 4K frame. The packet's 8 lanes share
+    // the tiles of its rectangle (every lane holds the same p after the butterfly).
     {
-        view.pkt_rect[slot >> 3] = p;
-        // tile cost = packet rectangles touching the tile: what the leaf scan of the render kernel tests against the tile's
-        // rectangle, and (tools/tile_log_probe.py) the cheapest of the predictors of a tile's duration that were compared —
-        // one atomic per (triangle, tile) pair instead costs the pre-pass 16 us on the 4K frame
-        int px0, px1, py0, py1;
+        int px0 = 0, px1 = -1, py0 = 0, py1 = -1;
         bool all = false;
-        if (film_rect_tiles(vp, FilmRect{p.x, p.y, p.z, p.w}, px0, px1, py0, py1, all) && !all &&
-            (px1 - px0 + 1) * (py1 - py0 + 1) <= 64)
-            for (int ty = py0; ty <= py1; ++ty)
-                for (int tx = px0; tx <= px1; ++tx) atomicAdd(&view.tile_cost[ty * vp.tiles_x + tx], 1u);
+        if (film_rect_tiles(vp, FilmRect{p.x, p.y, p.z, p.w}, px0, px1, py0, py1, all) && !all)
+        {
+            const int w = px1 - px0 + 1, n = w * (py1 - py0 + 1);
+            if (n <= 64)
+                for (int i = lane & 7; i < n; i += 8) atomicAdd(&view.tile_cost[(py0 + i / w) * vp.tiles_x + px0 + i % w], 1u);
+        }
     }
 }
 

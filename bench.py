@@ -170,7 +170,7 @@ def run_reference(args):
                  "e2e": {"value": val, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                  "gpu_launches": 0})
     line["config"]["host_threads"] = threads
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ---- our arm -----------------------------------------------------------------------------------------------------------
@@ -402,12 +402,30 @@ def run_ours(args):
     if dist is not None:
         dist.destroy_process_group()
     if rank == 0:
-        print(json.dumps(line), flush=True)
+        emit(line)
+
+
+_RESULT_FD = None
+
+
+def emit(line):
+    """The result line goes to the process's ORIGINAL stdout (see main)."""
+    data = (json.dumps(line) + "\n").encode()
+    if _RESULT_FD is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_RESULT_FD, data)
 
 
 def main():
-    # NCCL writes its version banner to stdout when NCCL_DEBUG is set by the environment; the contract is ONE JSON line there
-    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+    # The contract is ONE JSON line on stdout, but native libraries write there too (NCCL prints its version banner with
+    # printf when NCCL_DEBUG is set in the environment): keep the original stdout for the result line and point fd 1 at
+    # stderr for everything else.
+    global _RESULT_FD
+    sys.stdout.flush()
+    _RESULT_FD = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=100)
