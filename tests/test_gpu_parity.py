@@ -415,6 +415,46 @@ def test_reference_call_sequence(A, port, meshes):
     o.close()
 
 
+def test_heaviest_first_tile_schedule(A, meshes, monkeypatch):
+    """The busy tiles are listed per cost class and started most expensive class first (ATRAY_TILE_LOG records it); the
+    frame does not depend on the schedule: any class shift, including a single class, gives the same bits."""
+    path, rescale = meshes["knot_mid"]
+    W, H = 1920, 1080
+    cam = A.set_camera(W, H)
+    monkeypatch.setenv("ATRAY_TILE_LOG", "1")
+    frames = []
+    for shift in ("0", "2", "31"):
+        monkeypatch.setenv("ATRAY_COST_SHIFT", shift)
+        sc = gpu_scene(A, path, rescale)
+        ctx = sc.ctx
+        planes = [ctx.dev_alloc(W * H * 4) for _ in range(3)]
+        ctx.render_device(cam, ctx.opts(count_work=True), *planes)   # device frame: one slab, one list per class
+        ctx.sync()
+        out = {}
+        for k, dt, d in zip(("bgrx", "t", "prim"), (np.uint32, np.float32, np.uint32), planes):
+            out[k] = ctx.to_host(d, np.zeros((H, W), dt))
+            ctx.dev_free(d)
+        frames.append(out)
+        ctr = ctx.counters()
+        log = ctx.tile_log(((H + 7) // 8) * 2 * ((W + 7) // 8))
+        busy = log[log[:, 1] > 0]
+        assert len(busy) == ctr["tiles_busy"] > 0
+        if shift == "31":
+            assert (busy[:, 3] == 0).all()
+        else:
+            cls = busy[:, 3].astype(np.int64)
+            assert len(np.unique(cls)) > 1, "scene no longer spreads over several cost classes"
+            expect = np.clip(np.floor(np.log2(np.maximum(busy[:, 2], 1))).astype(np.int64) - int(shift), 0, 7)
+            assert (cls == expect).all()
+            # one cursor walks the classes downwards: a class's first tile starts after the first tile of every heavier
+            # class (2 us of slack: warps that draw neighbouring list positions read the timer in either order)
+            start = (busy[:, 0].astype(np.int64) - int(busy[:, 0].min())) & 0xffffffff
+            first = [start[cls == c].min() for c in sorted(np.unique(cls), reverse=True)]
+            assert all(a <= b + 2000 for a, b in zip(first, first[1:])), first
+    for f in frames[1:]:
+        assert (f["bgrx"] == frames[0]["bgrx"]).all() and (f["prim"] == frames[0]["prim"]).all() and same_bits(f["t"], frames[0]["t"])
+
+
 def test_pipelined_copy_out_equals_whole_frame(A, meshes, monkeypatch):
     """Frames of ≥ 1 Mpx through atray_render_begin are rendered slab by slab and copied out while later slabs are
     still being traced (copy stream waiting on the kernel's per-slab counters). The host frame must equal the
@@ -425,8 +465,17 @@ def test_pipelined_copy_out_equals_whole_frame(A, meshes, monkeypatch):
     cam = A.set_camera(W, H)
     ref_sc = gpu_scene(A, path, rescale)
     whole = ref_sc.ctx.render(cam)   # synchronous convenience call = begin + poll on pageable arrays (staged)
-    for slabs in ("1", "3", "8", "16"):
-        monkeypatch.setenv("ATRAY_SLABS", slabs)
+    for slabs in ("1", "3", "8", "16", "w:2,6,8,16", "w:1,1,1,9", "w:5,1", "w:2,6,8,8,6,2/1"):
+        monkeypatch.delenv("ATRAY_SLABS", raising=False)
+        monkeypatch.delenv("ATRAY_SLAB_WEIGHTS", raising=False)
+        monkeypatch.delenv("ATRAY_COPY_STREAMS", raising=False)
+        if slabs.startswith("w:"):   # graded slab heights; "/1" = one copy stream instead of two
+            plan = slabs[2:].split("/")
+            monkeypatch.setenv("ATRAY_SLAB_WEIGHTS", plan[0])
+            if len(plan) > 1:
+                monkeypatch.setenv("ATRAY_COPY_STREAMS", plan[1])
+        else:
+            monkeypatch.setenv("ATRAY_SLABS", slabs)
         sc = gpu_scene(A, path, rescale)
         tex, tt, tp = A.PinnedArray((H, W), np.uint32), A.PinnedArray((H, W), np.float32), A.PinnedArray((H, W), np.uint32)
         for rep in range(3):
