@@ -44,7 +44,7 @@ if args.host:
         dt = (time.perf_counter() - t0) / args.reps
         best = min(best, dt)
     print("host frame (slabs %s weights %s): %.1f us per frame (best of 3 x %d)" % (
-        os.environ.get("ATRAY_SLABS", "default"), os.environ.get("ATRAY_SLAB_WEIGHTS", "uniform"), 1e6 * best, args.reps), flush=True)
+        os.environ.get("ATRAY_SLABS", "default"), os.environ.get("ATRAY_SLAB_WEIGHTS", "default plan" if "ATRAY_SLABS" not in os.environ else "uniform"), 1e6 * best, args.reps), flush=True)
     sys.exit(0)
 planes = [ctx.dev_alloc(W * H * 4) for _ in range(3)]
 flush = ctx.dev_alloc(256 << 20)
