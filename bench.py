@@ -193,14 +193,32 @@ def load_traffic():
     return None
 
 
+def pick_device(local_rank, world, visible):
+    """GPU of a local rank. When the node shows at least twice as many GPUs as there are ranks, the ranks are spread evenly
+    over them (cuda:LOCAL_RANK * (visible // world)): on the 8-GPU B200 boxes GPUs 0-3 and 4-7 reach host memory through
+    two different paths (NVML reports one level for every pair, the copy rates do not: profiles/r01d_summary.md), and the
+    end-to-end frame is bound by exactly that path. ATRAY_BENCH_DEVICES="0,1" (one entry per local rank) overrides."""
+    env = os.environ.get("ATRAY_BENCH_DEVICES")
+    if env:
+        devs = [int(x) for x in env.split(",")]
+        if len(devs) >= world and all(0 <= d < visible for d in devs):
+            return devs[local_rank]
+    if world > 1 and visible >= 2 * world:
+        return local_rank * (visible // world)
+    return local_rank
+
+
 def run_ours(args):
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     dist = None
+    visible_gpus = 1
     if world > 1:
         import torch
         import torch.distributed as dist_mod
+        visible_gpus = torch.cuda.device_count()
+        local_rank = pick_device(local_rank, world, visible_gpus)
         torch.cuda.set_device(local_rank)
         dist_mod.init_process_group(backend="nccl", device_id=torch.device("cuda", local_rank))
         dist = dist_mod
@@ -393,6 +411,7 @@ def run_ours(args):
         line["config"].update({"fp_mode": args.fp, "band_rows": BAND_ROWS, "parallelism": "bands%d" % world,
                                "l2": "flushed between timed steps (256 MiB device memset outside the per-step event pair)",
                                "timing": "CUDA events on the library's stream around each frame's launch, summed over K steps, max over ranks",
+                               "devices": [pick_device(r, world, visible_gpus) for r in range(world)] if world > 1 else [local_rank],
                                "gather": "BGRX bitmap: direct peer stores into GPU 0's frame through CUDA IPC; t/prim planes stay on the tracing rank" if world > 1 else "none (1 GPU)"})
     barrier()
     if tex is not None:
