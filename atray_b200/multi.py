@@ -127,3 +127,15 @@ class ShmBarrier:
         self.slots = None
         if self.owner and os.path.exists(self.path):
             os.remove(self.path)
+
+
+def spread_devices(world, visible=None):
+    """GPUs for the `world` local ranks of one node: evenly spread over the `visible` devices when there are at least twice
+    as many (rank r → r * (visible // world)), else rank r → r. On the 8-GPU B200 boxes GPUs 0-3 and 4-7 reach host memory
+    through two different paths, which is what bounds the multi-GPU host frame (profiles/r01d_summary.md, r01e)."""
+    if visible is None:
+        from . import api
+        visible = api.device_count()
+    if world > 1 and visible >= 2 * world:
+        return [r * (visible // world) for r in range(world)]
+    return list(range(world))

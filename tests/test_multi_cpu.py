@@ -154,3 +154,15 @@ def test_shared_host_bitmap_gloo_world2(built):
         p.join(timeout=60)
         assert p.exitcode == 0
     assert all(ok for _, ok, _ in res) and not any(left for _, _, left in res)
+
+
+def test_rank_placement_spreads_over_the_node():
+    from atray_b200 import multi
+    assert multi.spread_devices(1, 8) == [0]
+    assert multi.spread_devices(2, 8) == [0, 4]
+    assert multi.spread_devices(4, 8) == [0, 2, 4, 6]
+    assert multi.spread_devices(8, 8) == list(range(8))
+    assert multi.spread_devices(2, 2) == [0, 1] and multi.spread_devices(3, 4) == [0, 1, 2]
+    import bench
+    for w, v in ((2, 8), (4, 8), (8, 8), (2, 2), (2, 3)):
+        assert [bench.pick_device(r, w, v) for r in range(w)] == multi.spread_devices(w, v)
