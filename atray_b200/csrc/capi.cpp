@@ -711,6 +711,9 @@ static int enqueue_render(atray_ctx* c, const AtrayCamera* cam, const AtrayRende
                     }
                 c->view.cost_shift = 0;
                 if (const char* env = std::getenv("ATRAY_COST_SHIFT")) c->view.cost_shift = std::atoi(env);
+                c->view.split_ratio16 = 16;   // <= 1 busy tile per warp; measured on C4: world 8 render kernel 86.5 -> 77.2 us,
+                                              // a loss from 1.9 tiles per warp (world 4: 98 -> 127 us), tools/split_sweep.sh
+                if (const char* env = std::getenv("ATRAY_SPLIT_RATIO16")) c->view.split_ratio16 = std::atoi(env);
             }
             if (!c->view.all_flag) CU(cudaMalloc(&c->view.all_flag, sizeof(uint32_t)));
             if (!c->view.busy_count)

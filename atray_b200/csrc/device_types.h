@@ -74,6 +74,9 @@ struct DevView
     uint32_t bucket_stride; // entries per cost class (>= tiles of the frame)
     uint4* tile_log;       // verification aid (ATRAY_TILE_LOG=1), else null: per local tile {start ns, duration ns, sampled cost, class}
     int32_t cost_shift;    // class = floor(log2(rectangles)) - cost_shift, clamped to [0, kCostBuckets)
+    int32_t split_ratio16; // a slab's busy tiles are traced as half-tiles (rows 0-1 / rows 2-3, 16 rays per warp, two list
+                           // positions per tile) when 16 x (busy tiles of this and the later slabs) <= split_ratio16 x warps of
+                           // the render grid: a rank with about one busy tile per warp (N = 8) ends sooner on halves
     uint32_t* busy_count;  // control words, see kCtl* below (per-slab list lengths, cursors, finished-tile counters, ticket)
     uint32_t frame_id;
     int32_t tiles_x;
@@ -109,14 +112,14 @@ static constexpr int kMaxSlabs = 16;
 static constexpr int kCostBuckets = 8;
 static constexpr int kCtlCount = 0;                              // [s * kCostBuckets + b] entries of slab s in class b
 static constexpr int kCtlCursor = kMaxSlabs * kCostBuckets;      // [s] consumer cursor of slab s
-static constexpr int kCtlDone = kCtlCursor + kMaxSlabs;          // [s] tiles of slab s whose stores are complete (sky + traced)
+static constexpr int kCtlDone = kCtlCursor + kMaxSlabs;          // [s] half-tiles of slab s whose stores are complete (sky + traced; a whole tile counts 2)
 static constexpr int kCtlTicket = kCtlDone + kMaxSlabs;          // end of the words k_view_bounds clears every frame
 static constexpr int kCtlWords = kCtlTicket + 4;
 struct DevSlabs
 {
     int32_t n;                              // 1 … kMaxSlabs
     uint32_t tile_begin[kMaxSlabs + 1];     // local tile index range of slab s = [tile_begin[s], tile_begin[s+1])
-    uint32_t live_tiles[kMaxSlabs];         // tiles of slab s that lie inside the image = final value of ctl[kCtlDone + s]
+    uint32_t live_tiles[kMaxSlabs];         // 2 x tiles of slab s that lie inside the image = final value of ctl[kCtlDone + s] (half-tile units)
 };
 
 // Per-warp spill area for rays whose leaf list / inner-node stack outgrow the per-lane arrays.

@@ -1119,7 +1119,7 @@ __device__ __forceinline__ void trace_tile_culled(const DevScene& sc, const DevS
 // those no triangle rectangle can touch (≈90 % of a typical frame: a pure store stream). Phase B: the slab's busy tiles
 // listed by k_view_finish are pulled one at a time from an atomic cursor (dynamic balance where the work is). A warp
 // that runs out of work in a slab publishes the number of tiles it completed there (stores fenced first) and moves on:
-// ctl[kCtlDone + s] == tiles of slab s ⇔ every scanline of the slab is final — the host side's copy stream waits for
+// ctl[kCtlDone + s] == 2 x tiles of slab s (half-tile units) ⇔ every scanline of the slab is final — the host side's copy stream waits for
 // exactly that value (stream memory operation) and copies the slab out while later slabs are still being traced.
 template <bool STRICT, bool COUNT>
 __global__ void __launch_bounds__(kBlock) k_render_culled(DevScene sc, DevCamera cm, DevPartition part, DevOut out, DevScratch scratch,
@@ -1151,10 +1151,28 @@ __global__ void __launch_bounds__(kBlock) k_render_culled(DevScene sc, DevCamera
     const bool vec_ok = (cm.W & 3) == 0 &&
                         (((size_t)out.bgrx | (size_t)out.t | (size_t)out.prim) & 15) == 0;
 
+    // Half-tile mode per slab (DevView::split_ratio16): bit s set ⇔ the busy tiles of slab s and of the later slabs together
+    // are so few per warp of the grid that single-tile latency sets the end of the kernel. The list lengths are final
+    // (k_view_finish has completed), so every warp takes the same decision.
+    unsigned int split_mask = 0u;
+    if (vw.split_ratio16 > 0)
+    {
+        unsigned long long later = 0ull;
+        for (int s = slabs.n - 1; s >= 0; --s)
+        {
+            unsigned int c = lane < kCostBuckets ? __ldg(&vw.busy_count[kCtlCount + s * kCostBuckets + lane]) : 0u;
+#pragma unroll
+            for (int off = 16; off > 0; off >>= 1) c += __shfl_xor_sync(FULL_MASK, c, off);
+            later += c;
+            if (16ull * later <= (unsigned long long)vw.split_ratio16 * n_warps) split_mask |= 1u << s;
+        }
+    }
+
   for (int slab = 0; slab < slabs.n; ++slab)
   {
     const unsigned int tile_lo = slabs.tile_begin[slab], tile_hi = min(slabs.tile_begin[slab + 1], n_tiles);
-    unsigned int finished = 0;  // tiles of this slab completed by this warp
+    const bool split = (split_mask >> slab) & 1u;
+    unsigned int finished = 0;  // half-tiles of this slab completed by this warp (a whole tile counts 2)
     // ---- phase A: sky tiles ------------------------------------------------------------------------------------------
     // One strip of 32 consecutive tiles (256×4 pixels) per step: one coalesced stamp load, then 512-byte row segments.
     if (!all_busy && vec_ok)
@@ -1176,7 +1194,7 @@ __global__ void __launch_bounds__(kBlock) k_render_culled(DevScene sc, DevCamera
             const bool sky = tcol < tiles_x && __ldg(&vw.stamps[(y0 >> 2) * vw.tiles_x + tcol]) != vw.frame_id;
             const unsigned skym = __ballot_sync(FULL_MASK, sky);
             if (!skym) continue;
-            finished += (unsigned int)__popc(skym);
+            finished += 2u * (unsigned int)__popc(skym);
             if (COUNT && lane == 0) wc.tsky += (unsigned int)__popc(skym);
 #pragma unroll
             for (int h = 0; h < 2; ++h)
@@ -1215,7 +1233,7 @@ __global__ void __launch_bounds__(kBlock) k_render_culled(DevScene sc, DevCamera
                 if (out.prim) out.prim[idx] = 0xffffffffu;
                 rays_done += cm.spp;
             }
-            ++finished;
+            finished += 2u;
             if (COUNT && lane == 0) wc.tsky++;
         }
     }
@@ -1227,6 +1245,9 @@ __global__ void __launch_bounds__(kBlock) k_render_culled(DevScene sc, DevCamera
         unsigned int bi = 0;
         if (lane == 0) bi = atomicAdd(&vw.busy_count[kCtlCursor + slab], 1u);
         bi = __shfl_sync(FULL_MASK, bi, 0);
+        // half-tile mode: two consecutive cursor values per listed tile; half 1 = tile rows 0-1 (lanes 0-15), half 2 = rows 2-3
+        const unsigned int half = split ? (bi & 1u) + 1u : 0u;
+        if (split) bi >>= 1;
         const unsigned int cnt = lane < kCostBuckets ? __ldg(&vw.busy_count[kCtlCount + slab * kCostBuckets + (kCostBuckets - 1 - lane)]) : 0u;
         unsigned int end = cnt;   // inclusive prefix sum over the lanes
 #pragma unroll
@@ -1242,14 +1263,14 @@ __global__ void __launch_bounds__(kBlock) k_render_culled(DevScene sc, DevCamera
         const unsigned int tile = __ldg(&vw.busy_list[(unsigned int)(kCostBuckets - 1 - r) * vw.bucket_stride + tile_lo + (bi - start)]);
         unsigned long long log_t0 = 0;
         if (vw.tile_log) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(log_t0));
-        ++finished;
+        finished += half ? 1u : 2u;
         const unsigned int lb = tile / tiles_per_band, rem = tile - lb * tiles_per_band;
         const int trow = (int)(rem / (unsigned int)tiles_x), tcol = (int)(rem - (unsigned int)trow * (unsigned int)tiles_x);
         const int x = tcol * 8 + (lane & 7);
         const int y = ((int)lb * part.world + part.rank) * part.band_rows + trow * 4 + (lane >> 3);
-        const bool active = x < cm.W && y < cm.H;
+        const bool active = x < cm.W && y < cm.H && (half == 0u || (half == 1u) == (lane < 16));
         const size_t idx = (size_t)y * (size_t)cm.W + (size_t)x;
-        if (COUNT && lane == 0) wc.tbusy++;
+        if (COUNT && lane == 0 && half != 2u) wc.tbusy++;
         const float film_y = film_coord(y, cm.H);
         const float film_x = mulr(mulr(film_coord(x, cm.W), cm.h_fov), cm.aspect);
         float t = kMaxFloat;
@@ -1656,7 +1677,7 @@ DevSlabs make_slabs(const DevCamera& cam, const DevPartition& part, int n_slabs,
             if (rows > part.band_rows) rows = part.band_rows;
             if (rows > 0) live += (uint32_t)(((rows + 3) >> 2) * tiles_x);
         }
-        s.live_tiles[k] = live;
+        s.live_tiles[k] = 2u * live;   // half-tile units, see kCtlDone
     }
     return s;
 }

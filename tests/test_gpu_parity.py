@@ -455,6 +455,48 @@ def test_heaviest_first_tile_schedule(A, meshes, monkeypatch):
         assert (f["bgrx"] == frames[0]["bgrx"]).all() and (f["prim"] == frames[0]["prim"]).all() and same_bits(f["t"], frames[0]["t"])
 
 
+def test_half_tile_mode_gives_the_same_frame(A, meshes, monkeypatch):
+    """A rank with at most one busy tile per warp of the render grid traces its busy tiles as half-tiles (two list positions
+    per tile, 16 rays per warp; ATRAY_SPLIT_RATIO16, default 16). Never / default / always must give the same bits: device
+    frame with counters, a partitioned rank (the case the mode is for), the jittered path and the slab-pipelined host frame
+    (per-slab counters in half-tile units, last band partial)."""
+    path, rescale = meshes["knot_mid"]
+    W, H = 1920, 1084
+    results = []
+    for ratio in ("0", None, "100000000"):
+        if ratio is None:
+            monkeypatch.delenv("ATRAY_SPLIT_RATIO16", raising=False)
+        else:
+            monkeypatch.setenv("ATRAY_SPLIT_RATIO16", ratio)
+        sc = gpu_scene(A, path, rescale)
+        ctx = sc.ctx
+        out = {}
+        for tag, cam, opts in (("whole", A.set_camera(W, H), ctx.opts(count_work=True)),
+                               ("rank5of8", A.set_camera(W, H), ctx.opts(rank=5, world=8, band_rows=8, count_work=True)),
+                               ("aa", A.set_camera(640, 362, anti_aliasing=True, samples_per_pixel=4), ctx.opts(count_work=True))):
+            h, w = cam.height, cam.width
+            planes = [ctx.dev_alloc(w * h * 4) for _ in range(3)]
+            for d in planes:
+                ctx.dev_memset(d, 0, w * h * 4)
+            ctx.render_device(cam, opts, *planes)
+            ctx.sync()
+            for k, dt, d in zip(("bgrx", "t", "prim"), (np.uint32, np.float32, np.uint32), planes):
+                out[tag + "." + k] = ctx.to_host(d, np.zeros((h, w), dt)).view(np.uint32)
+                ctx.dev_free(d)
+            ctr = ctx.counters()
+            out[tag + ".ctr"] = np.array([ctr["tiles_busy"], ctr["tiles_sky"], ctr["rays"]], np.uint64)
+            assert ctr["tiles_busy"] > 0
+        host = ctx.render(A.set_camera(W, H))
+        for k in ("bgrx", "t", "prim"):
+            out["host." + k] = np.ascontiguousarray(host[k]).view(np.uint32)
+        results.append(out)
+    for other in results[1:]:
+        assert other.keys() == results[0].keys()
+        for k in results[0]:
+            assert (other[k] == results[0][k]).all(), k
+    assert (results[0]["host.bgrx"] == results[0]["whole.bgrx"]).all()
+
+
 def test_pipelined_copy_out_equals_whole_frame(A, meshes, monkeypatch):
     """Frames of ≥ 1 Mpx through atray_render_begin are rendered slab by slab and copied out while later slabs are
     still being traced (copy stream waiting on the kernel's per-slab counters). The host frame must equal the
