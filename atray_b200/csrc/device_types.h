@@ -77,6 +77,7 @@ struct DevView
     int32_t split_ratio16; // a slab's busy tiles are traced as half-tiles (rows 0-1 / rows 2-3, 16 rays per warp, two list
                            // positions per tile) when 16 x (busy tiles of this and the later slabs) <= split_ratio16 x warps of
                            // the render grid: a rank with about one busy tile per warp (N = 8) ends sooner on halves
+    int32_t split_min_class; // in half-tile mode only the tiles of this cost class and above are halved (0 = all)
     uint32_t* busy_count;  // control words, see kCtl* below (per-slab list lengths, cursors, finished-tile counters, ticket)
     uint32_t frame_id;
     int32_t tiles_x;

@@ -1245,10 +1245,9 @@ __global__ void __launch_bounds__(kBlock) k_render_culled(DevScene sc, DevCamera
         unsigned int bi = 0;
         if (lane == 0) bi = atomicAdd(&vw.busy_count[kCtlCursor + slab], 1u);
         bi = __shfl_sync(FULL_MASK, bi, 0);
-        // half-tile mode: two consecutive cursor values per listed tile; half 1 = tile rows 0-1 (lanes 0-15), half 2 = rows 2-3
-        const unsigned int half = split ? (bi & 1u) + 1u : 0u;
-        if (split) bi >>= 1;
-        const unsigned int cnt = lane < kCostBuckets ? __ldg(&vw.busy_count[kCtlCount + slab * kCostBuckets + (kCostBuckets - 1 - lane)]) : 0u;
+        // half-tile mode: a tile of class >= split_min_class takes two consecutive cursor values
+        const unsigned int per = (split && lane < kCostBuckets && kCostBuckets - 1 - lane >= vw.split_min_class) ? 2u : 1u;
+        const unsigned int cnt = lane < kCostBuckets ? per * __ldg(&vw.busy_count[kCtlCount + slab * kCostBuckets + (kCostBuckets - 1 - lane)]) : 0u;
         unsigned int end = cnt;   // inclusive prefix sum over the lanes
 #pragma unroll
         for (int off = 1; off < kCostBuckets; off <<= 1)
@@ -1260,7 +1259,10 @@ __global__ void __launch_bounds__(kBlock) k_render_culled(DevScene sc, DevCamera
         if (!hit) break;   // past the slab's last busy tile
         const int r = __ffs(hit) - 1;
         const unsigned int start = __shfl_sync(FULL_MASK, end - cnt, r);
-        const unsigned int tile = __ldg(&vw.busy_list[(unsigned int)(kCostBuckets - 1 - r) * vw.bucket_stride + tile_lo + (bi - start)]);
+        const bool halves = __shfl_sync(FULL_MASK, per, r) == 2u;
+        const unsigned int pos = bi - start;
+        const unsigned int half = halves ? (pos & 1u) + 1u : 0u;   // half 1 = tile rows 0-1 (lanes 0-15), half 2 = rows 2-3
+        const unsigned int tile = __ldg(&vw.busy_list[(unsigned int)(kCostBuckets - 1 - r) * vw.bucket_stride + tile_lo + (halves ? pos >> 1 : pos)]);
         unsigned long long log_t0 = 0;
         if (vw.tile_log) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(log_t0));
         finished += half ? 1u : 2u;

@@ -457,17 +457,19 @@ def test_heaviest_first_tile_schedule(A, meshes, monkeypatch):
 
 def test_half_tile_mode_gives_the_same_frame(A, meshes, monkeypatch):
     """A rank with at most one busy tile per warp of the render grid traces its busy tiles as half-tiles (two list positions
-    per tile, 16 rays per warp; ATRAY_SPLIT_RATIO16, default 16). Never / default / always must give the same bits: device
+    per tile, 16 rays per warp; ATRAY_SPLIT_RATIO16, default 16; only cost classes >= ATRAY_SPLIT_MIN_CLASS, default 5).
+    Never / default / every tile / classes >= 3 must give the same bits: device
     frame with counters, a partitioned rank (the case the mode is for), the jittered path and the slab-pipelined host frame
     (per-slab counters in half-tile units, last band partial)."""
     path, rescale = meshes["knot_mid"]
     W, H = 1920, 1084
     results = []
-    for ratio in ("0", None, "100000000"):
-        if ratio is None:
-            monkeypatch.delenv("ATRAY_SPLIT_RATIO16", raising=False)
-        else:
-            monkeypatch.setenv("ATRAY_SPLIT_RATIO16", ratio)
+    for ratio, min_class in (("0", None), (None, None), ("100000000", "0"), ("100000000", "3")):
+        for name, val in (("ATRAY_SPLIT_RATIO16", ratio), ("ATRAY_SPLIT_MIN_CLASS", min_class)):
+            if val is None:
+                monkeypatch.delenv(name, raising=False)
+            else:
+                monkeypatch.setenv(name, val)
         sc = gpu_scene(A, path, rescale)
         ctx = sc.ctx
         out = {}

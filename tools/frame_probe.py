@@ -17,6 +17,7 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--reps", type=int, default=10)
 ap.add_argument("--raster", action="store_true")
 ap.add_argument("--world", type=int, default=1)
+ap.add_argument("--rank", type=int, default=0)
 ap.add_argument("--count", action="store_true")
 ap.add_argument("--host", action="store_true")
 args = ap.parse_args()
@@ -48,7 +49,7 @@ if args.host:
     sys.exit(0)
 planes = [ctx.dev_alloc(W * H * 4) for _ in range(3)]
 flush = ctx.dev_alloc(256 << 20)
-opts = ctx.opts(rank=0, world=args.world, band_rows=8, raster=args.raster, count_work=args.count)
+opts = ctx.opts(rank=args.rank, world=args.world, band_rows=8, raster=args.raster, count_work=args.count)
 ms, rms = [], []
 for i in range(args.reps + 2):
     ctx.dev_memset(flush, 0, 256 << 20)
@@ -58,7 +59,7 @@ for i in range(args.reps + 2):
         ms.append(ctx.last_kernel_ms())
         if not args.raster:
             rms.append(ctx.last_render_kernel_ms())
-print("world %d rank 0 raster=%s: %.1f us per frame (min %.1f)" % (args.world, args.raster, 1e3 * sum(ms) / len(ms), 1e3 * min(ms)), flush=True)
+print("world %d rank %d raster=%s: %.1f us per frame (min %.1f)" % (args.world, args.rank, args.raster, 1e3 * sum(ms) / len(ms), 1e3 * min(ms)), flush=True)
 if rms:
     print("  render kernel alone %.1f us, view pass %.1f us" % (1e3 * sum(rms) / len(rms), 1e3 * (sum(ms) - sum(rms)) / len(ms)), flush=True)
 if args.count:

@@ -14,6 +14,8 @@ from tools import gen_standin_obj  # noqa: E402
 
 ap = argparse.ArgumentParser()
 ap.add_argument("--world", type=int, default=1)
+ap.add_argument("--rank", type=int, default=0)
+ap.add_argument("--brief", action="store_true")
 args = ap.parse_args()
 W, H = 3840, 2160
 path = gen_standin_obj.ensure(os.path.join(os.environ.get("ATRAY_MESH_CACHE", "/tmp/atray_meshes"), "standin_272x256.obj"))
@@ -25,13 +27,13 @@ ctx = sc.ctx
 cam = A.set_camera(W, H)
 planes = [ctx.dev_alloc(W * H * 4) for _ in range(3)]
 flush = ctx.dev_alloc(256 << 20)
-opts = ctx.opts(rank=0, world=args.world, band_rows=8)
+opts = ctx.opts(rank=args.rank, world=args.world, band_rows=8)
 for i in range(4):
     ctx.dev_memset(flush, 0, 256 << 20)
     ctx.render_device(cam, opts, *planes)
     ctx.sync()
 n_bands = (H + 7) // 8
-my_bands = (n_bands - 0 + args.world - 1) // args.world
+my_bands = (n_bands - args.rank + args.world - 1) // args.world
 n_tiles = my_bands * 2 * ((W + 7) // 8)
 log = ctx.tile_log(n_tiles)
 busy = log[log[:, 1] > 0]
@@ -51,6 +53,10 @@ for c in range(15, -1, -1):
     print("%5d %6d %8d..%-7d %8.1f %6.1f %6.1f %6.1f %12.1f %11.1f %9.1f" % (
         c, k.sum(), busy[k, 2].min(), busy[k, 2].max(), d.mean(), np.percentile(d, 50), np.percentile(d, 90), d.max(),
         start[k].min() / 1e3, start[k].max() / 1e3, end[k].max() / 1e3))
+if args.brief:
+    print("world %d rank %d: busy %d, per class (7..0) %s, longest tile %.1f us" % (
+        args.world, args.rank, len(busy), [int((busy[:, 3] == c).sum()) for c in range(7, -1, -1)], dur.max() / 1e3))
+    sys.exit(0)
 last_start = start.max()
 print("list exhausted at %.1f us; tiles still running then: %d; of those, per class:" % (last_start / 1e3, int((end > last_start).sum())),
       {int(c): int(((end > last_start) & (busy[:, 3] == c)).sum()) for c in np.unique(busy[:, 3])})
