@@ -390,8 +390,10 @@ def run_ours(args):
                     "north_star_roofline_mrays_per_gpu": {"fp32_issue_bound": bound_fp32, "hbm_bytes_bound": bound_hbm,
                                                           "slower": min(bound_fp32, bound_hbm),
                                                           "achieved_frac_of_slower": per_gpu / min(bound_fp32, bound_hbm)},
-                    "note": "frac > 1 against HBM because the 10 MB scene is L2/L1-resident by design: the HBM figure is the "
-                            "north_star's bytes-per-ray bound, not the kernel's limiter (see fp32.frac and profiles/)"}
+                    "note": "achieved = algorithmic bytes per ray (32 B per box test + 48 B per triangle test actually made, "
+                            "+ 12 B output; counters of a separate counted frame) x rays / render-kernel time. The 10 MB scene is "
+                            "L2/L1-resident, so DRAM traffic is the output planes; the kernel is bound by dependent-load "
+                            "latency per warp, not by HBM (see fp32.frac, l2_read_gbs_measured and profiles/)"}
         cpu_baseline = None
         if world == 1 and not args.no_cpu_baseline:
             _, cscene, kind = cpu_scene()
