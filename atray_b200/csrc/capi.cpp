@@ -711,11 +711,12 @@ static int enqueue_render(atray_ctx* c, const AtrayCamera* cam, const AtrayRende
                     }
                 c->view.cost_shift = 0;
                 if (const char* env = std::getenv("ATRAY_COST_SHIFT")) c->view.cost_shift = std::atoi(env);
-                // <= 1 busy tile per warp, classes >= 5 (>= 32 packet rectangles). Measured on C4 (profiles/r01f_summary.md): the
+                // <= 22/16 busy tiles per warp, classes >= 5 (>= 32 packet rectangles). Measured on C4 (profiles/r01f_summary.md):
+                // rank 0 of world 7 / 6 (1.09 / 1.27 tiles per warp) 82.1 -> 76.4 / 90.1 -> 83.9 us, world 5 (1.52) 87.0 -> 98.1; the
                 // render kernel of the slowest of the 8 ranks of world 8 goes 86.7 -> 81.8 us (all classes halved: 88.7, the
                 // added work outweighs the shorter critical path on most ranks); from 1.9 tiles per warp (world 4) any
                 // halving loses (98 -> 103..127 us)
-                c->view.split_ratio16 = 16;
+                c->view.split_ratio16 = 22;
                 if (const char* env = std::getenv("ATRAY_SPLIT_RATIO16")) c->view.split_ratio16 = std::atoi(env);
                 c->view.split_min_class = 5;
                 if (const char* env = std::getenv("ATRAY_SPLIT_MIN_CLASS")) c->view.split_min_class = std::atoi(env);

@@ -457,7 +457,7 @@ def test_heaviest_first_tile_schedule(A, meshes, monkeypatch):
 
 def test_half_tile_mode_gives_the_same_frame(A, meshes, monkeypatch):
     """A rank with at most one busy tile per warp of the render grid traces its busy tiles as half-tiles (two list positions
-    per tile, 16 rays per warp; ATRAY_SPLIT_RATIO16, default 16; only cost classes >= ATRAY_SPLIT_MIN_CLASS, default 5).
+    per tile, 16 rays per warp; ATRAY_SPLIT_RATIO16, default 22; only cost classes >= ATRAY_SPLIT_MIN_CLASS, default 5).
     Never / default / every tile / classes >= 3 must give the same bits: device
     frame with counters, a partitioned rank (the case the mode is for), the jittered path and the slab-pipelined host frame
     (per-slab counters in half-tile units, last band partial)."""
