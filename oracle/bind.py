@@ -186,9 +186,13 @@ class Scene:
     def accepted_hits(self, W, H, threads=1, eye=DEFAULT_EYE, facing=DEFAULT_FACING, hfov=DEFAULT_HFOV, cap=None):
         """port() only: every (pixel, leaf node, position in leaf) the triangle test accepts in any listed leaf."""
         cap = cap or 8 * W * H
-        px, node, pos = np.zeros(cap, np.uint32), np.zeros(cap, np.uint32), np.zeros(cap, np.uint32)
         e, f = _f3(eye), _f3(facing)
-        n = self.b.accepted_hits(self.h, W, H, _p(e), _p(f), hfov, threads, cap, _p(px), _p(node), _p(pos))
+        for _ in range(2):   # the call returns the number of hits even when they did not fit: second pass with that size
+            px, node, pos = np.zeros(cap, np.uint32), np.zeros(cap, np.uint32), np.zeros(cap, np.uint32)
+            n = self.b.accepted_hits(self.h, W, H, _p(e), _p(f), hfov, threads, cap, _p(px), _p(node), _p(pos))
+            if n <= cap:
+                break
+            cap = int(n)
         assert n <= cap, "accepted_hits: capacity too small (%d > %d)" % (n, cap)
         return px[:n], node[:n], pos[:n]
 

@@ -119,3 +119,38 @@ def test_degenerate_camera_disables_culling(built, meshes):
     cam = A.set_camera(64, 36, facing=(0.0, 1.0, 0.0))     # facing ∥ up: camera_x = normalize(0) is not finite
     with pytest.raises(A.AtrayError):
         m.film_rects(cam)
+
+
+@pytest.mark.parametrize("name", ["knot_sah300", "knot_center32", "monkey", "slivers"])
+def test_random_cameras_keep_every_accepted_hit(name, built, port, meshes, tmp_path):
+    """The fuzz cameras of tests/test_gpu_fuzz.py (a prefix of the same seeded sequence) on the CPU: every hit the oracle
+    accepts lies in the triangle's film rectangle and in a tile stamped busy."""
+    import atray_b200 as A
+    from oracle import bind as B
+    from fuzz_cams import fuzz_cameras, sliver_mesh
+    from helpers import write_obj
+    if name == "slivers":
+        v, f = sliver_mesh()
+        path, rescale, method, cap = write_obj(str(tmp_path / "slivers.obj"), v, f), 40.0, 1, 64
+    else:
+        mesh, method, cap = {"knot_sah300": ("knot_mid", 1, 300), "knot_center32": ("knot_mid", 0, 32),
+                             "monkey": ("Monkey", 1, 300)}[name]
+        if mesh not in meshes:
+            pytest.skip("mesh not staged")
+        path, rescale = meshes[mesh]
+    m = A.load_model_data(path, 2)
+    A.place_default(m, rescale)
+    A.build_KD_tree(m, method, cap)
+    tree = m.tree()
+    cams = fuzz_cameras(120, 1000 + len(name), m.dump()["aabb"], tree["boxes"][tree["children_start"] == 0])
+    checked = hits = 0
+    for kw in cams:
+        kw = dict(kw)
+        W, H = kw.pop("width"), kw.pop("height")
+        kw.pop("anti_aliasing"), kw.pop("samples_per_pixel")
+        try:
+            hits += check(A, B, port, path, rescale, method, cap, W, H, kw)[0]
+        except A.AtrayError:
+            continue        # camera the culling refuses (degenerate basis): the product renders it unculled
+        checked += 1
+    assert checked > 100 and hits > 1000
