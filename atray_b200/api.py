@@ -95,7 +95,7 @@ _SIGS = {
     "atray_model_tree_dump": [_vp] * 7,
     "atray_model_flatten": [_vp, _vp, _vp, _vp, _vp],
     "atray_write_bmp": [_vp, C.c_uint32, C.c_uint32, C.c_char_p, C.c_char_p, C.c_size_t],
-    "atray_debug_film_rects": [_vp, C.POINTER(CameraStruct), _vp, _vp, _vp, _vp, _vp],
+    "atray_debug_film_rects": [_vp, C.POINTER(CameraStruct), _vp, _vp, _vp, _vp, _vp, _vp],
     "atray_camera_set": [C.POINTER(CameraStruct), _i, _i, _i, _u, _i, _vp, _vp, _f],
     "atray_device_count": [C.POINTER(_i)],
     "atray_ctx_create": [_i, C.POINTER(_vp)],
@@ -208,9 +208,10 @@ class Model:
         _ck(_L.atray_model_flatten(self.h, None, None, _p(nodes), _p(tris)))
         return nodes, tris
 
-    def film_rects(self, cam, hulls=False):
+    def film_rects(self, cam, hulls=False, px=False):
         """Host evaluation of the per-frame film rectangles (view_bounds.h): rects n_slots×4, owning leaf, position in
-        the reference's leaf order, busy flag per 8x4 tile; hulls=True adds the n_slots×3×3 half-planes {a, b, c}."""
+        the reference's leaf order, busy flag per 8x4 tile; hulls=True adds the n_slots×3×3 half-planes {a, b, c}, px=True the
+        n_slots×4 inclusive pixel ranges {x0, x1, y0, y1} the kernels use."""
         nn, ns = C.c_uint32(0), C.c_uint32(0)
         _ck(_L.atray_model_flatten(self.h, C.byref(nn), C.byref(ns), None, None))
         rects = np.zeros((ns.value, 4), np.float32)
@@ -218,10 +219,15 @@ class Model:
         pos = np.zeros(ns.value, np.uint32)
         busy = np.zeros(((cam.height + 3) // 4, (cam.width + 7) // 8), np.uint8)
         hl = np.zeros((ns.value, 3, 3), np.float32) if hulls else None
-        _ck(_L.atray_debug_film_rects(self.h, C.byref(cam), _p(rects), _p(leaf), _p(pos), _p(busy), _p(hl) if hulls else None))
+        pr = np.zeros((ns.value, 4), np.int32) if px else None
+        _ck(_L.atray_debug_film_rects(self.h, C.byref(cam), _p(rects), _p(leaf), _p(pos), _p(busy), _p(hl) if hulls else None,
+                                      _p(pr) if px else None))
+        out = [rects, leaf, pos, busy]
         if hulls:
-            return rects, leaf, pos, busy, hl
-        return rects, leaf, pos, busy
+            out.append(hl)
+        if px:
+            out.append(pr)
+        return tuple(out)
 
 
 # ---- reference-named host functions (app.cpp:62-156 call order) ----------------------------------------------------

@@ -33,6 +33,8 @@ struct atray_ctx
     DevScratch scratch{};
     DevView view{};              // per-frame film rectangles + tile stamps (k_view_bounds)
     size_t stamp_cap = 0;        // tiles the stamp buffer holds
+    size_t bin_cap = 0;          // bins the bin lists hold
+    uint2* d_node_pk = nullptr;  // FlatScene::node_pk
     uint32_t frame_seq = 0;      // stamp value of the last frame (0 = buffer freshly cleared)
     // film-space rasteriser (raster.cuh): scene tables, per-frame tables / keys / lists
     uint32_t* d_packet_leaf = nullptr; uint32_t* d_leaf_seq = nullptr; uint32_t* d_seq_leaf = nullptr;
@@ -319,9 +321,12 @@ int atray_ctx_create(int device, atray_ctx** out)
 static void free_scene(atray_ctx* c)
 {
     cudaFree(c->d_nodes); cudaFree(c->d_tris); cudaFree(c->scratch.leaves); cudaFree(c->scratch.stack);
-    cudaFree(c->view.tri_rect); cudaFree(c->view.pkt_rect); cudaFree(c->view.node_rect);
+    cudaFree(c->view.tri_px); cudaFree(c->view.pkt_px); cudaFree(c->view.chunk_px); cudaFree(c->view.node_px);
+    cudaFree(c->view.tri_rect); cudaFree(c->d_node_pk);
     cudaFree(c->d_inner_order); cudaFree(c->d_level_start);
-    c->view.tri_rect = c->view.pkt_rect = c->view.node_rect = nullptr;
+    c->view.tri_px = c->view.pkt_px = c->view.chunk_px = c->view.node_px = nullptr;
+    c->view.tri_rect = nullptr;
+    c->d_node_pk = nullptr;
     c->d_inner_order = c->d_level_start = nullptr;
     c->d_nodes = c->d_tris = nullptr;
     cudaFree(c->d_fnorm); cudaFree(c->d_spheres); cudaFree(c->d_planes);
@@ -346,6 +351,7 @@ void atray_ctx_destroy(atray_ctx* c)
     cudaFree(c->d_tile_counter); cudaFree(c->d_counters); cudaFree(c->d_casts);
     cudaFree(c->view.stamps); cudaFree(c->view.all_flag); cudaFree(c->view.busy_list); cudaFree(c->view.busy_count);
     cudaFree(c->view.tile_cost); cudaFree(c->view.tile_log);
+    cudaFree(c->view.bin_cnt); cudaFree(c->view.bin_leaf); cudaFree(c->view.bin_inner);
     cudaFree(c->rs.tabx); cudaFree(c->rs.taby); cudaFree(c->rs.key1); cudaFree(c->rs.key2); cudaFree(c->rs.hit_a);
     cudaFree(c->rs.hit_pos); cudaFree(c->rs.ctl);
     cudaFree(c->d_bgrx); cudaFree(c->d_t); cudaFree(c->d_prim);
@@ -383,9 +389,13 @@ int atray_scene_upload(atray_ctx* c, const atray_model* m, const AtrayMaterial* 
     c->scratch.stack_cap = f.n_nodes + 8;
     CU(cudaMalloc(&c->scratch.leaves, size_t(warps) * c->scratch.leaf_cap * sizeof(uint2)));
     CU(cudaMalloc(&c->scratch.stack, size_t(warps) * c->scratch.stack_cap * sizeof(uint32_t)));
-    CU(cudaMalloc(&c->view.tri_rect, size_t(f.n_slots ? f.n_slots : 1) * sizeof(float4)));
-    CU(cudaMalloc(&c->view.pkt_rect, size_t(f.n_slots / 8 + 1) * sizeof(float4)));
-    CU(cudaMalloc(&c->view.node_rect, size_t(f.n_nodes) * sizeof(float4)));
+    CU(cudaMalloc(&c->view.tri_px, size_t(f.n_slots ? f.n_slots : 1) * sizeof(uint2)));
+    CU(cudaMalloc(&c->view.pkt_px, size_t(f.n_slots / 8 + 1) * sizeof(uint2)));
+    CU(cudaMalloc(&c->view.chunk_px, size_t(f.n_slots / 256 + 1) * sizeof(uint2)));
+    CU(cudaMalloc(&c->view.node_px, size_t(f.n_nodes) * sizeof(uint2)));
+    CU(cudaMalloc(&c->d_node_pk, size_t(f.n_nodes) * sizeof(uint2)));
+    CU(cudaMemcpy(c->d_node_pk, f.node_pk.data(), size_t(f.n_nodes) * sizeof(uint2), cudaMemcpyHostToDevice));
+    c->scene.node_pk = c->d_node_pk;
     CU(cudaMalloc(&c->d_inner_order, (f.inner_order.size() + 1) * sizeof(uint32_t)));
     CU(cudaMalloc(&c->d_level_start, f.level_start.size() * sizeof(uint32_t)));
     if (!f.inner_order.empty())
@@ -612,11 +622,15 @@ static ViewParams make_view_params(const AtrayCamera* cam)
     }
     const double dmin = 1.0 / std::sqrt(fro);
     vp.ang = 2.0 * (std::sqrt(e2) / dmin + 4.0 * U);
-    // film→pixel inversion slack: 6 roundings in film_x (rel. u each) ≈ 3u·W pixels; one full pixel is added on top,
-    // and half a pixel more when the samples are jittered (renderer.cpp:340-341: |rand_bi| <= 1)
-    vp.px_slack_x = 1.0 + 1e-6 * vp.W + (cam->anti_aliasing ? 0.51 : 0.0);
-    vp.px_slack_y = 1.0 + 1e-6 * vp.H + (cam->anti_aliasing ? 0.51 : 0.0);
-    bool fin = std::isfinite(vp.ang) && std::isfinite(eye_inf) && eye_inf < 1073741824.0;
+    // film→pixel inversion slack (view_bounds.h: film_rect_px): the float film coordinate of a pixel is within 2.6u*W pixels
+    // of the real one; a jittered sample (renderer.cpp:340-341, |rand_bi| <= 1) moves the film point by at most
+    // |half_pixel_width| = that many film units = |hpw|*W/(2|kx|) pixels, |half_pixel_height|*H/2 pixels in y — taken from
+    // the camera the kernel uses, whatever the caller put there
+    vp.inv_kx = 1.0 / vp.kx;
+    vp.px_slack_x = 2e-6 * vp.W + 1e-9 + (cam->anti_aliasing ? aa_x * vp.W * 0.5 * std::fabs(vp.inv_kx) * (1.0 + 1e-6) : 0.0);
+    vp.px_slack_y = 2e-6 * vp.H + 1e-9 + (cam->anti_aliasing ? aa_y * vp.H * 0.5 * (1.0 + 1e-6) : 0.0);
+    bool fin = std::isfinite(vp.ang) && std::isfinite(eye_inf) && eye_inf < 1073741824.0 && std::isfinite(vp.px_slack_x) &&
+               std::isfinite(vp.px_slack_y) && cam->width < 65535 && cam->height < 65535;   // pixel ranges are packed in 16 bits
     for (int r = 0; r < 3; ++r)
         for (int k = 0; k < 3; ++k) fin = fin && std::isfinite(vp.minv[r][k]);
     vp.valid = fin ? 1 : 0;
@@ -711,15 +725,6 @@ static int enqueue_render(atray_ctx* c, const AtrayCamera* cam, const AtrayRende
                     }
                 c->view.cost_shift = 0;
                 if (const char* env = std::getenv("ATRAY_COST_SHIFT")) c->view.cost_shift = std::atoi(env);
-                // <= 22/16 busy tiles per warp, classes >= 5 (>= 32 packet rectangles). Measured on C4 (profiles/r01f_summary.md):
-                // rank 0 of world 7 / 6 (1.09 / 1.27 tiles per warp) 82.1 -> 76.4 / 90.1 -> 83.9 us, world 5 (1.52) 87.0 -> 98.1; the
-                // render kernel of the slowest of the 8 ranks of world 8 goes 86.7 -> 81.8 us (all classes halved: 88.7, the
-                // added work outweighs the shorter critical path on most ranks); from 1.9 tiles per warp (world 4) any
-                // halving loses (98 -> 103..127 us)
-                c->view.split_ratio16 = 22;
-                if (const char* env = std::getenv("ATRAY_SPLIT_RATIO16")) c->view.split_ratio16 = std::atoi(env);
-                c->view.split_min_class = 5;
-                if (const char* env = std::getenv("ATRAY_SPLIT_MIN_CLASS")) c->view.split_min_class = std::atoi(env);
             }
             if (!c->view.all_flag) CU(cudaMalloc(&c->view.all_flag, sizeof(uint32_t)));
             if (!c->view.busy_count)
@@ -734,6 +739,23 @@ static int enqueue_render(atray_ctx* c, const AtrayCamera* cam, const AtrayRende
         vp.frame_id = ++c->frame_seq;
         c->view.frame_id = vp.frame_id;
         c->view.tiles_x = vp.tiles_x;
+        // bins of 64 x 32 pixels with flat node lists (k_view_nodes); a bin whose list outgrows its capacity sends its tiles
+        // through the unculled core, so the capacities only bound memory: 192 leaves + 64 inner nodes = 11 KB per bin
+        c->view.bins_x = (cam->width + (1 << kBinShiftX) - 1) >> kBinShiftX;
+        c->view.bins_y = (cam->height + (1 << kBinShiftY) - 1) >> kBinShiftY;
+        const size_t bins = size_t(c->view.bins_x) * size_t(c->view.bins_y);
+        if (bins > c->bin_cap)
+        {
+            cudaFree(c->view.bin_cnt); cudaFree(c->view.bin_leaf); cudaFree(c->view.bin_inner);
+            c->view.bin_cnt = nullptr; c->view.bin_leaf = nullptr; c->view.bin_inner = nullptr; c->bin_cap = 0;
+            c->view.bin_leaf_cap = 192; c->view.bin_inner_cap = 64;
+            if (const char* env = std::getenv("ATRAY_BIN_LEAF_CAP")) c->view.bin_leaf_cap = uint32_t(std::atoi(env) > 0 ? std::atoi(env) : 1);
+            if (const char* env = std::getenv("ATRAY_BIN_INNER_CAP")) c->view.bin_inner_cap = uint32_t(std::atoi(env) > 0 ? std::atoi(env) : 1);
+            CU(cudaMalloc(&c->view.bin_cnt, bins * 2 * sizeof(uint32_t)));
+            CU(cudaMalloc(&c->view.bin_leaf, bins * c->view.bin_leaf_cap * 3 * sizeof(uint4)));
+            CU(cudaMalloc(&c->view.bin_inner, bins * c->view.bin_inner_cap * 2 * sizeof(uint4)));
+            c->bin_cap = bins;
+        }
     }
     // opt-in, AA off and a real tree: the frame is rasterised triangle by triangle (raster.cuh) — same bits, no per-tile traversal
     const bool raster = cull && (c->use_raster || (o->flags & ATRAY_RENDER_RASTER)) && !cam->anti_aliasing && !c->scene.root_is_leaf;
@@ -741,6 +763,7 @@ static int enqueue_render(atray_ctx* c, const AtrayCamera* cam, const AtrayRende
     {
         int rc = ensure_raster_buffers(c, cam);
         if (rc) return rc;
+        if (!c->view.tri_rect) CU(cudaMalloc(&c->view.tri_rect, size_t(c->scene.n_slots ? c->scene.n_slots : 1) * sizeof(float4)));
     }
     CU(cudaEventRecord(c->ev_k0, c->stream));
     if (raster)
@@ -1061,7 +1084,7 @@ int atray_get_counters(atray_ctx* c, AtrayCounters* out)
 
 // ---- verification aid: the film rectangles of view_bounds.h evaluated on the host ------------------------------------
 int atray_debug_film_rects(const atray_model* m, const AtrayCamera* cam, float* rects, uint32_t* slot_leaf, uint32_t* slot_pos,
-                           uint8_t* tile_busy, float* hulls)
+                           uint8_t* tile_busy, float* hulls, int32_t* px_ranges)
 {
     if (!m || !cam) return fail(ATRAY_EINVAL, "null argument");
     if (m->m.tree.empty()) return fail(ATRAY_ESTATE, "film_rects before build_tree");
@@ -1088,17 +1111,16 @@ int atray_debug_film_rects(const atray_model* m, const AtrayCamera* cam, float* 
         if (rects) { rects[4 * size_t(s)] = r.xlo; rects[4 * size_t(s) + 1] = r.ylo; rects[4 * size_t(s) + 2] = r.xhi; rects[4 * size_t(s) + 3] = r.yhi; }
         if (slot_leaf) slot_leaf[s] = f.packet_leaf[s / 8];
         if (slot_pos) slot_pos[s] = face != 0xffffffffu ? pos : 0xffffffffu;
-        if (tile_busy)
+        PxRect pr;
+        const bool any = film_rect_px(vp, r, pr);   // pr is {0, -1, 0, -1} when no pixel can hold such a ray
+        if (px_ranges) { px_ranges[4 * size_t(s)] = pr.x0; px_ranges[4 * size_t(s) + 1] = pr.x1; px_ranges[4 * size_t(s) + 2] = pr.y0; px_ranges[4 * size_t(s) + 3] = pr.y1; }
+        if (tile_busy && any)
         {
-            int tx0, tx1, ty0, ty1;
-            bool all = false;
-            if (film_rect_tiles(vp, r, tx0, tx1, ty0, ty1, all))
-            {
-                if (all) std::memset(tile_busy, 1, tiles);
-                else
-                    for (int ty = ty0; ty <= ty1; ++ty)
-                        for (int tx = tx0; tx <= tx1; ++tx) tile_busy[size_t(ty) * vp.tiles_x + tx] = 1;
-            }
+            const int tx0 = pr.x0 >> 3, tx1 = pr.x1 >> 3, ty0 = pr.y0 >> 2, ty1 = pr.y1 >> 2;
+            if (2 * (tx1 - tx0 + 1) * (ty1 - ty0 + 1) >= int(tiles)) std::memset(tile_busy, 1, tiles);
+            else
+                for (int ty = ty0; ty <= ty1; ++ty)
+                    for (int tx = tx0; tx <= tx1; ++tx) tile_busy[size_t(ty) * vp.tiles_x + tx] = 1;
         }
     }
     return ATRAY_OK;

@@ -33,6 +33,8 @@ struct DevScene
     const uint32_t* seq_leaf;      // n_leaves : inverse of leaf_seq
     const uint32_t* parent;        // n_nodes  : parent node, 0xffffffff for the root
     const uint32_t* pos_face;      // n_slots  : [first_slot + position in the reference's leaf order] → face index
+    const uint2* node_pk;          // n_nodes  : packets [x, y) of the node's subtree (leaf slots are laid out in depth-first order,
+                                   //            so every subtree owns one contiguous packet range; FlatScene::node_pk)
     // ---- no-tree path (renderer.cpp:58-82, the #ifndef USE_KD_TREE branch): model box, then every face in file order ----
     const float4* faces;           // 3 float4 per face: {a, 0} {b - a, 0} {c - a, 0} from the vertex arrays
     uint32_t n_faces;
@@ -60,28 +62,38 @@ struct DevCounters  // mirrors AtrayCounters
     unsigned long long rect_tests, tiles_sky, tiles_busy;
 };
 
-// Per-frame film-space bounds written by k_view_bounds and read by the culled render kernel (view_bounds.h).
+// Per-frame film-space bounds written by k_view_bounds / k_view_nodes and read by the culled render kernel (view_bounds.h).
+// Every bound is an inclusive pixel range packed as uint2 {x0 | y0 << 16, x1 | y1 << 16} (film_rect_px: the pixels that
+// can hold a ray whose film point lies in the float rectangle); empty = {0xffffffff, 0}.
 struct DevView
 {
-    float4* tri_rect;      // n_slots   {xlo, ylo, xhi, yhi}
-    float4* pkt_rect;      // n_slots/8 union over the packet's slots
-    float4* node_rect;     // n_nodes   leaf: union over its packets; inner node: union over its children
-    uint32_t* stamps;      // one per 8x4-pixel tile: == frame_id ⇔ some triangle rectangle may touch the tile
-    uint32_t* tile_cost;   // one per tile: packet rectangles that touch it this frame (k_view_finish reads and clears it)
-    uint32_t* all_flag;    // == frame_id ⇔ an unbounded rectangle exists: every tile is busy
+    uint2* tri_px;         // n_slots
+    uint2* pkt_px;         // n_slots/8  union over the packet's slots
+    uint2* chunk_px;       // n_slots/256 union over 32 consecutive packets (one k_view_bounds block)
+    uint2* node_px;        // n_nodes    union over the packets of the node's subtree
+    float4* tri_rect;      // n_slots {xlo, ylo, xhi, yhi} float rectangles; only the rasteriser reads them (null otherwise)
+    uint32_t* stamps;      // one per 8x4-pixel tile: == frame_id ⇔ some triangle's pixel range touches the tile
+    uint32_t* tile_cost;   // one per tile: packet ranges that touch it this frame (k_view_nodes reads and clears it)
+    uint32_t* all_flag;    // == frame_id ⇔ a triangle covers half the frame or more: every tile is busy
     uint32_t* busy_list;   // tiles of this rank's bands that must be traced (local tile numbering of the render kernel):
                            // kCostBuckets regions of bucket_stride entries, see below
     uint32_t bucket_stride; // entries per cost class (>= tiles of the frame)
     uint4* tile_log;       // verification aid (ATRAY_TILE_LOG=1), else null: per local tile {start ns, duration ns, sampled cost, class}
-    int32_t cost_shift;    // class = floor(log2(rectangles)) - cost_shift, clamped to [0, kCostBuckets)
-    int32_t split_ratio16; // a slab's busy tiles are traced as half-tiles (rows 0-1 / rows 2-3, 16 rays per warp, two list
-                           // positions per tile) when 16 x (busy tiles of this and the later slabs) <= split_ratio16 x warps of
-                           // the render grid: a rank with about one busy tile per warp (N = 8) ends sooner on halves
-    int32_t split_min_class; // in half-tile mode only the tiles of this cost class and above are halved (0 = all)
+    int32_t cost_shift;    // class = floor(log2(ranges)) - cost_shift, clamped to [0, kCostBuckets)
+    // Bins of kBinW x kBinH pixels: the tree nodes whose pixel range touches the bin, as flat lists (k_view_nodes). A tile
+    // (8x4 pixels, inside exactly one bin) filters its bin's lists instead of walking the tree.
+    //   leaf entry  = 3 uint4: {px.lo, px.hi, leaf_seq, first_slot} {box lo.xyz, count} {box hi.xyz, node}
+    //   inner entry = 2 uint4: {px.lo, px.hi, node, 0} {split point xyz (= hi corner of child 0, kd_tree.cpp:120-148), 0}
+    uint32_t* bin_cnt;     // 2 per bin: leaf entries, inner entries (may exceed the capacities: the bin is then unusable)
+    uint4* bin_leaf;       // bins x bin_leaf_cap x 3
+    uint4* bin_inner;      // bins x bin_inner_cap x 2
+    int32_t bins_x, bins_y;
+    uint32_t bin_leaf_cap, bin_inner_cap;
     uint32_t* busy_count;  // control words, see kCtl* below (per-slab list lengths, cursors, finished-tile counters, ticket)
     uint32_t frame_id;
     int32_t tiles_x;
 };
+static constexpr int kBinShiftX = 6, kBinShiftY = 5;   // 64 x 32 pixels = 8 x 8 tiles
 
 // Per-frame state of the film-space rasteriser (render.cu: k_film_tables, k_raster, k_raster_big, k_hit_filter, k_resolve).
 // key1/key2 hold one 64-bit word per pixel each and are all-ones between frames (k_resolve restores what it consumes):
@@ -113,14 +125,14 @@ static constexpr int kMaxSlabs = 16;
 static constexpr int kCostBuckets = 8;
 static constexpr int kCtlCount = 0;                              // [s * kCostBuckets + b] entries of slab s in class b
 static constexpr int kCtlCursor = kMaxSlabs * kCostBuckets;      // [s] consumer cursor of slab s
-static constexpr int kCtlDone = kCtlCursor + kMaxSlabs;          // [s] half-tiles of slab s whose stores are complete (sky + traced; a whole tile counts 2)
+static constexpr int kCtlDone = kCtlCursor + kMaxSlabs;          // [s] tiles of slab s whose stores are complete (sky + traced)
 static constexpr int kCtlTicket = kCtlDone + kMaxSlabs;          // end of the words k_view_bounds clears every frame
 static constexpr int kCtlWords = kCtlTicket + 4;
 struct DevSlabs
 {
     int32_t n;                              // 1 … kMaxSlabs
     uint32_t tile_begin[kMaxSlabs + 1];     // local tile index range of slab s = [tile_begin[s], tile_begin[s+1])
-    uint32_t live_tiles[kMaxSlabs];         // 2 x tiles of slab s that lie inside the image = final value of ctl[kCtlDone + s] (half-tile units)
+    uint32_t live_tiles[kMaxSlabs];         // tiles of slab s that lie inside the image = final value of ctl[kCtlDone + s]
 };
 
 // Per-warp spill area for rays whose leaf list / inner-node stack outgrow the per-lane arrays.
@@ -138,8 +150,8 @@ cudaError_t launch_render(const DevScene& sc, const DevCamera& cam, const DevPar
                           const DevScratch& scratch, unsigned int* tile_counter, DevCounters* counters, int fp_fast,
                           unsigned long long jitter_seed, LaunchCfg cfg, cudaStream_t stream);
 // culled frame = k_view_bounds (per-frame film rectangles + tile stamps) followed by k_render_culled
-// k_view_bounds (per-slot rectangles, packet unions, tile stamps) + k_view_finish (leaf and inner-node unions,
-// compact list of this rank's busy tiles)
+// k_view_bounds (per-slot pixel ranges, packet / chunk unions, tile stamps) + k_view_nodes (node unions, bins, compact list
+// of this rank's busy tiles)
 cudaError_t launch_view_bounds(const DevScene& sc, const ViewParams& vp, const DevView& view, const DevCamera& cam,
                                const DevPartition& part, const DevSlabs& slabs, cudaStream_t stream, cudaEvent_t after_reset,
                                bool finish = true);

@@ -413,11 +413,50 @@ void flatten(const HostModel& m, FlatScene& out)
     out.tris.assign(size_t(slots / 8) * 24 * 4, 0.f);
     out.packet_leaf.assign(slots / 8, 0u);
     out.pos_face.assign(slots, 0xffffffffu);
-    uint32_t cursor = 0;
+    // Leaf slots are laid out in depth-first order of the tree (children in index order), not in node order: the packets
+    // of every subtree are then one contiguous range node_pk[node] = [begin, end), and the per-frame pixel range of an
+    // inner node is a union over that range (render.cu: k_view_nodes) instead of a bottom-up pass over the levels.
+    std::vector<uint32_t> first_slot(out.n_nodes, 0u);
+    out.node_pk.assign(size_t(out.n_nodes) * 2, 0u);
+    {
+        uint32_t at = 0;
+        std::vector<std::pair<uint32_t, int>> st;   // (node, next child to descend into; -1 = entering)
+        if (out.n_nodes) st.push_back({0u, -1});
+        while (!st.empty())
+        {
+            auto& top = st.back();
+            const uint32_t nd = top.first;
+            const TreeNode& n = m.tree[nd];
+            if (top.second < 0)
+            {
+                out.node_pk[2 * size_t(nd)] = at / 8;
+                if (n.children_start == 0)
+                {
+                    first_slot[nd] = at;
+                    at += (uint32_t(n.prims.size()) + 7u) & ~7u;
+                    out.node_pk[2 * size_t(nd) + 1] = at / 8;
+                    st.pop_back();
+                    continue;
+                }
+                top.second = 0;
+            }
+            if (top.second < 8)
+            {
+                const uint32_t ch = uint32_t(n.children_start) + uint32_t(top.second++);
+                st.push_back({ch, -1});
+            }
+            else
+            {
+                out.node_pk[2 * size_t(nd) + 1] = at / 8;
+                st.pop_back();
+            }
+        }
+    }
     std::vector<uint32_t> order;
     for (uint32_t i = 0; i < out.n_nodes; ++i)
     {
         const TreeNode& n = m.tree[i];
+        const uint32_t cursor = first_slot[i];
         float* q = &out.nodes[size_t(i) * 8];
         q[0] = n.box.lo.x; q[1] = n.box.lo.y; q[2] = n.box.lo.z;
         q[4] = n.box.hi.x; q[5] = n.box.hi.y; q[6] = n.box.hi.z;
@@ -456,7 +495,6 @@ void flatten(const HostModel& m, FlatScene& out)
                 AB[3] = bits_to_float(0xffffffffu);
             }
         }
-        cursor += padded;
     }
     // depth of every node (children always follow their parent in the array), inner nodes bucketed deepest first
     std::vector<uint32_t> depth(out.n_nodes, 0u);

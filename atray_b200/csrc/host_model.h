@@ -50,6 +50,8 @@ struct FlatScene
     // seq_leaf        = inverse of leaf_seq over the leaves; parent[node] = parent node (root: 0xffffffff);
     // pos_face[first_slot + pos] = face index of the leaf's primitive at position `pos` of the reference's leaf order.
     std::vector<uint32_t> leaf_seq, seq_leaf, parent, pos_face;
+    // node_pk[2*node], node_pk[2*node+1] = packets [begin, end) of the node's subtree (slots are laid out depth-first)
+    std::vector<uint32_t> node_pk;
     uint32_t n_nodes = 0, n_slots = 0, n_leaves = 0, max_leaf_prims = 0;
 };
 

@@ -150,10 +150,9 @@ __device__ __forceinline__ SlotSpan slot_span(const ViewParams& vp, const RankRo
     s.x0 = 0; s.w = 0; s.m0 = 0; s.cnt = 0;
     FilmRect fr;
     fr.xlo = R.x; fr.ylo = R.y; fr.xhi = R.z; fr.yhi = R.w;
-    int x0 = 0, x1 = -1, y0 = 0, y1 = -1;
-    bool all = false;
-    if (!film_rect_pixels(vp, fr, x0, x1, y0, y1, all)) return s;
-    if (all) { x0 = 0; x1 = vp.W - 1; y0 = 0; y1 = vp.H - 1; }
+    PxRect pr;
+    if (!film_rect_px(vp, fr, pr)) return s;
+    const int x0 = pr.x0, x1 = pr.x1, y0 = pr.y0, y1 = pr.y1;
     s.x0 = x0;
     s.w = x1 - x0 + 1;
     s.m0 = rr.before(y0);

@@ -488,71 +488,87 @@ __global__ void __launch_bounds__(kBlock) k_render(DevScene sc, DevCamera cm, De
     if (COUNT) flush_counters(counters, wc, rays_done);
 }
 
-// ---- per-frame film-space bounds (view_bounds.h) ----------------------------------------------------------------------
-__device__ __forceinline__ float4 rect_union_xor(float4 r, int off)
+// ---- per-frame film-space bounds (view_bounds.h) as packed pixel ranges ---------------------------------------------------
+// uint2 {x0 | y0 << 16, x1 | y1 << 16}, inclusive; coordinates < 65535 (checked on the host), empty = {0xffffffff, 0}.
+__device__ __forceinline__ uint2 px_empty() { return make_uint2(0xffffffffu, 0u); }
+__device__ __forceinline__ uint2 px_pack(const PxRect& p)
 {
-    r.x = fminf(r.x, __shfl_xor_sync(FULL_MASK, r.x, off)); r.y = fminf(r.y, __shfl_xor_sync(FULL_MASK, r.y, off));
-    r.z = fmaxf(r.z, __shfl_xor_sync(FULL_MASK, r.z, off)); r.w = fmaxf(r.w, __shfl_xor_sync(FULL_MASK, r.w, off));
-    return r;
+    return make_uint2((uint32_t)p.x0 | ((uint32_t)p.y0 << 16), (uint32_t)p.x1 | ((uint32_t)p.y1 << 16));
+}
+__device__ __forceinline__ uint2 px_union(uint2 a, uint2 b) { return make_uint2(__vminu2(a.x, b.x), __vmaxu2(a.y, b.y)); }
+// both halfwords of a.lo <= b.hi and of a.hi >= b.lo (an empty range overlaps nothing: its lo halves are 0xffff)
+__device__ __forceinline__ bool px_overlap(uint2 a, uint2 b)
+{
+    return (__vcmpleu2(a.x, b.y) & __vcmpgeu2(a.y, b.x)) == 0xffffffffu;
+}
+__device__ __forceinline__ bool px_contains(uint2 a, uint32_t p) { return (__vcmpleu2(a.x, p) & __vcmpgeu2(a.y, p)) == 0xffffffffu; }
+__device__ __forceinline__ bool px_is_empty(uint2 a) { return (a.x & 0xffffu) > (a.y & 0xffffu) || (a.x >> 16) > (a.y >> 16); }
+__device__ __forceinline__ uint2 px_union_xor(uint2 r, int off)
+{
+    return px_union(r, make_uint2(__shfl_xor_sync(FULL_MASK, r.x, off), __shfl_xor_sync(FULL_MASK, r.y, off)));
+}
+// tile row ty (4 scanlines) belongs to this rank: band_rows is a multiple of 4, band b -> rank b % world
+__device__ __forceinline__ bool owns_tile_row(const DevPartition& part, int ty)
+{
+    return part.world <= 1 || ((ty * 4) / part.band_rows) % part.world == part.rank;
+}
+// some scanline of bin row `by` (kBinH scanlines) belongs to this rank
+__device__ __forceinline__ bool owns_bin_row(const DevPartition& part, int by, int H)
+{
+    if (part.world <= 1) return true;
+    const int y0 = by << kBinShiftY;
+    int y1 = y0 + (1 << kBinShiftY) - 1;
+    if (y1 > H - 1) y1 = H - 1;
+    const int b0 = y0 / part.band_rows, b1 = y1 / part.band_rows;
+    if (b1 - b0 + 1 >= part.world) return true;
+    const int d = ((part.rank - b0) % part.world + part.world) % part.world;   // bands from b0 to the next band of this rank
+    return d <= b1 - b0;
 }
 
-// Order-independent float min/max on global memory (the sign decides which integer order matches the float order;
-// -0 is folded into +0 first, NaN never wins as with fminf/fmaxf).
-__device__ __forceinline__ void atomic_min_float(float* p, float v)
-{
-    v += 0.0f;
-    if (v >= 0.0f) atomicMin(reinterpret_cast<int*>(p), __float_as_int(v));
-    else if (v < 0.0f) atomicMax(reinterpret_cast<unsigned int*>(p), __float_as_uint(v));
-}
-__device__ __forceinline__ void atomic_max_float(float* p, float v)
-{
-    v += 0.0f;
-    if (v >= 0.0f) atomicMax(reinterpret_cast<int*>(p), __float_as_int(v));
-    else if (v < 0.0f) atomicMin(reinterpret_cast<unsigned int*>(p), __float_as_uint(v));
-}
-
-// One thread per triangle slot: film rectangle, union per packet (8 lanes), tile stamps.
-__global__ void __launch_bounds__(kBlock, 4) k_view_bounds(DevScene sc, ViewParams vp, DevView view)
+// One thread per triangle slot: film rectangle (FP64, view_bounds.h) -> pixel range, unions per packet (8 lanes) and per
+// chunk of 32 packets (the block), tile stamps and tile costs for the tiles of this rank's bands.
+__global__ void __launch_bounds__(kBlock, 4) k_view_bounds(DevScene sc, ViewParams vp, DevView view, DevPartition part)
 {
     const int lane = threadIdx.x & 31;
     const uint32_t slot = blockIdx.x * kBlock + threadIdx.x;
-    const uint32_t slots_up = (sc.n_slots + 31u) & ~31u;
     for (uint32_t i = slot; i < (uint32_t)kCtlTicket; i += gridDim.x * kBlock) view.busy_count[i] = 0u;  // list lengths, cursors, finished-tile counters
-    // node rectangles start empty: k_view_finish accumulates every leaf's rectangle into its ancestors with atomics
-    for (uint32_t i = slot; i < sc.n_nodes; i += gridDim.x * kBlock) view.node_rect[i] = make_float4(INFINITY, INFINITY, -INFINITY, -INFINITY);
-    if (slot >= slots_up) return;  // whole warps only beyond this point
+    for (uint32_t i = slot; i < 2u * (uint32_t)(view.bins_x * view.bins_y); i += gridDim.x * kBlock) view.bin_cnt[i] = 0u;
     const bool in_range = slot < sc.n_slots;
     const int n_tiles = vp.tiles_x * vp.tiles_y;
-    float4 r = make_float4(INFINITY, INFINITY, -INFINITY, -INFINITY);
+    uint2 px = px_empty();
     int tx0 = 0, tx1 = -1, ty0 = 0, ty1 = -1;
     bool big = false;
     if (in_range)
     {
         const float4* rec = sc.tris + (size_t)(slot >> 3) * 24 + (slot & 7);
         const float4 A = __ldg(rec), AB = __ldg(rec + 8), AC = __ldg(rec + 16);
+        float4 r = make_float4(INFINITY, INFINITY, -INFINITY, -INFINITY);
         if (__float_as_uint(A.w) != 0xffffffffu)
         {
             const FilmRect fr = tri_film_rect(vp, &A.x, &AB.x, &AC.x);
             r = make_float4(fr.xlo, fr.ylo, fr.xhi, fr.yhi);
-            bool all = false;
-            if (film_rect_tiles(vp, fr, tx0, tx1, ty0, ty1, all))
+            PxRect p;
+            if (film_rect_px(vp, fr, p))
             {
+                px = px_pack(p);
+                tx0 = p.x0 >> 3; tx1 = p.x1 >> 3; ty0 = p.y0 >> 2; ty1 = p.y1 >> 2;
                 const int nt = (tx1 - tx0 + 1) * (ty1 - ty0 + 1);
-                if (all || 2 * nt >= n_tiles) { *view.all_flag = vp.frame_id; tx1 = tx0 - 1; }
+                if (2 * nt >= n_tiles) { *view.all_flag = vp.frame_id; tx1 = tx0 - 1; }
                 else if (nt > 48) big = true;
                 else
                 {
                     for (int ty = ty0; ty <= ty1; ++ty)
-                        for (int tx = tx0; tx <= tx1; ++tx)
-                        {
-                            view.stamps[ty * vp.tiles_x + tx] = vp.frame_id;
-                        }
+                    {
+                        if (!owns_tile_row(part, ty)) continue;
+                        for (int tx = tx0; tx <= tx1; ++tx) view.stamps[ty * vp.tiles_x + tx] = vp.frame_id;
+                    }
                 }
             }
         }
-        view.tri_rect[slot] = r;
+        view.tri_px[slot] = px;
+        if (view.tri_rect) view.tri_rect[slot] = r;
     }
-    // large rectangles: the whole warp stamps the tiles of one triangle at a time
+    // large ranges: the whole warp stamps the tiles of one triangle at a time
     unsigned bm = __ballot_sync(FULL_MASK, big);
     while (bm)
     {
@@ -563,31 +579,44 @@ __global__ void __launch_bounds__(kBlock, 4) k_view_bounds(DevScene sc, ViewPara
         const int w = ax1 - ax0 + 1, n = w * (ay1 - ay0 + 1);
         for (int i = lane; i < n; i += 32)
         {
-            view.stamps[(ay0 + i / w) * vp.tiles_x + ax0 + i % w] = vp.frame_id;
+            const int ty = ay0 + i / w;
+            if (owns_tile_row(part, ty)) view.stamps[ty * vp.tiles_x + ax0 + i % w] = vp.frame_id;
         }
     }
-    float4 p = r;
-    p = rect_union_xor(p, 4); p = rect_union_xor(p, 2); p = rect_union_xor(p, 1);
-    if (in_range && (lane & 7) == 0) view.pkt_rect[slot >> 3] = p;
-    // tile cost = packet rectangles touching the tile: what the leaf scan of the render kernel tests against the tile's
-    // rectangle, and (tools/tile_log_probe.py) the cheapest of the predictors of a tile's duration that were compared —
-    // one atomic per (triangle, tile) pair instead costs the pre-pass 16 us on the 4K frame. The packet's 8 lanes share
-    // the tiles of its rectangle (every lane holds the same p after the butterfly).
+    uint2 p = px;
+    p = px_union_xor(p, 4); p = px_union_xor(p, 2); p = px_union_xor(p, 1);
+    if (in_range && (lane & 7) == 0) view.pkt_px[slot >> 3] = p;
+    // tile cost = packet ranges touching the tile (what the leaf scan of the render kernel tests against the tile); the
+    // packet's 8 lanes share the tiles of its range (every lane holds the same p after the butterfly)
+    if (!px_is_empty(p))
     {
-        int px0 = 0, px1 = -1, py0 = 0, py1 = -1;
-        bool all = false;
-        if (film_rect_tiles(vp, FilmRect{p.x, p.y, p.z, p.w}, px0, px1, py0, py1, all) && !all)
-        {
-            const int w = px1 - px0 + 1, n = w * (py1 - py0 + 1);
-            if (n <= 64)
-                for (int i = lane & 7; i < n; i += 8) atomicAdd(&view.tile_cost[(py0 + i / w) * vp.tiles_x + px0 + i % w], 1u);
-        }
+        const int qx0 = (int)(p.x & 0xffffu) >> 3, qy0 = (int)(p.x >> 16) >> 2, qx1 = (int)(p.y & 0xffffu) >> 3, qy1 = (int)(p.y >> 16) >> 2;
+        const int w = qx1 - qx0 + 1, n = w * (qy1 - qy0 + 1);
+        if (n <= 64)
+            for (int i = lane & 7; i < n; i += 8)
+            {
+                const int ty = qy0 + i / w;
+                if (owns_tile_row(part, ty)) atomicAdd(&view.tile_cost[ty * vp.tiles_x + qx0 + i % w], 1u);
+            }
+    }
+    // chunk = the 32 packets of this block
+    p = px_union_xor(p, 8); p = px_union_xor(p, 16);
+    __shared__ uint2 s_px[kBlock / 32];
+    if (lane == 0) s_px[threadIdx.x >> 5] = p;
+    __syncthreads();
+    if (threadIdx.x == 0)
+    {
+        uint2 c = s_px[0];
+#pragma unroll
+        for (int w = 1; w < kBlock / 32; ++w) c = px_union(c, s_px[w]);
+        view.chunk_px[blockIdx.x] = c;
     }
 }
 
 // Second pass, two kinds of blocks running side by side:
-//  * blocks [0, leaf_blocks): one warp per leaf unions its packet rectangles and folds the result into every ancestor's
-//    rectangle (order-independent atomics: no level-by-level pass);
+//  * blocks [0, node_blocks): one warp per tree node (leaf or inner) unions the packet ranges of the node's subtree — one
+//    contiguous range of packets, whole chunks of 32 read from chunk_px — and appends the node to the bins its range
+//    touches (flat per-bin lists the render kernel filters per tile instead of walking the tree);
 //  * the other blocks compact the stamps of this rank's tiles into the busy list, kTilesPerThread tiles per thread and ONE
 //    global atomic per block and slab (the warps reserve their places in shared memory first; per-warp global atomics
 //    would serialise on the handful of slab counters).
@@ -599,63 +628,67 @@ __device__ __forceinline__ int tile_cost_class(uint32_t cost, int shift)
     const int c = 31 - __clz((int)(cost | 1u)) - shift;
     return c < 0 ? 0 : (c > kCostBuckets - 1 ? kCostBuckets - 1 : c);
 }
-__global__ void __launch_bounds__(kBlock) k_view_finish(DevScene sc, DevView view, DevCamera cm, DevPartition part, DevSlabs slabs,
-                                                        uint32_t leaf_blocks)
+__global__ void __launch_bounds__(kBlock) k_view_nodes(DevScene sc, DevView view, DevCamera cm, DevPartition part, DevSlabs slabs,
+                                                       uint32_t node_blocks)
 {
     const int lane = threadIdx.x & 31;
-    if (blockIdx.x < leaf_blocks)
+    if (blockIdx.x < node_blocks)
     {
         const uint32_t warp = (blockIdx.x * kBlock + threadIdx.x) >> 5;
-        const uint32_t n_warps = (leaf_blocks * kBlock) >> 5;
-        float4 mine = make_float4(INFINITY, INFINITY, -INFINITY, -INFINITY);  // union over the leaves this warp handled (lane 0)
+        const uint32_t n_warps = (node_blocks * kBlock) >> 5;
         for (uint32_t node = warp; node < sc.n_nodes; node += n_warps)
         {
-            const float4 n0 = __ldg(&sc.nodes[2 * node]);
-            if (__float_as_int(n0.w) > 0) continue;
-            const uint32_t first = ~(uint32_t)__float_as_int(n0.w);
-            const uint32_t cnt = (uint32_t)__float_as_int(__ldg(&sc.nodes[2 * node + 1]).w);
-            const uint32_t npk = (cnt + 7u) >> 3, pk0 = first >> 3;
-            float4 acc = make_float4(INFINITY, INFINITY, -INFINITY, -INFINITY);
-            for (uint32_t k = lane; k < npk; k += 32)
+            const uint2 pk = __ldg(&sc.node_pk[node]);
+            const uint32_t pb = pk.x, pe = pk.y;
+            uint32_t hb = (pb + 31u) & ~31u;   // packets before the first whole chunk
+            if (hb > pe) hb = pe;
+            uint2 acc = px_empty();
+            for (uint32_t k = pb + lane; k < hb; k += 32) acc = px_union(acc, view.pkt_px[k]);
+            if (hb < pe)
             {
-                const float4 q = view.pkt_rect[pk0 + k];
-                acc.x = fminf(acc.x, q.x); acc.y = fminf(acc.y, q.y); acc.z = fmaxf(acc.z, q.z); acc.w = fmaxf(acc.w, q.w);
+                const uint32_t ce = pe >> 5;
+                for (uint32_t c = (hb >> 5) + lane; c < ce; c += 32) acc = px_union(acc, view.chunk_px[c]);
+                uint32_t tb = ce << 5;
+                if (tb < hb) tb = hb;
+                for (uint32_t k = tb + lane; k < pe; k += 32) acc = px_union(acc, view.pkt_px[k]);
             }
 #pragma unroll
-            for (int off = 16; off > 0; off >>= 1) acc = rect_union_xor(acc, off);
-            if (lane == 0)
+            for (int off = 16; off > 0; off >>= 1) acc = px_union_xor(acc, off);
+            if (lane == 0) view.node_px[node] = acc;
+            if (px_is_empty(acc) || node == 0u) continue;   // (the root is tested by every tile directly)
+            const float4 n0 = __ldg(&sc.nodes[2 * node]), n1 = __ldg(&sc.nodes[2 * node + 1]);
+            const bool inner = __float_as_int(n0.w) > 0;
+            float4 sp4 = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (inner) sp4 = __ldg(&sc.nodes[2 * (uint32_t)__float_as_int(n0.w) + 1]);   // split point = hi corner of child 0
+            const int bx0 = (int)(acc.x & 0xffffu) >> kBinShiftX, by0 = (int)(acc.x >> 16) >> kBinShiftY;
+            const int bx1 = (int)(acc.y & 0xffffu) >> kBinShiftX, by1 = (int)(acc.y >> 16) >> kBinShiftY;
+            const int w = bx1 - bx0 + 1, n = w * (by1 - by0 + 1);
+            for (int i = lane; i < n; i += 32)
             {
-                view.node_rect[node] = acc;
-                if (acc.x <= acc.z && acc.y <= acc.w)   // an empty rectangle changes no ancestor
+                const int by = by0 + i / w, bx = bx0 + i % w;
+                if (!owns_bin_row(part, by, cm.H)) continue;
+                const uint32_t b = (uint32_t)(by * view.bins_x + bx);
+                if (inner)
                 {
-                    // every ancestor but the root: a few hundred updates per address at most
-                    for (uint32_t p = __ldg(&sc.parent[node]); p != 0xffffffffu && p != 0u; p = __ldg(&sc.parent[p]))
+                    const uint32_t at = atomicAdd(&view.bin_cnt[2 * b + 1], 1u);
+                    if (at < view.bin_inner_cap)
                     {
-                        float* q = reinterpret_cast<float*>(&view.node_rect[p]);
-                        atomic_min_float(q + 0, acc.x); atomic_min_float(q + 1, acc.y);
-                        atomic_max_float(q + 2, acc.z); atomic_max_float(q + 3, acc.w);
+                        uint4* e = view.bin_inner + ((size_t)b * view.bin_inner_cap + at) * 2;
+                        e[0] = make_uint4(acc.x, acc.y, node, 0u);
+                        e[1] = make_uint4(__float_as_uint(sp4.x), __float_as_uint(sp4.y), __float_as_uint(sp4.z), 0u);
                     }
-                    mine.x = fminf(mine.x, acc.x); mine.y = fminf(mine.y, acc.y); mine.z = fmaxf(mine.z, acc.z); mine.w = fmaxf(mine.w, acc.w);
                 }
-            }
-        }
-        // the root takes one update per block (every leaf is below it: per-leaf atomics would serialise on one address)
-        __shared__ float4 s_mine[kBlock / 32];
-        if (lane == 0) s_mine[threadIdx.x >> 5] = mine;
-        __syncthreads();
-        if (threadIdx.x == 0 && !sc.root_is_leaf)
-        {
-            float4 m = s_mine[0];
-            for (int w = 1; w < kBlock / 32; ++w)
-            {
-                const float4 q = s_mine[w];
-                m.x = fminf(m.x, q.x); m.y = fminf(m.y, q.y); m.z = fmaxf(m.z, q.z); m.w = fmaxf(m.w, q.w);
-            }
-            if (m.x <= m.z && m.y <= m.w)
-            {
-                float* q = reinterpret_cast<float*>(&view.node_rect[0]);
-                atomic_min_float(q + 0, m.x); atomic_min_float(q + 1, m.y);
-                atomic_max_float(q + 2, m.z); atomic_max_float(q + 3, m.w);
+                else
+                {
+                    const uint32_t at = atomicAdd(&view.bin_cnt[2 * b], 1u);
+                    if (at < view.bin_leaf_cap)
+                    {
+                        uint4* e = view.bin_leaf + ((size_t)b * view.bin_leaf_cap + at) * 3;
+                        e[0] = make_uint4(acc.x, acc.y, __ldg(&sc.leaf_seq[node]), ~(uint32_t)__float_as_int(n0.w));
+                        e[1] = make_uint4(__float_as_uint(n0.x), __float_as_uint(n0.y), __float_as_uint(n0.z), __float_as_uint(n1.w));
+                        e[2] = make_uint4(__float_as_uint(n1.x), __float_as_uint(n1.y), __float_as_uint(n1.z), node);
+                    }
+                }
             }
         }
         return;
@@ -668,7 +701,7 @@ __global__ void __launch_bounds__(kBlock) k_view_finish(DevScene sc, DevView vie
     const unsigned int tiles_per_band = (unsigned int)(tiles_x * rows_per_band);
     const unsigned int n_tiles = (unsigned int)my_bands * tiles_per_band;
     const bool all_busy = *((volatile uint32_t*)view.all_flag) == view.frame_id;
-    const unsigned int blk = blockIdx.x - leaf_blocks, n_blk = gridDim.x - leaf_blocks;
+    const unsigned int blk = blockIdx.x - node_blocks, n_blk = gridDim.x - node_blocks;
     constexpr unsigned int kStep = kBlock * kTilesPerThread;
     __shared__ unsigned int s_count[kMaxSlabs * kCostBuckets], s_at[kMaxSlabs * kCostBuckets];
     for (unsigned int base = blk * kStep; base < n_tiles; base += n_blk * kStep)
@@ -688,14 +721,19 @@ __global__ void __launch_bounds__(kBlock) k_view_finish(DevScene sc, DevView vie
                 const unsigned int lb = tile / tiles_per_band, rem = tile - lb * tiles_per_band;
                 const int trow = (int)(rem / (unsigned int)tiles_x), tcol = (int)(rem - (unsigned int)trow * (unsigned int)tiles_x);
                 const int y0 = ((int)lb * part.world + part.rank) * part.band_rows + trow * 4;
-                const int gt = (y0 >> 2) * view.tiles_x + tcol;
-                busy[k] = y0 < cm.H && (all_busy || view.stamps[gt] == view.frame_id);
-                if (busy[k])
+                if (y0 < cm.H)
                 {
+                    const int gt = (y0 >> 2) * view.tiles_x + tcol;
+                    busy[k] = all_busy || view.stamps[gt] == view.frame_id;
+                    // every tile this rank examines starts the next frame at cost zero (k_view_bounds adds cost to this
+                    // rank's tiles only, so no tile keeps a stale count when the camera or the partition changes)
                     const uint32_t cost = view.tile_cost[gt];
-                    cls = tile_cost_class(cost, view.cost_shift);
-                    view.tile_cost[gt] = 0u;   // the next frame counts from zero
-                    if (view.tile_log) { view.tile_log[tile].z = cost; view.tile_log[tile].w = (uint32_t)cls; }
+                    if (cost) view.tile_cost[gt] = 0u;
+                    if (busy[k])
+                    {
+                        cls = tile_cost_class(cost, view.cost_shift);
+                        if (view.tile_log) { view.tile_log[tile].z = cost; view.tile_log[tile].w = (uint32_t)cls; }
+                    }
                 }
             }
             int sl = 0;
@@ -743,26 +781,35 @@ __global__ void __launch_bounds__(kBlock) k_view_finish(DevScene sc, DevView vie
     }
 }
 
-// ---- culled phase 2: the warp walks the k-th listed leaf of each of its rays; rays that share the leaf form a group.
-// Candidate records are found hierarchically (packet rectangle, then triangle rectangle, against the tile's film
-// rectangle); each candidate is broadcast and every ray of the group whose film point lies inside the triangle's
-// rectangle runs the reference triangle test on it. A ray's result is the lexicographic minimum (t, position in the
-// reference's leaf order) over the accepted records of its first leaf that has any (kd_tree.cpp:437-462).
-__device__ __forceinline__ bool rect_overlap(const float4 R, const float4 T)
-{
-    return !(R.x > T.z || R.z < T.x || R.y > T.w || R.w < T.y);
-}
-
-// Per-warp shared scratch of the culled phase 2: queue of (ray lane, slot) pairs whose film point lies inside the
-// triangle's rectangle, and the per-ray running minimum of (t bits, position in the reference's leaf order).
+// ---- culled busy tile, flat: ONE warp, one 8x4 tile, no tree walk ----------------------------------------------------------
+// For one camera ray the reference returns (kd_tree.cpp:337-465): among the leaves the ray lists, in ascending (entry
+// distance, insertion order) order, the first one in which some triangle passes the float test, and inside it the minimum
+// (t, position). A leaf L is listed iff every inner node above it passes check_ray_AABB_intersection, its own entry distance
+// is > 0 and no "at most 5 accepted children" cut (kd_tree.cpp:374) removes it. With the per-frame pixel ranges:
+//  * a ray whose pixel lies outside node_px[L] is accepted by no triangle of L (view_bounds.h), so L can be dropped from its
+//    list without changing the result — the candidates of a tile are the leaves of its bin whose range touches the tile;
+//  * for a ray with finite origin, direction and reciprocals every slab value is a monotone function of the plane it comes
+//    from and the child boxes nest (kd_tree.cpp:120-148): a leaf that passes its own slab test passes the test of every
+//    ancestor, the leaf's entry distance alone decides (tiles with another ray take the unculled core);
+//  * the cut at an inner node n can only trigger for a ray whose three split-plane parameters (s - o)*inv of n's split
+//    point s are not pairwise different: the children are the 8 octants around s, both octants that share a split plane
+//    use the same float t(s), and with pairwise different parameters at most 4 octants contain a ray parameter in their
+//    closed slab intervals. The inner nodes above any candidate leaf of the tile are in the bin's inner list (their range
+//    contains the leaf's); a ray with a tie at one of them ("risky", a ray through a split edge up to rounding) is traced
+//    by the unculled core instead;
+//  * the order in which the leaves are examined is free: per ray the best (entry distance, leaf_seq) key with a hit is
+//    kept, a leaf is skipped for the rays that already hold a better key, and (t, position) is minimised inside a leaf —
+//    the lexicographic minimum the reference's list order + early exit (kd_tree.cpp:437-462) computes. The candidates of
+//    a chunk are taken nearest first (entry distance of the tile's first ray) so that later leaves are mostly skipped.
 static constexpr int kPairCap = 128;
 struct WarpPairs
 {
-    unsigned long long key[32];
+    unsigned long long key[32];        // per ray: min (t bits, position in the reference's leaf order) in the current leaf
     uint32_t face[32];
-    uint32_t pair_slot[kPairCap];
+    uint32_t pair_slot[kPairCap];      // queue of (ray lane, slot) pairs whose pixel lies inside the triangle's range
     unsigned char pair_lane[kPairCap];
 };
+struct WarpScratch { WarpPairs pairs; };
 
 // The reference triangle test (model.h:75-103) for one ray and one record; true iff the caller would accept the
 // distance (t > tolerance && t < MAX_FLOAT, renderer.cpp:52 / kd_tree.cpp:446).
@@ -794,9 +841,10 @@ __device__ __forceinline__ bool tri_accept(const float4* __restrict__ rec, float
     return t > kTol && t < kMaxFloat;
 }
 
-// Runs the triangle test on every queued pair, 32 pairs per step: each lane takes one pair, fetches the ray from its
-// owner lane by shuffle and gathers the record. Accepted hits lower key[ray] = (t bits, position) — t > 0, so the float
-// bits order like the values, and the lexicographic minimum equals the reference's sequential strict-< scan.
+// Runs the triangle test on every queued pair, 32 pairs per step: each lane takes one pair, fetches the ray direction
+// from its owner lane by shuffle (every camera ray starts at the eye) and gathers the record. Accepted hits lower
+// key[ray] = (t bits, position) — t > 0, so the float bits order like the values, and the lexicographic minimum equals
+// the reference's sequential strict-< scan.
 template <bool STRICT, bool COUNT>
 __device__ __forceinline__ void drain_pairs(const DevScene& sc, WarpPairs& wp, int lane, int& qn, const RayL& ray, WorkCount& wc)
 {
@@ -806,12 +854,11 @@ __device__ __forceinline__ void drain_pairs(const DevScene& sc, WarpPairs& wp, i
         const bool have = base + lane < qn;
         const int src = have ? (int)wp.pair_lane[base + lane] : lane;
         const uint32_t s = have ? wp.pair_slot[base + lane] : 0u;
-        const float ox = __shfl_sync(FULL_MASK, ray.ox, src), oy = __shfl_sync(FULL_MASK, ray.oy, src), oz = __shfl_sync(FULL_MASK, ray.oz, src);
         const float dx = __shfl_sync(FULL_MASK, ray.dx, src), dy = __shfl_sync(FULL_MASK, ray.dy, src), dz = __shfl_sync(FULL_MASK, ray.dz, src);
         float t = 0.f;
         uint32_t pos = 0u, face = 0u;
         bool acc = false;
-        if (have) acc = tri_accept<STRICT, COUNT>(sc.tris + (size_t)(s >> 3) * 24 + (s & 7), ox, oy, oz, dx, dy, dz, t, pos, face, wc);
+        if (have) acc = tri_accept<STRICT, COUNT>(sc.tris + (size_t)(s >> 3) * 24 + (s & 7), ray.ox, ray.oy, ray.oz, dx, dy, dz, t, pos, face, wc);
         const unsigned long long mk = ((unsigned long long)__float_as_uint(t) << 32) | (unsigned long long)pos;
         if (acc) atomicMin(&wp.key[src], mk);
         __syncwarp();
@@ -821,296 +868,268 @@ __device__ __forceinline__ void drain_pairs(const DevScene& sc, WarpPairs& wp, i
     qn = 0;
 }
 
+// One leaf against the rays `ing` of the tile: packets whose range touches the tile, then their triangles, then the rays
+// inside each triangle's range (a bit mask computed from the range and the tile origin), queued as pairs and tested.
+// On return key[lane] / face[lane] hold the leaf's best hit of ray `lane` (all-ones when it has none).
 template <bool STRICT, bool COUNT>
-__device__ __forceinline__ void scan_tile_leaves(const DevScene& sc, const DevView& vw, WarpPairs& wp, int lane, const RayL& ray,
-                                                 float fx, float fy, const float4 trect, const uint2* list, int nleaf,
-                                                 float& t_out, uint32_t& face_out, WorkCount& wc)
+__device__ __forceinline__ void scan_leaf_flat(const DevScene& sc, const DevView& vw, WarpPairs& wp, int lane, const RayL& ray,
+                                               uint32_t first, uint32_t cnt, bool ing, uint2 tr, int tile_x0, int tile_y0, WorkCount& wc)
 {
-    bool done = nleaf <= 0;
-    int k = 0;
+    const unsigned gmask = __ballot_sync(FULL_MASK, ing);
+    const uint32_t npk = (cnt + 7u) >> 3, pk0 = first >> 3;
     int qn = 0;
-    float bt = kMaxFloat;
-    uint32_t bface = 0xffffffffu;
-    wp.key[lane] = ~0ull;
-    __syncwarp();
-    while (__any_sync(FULL_MASK, !done))
+    for (uint32_t pb = 0; pb < npk; pb += 32)
     {
-        const uint32_t myleaf = done ? 0xffffffffu : list[k].x;
-        unsigned pending = __ballot_sync(FULL_MASK, !done);
-        while (pending)
+        bool pov = false;
+        if (pb + lane < npk)
         {
-            const int leader = __ffs(pending) - 1;
-            const uint32_t id = __shfl_sync(FULL_MASK, myleaf, leader);
-            const bool ingrp = myleaf == id;
-            pending &= ~__ballot_sync(FULL_MASK, ingrp);
-            if (COUNT && ingrp) wc.scanned++;
-            const uint32_t first = ~(uint32_t)__float_as_int(__ldg(&sc.nodes[2 * id]).w);
-            const uint32_t cnt = (uint32_t)__float_as_int(__ldg(&sc.nodes[2 * id + 1]).w);
-            const uint32_t npk = (cnt + 7u) >> 3, pk0 = first >> 3;
-            for (uint32_t pb = 0; pb < npk; pb += 32)
+            pov = px_overlap(__ldg(&vw.pkt_px[pk0 + pb + lane]), tr);
+            if (COUNT) wc.rect++;
+        }
+        unsigned pmask = __ballot_sync(FULL_MASK, pov);
+        while (pmask)
+        {
+            // the next (up to) four touching packets, one per group of 8 lanes
+            int sel = -1;
             {
-                bool pov = false;
-                if (pb + lane < npk)
-                {
-                    pov = rect_overlap(__ldg(&vw.pkt_rect[pk0 + pb + lane]), trect);
-                    if (COUNT) wc.rect++;
-                }
-                unsigned pmask = __ballot_sync(FULL_MASK, pov);
-                while (pmask)
-                {
-                    // the next (up to) four overlapping packets, one per group of 8 lanes
-                    int sel = -1;
-                    {
-                        unsigned m = pmask;
-                        const int j = lane >> 3;
+                unsigned m = pmask;
+                const int j = lane >> 3;
 #pragma unroll
-                        for (int q = 0; q < 4; ++q)
-                        {
-                            const int b = m ? __ffs(m) - 1 : -1;
-                            if (q == j) sel = b;
-                            m &= m - 1;  // m == 0 stays 0
-                        }
-                        pmask = m;
-                    }
-                    bool cov = false;
-                    uint32_t myslot = 0;
-                    float4 myrect = make_float4(0.f, 0.f, 0.f, 0.f);
-                    if (sel >= 0)
+                for (int q = 0; q < 4; ++q)
+                {
+                    const int b = m ? __ffs(m) - 1 : -1;
+                    if (q == j) sel = b;
+                    m &= m - 1;  // m == 0 stays 0
+                }
+                pmask = m;
+            }
+            uint32_t myslot = 0, m32 = 0;
+            if (sel >= 0)
+            {
+                myslot = ((pk0 + pb + (uint32_t)sel) << 3) + (lane & 7);
+                const uint2 r = __ldg(&vw.tri_px[myslot]);
+                if (COUNT) wc.rect++;
+                if (px_overlap(r, tr))
+                {
+                    // rays of the tile inside the range: columns cx0..cx1 and rows ry0..ry1 relative to the tile origin
+                    const int cx0 = max((int)(r.x & 0xffffu) - tile_x0, 0), cx1 = min((int)(r.y & 0xffffu) - tile_x0, 7);
+                    const int ry0 = max((int)(r.x >> 16) - tile_y0, 0), ry1 = min((int)(r.y >> 16) - tile_y0, 3);
+                    const uint32_t cols = (0xffu >> (7 - cx1)) & (0xffu << cx0) & 0xffu;
+                    const uint32_t rows = (0xfu >> (3 - ry1)) & (0xfu << ry0) & 0xfu;
+                    const uint32_t spread = (rows & 1u) | ((rows & 2u) << 7) | ((rows & 4u) << 14) | ((rows & 8u) << 21);
+                    m32 = (cols * spread) & gmask;
+                }
+            }
+            // pairs of this step: exclusive prefix sum of the per-lane pair counts
+            const int n = __popc(m32);
+            int incl = n;
+#pragma unroll
+            for (int off = 1; off < 32; off <<= 1)
+            {
+                const int v = __shfl_up_sync(FULL_MASK, incl, off);
+                if (lane >= off) incl += v;
+            }
+            const int total = __shfl_sync(FULL_MASK, incl, 31);
+            if (total == 0) continue;
+            if (qn + total > kPairCap) drain_pairs<STRICT, COUNT>(sc, wp, lane, qn, ray, wc);
+            if (total <= kPairCap)
+            {
+                int at = qn + incl - n;
+                while (m32)
+                {
+                    const int b = __ffs(m32) - 1;
+                    m32 &= m32 - 1;
+                    wp.pair_slot[at] = myslot;
+                    wp.pair_lane[at] = (unsigned char)b;
+                    ++at;
+                }
+                qn += total;
+            }
+            else
+            {
+                // more pairs than the queue holds (large triangles over the whole tile): one triangle at a time
+                unsigned cm = __ballot_sync(FULL_MASK, m32 != 0u);
+                while (cm)
+                {
+                    const int b = __ffs(cm) - 1;
+                    cm &= cm - 1;
+                    const uint32_t m = __shfl_sync(FULL_MASK, m32, b), s = __shfl_sync(FULL_MASK, myslot, b);
+                    if ((m >> lane) & 1u)
                     {
-                        myslot = ((pk0 + pb + (uint32_t)sel) << 3) + (lane & 7);
-                        myrect = __ldg(&vw.tri_rect[myslot]);
-                        cov = rect_overlap(myrect, trect);
-                        if (COUNT) wc.rect++;
+                        const int at = qn + __popc(m & ((1u << lane) - 1u));
+                        wp.pair_slot[at] = s;
+                        wp.pair_lane[at] = (unsigned char)lane;
                     }
-                    unsigned cmask = __ballot_sync(FULL_MASK, cov);
-                    while (cmask)
-                    {
-                        const int b = __ffs(cmask) - 1;
-                        cmask &= cmask - 1;
-                        const uint32_t s = __shfl_sync(FULL_MASK, myslot, b);
-                        const float rx0 = __shfl_sync(FULL_MASK, myrect.x, b), ry0 = __shfl_sync(FULL_MASK, myrect.y, b);
-                        const float rx1 = __shfl_sync(FULL_MASK, myrect.z, b), ry1 = __shfl_sync(FULL_MASK, myrect.w, b);
-                        const bool in = ingrp && !(fx < rx0 || fx > rx1 || fy < ry0 || fy > ry1);
-                        const unsigned m = __ballot_sync(FULL_MASK, in);
-                        if (!m) continue;
-                        if (in)
-                        {
-                            const int at = qn + __popc(m & ((1u << lane) - 1u));
-                            wp.pair_slot[at] = s;
-                            wp.pair_lane[at] = (unsigned char)lane;
-                        }
-                        qn += __popc(m);
-                        if (qn > kPairCap - 32) drain_pairs<STRICT, COUNT>(sc, wp, lane, qn, ray, wc);
-                    }
+                    qn += __popc(m);
+                    if (qn > kPairCap - 32) drain_pairs<STRICT, COUNT>(sc, wp, lane, qn, ray, wc);
                 }
             }
         }
-        drain_pairs<STRICT, COUNT>(sc, wp, lane, qn, ray, wc);
-        if (!done)
+    }
+    drain_pairs<STRICT, COUNT>(sc, wp, lane, qn, ray, wc);
+}
+
+template <bool STRICT, bool COUNT>
+__device__ __forceinline__ void trace_tile_flat(const DevScene& sc, const DevScratch& scratch, const DevView& vw, WarpScratch& ws,
+                                                int warp_slot, int lane, bool active, const RayL& ray, int px_x, int px_y,
+                                                int tile_x0, int tile_y0, uint2* leaves, uint32_t* stack, float& t_out,
+                                                uint32_t& face_out, WorkCount& wc)
+{
+    WarpPairs& wp = ws.pairs;
+    const float ix = __frcp_rn(ray.dx), iy = __frcp_rn(ray.dy), iz = __frcp_rn(ray.dz);
+    // finite origin, direction and reciprocals (no 0*inf, inf-inf or NaN in any slab product)
+    const float chk = (ray.ox - ray.ox) + (ray.oy - ray.oy) + (ray.oz - ray.oz) + (ix - ix) + (iy - iy) + (iz - iz) +
+                      (ray.dx - ray.dx) + (ray.dy - ray.dy) + (ray.dz - ray.dz);
+    const bool regular = chk == 0.0f;  // any NaN/Inf operand makes the sum NaN
+    t_out = kMaxFloat;
+    face_out = 0xffffffffu;
+    if (__any_sync(FULL_MASK, active && !regular))
+    {
+        trace_warp<STRICT, COUNT>(sc, scratch, warp_slot, lane, active, ray, leaves, stack, t_out, face_out, wc);
+        return;
+    }
+    const uint32_t mypx = (uint32_t)px_x | ((uint32_t)px_y << 16);
+    bool part = false;   // this lane's ray takes part in the flat search
+    if (active)
+    {
+        const float4 lo = __ldg(&sc.nodes[0]);
+        const float4 hi = __ldg(&sc.nodes[1]);
+        if (COUNT) wc.box++;
+        part = box_check(ray, ix, iy, iz, lo, hi) && px_contains(__ldg(&vw.node_px[0]), mypx);  // kd_tree.cpp:339
+    }
+    if (!__any_sync(FULL_MASK, part)) return;
+    // pixel range of the rays that can have work
+    uint2 tr;
+    {
+        const uint32_t x0 = __reduce_min_sync(FULL_MASK, part ? (uint32_t)px_x : 0xffffu), y0 = __reduce_min_sync(FULL_MASK, part ? (uint32_t)px_y : 0xffffu);
+        const uint32_t x1 = __reduce_max_sync(FULL_MASK, part ? (uint32_t)px_x : 0u), y1 = __reduce_max_sync(FULL_MASK, part ? (uint32_t)px_y : 0u);
+        tr = make_uint2(x0 | (y0 << 16), x1 | (y1 << 16));
+    }
+    wp.key[lane] = ~0ull;
+    __syncwarp();
+    if (sc.root_is_leaf)  // kd_tree.cpp:344-361: the root's primitives are scanned without an entry-distance filter
+    {
+        const uint32_t first = ~(uint32_t)__float_as_int(__ldg(&sc.nodes[0]).w);
+        const uint32_t cnt = (uint32_t)__float_as_int(__ldg(&sc.nodes[1]).w);
+        if (COUNT && part) { wc.listed++; wc.scanned++; }
+        scan_leaf_flat<STRICT, COUNT>(sc, vw, wp, lane, ray, first, cnt, part, tr, tile_x0, tile_y0, wc);
+        const unsigned long long kk = wp.key[lane];
+        if (part && kk != ~0ull) { t_out = __uint_as_float((uint32_t)(kk >> 32)); face_out = wp.face[lane]; }
+        return;
+    }
+    const uint32_t bin = (uint32_t)((tile_y0 >> kBinShiftY) * vw.bins_x + (tile_x0 >> kBinShiftX));
+    const uint32_t nL = __ldg(&vw.bin_cnt[2 * bin]), nI = __ldg(&vw.bin_cnt[2 * bin + 1]);
+    if (nL > vw.bin_leaf_cap || nI > vw.bin_inner_cap)   // a list of this bin did not fit: the tile takes the unculled core
+    {
+        if (COUNT && active) wc.ovf++;
+        trace_warp<STRICT, COUNT>(sc, scratch, warp_slot, lane, active, ray, leaves, stack, t_out, face_out, wc);
+        return;
+    }
+    // ---- rays with a tie of split-plane parameters at an inner node above a candidate leaf ("risky") ----
+    bool risky = false;
+    {
+        const float4 s = __ldg(&sc.nodes[2 * (uint32_t)__float_as_int(__ldg(&sc.nodes[0]).w) + 1]);   // root split point
+        const float tsx = mulr(subr(s.x, ray.ox), ix), tsy = mulr(subr(s.y, ray.oy), iy), tsz = mulr(subr(s.z, ray.oz), iz);
+        risky = part && (tsx == tsy || tsy == tsz || tsx == tsz);
+    }
+    for (uint32_t base = 0; base < nI; base += 32)
+    {
+        const bool valid = base + lane < nI;
+        uint4 e0 = make_uint4(0xffffffffu, 0u, 0u, 0u), e1 = make_uint4(0u, 0u, 0u, 0u);
+        if (valid)
         {
-            const unsigned long long kk = wp.key[lane];
-            if (kk != ~0ull)  // first leaf with a hit ends the ray (kd_tree.cpp:457-460)
+            const uint4* e = vw.bin_inner + ((size_t)bin * vw.bin_inner_cap + base + lane) * 2;
+            e0 = __ldg(e); e1 = __ldg(e + 1);
+        }
+        unsigned m = __ballot_sync(FULL_MASK, valid && px_overlap(make_uint2(e0.x, e0.y), tr));
+        while (m)
+        {
+            const int i = __ffs(m) - 1;
+            m &= m - 1;
+            const uint2 r = make_uint2(__shfl_sync(FULL_MASK, e0.x, i), __shfl_sync(FULL_MASK, e0.y, i));
+            const float sx = __uint_as_float(__shfl_sync(FULL_MASK, e1.x, i)), sy = __uint_as_float(__shfl_sync(FULL_MASK, e1.y, i)),
+                        sz = __uint_as_float(__shfl_sync(FULL_MASK, e1.z, i));
+            const float tsx = mulr(subr(sx, ray.ox), ix), tsy = mulr(subr(sy, ray.oy), iy), tsz = mulr(subr(sz, ray.oz), iz);
+            if (COUNT && part) wc.box++;
+            risky = risky || (part && px_contains(r, mypx) && (tsx == tsy || tsy == tsz || tsx == tsz));
+        }
+    }
+    const bool any_risky = __any_sync(FULL_MASK, risky);
+    if (risky) part = false;
+    // ---- candidate leaves of the bin ----
+    uint32_t best_dis = 0xffffffffu, best_seq = 0xffffffffu;   // key of the best leaf with a hit so far (entry distance bits, leaf_seq)
+    float bt = kMaxFloat;
+    uint32_t bface = 0xffffffffu;
+    // reference ray of the ordering heuristic: the first participating lane's
+    const int ref = __ffs(__ballot_sync(FULL_MASK, part)) - 1;
+    if (ref >= 0)
+    {
+        const float rdx = __shfl_sync(FULL_MASK, ix, ref), rdy = __shfl_sync(FULL_MASK, iy, ref), rdz = __shfl_sync(FULL_MASK, iz, ref);
+        for (uint32_t base = 0; base < nL; base += 32)
+        {
+            const bool valid = base + lane < nL;
+            uint4 e0 = make_uint4(0xffffffffu, 0u, 0u, 0u), e1 = make_uint4(0u, 0u, 0u, 0u), e2 = e1;
+            if (valid)
             {
-                bt = __uint_as_float((uint32_t)(kk >> 32));
-                bface = wp.face[lane];
-                done = true;
+                const uint4* e = vw.bin_leaf + ((size_t)bin * vw.bin_leaf_cap + base + lane) * 3;
+                e0 = __ldg(e); e1 = __ldg(e + 1); e2 = __ldg(e + 2);
             }
-            else if (++k >= nleaf) done = true;
+            const bool ov = valid && px_overlap(make_uint2(e0.x, e0.y), tr);
+            // ordering key: where the reference ray enters this lane's candidate box (max of the three near-slab parameters,
+            // clamped at 0); only the processing order depends on it
+            uint32_t okey = 0xffffffffu;
+            if (ov)
+            {
+                const float nx = rdx < 0.0f ? __uint_as_float(e2.x) : __uint_as_float(e1.x), ny = rdy < 0.0f ? __uint_as_float(e2.y) : __uint_as_float(e1.y),
+                            nz = rdz < 0.0f ? __uint_as_float(e2.z) : __uint_as_float(e1.z);
+                const float tn = fmaxf(fmaxf((nx - ray.ox) * rdx, (ny - ray.oy) * rdy), fmaxf((nz - ray.oz) * rdz, 0.0f));
+                okey = (__float_as_uint(tn) & ~31u) | (uint32_t)lane;   // tn >= 0 (NaN → 0 by fmaxf): bits order like values
+            }
+            unsigned rem = __ballot_sync(FULL_MASK, ov);
+            while (rem)
+            {
+                const uint32_t mn = __reduce_min_sync(FULL_MASK, ((rem >> lane) & 1u) ? okey : 0xffffffffu);
+                const int i = (int)(mn & 31u);
+                rem &= ~(1u << i);
+                const uint2 r = make_uint2(__shfl_sync(FULL_MASK, e0.x, i), __shfl_sync(FULL_MASK, e0.y, i));
+                const bool inr = part && px_contains(r, mypx);
+                if (!__any_sync(FULL_MASK, inr)) continue;
+                float4 lo, hi;
+                lo.x = __uint_as_float(__shfl_sync(FULL_MASK, e1.x, i)); lo.y = __uint_as_float(__shfl_sync(FULL_MASK, e1.y, i));
+                lo.z = __uint_as_float(__shfl_sync(FULL_MASK, e1.z, i)); hi.x = __uint_as_float(__shfl_sync(FULL_MASK, e2.x, i));
+                hi.y = __uint_as_float(__shfl_sync(FULL_MASK, e2.y, i)); hi.z = __uint_as_float(__shfl_sync(FULL_MASK, e2.z, i));
+                lo.w = hi.w = 0.f;
+                const uint32_t seq = __shfl_sync(FULL_MASK, e0.z, i);
+                const float dis = box_entry(ray, ix, iy, iz, lo, hi);   // get_ray_AABB_intersection, aabb.h:29-63
+                const uint32_t db = __float_as_uint(dis);
+                const bool listed = inr && dis > 0.0f;                  // kd_tree.cpp:385-388
+                if (COUNT && inr) { wc.box++; wc.listed += listed ? 1u : 0u; }
+                const bool ing = listed && (db < best_dis || (db == best_dis && seq < best_seq));
+                if (!__any_sync(FULL_MASK, ing)) continue;
+                const uint32_t first = __shfl_sync(FULL_MASK, e0.w, i), cnt = __shfl_sync(FULL_MASK, e1.w, i);
+                if (COUNT && ing) wc.scanned++;
+                scan_leaf_flat<STRICT, COUNT>(sc, vw, wp, lane, ray, first, cnt, ing, tr, tile_x0, tile_y0, wc);
+                const unsigned long long kk = wp.key[lane];
+                if (ing && kk != ~0ull)
+                {
+                    best_dis = db; best_seq = seq;
+                    bt = __uint_as_float((uint32_t)(kk >> 32));
+                    bface = wp.face[lane];
+                    wp.key[lane] = ~0ull;
+                }
+                __syncwarp();
+            }
         }
     }
     t_out = bt;
     face_out = bface;
-}
-
-// ---- culled phase 1: ONE traversal per tile. The warp walks the union of the subtrees its 32 rays need, in the
-// reference's own order (children pushed in index order, last pushed popped first, kd_tree.cpp:368-435), each stack
-// entry carrying the mask of lanes that reach the node. Per child:
-//  * pruning: a lane whose film point lies outside node_rect[child] cannot be accepted by any triangle below it
-//    (view_bounds.h) and drops out of that subtree;
-//  * inner children are not box-tested: for a ray with finite origin, direction and reciprocals every slab value is a
-//    monotone function of the plane it is computed from, the child boxes nest (kd_tree.cpp:120-148), hence a leaf that
-//    passes its own slab test passes the test of every ancestor — the leaf test alone decides. Tiles with a ray that
-//    is not finite in that sense take the unculled path;
-//  * leaves: the reference's entry distance (aabb.h:29-63) > 0, then the stable insertion of kd_tree.cpp:389-409. The
-//    union walk visits a lane's leaves in the same relative order as the lane's own walk would (a depth-first order
-//    restricted to an ancestor-closed subset), so ties keep the reference's order;
-//  * the "at most 5 accepted children" cut (kd_tree.cpp:374): child i >= 5 is processed by a lane iff at most 4 of the
-//    children 0..i-1 pass the reference's acceptance test for that lane; those are evaluated lazily, most distant
-//    octant first, until i-4 rejections are known. A lane that is cut leaves the node.
-// Returns false when the warp stack or a lane's list overflows (the tile then takes the unculled path).
-struct TileStack { uint32_t node[kStackCap]; uint32_t mask[kStackCap]; };
-
-template <bool COUNT>
-__device__ __forceinline__ bool collect_tile_leaves(const float4* __restrict__ nodes, const float4* __restrict__ node_rect,
-                                                    TileStack& ts, int lane, unsigned root_mask, const RayL& r, float ix, float iy,
-                                                    float iz, float fx, float fy, const float4 trect, uint2* leaves, int& nleaf,
-                                                    WorkCount& wc)
-{
-    nleaf = 0;
-    bool overflow = false;
-    int sp = 0;
-    if (root_mask)
+    if (any_risky)   // exact walk for the rays that might be cut (kd_tree.cpp:374)
     {
-        if (lane == 0) { ts.node[0] = 0u; ts.mask[0] = root_mask; }
-        sp = 1;
+        float t2 = kMaxFloat;
+        uint32_t f2 = 0xffffffffu;
+        trace_warp<STRICT, COUNT>(sc, scratch, warp_slot, lane, risky, ray, leaves, stack, t2, f2, wc);
+        if (risky) { t_out = t2; face_out = f2; }
     }
-    __syncwarp();
-    while (sp > 0)
-    {
-        --sp;
-        const uint32_t cur = ts.node[sp];
-        const bool here = (ts.mask[sp] >> lane) & 1u;
-        __syncwarp();
-        const uint32_t c0 = (uint32_t)__float_as_int(__ldg(&nodes[2 * cur]).w);
-        // children whose rectangle overlaps the tile's film rectangle (lanes 0..7, one child each)
-        const float4 myR = __ldg(&node_rect[c0 + (lane & 7)]);
-        // the 8 child boxes, one per lane of each group of 8, fetched together with the rectangles: the child loop below
-        // reads them by shuffle instead of waiting for a dependent load per child
-        const float4 myLo = __ldg(&nodes[2 * (c0 + (lane & 7))]);
-        const float4 myHi = __ldg(&nodes[2 * (c0 + (lane & 7)) + 1]);
-        if (COUNT && lane < 8) wc.rect++;
-        unsigned cm = __ballot_sync(FULL_MASK, rect_overlap(myR, trect)) & 0xffu;
-        unsigned ev = 0u, am = 0u;  // this lane: children of `cur` whose acceptance is known / that were accepted
-        bool alive = here;          // false once the lane is cut at this node
-        // Can the cut trigger at this node at all? The children are the 8 octants around the split point s = hi corner of
-        // child 0 (kd_tree.cpp:120-148) and every child's slab interval per axis is [t(lo), t(s)] or [t(s), t(hi)] with the
-        // SAME float t(s) = (s - o)*inv on both sides. If the three split-plane parameters are pairwise different, every
-        // ray parameter lies in the closed intervals of at most 4 octant triples in total, so at most 4 children can pass
-        // the slab test (leaf acceptance is stricter still) and the "accepted <= 4" guard never stops the loop. Only lanes
-        // with a tie (ray through a split edge, up to rounding) need the lazy sibling evaluation below.
-        float4 sp4;  // split point = hi corner of child 0
-        sp4.x = __shfl_sync(FULL_MASK, myHi.x, 0); sp4.y = __shfl_sync(FULL_MASK, myHi.y, 0); sp4.z = __shfl_sync(FULL_MASK, myHi.z, 0);
-        const float tsx = mulr(subr(sp4.x, r.ox), ix), tsy = mulr(subr(sp4.y, r.oy), iy), tsz = mulr(subr(sp4.z, r.oz), iz);
-        const bool risky = here && (tsx == tsy || tsy == tsz || tsx == tsz);
-        const bool any_risky = __any_sync(FULL_MASK, risky);
-        while (cm)
-        {
-            const int i = __ffs(cm) - 1;
-            cm &= cm - 1;
-            const float rx0 = __shfl_sync(FULL_MASK, myR.x, i), ry0 = __shfl_sync(FULL_MASK, myR.y, i);
-            const float rx1 = __shfl_sync(FULL_MASK, myR.z, i), ry1 = __shfl_sync(FULL_MASK, myR.w, i);
-            bool want = alive && !(fx < rx0 || fx > rx1 || fy < ry0 || fy > ry1);
-            if (!__any_sync(FULL_MASK, want)) continue;
-            if (i >= 5 && any_risky)
-            {
-                const unsigned below = (1u << i) - 1u;
-                int nrej = __popc(ev & ~am & below);
-                const unsigned ord = i == 5 ? 0x41302u : (i == 6 ? 0x425301u : 0x6534210u);
-                for (int q = 0; q < i; ++q)
-                {
-                    const int j = (int)((ord >> (4 * q)) & 7u);
-                    const bool need = want && risky && nrej < i - 4 && !((ev >> j) & 1u);
-                    if (!__any_sync(FULL_MASK, need)) continue;
-                    const float4 lo = __ldg(&nodes[2 * (c0 + j)]);
-                    const float4 hi = __ldg(&nodes[2 * (c0 + j) + 1]);
-                    const bool a = __float_as_int(lo.w) > 0 ? box_check(r, ix, iy, iz, lo, hi) : box_entry(r, ix, iy, iz, lo, hi) > 0.0f;
-                    if (need)
-                    {
-                        if (COUNT) wc.box++;
-                        ev |= 1u << j;
-                        if (a) am |= 1u << j; else ++nrej;
-                    }
-                }
-                if (want && risky && nrej < i - 4) { alive = false; want = false; }  // five earlier children accepted: cut
-                if (!__any_sync(FULL_MASK, want)) continue;
-            }
-            const uint32_t ch = c0 + (uint32_t)i;
-            const int low = __shfl_sync(FULL_MASK, __float_as_int(myLo.w), i);
-            if (low > 0)  // inner child: descend with the lanes that want it
-            {
-                const unsigned pm = __ballot_sync(FULL_MASK, want);
-                if (sp >= kStackCap) { overflow = true; break; }
-                if (lane == 0) { ts.node[sp] = ch; ts.mask[sp] = pm; }
-                ++sp;
-            }
-            else
-            {
-                float4 lo, hi;
-                lo.x = __shfl_sync(FULL_MASK, myLo.x, i); lo.y = __shfl_sync(FULL_MASK, myLo.y, i); lo.z = __shfl_sync(FULL_MASK, myLo.z, i);
-                hi.x = __shfl_sync(FULL_MASK, myHi.x, i); hi.y = __shfl_sync(FULL_MASK, myHi.y, i); hi.z = __shfl_sync(FULL_MASK, myHi.z, i);
-                lo.w = hi.w = 0.f;
-                const float dis = box_entry(r, ix, iy, iz, lo, hi);
-                if (want)
-                {
-                    if (COUNT) wc.box++;
-                    ev |= 1u << i;
-                    if (dis > 0.0f)
-                    {
-                        am |= 1u << i;
-                        if (nleaf >= kLeafCap) overflow = true;
-                        else
-                        {
-                            int k = nleaf;
-                            while (k > 0 && dis < __uint_as_float(leaves[k - 1].y))
-                            {
-                                leaves[k] = leaves[k - 1];
-                                --k;
-                            }
-                            leaves[k] = make_uint2(ch, __float_as_uint(dis));
-                            ++nleaf;
-                            if (COUNT) wc.listed++;
-                        }
-                    }
-                }
-            }
-        }
-        __syncwarp();
-        if (__any_sync(FULL_MASK, overflow)) return false;
-    }
-    return true;
-}
-
-// ---- one warp, one 8x4 tile, culled ------------------------------------------------------------------------------------
-struct WarpScratch { WarpPairs pairs; TileStack ts; };
-
-template <bool STRICT, bool COUNT>
-__device__ __forceinline__ void trace_tile_culled(const DevScene& sc, const DevScratch& scratch, const DevView& vw, WarpScratch& ws,
-                                                  int warp_slot, int lane, bool active, const RayL& ray, float fx, float fy,
-                                                  uint2* leaves, uint32_t* stack, float& t_out, uint32_t& face_out, WorkCount& wc)
-{
-    const float ix = __frcp_rn(ray.dx), iy = __frcp_rn(ray.dy), iz = __frcp_rn(ray.dz);
-    // finite origin, direction and reciprocals (no 0*inf, inf-inf or NaN in any slab product): see collect_tile_leaves
-    const float chk = (ray.ox - ray.ox) + (ray.oy - ray.oy) + (ray.oz - ray.oz) + (ix - ix) + (iy - iy) + (iz - iz) +
-                      (ray.dx - ray.dx) + (ray.dy - ray.dy) + (ray.dz - ray.dz);
-    const bool regular = chk == 0.0f;  // any NaN/Inf operand makes the sum NaN
-    bool fallback = __any_sync(FULL_MASK, active && !regular);
-    int nleaf = 0;
-    t_out = kMaxFloat;
-    face_out = 0xffffffffu;
-    float4 tr = make_float4(INFINITY, INFINITY, -INFINITY, -INFINITY);
-    if (!fallback)
-    {
-        bool in_root = false;
-        if (active)
-        {
-            const float4 lo = __ldg(&sc.nodes[0]);
-            const float4 hi = __ldg(&sc.nodes[1]);
-            if (COUNT) wc.box++;
-            const float4 R = __ldg(&vw.node_rect[0]);
-            in_root = box_check(ray, ix, iy, iz, lo, hi) && !(fx < R.x || fx > R.z || fy < R.y || fy > R.w);  // kd_tree.cpp:339
-        }
-        const unsigned root_mask = __ballot_sync(FULL_MASK, in_root);
-        if (!root_mask) return;
-        // film rectangle of the rays of this tile that can have work
-        if (in_root) tr = make_float4(fx, fy, fx, fy);
-#pragma unroll
-        for (int off = 16; off > 0; off >>= 1) tr = rect_union_xor(tr, off);
-        if (sc.root_is_leaf)  // kd_tree.cpp:344-361: the root's primitives are scanned without an entry-distance filter
-        {
-            if (in_root) { leaves[0] = make_uint2(0u, 0u); nleaf = 1; }
-        }
-        else
-            fallback = !collect_tile_leaves<COUNT>(sc.nodes, vw.node_rect, ws.ts, lane, root_mask, ray, ix, iy, iz, fx, fy, tr, leaves,
-                                                   nleaf, wc);
-    }
-    if (fallback)
-    {
-        // irregular ray, or a list / the warp stack outgrew its array: this tile takes the unculled path (global spill area)
-        trace_warp<STRICT, COUNT>(sc, scratch, warp_slot, lane, active, ray, leaves, stack, t_out, face_out, wc);
-        return;
-    }
-    if (!__any_sync(FULL_MASK, nleaf > 0)) return;
-    scan_tile_leaves<STRICT, COUNT>(sc, vw, ws.pairs, lane, ray, fx, fy, tr, leaves, nleaf, t_out, face_out, wc);
 }
 
 // ---- K1c: fused primary-ray render with film-space culling ----------------------------------------------------------
@@ -1119,7 +1138,7 @@ __device__ __forceinline__ void trace_tile_culled(const DevScene& sc, const DevS
 // those no triangle rectangle can touch (≈90 % of a typical frame: a pure store stream). Phase B: the slab's busy tiles
 // listed by k_view_finish are pulled one at a time from an atomic cursor (dynamic balance where the work is). A warp
 // that runs out of work in a slab publishes the number of tiles it completed there (stores fenced first) and moves on:
-// ctl[kCtlDone + s] == 2 x tiles of slab s (half-tile units) ⇔ every scanline of the slab is final — the host side's copy stream waits for
+// ctl[kCtlDone + s] == tiles of slab s ⇔ every scanline of the slab is final — the host side's copy stream waits for
 // exactly that value (stream memory operation) and copies the slab out while later slabs are still being traced.
 template <bool STRICT, bool COUNT>
 __global__ void __launch_bounds__(kBlock) k_render_culled(DevScene sc, DevCamera cm, DevPartition part, DevOut out, DevScratch scratch,
@@ -1151,28 +1170,10 @@ __global__ void __launch_bounds__(kBlock) k_render_culled(DevScene sc, DevCamera
     const bool vec_ok = (cm.W & 3) == 0 &&
                         (((size_t)out.bgrx | (size_t)out.t | (size_t)out.prim) & 15) == 0;
 
-    // Half-tile mode per slab (DevView::split_ratio16): bit s set ⇔ the busy tiles of slab s and of the later slabs together
-    // are so few per warp of the grid that single-tile latency sets the end of the kernel. The list lengths are final
-    // (k_view_finish has completed), so every warp takes the same decision.
-    unsigned int split_mask = 0u;
-    if (vw.split_ratio16 > 0)
-    {
-        unsigned long long later = 0ull;
-        for (int s = slabs.n - 1; s >= 0; --s)
-        {
-            unsigned int c = lane < kCostBuckets ? __ldg(&vw.busy_count[kCtlCount + s * kCostBuckets + lane]) : 0u;
-#pragma unroll
-            for (int off = 16; off > 0; off >>= 1) c += __shfl_xor_sync(FULL_MASK, c, off);
-            later += c;
-            if (16ull * later <= (unsigned long long)vw.split_ratio16 * n_warps) split_mask |= 1u << s;
-        }
-    }
-
   for (int slab = 0; slab < slabs.n; ++slab)
   {
     const unsigned int tile_lo = slabs.tile_begin[slab], tile_hi = min(slabs.tile_begin[slab + 1], n_tiles);
-    const bool split = (split_mask >> slab) & 1u;
-    unsigned int finished = 0;  // half-tiles of this slab completed by this warp (a whole tile counts 2)
+    unsigned int finished = 0;  // tiles of this slab completed by this warp
     // ---- phase A: sky tiles ------------------------------------------------------------------------------------------
     // One strip of 32 consecutive tiles (256×4 pixels) per step: one coalesced stamp load, then 512-byte row segments.
     if (!all_busy && vec_ok)
@@ -1194,7 +1195,7 @@ __global__ void __launch_bounds__(kBlock) k_render_culled(DevScene sc, DevCamera
             const bool sky = tcol < tiles_x && __ldg(&vw.stamps[(y0 >> 2) * vw.tiles_x + tcol]) != vw.frame_id;
             const unsigned skym = __ballot_sync(FULL_MASK, sky);
             if (!skym) continue;
-            finished += 2u * (unsigned int)__popc(skym);
+            finished += (unsigned int)__popc(skym);
             if (COUNT && lane == 0) wc.tsky += (unsigned int)__popc(skym);
 #pragma unroll
             for (int h = 0; h < 2; ++h)
@@ -1233,7 +1234,7 @@ __global__ void __launch_bounds__(kBlock) k_render_culled(DevScene sc, DevCamera
                 if (out.prim) out.prim[idx] = 0xffffffffu;
                 rays_done += cm.spp;
             }
-            finished += 2u;
+            finished += 1u;
             if (COUNT && lane == 0) wc.tsky++;
         }
     }
@@ -1245,9 +1246,7 @@ __global__ void __launch_bounds__(kBlock) k_render_culled(DevScene sc, DevCamera
         unsigned int bi = 0;
         if (lane == 0) bi = atomicAdd(&vw.busy_count[kCtlCursor + slab], 1u);
         bi = __shfl_sync(FULL_MASK, bi, 0);
-        // half-tile mode: a tile of class >= split_min_class takes two consecutive cursor values
-        const unsigned int per = (split && lane < kCostBuckets && kCostBuckets - 1 - lane >= vw.split_min_class) ? 2u : 1u;
-        const unsigned int cnt = lane < kCostBuckets ? per * __ldg(&vw.busy_count[kCtlCount + slab * kCostBuckets + (kCostBuckets - 1 - lane)]) : 0u;
+        const unsigned int cnt = lane < kCostBuckets ? __ldg(&vw.busy_count[kCtlCount + slab * kCostBuckets + (kCostBuckets - 1 - lane)]) : 0u;
         unsigned int end = cnt;   // inclusive prefix sum over the lanes
 #pragma unroll
         for (int off = 1; off < kCostBuckets; off <<= 1)
@@ -1259,20 +1258,18 @@ __global__ void __launch_bounds__(kBlock) k_render_culled(DevScene sc, DevCamera
         if (!hit) break;   // past the slab's last busy tile
         const int r = __ffs(hit) - 1;
         const unsigned int start = __shfl_sync(FULL_MASK, end - cnt, r);
-        const bool halves = __shfl_sync(FULL_MASK, per, r) == 2u;
-        const unsigned int pos = bi - start;
-        const unsigned int half = halves ? (pos & 1u) + 1u : 0u;   // half 1 = tile rows 0-1 (lanes 0-15), half 2 = rows 2-3
-        const unsigned int tile = __ldg(&vw.busy_list[(unsigned int)(kCostBuckets - 1 - r) * vw.bucket_stride + tile_lo + (halves ? pos >> 1 : pos)]);
+        const unsigned int tile = __ldg(&vw.busy_list[(unsigned int)(kCostBuckets - 1 - r) * vw.bucket_stride + tile_lo + (bi - start)]);
         unsigned long long log_t0 = 0;
         if (vw.tile_log) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(log_t0));
-        finished += half ? 1u : 2u;
+        finished += 1u;
         const unsigned int lb = tile / tiles_per_band, rem = tile - lb * tiles_per_band;
         const int trow = (int)(rem / (unsigned int)tiles_x), tcol = (int)(rem - (unsigned int)trow * (unsigned int)tiles_x);
         const int x = tcol * 8 + (lane & 7);
         const int y = ((int)lb * part.world + part.rank) * part.band_rows + trow * 4 + (lane >> 3);
-        const bool active = x < cm.W && y < cm.H && (half == 0u || (half == 1u) == (lane < 16));
+        const bool active = x < cm.W && y < cm.H;
+        const int tile_y0 = y - (lane >> 3);
         const size_t idx = (size_t)y * (size_t)cm.W + (size_t)x;
-        if (COUNT && lane == 0 && half != 2u) wc.tbusy++;
+        if (COUNT && lane == 0) wc.tbusy++;
         const float film_y = film_coord(y, cm.H);
         const float film_x = mulr(mulr(film_coord(x, cm.W), cm.h_fov), cm.aspect);
         float t = kMaxFloat;
@@ -1281,7 +1278,7 @@ __global__ void __launch_bounds__(kBlock) k_render_culled(DevScene sc, DevCamera
         if (!cm.aa)
         {
             const RayL ray = camera_ray(cm, film_x, film_y);
-            trace_tile_culled<STRICT, COUNT>(sc, scratch, vw, wscr[threadIdx.x >> 5], warp_slot, lane, active, ray, film_x, film_y, leaves, stack, t, face, wc);
+            trace_tile_flat<STRICT, COUNT>(sc, scratch, vw, wscr[threadIdx.x >> 5], warp_slot, lane, active, ray, x, y, tcol * 8, tile_y0, leaves, stack, t, face, wc);
             const bool hit = face != 0xffffffffu;
             const float er = hit ? sc.mdl[0] : sc.sky[0], eg = hit ? sc.mdl[1] : sc.sky[1], eb = hit ? sc.mdl[2] : sc.sky[2];
             for (uint32_t s = 0; s < cm.spp; ++s) { cr = addr(cr, er); cg = addr(cg, eg); cb = addr(cb, eb); }
@@ -1298,7 +1295,7 @@ __global__ void __launch_bounds__(kBlock) k_render_culled(DevScene sc, DevCamera
                 const float x_off = addr(mulr(pcg_bi(rng), cm.hpw), film_x);
                 const float y_off = addr(mulr(pcg_bi(rng), cm.hph), film_y);
                 const RayL ray = camera_ray(cm, x_off, y_off);
-                trace_tile_culled<STRICT, COUNT>(sc, scratch, vw, wscr[threadIdx.x >> 5], warp_slot, lane, active, ray, x_off, y_off, leaves, stack, t, face, wc);
+                trace_tile_flat<STRICT, COUNT>(sc, scratch, vw, wscr[threadIdx.x >> 5], warp_slot, lane, active, ray, x, y, tcol * 8, tile_y0, leaves, stack, t, face, wc);
                 const bool hit = face != 0xffffffffu;
                 if (hit) { pcg_bi(rng); pcg_bi(rng); pcg_bi(rng); }
                 cr = addr(cr, hit ? sc.mdl[0] : sc.sky[0]);
@@ -1679,7 +1676,7 @@ DevSlabs make_slabs(const DevCamera& cam, const DevPartition& part, int n_slabs,
             if (rows > part.band_rows) rows = part.band_rows;
             if (rows > 0) live += (uint32_t)(((rows + 3) >> 2) * tiles_x);
         }
-        s.live_tiles[k] = 2u * live;   // half-tile units, see kCtlDone
+        s.live_tiles[k] = live;
     }
     return s;
 }
@@ -1700,7 +1697,7 @@ cudaError_t launch_view_bounds(const DevScene& sc, const ViewParams& vp, const D
                                bool finish)
 {
     const int grid = (int)((sc.n_slots + kBlock - 1) / kBlock);
-    k_view_bounds<<<grid < 1 ? 1 : grid, kBlock, 0, stream>>>(sc, vp, view);
+    k_view_bounds<<<grid < 1 ? 1 : grid, kBlock, 0, stream>>>(sc, vp, view, part);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     if (after_reset)  // the per-slab counters of the previous frame are gone from here on
@@ -1708,9 +1705,11 @@ cudaError_t launch_view_bounds(const DevScene& sc, const ViewParams& vp, const D
         e = cudaEventRecord(after_reset, stream);
         if (e != cudaSuccess) return e;
     }
-    if (!finish) return cudaSuccess;  // rasterised frame: no tile lists, no node rectangles
-    // 296 + 296 blocks of 32 registers: all resident at once (4 per SM); one round of leaves, one of tiles for a 4K frame
-    k_view_finish<<<592, kBlock, 0, stream>>>(sc, view, cam, part, slabs, 296u);
+    if (!finish) return cudaSuccess;  // rasterised frame: no tile lists, no node ranges
+    // one warp per node + 296 compaction blocks of 32 registers: all resident at once
+    uint32_t node_blocks = (sc.n_nodes + kBlock / 32 - 1) / (kBlock / 32);
+    if (node_blocks > 296u) node_blocks = 296u;
+    k_view_nodes<<<node_blocks + 296u, kBlock, 0, stream>>>(sc, view, cam, part, slabs, node_blocks);
     return cudaGetLastError();
 }
 

@@ -48,7 +48,8 @@ struct ViewParams
     double row[3];       // Euclidean norms of the rows of minv, rounded up
     double ang;          // angular deviation bound of the float ray generation from the ideal line (radians)
     double kx;           // h_fov * aspect: film_x(x) = (-1 + 2x/W) * kx   (renderer.cpp:329)
-    double px_slack_x, px_slack_y;  // pixel slack for the tile stamps (rounding of film_x/film_y, + half a pixel with AA)
+    double px_slack_x, px_slack_y;  // pixel slack of film_rect_px: float rounding of film_x / film_y plus the jitter of an AA sample
+    double inv_kx;                  // 1 / kx
     double fx_max, fy_max;          // bounds of |film_x|, |film_y| over every ray of the frame (jitter included)
     int32_t W, H;
     int32_t tiles_x, tiles_y;      // 8x4-pixel tiles
@@ -247,34 +248,30 @@ ATRAY_HD FilmRect tri_film_rect(const ViewParams& vp, const float* a_f, const fl
     return r;
 }
 
-// Pixel range that can contain a ray whose film point lies in `r`:
-// film_x(x) = (-1 + 2(x/W))*h_fov*aspect, film_y(y) = -1 + 2(y/H) (renderer.cpp:317,329), inverted with slack.
-// Returns false when no pixel is touched; `all` is set when the range cannot be bounded.
-ATRAY_HD bool film_rect_pixels(const ViewParams& vp, const FilmRect& r, int& x0, int& x1, int& y0, int& y1, bool& all)
+// Pixels that can hold a ray whose film point lies in `r` (inclusive range; false when there is none).
+//   film_x(x) = fl(fl(fc(x)*h_fov)*aspect), fc(i) = fl(-1 + 2*fl(i/n))   (renderer.cpp:317,329; render.cu: film_coord)
+// deviates from the real F(x) = (-1 + 2x/W)*kx, kx = h_fov*aspect (exact product of the two floats), by at most 5.1u|kx|
+// (u = 2^-24: one rounding of i/n, one of the sum — both on values <= 1 — and one per product), i.e. by 2.6u*W = 1.6e-7*W
+// pixels; film_y by 1.5u*H pixels. A jittered sample (renderer.cpp:340-341: rand_bi*half_pixel_width + film_x, |rand_bi| <= 1)
+// moves the film point by at most |half_pixel_width| (1 + u) + u|film_x|. ViewParams::px_slack_x/y = 2e-6*W (+ the jitter
+// in pixels) covers both with a factor 10 to spare, so
+//        film point of a ray of pixel (x, y) lies in r   ==>   x0 <= x <= x1 and y0 <= y <= y1.
+// The inversion runs in double (relative error 1e-15). An unbounded rectangle gives the whole image.
+struct PxRect { int x0, x1, y0, y1; };
+ATRAY_HD bool film_rect_px(const ViewParams& vp, const FilmRect& r, PxRect& p)
 {
-    all = false;
+    p.x0 = 0; p.x1 = -1; p.y0 = 0; p.y1 = -1;
     if (film_rect_is_empty(r)) return false;
     const double W = (double)vp.W, H = (double)vp.H;
-    double xa = ((double)r.xlo / vp.kx + 1.0) * 0.5 * W, xb = ((double)r.xhi / vp.kx + 1.0) * 0.5 * W;
+    double xa = ((double)r.xlo * vp.inv_kx + 1.0) * 0.5 * W, xb = ((double)r.xhi * vp.inv_kx + 1.0) * 0.5 * W;
     if (xa > xb) { const double t = xa; xa = xb; xb = t; }
-    const double ya = ((double)r.ylo + 1.0) * 0.5 * H, yb = ((double)r.yhi + 1.0) * 0.5 * H;
-    if (!(xa == xa && xb == xb && ya == ya && yb == yb)) { all = true; return true; }   // NaN (kx = 0, inf/inf …)
-    xa -= vp.px_slack_x; xb += vp.px_slack_x;
-    const double yl = ya - vp.px_slack_y, yh = yb + vp.px_slack_y;
-    if (xb < 0.0 || xa > W - 1.0 || yh < 0.0 || yl > H - 1.0) return false;
-    const double cx0 = xa < 0.0 ? 0.0 : floor(xa), cx1 = xb > W - 1.0 ? W - 1.0 : ceil(xb);
-    const double cy0 = yl < 0.0 ? 0.0 : floor(yl), cy1 = yh > H - 1.0 ? H - 1.0 : ceil(yh);
-    x0 = (int)cx0; x1 = (int)cx1; y0 = (int)cy0; y1 = (int)cy1;
-    return true;
-}
-
-// Pixel-tile range (8x4 tiles) of the same pixels.
-ATRAY_HD bool film_rect_tiles(const ViewParams& vp, const FilmRect& r, int& tx0, int& tx1, int& ty0, int& ty1, bool& all)
-{
-    int x0 = 0, x1 = -1, y0 = 0, y1 = -1;
-    if (!film_rect_pixels(vp, r, x0, x1, y0, y1, all)) return false;
-    tx0 = x0 >> 3; tx1 = x1 >> 3; ty0 = y0 >> 2; ty1 = y1 >> 2;
-    return true;
+    double ya = ((double)r.ylo + 1.0) * 0.5 * H, yb = ((double)r.yhi + 1.0) * 0.5 * H;
+    if (!(xa == xa && xb == xb && ya == ya && yb == yb)) { p.x1 = vp.W - 1; p.y1 = vp.H - 1; return true; }   // NaN (inf*0 …)
+    xa -= vp.px_slack_x; xb += vp.px_slack_x; ya -= vp.px_slack_y; yb += vp.px_slack_y;
+    if (xb < 0.0 || xa > W - 1.0 || yb < 0.0 || ya > H - 1.0) return false;
+    p.x0 = xa <= 0.0 ? 0 : (int)ceil(xa); p.x1 = xb >= W - 1.0 ? vp.W - 1 : (int)floor(xb);
+    p.y0 = ya <= 0.0 ? 0 : (int)ceil(ya); p.y1 = yb >= H - 1.0 ? vp.H - 1 : (int)floor(yb);
+    return p.x0 <= p.x1 && p.y0 <= p.y1;
 }
 
 }  // namespace atray

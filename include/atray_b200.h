@@ -136,10 +136,11 @@ int atray_model_flatten(const atray_model* m, uint32_t* n_nodes, uint32_t* n_slo
  * verification without a GPU: rects = n_slots×4 {xlo,ylo,xhi,yhi} per triangle slot of the flat form, slot_leaf /
  * slot_pos = owning leaf node and position in the reference's leaf order (0xffffffff for padding slots), tile_busy =
  * one byte per 8x4-pixel tile (row-major, ceil(W/8) per row), hulls = n_slots×9 {a,b,c}×3: half-planes a*fx + b*fy <= c that
- * hold for every accepted ray of the slot. Any output may be NULL. Returns ATRAY_ESTATE when the camera cannot be used
- * for culling (the renderer then takes the unculled kernel). */
+ * hold for every accepted ray of the slot, px_ranges = n_slots×4 {x0,x1,y0,y1}: the inclusive pixel range the kernels use
+ * ({0,-1,0,-1} when no pixel can hold an accepted ray). Any output may be NULL. Returns ATRAY_ESTATE when the camera cannot
+ * be used for culling (the renderer then takes the unculled kernel). */
 int atray_debug_film_rects(const atray_model* m, const AtrayCamera* cam, float* rects, uint32_t* slot_leaf,
-                           uint32_t* slot_pos, uint8_t* tile_busy, float* hulls);
+                           uint32_t* slot_pos, uint8_t* tile_busy, float* hulls, int32_t* px_ranges);
 
 /* set_camera(Camera&, eye, facing, RenderSettings&, h_fov) — engine/renderer/camera.h:23-45 */
 int atray_camera_set(AtrayCamera* cam, int32_t width, int32_t height, int32_t anti_aliasing, uint32_t samples_per_pixel,
