@@ -128,6 +128,13 @@ _SIGS = {
     "atray_ipc_open": [_vp, _vp, C.POINTER(_vp)],
     "atray_ipc_close": [_vp, _vp],
     "atray_microbench": [_vp, C.POINTER(C.c_double), C.POINTER(C.c_double)],
+    "atray_view_share_create": [_vp, _i, _i, C.POINTER(_vp), C.POINTER(_sz)],
+    "atray_view_share_connect": [_vp, _i, _i, _vp],
+    "atray_view_share_off": [_vp],
+    "atray_view_share_rendezvous": [_vp],
+    "atray_view_share_check": [_vp],
+    "atray_ctx_enable_peer": [_vp, _vp],
+    "atray_debug_view_shards": [_vp, _i],
 }
 for _n, _a in _SIGS.items():
     getattr(_L, _n).argtypes = _a

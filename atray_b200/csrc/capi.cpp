@@ -34,6 +34,23 @@ struct atray_ctx
     DevView view{};              // per-frame film rectangles + tile stamps (k_view_bounds)
     size_t stamp_cap = 0;        // tiles the stamp buffer holds
     size_t bin_cap = 0;          // bins the bin lists hold
+    // Shared view pass (atray_view_share_*): one device block per rank holding two copies (even / odd frames) of the tables
+    // k_view_bounds fills — slot / packet / chunk ranges, tile stamps, tile costs, the all-busy flag — and a flag word per
+    // rank. Every rank computes 1/world of the slots and stores them into every peer's block over NVLink.
+    struct Share
+    {
+        bool on = false;
+        int rank = 0, world = 1;
+        char* block = nullptr;
+        size_t bytes = 0;
+        char* peer[kMaxPeers] = {};
+        size_t off_tri = 0, off_pkt = 0, off_chunk = 0, off_stamps = 0, off_cost = 0, off_all = 0, buf_stride = 0, off_flags = 0;
+        size_t tiles_cap = 0;
+        uint32_t n_slots = 0;
+        uint32_t seq = 0;        // frames rendered through the shared pass (the stamp value and the flag value of a frame)
+        uint32_t rdv = 0;        // rendezvous count (atray_view_share_rendezvous)
+        int debug_shards = 0;    // verification aid: run the pass as this many shard launches on this GPU alone
+    } share;
     uint2* d_node_pk = nullptr;  // FlatScene::node_pk
     uint32_t frame_seq = 0;      // stamp value of the last frame (0 = buffer freshly cleared)
     // film-space rasteriser (raster.cuh): scene tables, per-frame tables / keys / lists
@@ -340,6 +357,8 @@ static void free_scene(atray_ctx* c)
     c->scratch = DevScratch{};
     c->scene = DevScene{};
     c->has_scene = false;
+    cudaFree(c->share.block);   // sized for the scene: a new scene needs a new atray_view_share_create
+    c->share = atray_ctx::Share{};
 }
 
 void atray_ctx_destroy(atray_ctx* c)
@@ -352,6 +371,7 @@ void atray_ctx_destroy(atray_ctx* c)
     cudaFree(c->view.stamps); cudaFree(c->view.all_flag); cudaFree(c->view.busy_list); cudaFree(c->view.busy_count);
     cudaFree(c->view.tile_cost); cudaFree(c->view.tile_log);
     cudaFree(c->view.bin_cnt); cudaFree(c->view.bin_leaf); cudaFree(c->view.bin_inner);
+    cudaFree(c->share.block);
     cudaFree(c->rs.tabx); cudaFree(c->rs.taby); cudaFree(c->rs.key1); cudaFree(c->rs.key2); cudaFree(c->rs.hit_a);
     cudaFree(c->rs.hit_pos); cudaFree(c->rs.ctl);
     cudaFree(c->d_bgrx); cudaFree(c->d_t); cudaFree(c->d_prim);
@@ -779,9 +799,80 @@ static int enqueue_render(atray_ctx* c, const AtrayCamera* cam, const AtrayRende
     {
         // the film rectangles depend on the camera: recomputed every frame, inside the timed region
         const DevSlabs slabs = make_slabs(to_dev(cam), p, want_slabs, want_slabs > 1 ? c->slab_w : nullptr);
-        CU(launch_view_bounds(c->scene, vp, c->view, to_dev(cam), p, slabs, c->stream, want_slabs > 1 ? c->ev_reset : nullptr));
+        DevView vw = c->view;
+        atray_ctx::Share& sh = c->share;
+        const uint32_t n_blocks = (c->scene.n_slots + 255u) / 256u;
+        const size_t tiles = size_t(vp.tiles_x) * size_t(vp.tiles_y);
+        const bool shared = sh.on && o->part.world == sh.world && o->part.rank == sh.rank && sh.world > 1 && tiles <= sh.tiles_cap &&
+                            sh.n_slots == c->scene.n_slots;
+        if (shared)
+        {
+            // every rank computes blocks [lo, hi) of the pass and stores them into all ranks' tables of this frame's parity;
+            // then a flag per rank, and this rank's stream waits for the flags of the others before k_view_nodes reads the tables
+            const uint32_t seq = ++sh.seq;
+            const size_t bo = size_t(seq & 1u) * sh.buf_stride;
+            vp.frame_id = seq;
+            vw.frame_id = seq;
+            ViewPeers pe{};
+            pe.n = sh.world;
+            pe.self = sh.rank;
+            if (const char* env = std::getenv("ATRAY_SHARE_SKIP")) pe.debug_skip = uint32_t(std::atoi(env));
+            pe.block_lo = uint32_t(uint64_t(n_blocks) * uint64_t(sh.rank) / uint64_t(sh.world));
+            pe.block_hi = uint32_t(uint64_t(n_blocks) * uint64_t(sh.rank + 1) / uint64_t(sh.world));
+            for (int q = 0; q < sh.world; ++q)
+            {
+                char* b = sh.peer[q] + bo;
+                pe.tri_px[q] = reinterpret_cast<uint2*>(b + sh.off_tri); pe.pkt_px[q] = reinterpret_cast<uint2*>(b + sh.off_pkt);
+                pe.chunk_px[q] = reinterpret_cast<uint2*>(b + sh.off_chunk); pe.stamps[q] = reinterpret_cast<uint32_t*>(b + sh.off_stamps);
+                pe.tile_cost[q] = reinterpret_cast<uint32_t*>(b + sh.off_cost); pe.all_flag[q] = reinterpret_cast<uint32_t*>(b + sh.off_all);
+            }
+            vw.tri_px = pe.tri_px[sh.rank]; vw.pkt_px = pe.pkt_px[sh.rank]; vw.chunk_px = pe.chunk_px[sh.rank];
+            vw.stamps = pe.stamps[sh.rank]; vw.tile_cost = pe.tile_cost[sh.rank]; vw.all_flag = pe.all_flag[sh.rank];
+            vw.tri_rect = nullptr;
+            struct Arg { atray_ctx* c; uint32_t seq; std::string err; } arg{c, seq, std::string()};
+            ViewBetween bt;
+            bt.arg = &arg;
+            bt.fn = [](void* a, cudaStream_t st) -> cudaError_t {
+                Arg* g = static_cast<Arg*>(a);
+                atray_ctx::Share& s2 = g->c->share;
+                uint32_t* flags[kMaxPeers];
+                for (int q = 0; q < s2.world; ++q) flags[q] = reinterpret_cast<uint32_t*>(s2.peer[q] + s2.off_flags);
+                cudaError_t e = launch_view_signal(flags, s2.world, s2.rank, g->seq, st);
+                if (e != cudaSuccess) { g->err = std::string("view pass signal kernel: ") + cudaGetErrorString(e); return e; }
+                // the peers' flags land in this GPU's flag row; a one-warp kernel on the stream waits for them (bounded: 2 s)
+                uint32_t* row = reinterpret_cast<uint32_t*>(s2.block + s2.off_flags);
+                e = launch_view_wait(row, s2.world, s2.rank, g->seq, 2000000000ull, row + 32, st);
+                if (e != cudaSuccess) { g->err = std::string("view pass wait kernel: ") + cudaGetErrorString(e); return e; }
+                return cudaSuccess;
+            };
+            {
+                cudaError_t e = launch_view_bounds(c->scene, vp, vw, to_dev(cam), p, slabs, c->stream, want_slabs > 1 ? c->ev_reset : nullptr, true, &pe, &bt);
+                if (e != cudaSuccess) return arg.err.empty() ? cuda_fail(e, "shared view pass") : fail(ATRAY_ECUDA, arg.err);
+            }
+        }
+        else if (sh.debug_shards > 1)
+        {
+            // verification aid: the same pass as `debug_shards` shard launches on this GPU alone (every "peer" is this GPU)
+            ViewPeers pe{};
+            pe.n = sh.debug_shards > o->part.world ? sh.debug_shards : o->part.world;
+            if (pe.n > kMaxPeers) pe.n = kMaxPeers;
+            for (int q = 0; q < pe.n; ++q)
+            {
+                pe.tri_px[q] = vw.tri_px; pe.pkt_px[q] = vw.pkt_px; pe.chunk_px[q] = vw.chunk_px; pe.stamps[q] = vw.stamps;
+                pe.tile_cost[q] = vw.tile_cost; pe.all_flag[q] = vw.all_flag;
+            }
+            for (int sdx = 0; sdx < sh.debug_shards; ++sdx)
+            {
+                pe.block_lo = uint32_t(uint64_t(n_blocks) * uint64_t(sdx) / uint64_t(sh.debug_shards));
+                pe.block_hi = uint32_t(uint64_t(n_blocks) * uint64_t(sdx + 1) / uint64_t(sh.debug_shards));
+                const bool last = sdx == sh.debug_shards - 1;
+                CU(launch_view_bounds(c->scene, vp, vw, to_dev(cam), p, slabs, c->stream, last && want_slabs > 1 ? c->ev_reset : nullptr, last, &pe));
+            }
+        }
+        else
+            CU(launch_view_bounds(c->scene, vp, vw, to_dev(cam), p, slabs, c->stream, want_slabs > 1 ? c->ev_reset : nullptr));
         CU(cudaEventRecord(c->ev_kr, c->stream));
-        CU(launch_render_culled(c->scene, to_dev(cam), p, out, c->scratch, c->view, slabs, ctr, o->fp_mode == ATRAY_FP_FAST,
+        CU(launch_render_culled(c->scene, to_dev(cam), p, out, c->scratch, vw, slabs, ctr, o->fp_mode == ATRAY_FP_FAST,
                                 o->jitter_seed, c->cfg, c->stream));
         if (slabs_out) *slabs_out = slabs;
     }
@@ -1259,6 +1350,118 @@ int atray_ipc_close(atray_ctx* c, void* p)
     if (!c) return fail(ATRAY_EINVAL, "null context");
     CU(cudaSetDevice(c->device));
     CU(cudaIpcCloseMemHandle(p));
+    return ATRAY_OK;
+}
+
+// ---- shared view pass (multi-GPU) ------------------------------------------------------------------------------------
+int atray_view_share_create(atray_ctx* c, int32_t max_width, int32_t max_height, void** block, size_t* bytes)
+{
+    if (!c || !block || max_width <= 0 || max_height <= 0) return fail(ATRAY_EINVAL, "bad argument");
+    if (!c->has_scene) return fail(ATRAY_ESTATE, "view_share_create before scene_upload");
+    if (c->in_flight) return fail(ATRAY_ESTATE, "render in flight");
+    CU(cudaSetDevice(c->device));
+    CU(cudaStreamSynchronize(c->stream));
+    atray_ctx::Share& sh = c->share;
+    cudaFree(sh.block);
+    sh = atray_ctx::Share{};
+    auto up = [](size_t v) { return (v + 255) & ~size_t(255); };
+    const size_t tiles = size_t((max_width + 7) >> 3) * size_t((max_height + 3) >> 2);
+    const size_t ns = c->scene.n_slots;
+    size_t at = 0;
+    sh.off_tri = at; at += up((ns ? ns : 1) * sizeof(uint2));
+    sh.off_pkt = at; at += up((ns / 8 + 1) * sizeof(uint2));
+    sh.off_chunk = at; at += up((ns / 256 + 1) * sizeof(uint2));
+    sh.off_stamps = at; at += up(tiles * sizeof(uint32_t));
+    sh.off_cost = at; at += up(tiles * sizeof(uint32_t));
+    sh.off_all = at; at += 256;
+    sh.buf_stride = at;
+    sh.off_flags = 2 * at;
+    sh.bytes = 2 * at + 256;
+    sh.tiles_cap = tiles;
+    sh.n_slots = c->scene.n_slots;
+    CU(cudaMalloc(&sh.block, sh.bytes));
+    CU(cudaMemset(sh.block, 0, sh.bytes));
+    *block = sh.block;
+    if (bytes) *bytes = sh.bytes;
+    return ATRAY_OK;
+}
+
+int atray_view_share_connect(atray_ctx* c, int32_t rank, int32_t world, void* const* peer_blocks)
+{
+    if (!c || !peer_blocks) return fail(ATRAY_EINVAL, "null argument");
+    if (world < 1 || world > kMaxPeers || rank < 0 || rank >= world) return fail(ATRAY_EINVAL, "bad rank / world (at most 8 ranks)");
+    if (!c->share.block) return fail(ATRAY_ESTATE, "view_share_connect before view_share_create");
+    if (c->in_flight) return fail(ATRAY_ESTATE, "render in flight");
+    for (int q = 0; q < world; ++q)
+    {
+        if (!peer_blocks[q]) return fail(ATRAY_EINVAL, "null peer block");
+        c->share.peer[q] = static_cast<char*>(peer_blocks[q]);
+    }
+    if (c->share.peer[rank] != c->share.block) return fail(ATRAY_EINVAL, "peer_blocks[rank] must be this context's own block");
+    c->share.rank = rank;
+    c->share.world = world;
+    c->share.seq = 0;
+    c->share.rdv = 0;
+    c->share.on = world > 1;
+    return ATRAY_OK;
+}
+
+int atray_view_share_rendezvous(atray_ctx* c)
+{
+    if (!c) return fail(ATRAY_EINVAL, "null context");
+    atray_ctx::Share& sh = c->share;
+    if (!sh.on) return ATRAY_OK;
+    CU(cudaSetDevice(c->device));
+    // second flag row of the block: "rank r has reached rendezvous k" — same signal / wait pair as the view pass
+    const uint32_t k = ++sh.rdv;
+    uint32_t* flags[kMaxPeers];
+    for (int q = 0; q < sh.world; ++q) flags[q] = reinterpret_cast<uint32_t*>(sh.peer[q] + sh.off_flags) + 16;
+    CU(launch_view_signal(flags, sh.world, sh.rank, k, c->stream));
+    uint32_t* row = reinterpret_cast<uint32_t*>(sh.block + sh.off_flags);
+    CU(launch_view_wait(row + 16, sh.world, sh.rank, k, 2000000000ull, row + 33, c->stream));
+    return ATRAY_OK;
+}
+
+int atray_view_share_check(atray_ctx* c)
+{
+    if (!c) return fail(ATRAY_EINVAL, "null context");
+    atray_ctx::Share& sh = c->share;
+    if (!sh.block) return ATRAY_OK;
+    CU(cudaSetDevice(c->device));
+    CU(cudaStreamSynchronize(c->stream));
+    uint32_t w[2] = {0u, 0u};
+    CU(cudaMemcpy(w, reinterpret_cast<uint32_t*>(sh.block + sh.off_flags) + 32, sizeof w, cudaMemcpyDeviceToHost));
+    if (w[0]) return fail(ATRAY_ECUDA, "shared view pass: a peer did not signal frame " + std::to_string(w[0]) + " within 2 s (the frame is not valid)");
+    if (w[1]) return fail(ATRAY_ECUDA, "shared view pass: a peer did not reach rendezvous " + std::to_string(w[1]) + " within 2 s");
+    return ATRAY_OK;
+}
+
+int atray_view_share_off(atray_ctx* c)
+{
+    if (!c) return fail(ATRAY_EINVAL, "null context");
+    if (c->in_flight) return fail(ATRAY_ESTATE, "render in flight");
+    c->share.on = false;
+    return ATRAY_OK;
+}
+
+int atray_ctx_enable_peer(atray_ctx* c, atray_ctx* other)
+{
+    if (!c || !other) return fail(ATRAY_EINVAL, "null context");
+    if (c->device == other->device) return ATRAY_OK;
+    int can = 0;
+    CU(cudaDeviceCanAccessPeer(&can, c->device, other->device));
+    if (!can) return fail(ATRAY_ECUDA, "no peer access between the two devices");
+    CU(cudaSetDevice(c->device));
+    cudaError_t e = cudaDeviceEnablePeerAccess(other->device, 0);
+    if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) return cuda_fail(e, "cudaDeviceEnablePeerAccess");
+    cudaGetLastError();
+    return ATRAY_OK;
+}
+
+int atray_debug_view_shards(atray_ctx* c, int32_t shards)
+{
+    if (!c || shards < 0 || shards > 64) return fail(ATRAY_EINVAL, "bad argument");
+    c->share.debug_shards = shards;
     return ATRAY_OK;
 }
 

@@ -95,6 +95,25 @@ struct DevView
 };
 static constexpr int kBinShiftX = 6, kBinShiftY = 5;   // 64 x 32 pixels = 8 x 8 tiles
 
+// Where k_view_bounds stores what it computes. One GPU: n = 1 and the tables of `view`. N GPUs that share the per-frame view
+// pass (atray_view_share_*): every rank computes the pixel ranges of 1/N of the triangle slots — blocks [block_lo, block_hi)
+// of 256 slots — and stores them into the tables of ALL ranks through peer pointers (NVLink); a tile's stamp and cost go
+// to the one rank that owns the tile's band. The pass is then followed by a flag per rank that the peers' streams wait on.
+static constexpr int kMaxPeers = 8;
+struct ViewPeers
+{
+    int32_t n;                        // ranks the results go to (1 = only this GPU)
+    uint32_t block_lo, block_hi;      // this rank's share of the k_view_bounds blocks
+    uint32_t debug_skip;              // verification aid (ATRAY_SHARE_SKIP): 1 no remote cost, 2 no remote stamps, 4 no remote ranges
+    int32_t self;                     // this rank's index in the tables
+    uint2* tri_px[kMaxPeers];
+    uint2* pkt_px[kMaxPeers];
+    uint2* chunk_px[kMaxPeers];
+    uint32_t* stamps[kMaxPeers];
+    uint32_t* tile_cost[kMaxPeers];
+    uint32_t* all_flag[kMaxPeers];
+};
+
 // Per-frame state of the film-space rasteriser (render.cu: k_film_tables, k_raster, k_raster_big, k_hit_filter, k_resolve).
 // key1/key2 hold one 64-bit word per pixel each and are all-ones between frames (k_resolve restores what it consumes):
 //   key1 = (entry distance bits << 32) | leaf_seq   minimum over the (leaf, triangle) pairs the reference would accept for the
@@ -152,9 +171,17 @@ cudaError_t launch_render(const DevScene& sc, const DevCamera& cam, const DevPar
 // culled frame = k_view_bounds (per-frame film rectangles + tile stamps) followed by k_render_culled
 // k_view_bounds (per-slot pixel ranges, packet / chunk unions, tile stamps) + k_view_nodes (node unions, bins, compact list
 // of this rank's busy tiles)
+// `peers` = null: everything into `view` (one GPU, or a rank that computes the whole pass itself). `between` (optional) runs
+// after k_view_bounds and before k_view_nodes on the stream: the cross-rank flag exchange of a shared pass.
+struct ViewBetween { cudaError_t (*fn)(void*, cudaStream_t); void* arg; };
 cudaError_t launch_view_bounds(const DevScene& sc, const ViewParams& vp, const DevView& view, const DevCamera& cam,
                                const DevPartition& part, const DevSlabs& slabs, cudaStream_t stream, cudaEvent_t after_reset,
-                               bool finish = true);
+                               bool finish = true, const ViewPeers* peers = nullptr, const ViewBetween* between = nullptr);
+// one warp: flags[p][rank] = seq for every peer p, after a system-wide fence (the peers' streams wait for the value)
+cudaError_t launch_view_signal(uint32_t* const* peer_flags, int n, int rank, uint32_t seq, cudaStream_t stream);
+// one warp: waits (on the stream) until every other rank's flag in my_flags has reached seq; *timed_out = seq after timeout_ns
+cudaError_t launch_view_wait(const uint32_t* my_flags, int n, int rank, uint32_t seq, unsigned long long timeout_ns, uint32_t* timed_out,
+                             cudaStream_t stream);
 // rasterised frame (AA off, root is an inner node): k_film_tables → [k_view_bounds by the caller] → k_raster → k_raster_big →
 // k_hit_filter → k_resolve (sky fill + per-pixel decode + exact per-ray fallback, slab by slab like the culled kernel)
 cudaError_t launch_film_tables(const DevCamera& cam, const DevRaster& rs, cudaStream_t stream);

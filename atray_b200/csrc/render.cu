@@ -19,6 +19,9 @@
 // reference's operation order → bit-identical t and ids. FAST mode lets the triangle test contract into FMA.
 #include "device_types.h"
 
+#include <cstdio>
+#include <cstdlib>
+
 namespace atray {
 
 #define FULL_MASK 0xffffffffu
@@ -27,6 +30,9 @@ static constexpr float kMaxFloat = 3.402823466e+38F;  // PL_base_defs.h:70
 static constexpr int kLeafCap = 48;                   // per-lane leaf list (local memory); overflow → per-warp spill area
 static constexpr int kStackCap = 48;                  // per-lane inner-node stack
 static constexpr int kBlock = 256;                    // 8 warps per CTA
+#ifndef ATRAY_RENDER_MIN_BLOCKS
+#define ATRAY_RENDER_MIN_BLOCKS 3                     // resident CTAs per SM the culled render kernel is compiled for (register cap)
+#endif
 
 struct RayL { float ox, oy, oz, dx, dy, dz; };
 
@@ -526,15 +532,28 @@ __device__ __forceinline__ bool owns_bin_row(const DevPartition& part, int by, i
 }
 
 // One thread per triangle slot: film rectangle (FP64, view_bounds.h) -> pixel range, unions per packet (8 lanes) and per
-// chunk of 32 packets (the block), tile stamps and tile costs for the tiles of this rank's bands.
-__global__ void __launch_bounds__(kBlock, 4) k_view_bounds(DevScene sc, ViewParams vp, DevView view, DevPartition part)
+// chunk of 32 packets (the block), tile stamps and tile costs. One GPU (pe.n == 1): results go to this GPU's tables and only
+// the tiles of this rank's bands are stamped. Shared pass (pe.n == world): this grid covers the rank's share of the slots
+// and stores every result into the tables of all ranks — plain stores through peer pointers, the fused compute + NVLink
+// exchange of the pass — while the stamp and cost of a tile go to the rank that owns its band.
+__global__ void __launch_bounds__(kBlock, 4) k_view_bounds(DevScene sc, ViewParams vp, DevView view, DevPartition part, ViewPeers pe)
 {
     const int lane = threadIdx.x & 31;
-    const uint32_t slot = blockIdx.x * kBlock + threadIdx.x;
-    for (uint32_t i = slot; i < (uint32_t)kCtlTicket; i += gridDim.x * kBlock) view.busy_count[i] = 0u;  // list lengths, cursors, finished-tile counters
-    for (uint32_t i = slot; i < 2u * (uint32_t)(view.bins_x * view.bins_y); i += gridDim.x * kBlock) view.bin_cnt[i] = 0u;
-    const bool in_range = slot < sc.n_slots;
+    const uint32_t tid = blockIdx.x * kBlock + threadIdx.x;
+    for (uint32_t i = tid; i < (uint32_t)kCtlTicket; i += gridDim.x * kBlock) view.busy_count[i] = 0u;  // list lengths, cursors, finished-tile counters
+    for (uint32_t i = tid; i < 2u * (uint32_t)(view.bins_x * view.bins_y); i += gridDim.x * kBlock) view.bin_cnt[i] = 0u;
+    const uint32_t chunk = pe.block_lo + blockIdx.x;
+    const uint32_t slot = chunk * kBlock + threadIdx.x;
+    const bool shared = pe.n > 1;
+    const bool in_range = slot < sc.n_slots && chunk < pe.block_hi;   // (an empty share still launches one block for the resets above)
     const int n_tiles = vp.tiles_x * vp.tiles_y;
+    // owner of tile row ty in a shared pass (band b -> rank b % world); -1: not stamped (another rank's row, one-GPU pass)
+    auto owner = [&](int ty) -> int {
+        if (part.world <= 1) return 0;
+        const int o = ((ty * 4) / part.band_rows) % part.world;
+        return shared ? o : (o == part.rank ? 0 : -1);
+    };
+    const bool skip_cost = pe.debug_skip & 1u, skip_stamps = pe.debug_skip & 2u, skip_ranges = pe.debug_skip & 4u;
     uint2 px = px_empty();
     int tx0 = 0, tx1 = -1, ty0 = 0, ty1 = -1;
     bool big = false;
@@ -553,19 +572,26 @@ __global__ void __launch_bounds__(kBlock, 4) k_view_bounds(DevScene sc, ViewPara
                 px = px_pack(p);
                 tx0 = p.x0 >> 3; tx1 = p.x1 >> 3; ty0 = p.y0 >> 2; ty1 = p.y1 >> 2;
                 const int nt = (tx1 - tx0 + 1) * (ty1 - ty0 + 1);
-                if (2 * nt >= n_tiles) { *view.all_flag = vp.frame_id; tx1 = tx0 - 1; }
+                if (2 * nt >= n_tiles)
+                {
+                    for (int q = 0; q < pe.n; ++q) *pe.all_flag[q] = vp.frame_id;
+                    tx1 = tx0 - 1;
+                }
                 else if (nt > 48) big = true;
                 else
                 {
                     for (int ty = ty0; ty <= ty1; ++ty)
                     {
-                        if (!owns_tile_row(part, ty)) continue;
-                        for (int tx = tx0; tx <= tx1; ++tx) view.stamps[ty * vp.tiles_x + tx] = vp.frame_id;
+                        const int o = owner(ty);
+                        if (o < 0 || (skip_stamps && o != pe.self)) continue;
+                        uint32_t* st = pe.stamps[o] + ty * vp.tiles_x;
+                        for (int tx = tx0; tx <= tx1; ++tx) st[tx] = vp.frame_id;
                     }
                 }
             }
         }
-        view.tri_px[slot] = px;
+        for (int q = 0; q < pe.n; ++q)
+            if (!skip_ranges || q == pe.self) pe.tri_px[q][slot] = px;
         if (view.tri_rect) view.tri_rect[slot] = r;
     }
     // large ranges: the whole warp stamps the tiles of one triangle at a time
@@ -579,13 +605,15 @@ __global__ void __launch_bounds__(kBlock, 4) k_view_bounds(DevScene sc, ViewPara
         const int w = ax1 - ax0 + 1, n = w * (ay1 - ay0 + 1);
         for (int i = lane; i < n; i += 32)
         {
-            const int ty = ay0 + i / w;
-            if (owns_tile_row(part, ty)) view.stamps[ty * vp.tiles_x + ax0 + i % w] = vp.frame_id;
+            const int ty = ay0 + i / w, o = owner(ty);
+            if (o >= 0 && !(skip_stamps && o != pe.self)) pe.stamps[o][ty * vp.tiles_x + ax0 + i % w] = vp.frame_id;
         }
     }
     uint2 p = px;
     p = px_union_xor(p, 4); p = px_union_xor(p, 2); p = px_union_xor(p, 1);
-    if (in_range && (lane & 7) == 0) view.pkt_px[slot >> 3] = p;
+    if (in_range && (lane & 7) == 0)
+        for (int q = 0; q < pe.n; ++q)
+            if (!skip_ranges || q == pe.self) pe.pkt_px[q][slot >> 3] = p;
     // tile cost = packet ranges touching the tile (what the leaf scan of the render kernel tests against the tile); the
     // packet's 8 lanes share the tiles of its range (every lane holds the same p after the butterfly)
     if (!px_is_empty(p))
@@ -595,8 +623,8 @@ __global__ void __launch_bounds__(kBlock, 4) k_view_bounds(DevScene sc, ViewPara
         if (n <= 64)
             for (int i = lane & 7; i < n; i += 8)
             {
-                const int ty = qy0 + i / w;
-                if (owns_tile_row(part, ty)) atomicAdd(&view.tile_cost[ty * vp.tiles_x + qx0 + i % w], 1u);
+                const int ty = qy0 + i / w, o = owner(ty);
+                if (o >= 0 && !(skip_cost && o != pe.self)) atomicAdd(&pe.tile_cost[o][ty * vp.tiles_x + qx0 + i % w], 1u);
             }
     }
     // chunk = the 32 packets of this block
@@ -609,7 +637,9 @@ __global__ void __launch_bounds__(kBlock, 4) k_view_bounds(DevScene sc, ViewPara
         uint2 c = s_px[0];
 #pragma unroll
         for (int w = 1; w < kBlock / 32; ++w) c = px_union(c, s_px[w]);
-        view.chunk_px[blockIdx.x] = c;
+        if (chunk < pe.block_hi || pe.block_hi == 0u)
+            for (int q = 0; q < pe.n; ++q)
+                if (!skip_ranges || q == pe.self) pe.chunk_px[q][chunk] = c;
     }
 }
 
@@ -647,7 +677,8 @@ __global__ void __launch_bounds__(kBlock) k_view_nodes(DevScene sc, DevView view
             if (hb < pe)
             {
                 const uint32_t ce = pe >> 5;
-                for (uint32_t c = (hb >> 5) + lane; c < ce; c += 32) acc = px_union(acc, view.chunk_px[c]);
+#pragma unroll 4
+                for (uint32_t c = (hb >> 5) + lane; c < ce; c += 32) acc = px_union(acc, view.chunk_px[c]);   // (root: ~30 rounds, 4 in flight)
                 uint32_t tb = ce << 5;
                 if (tb < hb) tb = hb;
                 for (uint32_t k = tb + lane; k < pe; k += 32) acc = px_union(acc, view.pkt_px[k]);
@@ -1141,7 +1172,7 @@ __device__ __forceinline__ void trace_tile_flat(const DevScene& sc, const DevScr
 // ctl[kCtlDone + s] == tiles of slab s ⇔ every scanline of the slab is final — the host side's copy stream waits for
 // exactly that value (stream memory operation) and copies the slab out while later slabs are still being traced.
 template <bool STRICT, bool COUNT>
-__global__ void __launch_bounds__(kBlock) k_render_culled(DevScene sc, DevCamera cm, DevPartition part, DevOut out, DevScratch scratch,
+__global__ void __launch_bounds__(kBlock, ATRAY_RENDER_MIN_BLOCKS) k_render_culled(DevScene sc, DevCamera cm, DevPartition part, DevOut out, DevScratch scratch,
                                                           DevView vw, DevSlabs slabs, DevCounters* counters,
                                                           unsigned long long jitter_seed)
 {
@@ -1692,25 +1723,88 @@ cudaError_t launch_slabs_final(const DevView& view, const DevSlabs& slabs, cudaS
     return cudaGetLastError();
 }
 
+struct SignalArgs { uint32_t* flags[kMaxPeers]; };
+__global__ void k_view_signal_v(SignalArgs a, int n, int rank, uint32_t seq)
+{
+    if ((int)threadIdx.x < n)
+    {
+        __threadfence_system();
+        *((volatile uint32_t*)(a.flags[threadIdx.x] + rank)) = seq;
+    }
+}
+cudaError_t launch_view_signal(uint32_t* const* peer_flags, int n, int rank, uint32_t seq, cudaStream_t stream)
+{
+    SignalArgs a{};
+    for (int i = 0; i < n && i < kMaxPeers; ++i) a.flags[i] = peer_flags[i];
+    k_view_signal_v<<<1, 32, 0, stream>>>(a, n, rank, seq);
+    return cudaGetLastError();
+}
+// One warp: lane q waits until rank q's flag in THIS GPU's flag row has reached `seq` (written by the peer GPU's
+// k_view_signal_v over NVLink). The ranks run on different GPUs, so the wait never depends on a kernel of the same GPU. A
+// peer that never signals (a dead rank) ends the wait after `timeout_ns` with *timed_out = seq instead of hanging the GPU.
+__global__ void k_view_wait(const uint32_t* my_flags, int n, int rank, uint32_t seq, unsigned long long timeout_ns, uint32_t* timed_out)
+{
+    const int q = threadIdx.x;
+    if (q >= n || q == rank) return;
+    unsigned long long t0;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    const volatile uint32_t* f = my_flags + q;
+    for (;;)
+    {
+        if ((int32_t)(*f - seq) >= 0) break;
+        unsigned long long t1;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+        if (t1 - t0 > timeout_ns) { *timed_out = seq; break; }
+        __nanosleep(100);
+    }
+    __threadfence_system();
+}
+cudaError_t launch_view_wait(const uint32_t* my_flags, int n, int rank, uint32_t seq, unsigned long long timeout_ns, uint32_t* timed_out,
+                             cudaStream_t stream)
+{
+    k_view_wait<<<1, 32, 0, stream>>>(my_flags, n, rank, seq, timeout_ns, timed_out);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_view_bounds(const DevScene& sc, const ViewParams& vp, const DevView& view, const DevCamera& cam,
                                const DevPartition& part, const DevSlabs& slabs, cudaStream_t stream, cudaEvent_t after_reset,
-                               bool finish)
+                               bool finish, const ViewPeers* peers, const ViewBetween* between)
 {
-    const int grid = (int)((sc.n_slots + kBlock - 1) / kBlock);
-    k_view_bounds<<<grid < 1 ? 1 : grid, kBlock, 0, stream>>>(sc, vp, view, part);
+    ViewPeers pe{};
+    if (peers) pe = *peers;
+    else
+    {
+        pe.n = 1;
+        pe.block_lo = 0;
+        pe.block_hi = (sc.n_slots + kBlock - 1) / kBlock;
+        pe.tri_px[0] = view.tri_px; pe.pkt_px[0] = view.pkt_px; pe.chunk_px[0] = view.chunk_px;
+        pe.stamps[0] = view.stamps; pe.tile_cost[0] = view.tile_cost; pe.all_flag[0] = view.all_flag;
+    }
+    const int grid = (int)(pe.block_hi - pe.block_lo);
+    k_view_bounds<<<grid < 1 ? 1 : grid, kBlock, 0, stream>>>(sc, vp, view, part, pe);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;
+    static const bool sync_debug = std::getenv("ATRAY_SYNC_DEBUG") != nullptr;   // verification aid: find the faulting launch
+    if (sync_debug && (e = cudaStreamSynchronize(stream)) != cudaSuccess) { std::fprintf(stderr, "k_view_bounds: %s\n", cudaGetErrorString(e)); return e; }
     if (after_reset)  // the per-slab counters of the previous frame are gone from here on
     {
         e = cudaEventRecord(after_reset, stream);
         if (e != cudaSuccess) return e;
+    }
+    if (between)
+    {
+        e = between->fn(between->arg, stream);
+        if (e != cudaSuccess) return e;
+        if (sync_debug && (e = cudaStreamSynchronize(stream)) != cudaSuccess) { std::fprintf(stderr, "view pass signal/wait: %s\n", cudaGetErrorString(e)); return e; }
     }
     if (!finish) return cudaSuccess;  // rasterised frame: no tile lists, no node ranges
     // one warp per node + 296 compaction blocks of 32 registers: all resident at once
     uint32_t node_blocks = (sc.n_nodes + kBlock / 32 - 1) / (kBlock / 32);
     if (node_blocks > 296u) node_blocks = 296u;
     k_view_nodes<<<node_blocks + 296u, kBlock, 0, stream>>>(sc, view, cam, part, slabs, node_blocks);
-    return cudaGetLastError();
+    e = cudaGetLastError();
+    if (e == cudaSuccess && sync_debug && (e = cudaStreamSynchronize(stream)) != cudaSuccess) std::fprintf(stderr, "k_view_nodes: %s\n", cudaGetErrorString(e));
+    return e;
 }
 
 // The culled kernel is persistent: its grid is exactly what is resident at once (a slab completes only when every warp

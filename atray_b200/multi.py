@@ -74,6 +74,48 @@ class FrameGather:
         self._opened, self._owned = [], []
 
 
+class ViewShare:
+    """Shared per-frame view pass (atray_view_share_*): every rank computes the pixel ranges of 1/world of the triangle
+    slots and stores them into all ranks' tables over NVLink. One process per GPU: the blocks travel as CUDA-IPC handles
+    (all_gather_object over the control-plane backend); `connect_local` wires several contexts of ONE process instead."""
+
+    def __init__(self, ctx, dist, rank, world, width, height):
+        self.ctx, self.world, self._opened = ctx, world, []
+        if world <= 1:
+            return
+        block, _ = ctx.view_share_create(width, height)
+        handles = [None] * world
+        dist.all_gather_object(handles, ctx.ipc_export(block))
+        peers = []
+        for r in range(world):
+            if r == rank:
+                peers.append(block)
+            else:
+                ptr = ctx.ipc_open(handles[r])
+                self._opened.append(ptr)
+                peers.append(ptr)
+        ctx.view_share_connect(rank, world, peers)
+
+    @staticmethod
+    def connect_local(ctxs, width, height):
+        """Contexts of one process, one per GPU (rank r = ctxs[r]): peer access both ways, blocks handed over directly."""
+        world = len(ctxs)
+        for a in ctxs:
+            for b in ctxs:
+                if a is not b:
+                    a.enable_peer(b)
+        blocks = [c.view_share_create(width, height)[0] for c in ctxs]
+        for r, c in enumerate(ctxs):
+            c.view_share_connect(r, world, blocks)
+
+    def close(self):
+        if self.world > 1:
+            self.ctx.view_share_off()
+        for p in self._opened:
+            self.ctx.ipc_close(p)
+        self._opened = []
+
+
 class SharedBitmap:
     """The host bitmap (Texture.bmb.buffer_memory) of a multi-process job: a file in /dev/shm mapped by every rank and
     page-locked in each process (atray_host_register). With a partition, atray_render_begin writes exactly the rank's

@@ -181,6 +181,32 @@ class Context:
     def ipc_close(self, p):
         _ck(_L.atray_ipc_close(self.h, p))
 
+    # -- shared view pass (multi-GPU) ---------------------------------------------------------------------------------
+    def view_share_create(self, max_width, max_height):
+        """Allocates this context's block of the shared view pass; returns (device pointer, bytes)."""
+        p, n = _vp(), C.c_size_t(0)
+        _ck(_L.atray_view_share_create(self.h, max_width, max_height, C.byref(p), C.byref(n)))
+        return p.value, n.value
+
+    def view_share_connect(self, rank, world, peer_blocks):
+        arr = (C.c_void_p * world)(*peer_blocks)
+        _ck(_L.atray_view_share_connect(self.h, rank, world, C.cast(arr, C.c_void_p)))
+
+    def view_share_rendezvous(self):
+        _ck(_L.atray_view_share_rendezvous(self.h))
+
+    def view_share_check(self):
+        _ck(_L.atray_view_share_check(self.h))
+
+    def view_share_off(self):
+        _ck(_L.atray_view_share_off(self.h))
+
+    def enable_peer(self, other):
+        _ck(_L.atray_ctx_enable_peer(self.h, other.h))
+
+    def debug_view_shards(self, shards):
+        _ck(_L.atray_debug_view_shards(self.h, shards))
+
     def microbench(self):
         a, b = C.c_double(0), C.c_double(0)
         _ck(_L.atray_microbench(self.h, C.byref(a), C.byref(b)))

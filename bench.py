@@ -182,12 +182,12 @@ def ops_and_bytes_per_ray(c):
     return ops, byts
 
 
-def load_traffic():
-    """dram bytes per launch of the render kernel from the committed ncu capture (profiles/), or None."""
+def load_traffic(key="dram_bytes_per_launch"):
+    """dram bytes (or warp instructions) per launch of the render kernel from the committed ncu capture (profiles/), or None."""
     p = os.path.join(ROOT, "profiles", "render_kernel_traffic.json")
     if os.path.exists(p):
         try:
-            return json.load(open(p)).get("dram_bytes_per_launch")
+            return json.load(open(p)).get(key)
         except Exception:
             return None
     return None
@@ -245,6 +245,9 @@ def run_ours(args):
     # traced them: 4 instead of 12 bytes per pixel cross NVLink into GPU 0 (device-resident leg; the e2e leg writes the host
     # bitmap directly from every rank, see below)
     gather = multi.FrameGather(ctx, dist, rank, world, W, H, local=("t", "prim"))
+    # N > 1: the per-frame view pass is shared — every rank computes 1/N of the slot ranges and stores them into all ranks'
+    # tables over NVLink (atray_view_share_*, CUDA-IPC between the rank processes)
+    share = multi.ViewShare(ctx, dist, rank, world, W, H) if (world > 1 and not args.no_share) else None
     opts = ctx.opts(fp_mode=fp_mode, rank=rank, world=world, band_rows=BAND_ROWS)
     my_rays = multi.rays_of_rank(W, H, SPP, BAND_ROWS, rank, world)
     flush_bytes = 256 << 20                            # > 126 MB L2
@@ -262,6 +265,10 @@ def run_ours(args):
             dist.barrier()
 
     def step_device():
+        # every rank's frame starts when all ranks are ready (flag exchange queued on the streams, outside the step's event
+        # pair): a step's duration is then the frame's, not the skew between the Python loops of the rank processes
+        if share is not None:
+            ctx.view_share_rendezvous()
         ctx.render_device(cam, opts, gather.planes["bgrx"], gather.planes["t"], gather.planes["prim"])
 
     # ---- HBM-resident leg: `value` -------------------------------------------------------------------------------------
@@ -283,17 +290,27 @@ def run_ours(args):
     barrier()
     wall_ms = 1e3 * (time.perf_counter() - wall0)
     dev_ms = float(sum(per_step_ms))
+    gather_check = None
     if dist is not None:
         import torch
-        tt = torch.tensor([dev_ms], dtype=torch.float64, device="cuda")
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        dev_ms_max = float(tt.item())
-        allms = [torch.zeros(1, dtype=torch.float64, device="cuda") for _ in range(world)]
-        dist.all_gather(allms, torch.tensor([dev_ms / args.steps], dtype=torch.float64, device="cuda"))
-        per_rank_ms = [float(x.item()) for x in allms]
+        # a frame is complete when its slowest rank is: per step the maximum over the ranks, summed over the steps
+        mine = torch.tensor(per_step_ms, dtype=torch.float64, device="cuda")
+        allsteps = [torch.zeros_like(mine) for _ in range(world)]
+        dist.all_gather(allsteps, mine)
+        steps_by_rank = torch.stack(allsteps).cpu().numpy()          # (world, K)
+        dev_ms_max = float(steps_by_rank.max(axis=0).sum())
+        per_rank_ms = [float(x) for x in steps_by_rank.mean(axis=1)]
+        max_of_sums_ms = float(steps_by_rank.sum(axis=1).max())
+        # what GPU 0 gathered (every rank's peer stores) is the frame one GPU renders alone
+        if rank == 0:
+            got = ctx.to_host(gather.planes["bgrx"], np.zeros((H, W), np.uint32))
+            ref = ctx.render(cam, ctx.opts(fp_mode=fp_mode), want=("bgrx",))["bgrx"]
+            gather_check = bool((got == ref).all())
+        barrier()
     else:
         dev_ms_max = dev_ms
         per_rank_ms = [dev_ms / args.steps]
+        max_of_sums_ms = dev_ms
     total_rays = W * H * SPP * args.steps
     value = total_rays / (dev_ms_max * 1e-3) / 1e6
 
@@ -380,10 +397,21 @@ def run_ours(args):
         bound_fp32 = k0["fp32_lane_ops_per_s"] / ops_ray / 1e6         # Mrays/s per GPU
         bound_hbm = hbm_peak * 1e9 / bytes_ray / 1e6
         per_gpu = value / world
-        roofline = {"bound": "hbm", "achieved": achieved_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": achieved_gbs / hbm_peak,
+        # The kernel is bound by instruction issue / dependent-operation latency, not by HBM (measured DRAM traffic is the output
+        # planes, ~4 % of the HBM peak): `issue` is the fraction of the SMs' issue slots the kernel's warp instructions fill
+        # (warp instructions per launch from the committed ncu capture of the same workload, profiles/render_kernel_traffic.json).
+        warp_inst = load_traffic("warp_instructions_per_launch")
+        sm_hz = 1e6 * (clocks["sm_mhz"] if clocks and clocks.get("sm_mhz") else 1965.0)
+        issue = None
+        if warp_inst and world == 1:
+            issue = {"warp_instructions_per_launch": warp_inst, "issue_slots_per_s": 148 * 4 * sm_hz,
+                     "frac": warp_inst / (148 * 4 * sm_hz * launch_ms * 1e-3), "source": "profiles/render_kernel_traffic.json (ncu --set full)"}
+        roofline = {"bound": "hbm", "bound_note": "nominal: the contract's HBM line; the kernel is issue/latency-bound, see `issue` and fp32",
+                    "achieved": achieved_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": achieved_gbs / hbm_peak,
                     "traffic": load_traffic(), "peak_source": peak_src, "kernel": "k_render_culled<STRICT>" if args.fp == "strict" else "k_render_culled<FAST>",
                     "kernel_ms_per_launch": launch_ms, "kernel_share_of_step": launch_ms / (dev_ms / args.steps),
                     "algorithmic_bytes_per_ray": bytes_ray, "algorithmic_fp32_ops_per_ray": ops_ray,
+                    "issue": issue,
                     "fp32": {"achieved_lane_ops_per_s": fp32_achieved, "peak_lane_ops_per_s": k0["fp32_lane_ops_per_s"],
                              "frac": fp32_achieved / k0["fp32_lane_ops_per_s"], "peak_source": "K0 FFMA microbenchmark, this run"},
                     "l2_read_gbs_measured": k0["l2_read_gbs"],
@@ -392,8 +420,8 @@ def run_ours(args):
                                                           "achieved_frac_of_slower": per_gpu / min(bound_fp32, bound_hbm)},
                     "note": "achieved = algorithmic bytes per ray (32 B per box test + 48 B per triangle test actually made, "
                             "+ 12 B output; counters of a separate counted frame) x rays / render-kernel time. The 10 MB scene is "
-                            "L2/L1-resident, so DRAM traffic is the output planes; the kernel is bound by dependent-load "
-                            "latency per warp, not by HBM (see fp32.frac, l2_read_gbs_measured and profiles/)"}
+                            "L2/L1-resident, so DRAM traffic is the output planes; the kernel is bound by dependent-operation "
+                            "latency per warp, not by HBM (see issue.frac, fp32.frac, l2_read_gbs_measured and profiles/)"}
         cpu_baseline = None
         if world == 1 and not args.no_cpu_baseline:
             _, cscene, kind = cpu_scene()
@@ -408,17 +436,24 @@ def run_ours(args):
         line.update({"impl": "ours", "value": value, "ms_per_step": dev_ms_max / args.steps, "e2e": e2e, "roofline": roofline,
                      "cpu_baseline": cpu_baseline, "clocks": clocks,
                      # timed `value` region: k_view_bounds + k_view_finish + k_render_culled per step and rank
-                     "gpu_launches": 3 * args.steps * world,
-                     "wall_ms_bracket": wall_ms, "per_step_ms_rank0": per_step_ms, "ms_per_step_by_rank": per_rank_ms, "counters": ctr, "setup_s": setup_s})
+                     "gpu_launches": (3 if share is None else 5) * args.steps * world,   # + flag kernels of the pass and of the rendezvous
+                     "wall_ms_bracket": wall_ms, "per_step_ms_rank0": per_step_ms, "ms_per_step_by_rank": per_rank_ms,
+                     "ms_per_step_max_of_rank_sums": max_of_sums_ms / args.steps, "gathered_frame_equals_one_gpu_frame": gather_check,
+                     "counters": ctr, "setup_s": setup_s})
         line["config"].update({"fp_mode": args.fp, "band_rows": BAND_ROWS, "parallelism": "bands%d" % world,
                                "l2": "flushed between timed steps (256 MiB device memset outside the per-step event pair)",
-                               "timing": "CUDA events on the library's stream around each frame's launch, summed over K steps, max over ranks",
+                               "timing": "CUDA events on the library's stream around each frame's launch; per step the MAX over the ranks, summed over the K steps"
+                                         + ("; every step starts after an on-stream flag rendezvous of the ranks" if share is not None else ""),
+                               "view_pass": ("shared: each rank computes 1/%d of the slot ranges and peer-stores them into all ranks' tables (NVLink, CUDA IPC)" % world) if share is not None else "computed by every rank",
                                "devices": [pick_device(r, world, visible_gpus) for r in range(world)] if world > 1 else [local_rank],
                                "gather": "BGRX bitmap: direct peer stores into GPU 0's frame through CUDA IPC; t/prim planes stay on the tracing rank" if world > 1 else "none (1 GPU)"})
     barrier()
     if tex is not None:
         tex.free()
     ctx.dev_free(d_flush)
+    if share is not None:
+        ctx.view_share_check()
+        share.close()
     gather.close()
     if dist is not None:
         dist.destroy_process_group()
@@ -454,6 +489,7 @@ def main():
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--fp", choices=["strict", "fast"], default="strict")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-share", action="store_true", help="N > 1: every rank computes the whole per-frame view pass itself")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = 3  # timing rule: at least 3 warm-up steps

@@ -232,6 +232,31 @@ int atray_ipc_export(atray_ctx* ctx, void* dev, unsigned char* handle64);
 int atray_ipc_open(atray_ctx* ctx, const unsigned char* handle64, void** out);
 int atray_ipc_close(atray_ctx* ctx, void* p);
 
+/* Shared per-frame view pass for N GPUs (N <= 8) that render one frame together, scene replicated on every GPU: each rank
+ * computes the pixel ranges of 1/N of the triangle slots and stores them into the tables of ALL ranks with plain peer stores
+ * over NVLink (k_view_bounds), then raises a flag per rank that a one-warp kernel on each peer's stream waits for —
+ * the part of a frame that does not shrink with N when every rank computes it alone. No counterpart in the reference (its
+ * workers share one address space, renderer.cpp:371-399).
+ *   atray_view_share_create : after atray_scene_upload; allocates this context's block for frames up to max_width x
+ *                             max_height and returns its device pointer (export it with atray_ipc_export for other processes);
+ *   atray_view_share_connect: peer_blocks[world] = the blocks of all ranks as pointers valid in THIS process (own block at
+ *                             [rank]; atray_ipc_open of a peer's handle, or the peer context's pointer after
+ *                             atray_ctx_enable_peer in a single process). From then on frames rendered with
+ *                             opts.part = {rank, world, …} take the shared pass; all ranks must render the same frames.
+ *   atray_view_share_off    : back to every rank computing the whole pass itself. */
+int atray_view_share_create(atray_ctx* ctx, int32_t max_width, int32_t max_height, void** block, size_t* bytes);
+int atray_view_share_connect(atray_ctx* ctx, int32_t rank, int32_t world, void* const* peer_blocks);
+int atray_view_share_off(atray_ctx* ctx);
+/* queues "every rank has reached this point" on the context stream (a flag per rank + stream waits, no host round trip):
+ * frames queued after it start together on all GPUs. No-op when the shared pass is off. */
+int atray_view_share_rendezvous(atray_ctx* ctx);
+/* drains the stream and reports ATRAY_ECUDA if a wait for a peer's flag ever timed out (2 s): a rank died or rendered other frames */
+int atray_view_share_check(atray_ctx* ctx);
+/* single process, several contexts: lets ctx's device store into other's device memory (cudaDeviceEnablePeerAccess) */
+int atray_ctx_enable_peer(atray_ctx* ctx, atray_ctx* other);
+/* verification aid: run the view pass of every later frame as `shards` shard launches on this GPU alone (0 = off) */
+int atray_debug_view_shards(atray_ctx* ctx, int32_t shards);
+
 /* K0 microbenchmarks for the roofline denominators: FP32 issue slots/s and L2 read GB/s. */
 int atray_microbench(atray_ctx* ctx, double* fp32_lane_ops_per_s, double* l2_read_gbs);
 

@@ -455,23 +455,18 @@ def test_heaviest_first_tile_schedule(A, meshes, monkeypatch):
         assert (f["bgrx"] == frames[0]["bgrx"]).all() and (f["prim"] == frames[0]["prim"]).all() and same_bits(f["t"], frames[0]["t"])
 
 
-def test_half_tile_mode_gives_the_same_frame(A, meshes, monkeypatch):
-    """A rank with at most one busy tile per warp of the render grid traces its busy tiles as half-tiles (two list positions
-    per tile, 16 rays per warp; ATRAY_SPLIT_RATIO16, default 22; only cost classes >= ATRAY_SPLIT_MIN_CLASS, default 5).
-    Never / default / every tile / classes >= 3 must give the same bits: device
-    frame with counters, a partitioned rank (the case the mode is for), the jittered path and the slab-pipelined host frame
-    (per-slab counters in half-tile units, last band partial)."""
+def test_view_pass_in_shards_gives_the_same_frame(A, meshes):
+    """The per-frame view pass split into shards of the triangle slots (what N GPUs that share the pass run, one shard per
+    GPU with stores into every peer's tables) — executed here as shard launches on ONE GPU with this GPU standing in for
+    every peer (atray_debug_view_shards): whole frame, a rank of 8, the jittered path and the slab-pipelined host frame
+    give the same bits and the same tile counts as the unsharded pass."""
     path, rescale = meshes["knot_mid"]
     W, H = 1920, 1084
     results = []
-    for ratio, min_class in (("0", None), (None, None), ("100000000", "0"), ("100000000", "3")):
-        for name, val in (("ATRAY_SPLIT_RATIO16", ratio), ("ATRAY_SPLIT_MIN_CLASS", min_class)):
-            if val is None:
-                monkeypatch.delenv(name, raising=False)
-            else:
-                monkeypatch.setenv(name, val)
+    for shards in (0, 2, 3, 8):
         sc = gpu_scene(A, path, rescale)
         ctx = sc.ctx
+        ctx.debug_view_shards(shards)
         out = {}
         for tag, cam, opts in (("whole", A.set_camera(W, H), ctx.opts(count_work=True)),
                                ("rank5of8", A.set_camera(W, H), ctx.opts(rank=5, world=8, band_rows=8, count_work=True)),
@@ -480,7 +475,8 @@ def test_half_tile_mode_gives_the_same_frame(A, meshes, monkeypatch):
             planes = [ctx.dev_alloc(w * h * 4) for _ in range(3)]
             for d in planes:
                 ctx.dev_memset(d, 0, w * h * 4)
-            ctx.render_device(cam, opts, *planes)
+            for _ in range(2):      # twice: the second frame meets the tables the first one left behind
+                ctx.render_device(cam, opts, *planes)
             ctx.sync()
             for k, dt, d in zip(("bgrx", "t", "prim"), (np.uint32, np.float32, np.uint32), planes):
                 out[tag + "." + k] = ctx.to_host(d, np.zeros((h, w), dt)).view(np.uint32)
@@ -497,6 +493,46 @@ def test_half_tile_mode_gives_the_same_frame(A, meshes, monkeypatch):
         for k in results[0]:
             assert (other[k] == results[0][k]).all(), k
     assert (results[0]["host.bgrx"] == results[0]["whole.bgrx"]).all()
+
+
+def test_shared_view_pass_on_two_gpus(A, meshes):
+    """Two GPUs of one process share the view pass (atray_view_share_*): each computes half of the slot ranges and stores
+    them into both GPUs' tables over NVLink, a flag per rank orders the exchange, and each renders its bands straight into
+    GPU 0's frame (peer stores). The gathered frame equals the 1-GPU frame bit for bit, frame after frame (the tables are
+    double-buffered), for two cameras."""
+    if A.device_count() < 2:
+        pytest.skip("needs two GPUs (run under gpurun --gpus 2)")
+    from atray_b200 import multi
+    from atray_b200.renderer import Context
+    path, rescale = meshes["knot_mid"]
+    W, H = 1920, 1084
+    m = A.load_model_data(path, 4)
+    A.place_default(m, rescale)
+    A.build_KD_tree(m)
+    ctxs = [Context(0), Context(1)]
+    for c in ctxs:
+        c.upload(m)
+    multi.ViewShare.connect_local(ctxs, W, H)
+    planes = [ctxs[0].dev_alloc(W * H * 4) for _ in range(3)]      # GPU 0 owns the frame; GPU 1 stores into it
+    for cam in (A.set_camera(W, H), A.set_camera(W, H, eye=(3.0, -4.0, 9.0), facing=(-0.2, -0.4, -1.0), h_fov=0.7)):
+        ref = ctxs[0].render(cam)                                   # whole frame, pass computed by one GPU
+        for frame in range(5):
+            for d in planes:
+                ctxs[0].dev_memset(d, 0xEE, W * H * 4)
+            ctxs[0].sync()
+            for r, c in enumerate(ctxs):                            # both ranks are queued before either is waited for
+                c.render_device(cam, c.opts(rank=r, world=2, band_rows=8), *planes)
+            for c in ctxs:
+                c.sync()
+            got = [ctxs[0].to_host(d, np.zeros((H, W), np.uint32)) for d in planes]
+            assert (got[0] == ref["bgrx"]).all(), frame
+            assert (got[1] == ref["t"].view(np.uint32)).all() and (got[2] == ref["prim"]).all(), frame
+    for c in ctxs:
+        c.view_share_check()       # no wait for a peer's flag timed out
+    for d in planes:
+        ctxs[0].dev_free(d)
+    for c in ctxs:
+        c.close()
 
 
 def test_pipelined_copy_out_equals_whole_frame(A, meshes, monkeypatch):
