@@ -112,6 +112,7 @@ _SIGS = {
     "atray_ctx_sync": [_vp],
     "atray_last_kernel_ms": [_vp, C.POINTER(_f)],
     "atray_last_render_kernel_ms": [_vp, C.POINTER(_f)],
+    "atray_last_view_split_ms": [_vp, C.POINTER(_f), C.POINTER(_f)],
     "atray_trace_rays": [_vp, _vp, _u64, _i, _i, _vp, _vp],
     "atray_trace_rays_device": [_vp, _vp, _u64, _i, _i, _vp, _vp],
     "atray_get_counters": [_vp, C.POINTER(Counters)],

@@ -83,6 +83,7 @@ struct atray_ctx
     bool in_flight = false;
     cudaEvent_t ev_k0 = nullptr, ev_k1 = nullptr, ev_done = nullptr;
     cudaEvent_t ev_kr = nullptr;     // between the per-frame view pass and the render kernel (atray_last_render_kernel_ms)
+    cudaEvent_t ev_vb = nullptr;     // between k_view_bounds and k_view_nodes (atray_last_view_split_ms)
     bool have_split = false;
     bool have_kernel_time = false;
     // slab-pipelined copy-out (atray_render_begin): the copy stream waits on the render kernel's per-slab counters
@@ -293,6 +294,7 @@ int atray_ctx_create(int device, atray_ctx** out)
     if (e == cudaSuccess) e = cudaEventCreate(&c->ev_k0);
     if (e == cudaSuccess) e = cudaEventCreate(&c->ev_k1);
     if (e == cudaSuccess) e = cudaEventCreate(&c->ev_kr);
+    if (e == cudaSuccess) e = cudaEventCreate(&c->ev_vb);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_done, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->copy_stream2, cudaStreamNonBlocking);
@@ -380,6 +382,7 @@ void atray_ctx_destroy(atray_ctx* c)
     if (c->ev_k0) cudaEventDestroy(c->ev_k0);
     if (c->ev_k1) cudaEventDestroy(c->ev_k1);
     if (c->ev_kr) cudaEventDestroy(c->ev_kr);
+    if (c->ev_vb) cudaEventDestroy(c->ev_vb);
     if (c->ev_done) cudaEventDestroy(c->ev_done);
     if (c->ev_reset) cudaEventDestroy(c->ev_reset);
     for (int k = 0; k < kMaxSlabs; ++k)
@@ -829,26 +832,13 @@ static int enqueue_render(atray_ctx* c, const AtrayCamera* cam, const AtrayRende
             vw.tri_px = pe.tri_px[sh.rank]; vw.pkt_px = pe.pkt_px[sh.rank]; vw.chunk_px = pe.chunk_px[sh.rank];
             vw.stamps = pe.stamps[sh.rank]; vw.tile_cost = pe.tile_cost[sh.rank]; vw.all_flag = pe.all_flag[sh.rank];
             vw.tri_rect = nullptr;
-            struct Arg { atray_ctx* c; uint32_t seq; std::string err; } arg{c, seq, std::string()};
-            ViewBetween bt;
-            bt.arg = &arg;
-            bt.fn = [](void* a, cudaStream_t st) -> cudaError_t {
-                Arg* g = static_cast<Arg*>(a);
-                atray_ctx::Share& s2 = g->c->share;
-                uint32_t* flags[kMaxPeers];
-                for (int q = 0; q < s2.world; ++q) flags[q] = reinterpret_cast<uint32_t*>(s2.peer[q] + s2.off_flags);
-                cudaError_t e = launch_view_signal(flags, s2.world, s2.rank, g->seq, st);
-                if (e != cudaSuccess) { g->err = std::string("view pass signal kernel: ") + cudaGetErrorString(e); return e; }
-                // the peers' flags land in this GPU's flag row; a one-warp kernel on the stream waits for them (bounded: 2 s)
-                uint32_t* row = reinterpret_cast<uint32_t*>(s2.block + s2.off_flags);
-                e = launch_view_wait(row, s2.world, s2.rank, g->seq, 2000000000ull, row + 32, st);
-                if (e != cudaSuccess) { g->err = std::string("view pass wait kernel: ") + cudaGetErrorString(e); return e; }
-                return cudaSuccess;
-            };
-            {
-                cudaError_t e = launch_view_bounds(c->scene, vp, vw, to_dev(cam), p, slabs, c->stream, want_slabs > 1 ? c->ev_reset : nullptr, true, &pe, &bt);
-                if (e != cudaSuccess) return arg.err.empty() ? cuda_fail(e, "shared view pass") : fail(ATRAY_ECUDA, arg.err);
-            }
+            uint32_t* row = reinterpret_cast<uint32_t*>(sh.block + sh.off_flags);
+            for (int q = 0; q < sh.world; ++q) pe.flags[q] = reinterpret_cast<uint32_t*>(sh.peer[q] + sh.off_flags);
+            pe.seq = seq;
+            pe.ticket = row + 48;
+            ViewWait wt{};
+            wt.my_flags = row; wt.n = sh.world; wt.rank = sh.rank; wt.seq = seq; wt.timeout_ns = 2000000000ull; wt.timed_out = row + 32;
+            CU(launch_view_bounds(c->scene, vp, vw, to_dev(cam), p, slabs, c->stream, want_slabs > 1 ? c->ev_reset : nullptr, true, &pe, &wt, c->ev_vb));
         }
         else if (sh.debug_shards > 1)
         {
@@ -866,11 +856,13 @@ static int enqueue_render(atray_ctx* c, const AtrayCamera* cam, const AtrayRende
                 pe.block_lo = uint32_t(uint64_t(n_blocks) * uint64_t(sdx) / uint64_t(sh.debug_shards));
                 pe.block_hi = uint32_t(uint64_t(n_blocks) * uint64_t(sdx + 1) / uint64_t(sh.debug_shards));
                 const bool last = sdx == sh.debug_shards - 1;
-                CU(launch_view_bounds(c->scene, vp, vw, to_dev(cam), p, slabs, c->stream, last && want_slabs > 1 ? c->ev_reset : nullptr, last, &pe));
+                CU(launch_view_bounds(c->scene, vp, vw, to_dev(cam), p, slabs, c->stream, last && want_slabs > 1 ? c->ev_reset : nullptr, last, &pe,
+                                      nullptr, last ? c->ev_vb : nullptr));
             }
         }
         else
-            CU(launch_view_bounds(c->scene, vp, vw, to_dev(cam), p, slabs, c->stream, want_slabs > 1 ? c->ev_reset : nullptr));
+            CU(launch_view_bounds(c->scene, vp, vw, to_dev(cam), p, slabs, c->stream, want_slabs > 1 ? c->ev_reset : nullptr, true, nullptr,
+                                  nullptr, c->ev_vb));
         CU(cudaEventRecord(c->ev_kr, c->stream));
         CU(launch_render_culled(c->scene, to_dev(cam), p, out, c->scratch, vw, slabs, ctr, o->fp_mode == ATRAY_FP_FAST,
                                 o->jitter_seed, c->cfg, c->stream));
@@ -1112,6 +1104,17 @@ int atray_last_render_kernel_ms(atray_ctx* c, float* ms)
     CU(cudaSetDevice(c->device));
     CU(cudaEventSynchronize(c->ev_k1));
     CU(cudaEventElapsedTime(ms, c->ev_kr, c->ev_k1));
+    return ATRAY_OK;
+}
+
+int atray_last_view_split_ms(atray_ctx* c, float* bounds_ms, float* nodes_ms)
+{
+    if (!c || !bounds_ms || !nodes_ms) return fail(ATRAY_EINVAL, "null argument");
+    if (!c->have_kernel_time || !c->have_split) return fail(ATRAY_ESTATE, "the last launch was not a culled frame");
+    CU(cudaSetDevice(c->device));
+    CU(cudaEventSynchronize(c->ev_k1));
+    CU(cudaEventElapsedTime(bounds_ms, c->ev_k0, c->ev_vb));
+    CU(cudaEventElapsedTime(nodes_ms, c->ev_vb, c->ev_kr));
     return ATRAY_OK;
 }
 

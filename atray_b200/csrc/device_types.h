@@ -112,6 +112,19 @@ struct ViewPeers
     uint32_t* stamps[kMaxPeers];
     uint32_t* tile_cost[kMaxPeers];
     uint32_t* all_flag[kMaxPeers];
+    // shared pass only: the last block of k_view_bounds to finish raises flags[q][self] = seq on every rank q (after a
+    // system-wide fence by every thread); k_view_nodes of rank q waits for the flags of all ranks before it reads the tables
+    uint32_t* flags[kMaxPeers];
+    uint32_t seq;
+    uint32_t* ticket;                 // this GPU: blocks of the pass that have finished (reset by the last one)
+};
+struct ViewWait
+{
+    const uint32_t* my_flags;         // null: nothing to wait for
+    int32_t n, rank;
+    uint32_t seq;
+    unsigned long long timeout_ns;    // a peer that never signals ends the wait with *timed_out = seq instead of hanging the GPU
+    uint32_t* timed_out;
 };
 
 // Per-frame state of the film-space rasteriser (render.cu: k_film_tables, k_raster, k_raster_big, k_hit_filter, k_resolve).
@@ -171,12 +184,12 @@ cudaError_t launch_render(const DevScene& sc, const DevCamera& cam, const DevPar
 // culled frame = k_view_bounds (per-frame film rectangles + tile stamps) followed by k_render_culled
 // k_view_bounds (per-slot pixel ranges, packet / chunk unions, tile stamps) + k_view_nodes (node unions, bins, compact list
 // of this rank's busy tiles)
-// `peers` = null: everything into `view` (one GPU, or a rank that computes the whole pass itself). `between` (optional) runs
-// after k_view_bounds and before k_view_nodes on the stream: the cross-rank flag exchange of a shared pass.
-struct ViewBetween { cudaError_t (*fn)(void*, cudaStream_t); void* arg; };
+// `peers` = null: everything into `view` (one GPU, or a rank that computes the whole pass itself). `wait` (shared pass):
+// k_view_nodes starts by waiting for the flags of the other ranks.
 cudaError_t launch_view_bounds(const DevScene& sc, const ViewParams& vp, const DevView& view, const DevCamera& cam,
                                const DevPartition& part, const DevSlabs& slabs, cudaStream_t stream, cudaEvent_t after_reset,
-                               bool finish = true, const ViewPeers* peers = nullptr, const ViewBetween* between = nullptr);
+                               bool finish = true, const ViewPeers* peers = nullptr, const ViewWait* wait = nullptr,
+                               cudaEvent_t after_bounds = nullptr);   // (timing event between the two kernels)
 // one warp: flags[p][rank] = seq for every peer p, after a system-wide fence (the peers' streams wait for the value)
 cudaError_t launch_view_signal(uint32_t* const* peer_flags, int n, int rank, uint32_t seq, cudaStream_t stream);
 // one warp: waits (on the stream) until every other rank's flag in my_flags has reached seq; *timed_out = seq after timeout_ns

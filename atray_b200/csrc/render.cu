@@ -548,9 +548,12 @@ __global__ void __launch_bounds__(kBlock, 4) k_view_bounds(DevScene sc, ViewPara
     const bool in_range = slot < sc.n_slots && chunk < pe.block_hi;   // (an empty share still launches one block for the resets above)
     const int n_tiles = vp.tiles_x * vp.tiles_y;
     // owner of tile row ty in a shared pass (band b -> rank b % world); -1: not stamped (another rank's row, one-GPU pass)
+    const int rpb = part.band_rows >> 2;   // tile rows per band; shifts when both are powers of two (the usual 8-row bands on 2/4/8 GPUs)
+    const bool pow2 = (rpb & (rpb - 1)) == 0 && (part.world & (part.world - 1)) == 0;
+    const int rsh = __ffs(rpb) - 1, wmask = part.world - 1;
     auto owner = [&](int ty) -> int {
         if (part.world <= 1) return 0;
-        const int o = ((ty * 4) / part.band_rows) % part.world;
+        const int o = pow2 ? ((ty >> rsh) & wmask) : ((ty / rpb) % part.world);
         return shared ? o : (o == part.rank ? 0 : -1);
     };
     const bool skip_cost = pe.debug_skip & 1u, skip_stamps = pe.debug_skip & 2u, skip_ranges = pe.debug_skip & 4u;
@@ -619,12 +622,13 @@ __global__ void __launch_bounds__(kBlock, 4) k_view_bounds(DevScene sc, ViewPara
     if (!px_is_empty(p))
     {
         const int qx0 = (int)(p.x & 0xffffu) >> 3, qy0 = (int)(p.x >> 16) >> 2, qx1 = (int)(p.y & 0xffffu) >> 3, qy1 = (int)(p.y >> 16) >> 2;
-        const int w = qx1 - qx0 + 1, n = w * (qy1 - qy0 + 1);
-        if (n <= 64)
-            for (int i = lane & 7; i < n; i += 8)
+        if ((qx1 - qx0 + 1) * (qy1 - qy0 + 1) <= 64)
+            for (int ty = qy0; ty <= qy1; ++ty)   // rows in turn, the 8 lanes stride over the columns (no division per tile)
             {
-                const int ty = qy0 + i / w, o = owner(ty);
-                if (o >= 0 && !(skip_cost && o != pe.self)) atomicAdd(&pe.tile_cost[o][ty * vp.tiles_x + qx0 + i % w], 1u);
+                const int o = owner(ty);
+                if (o < 0 || (skip_cost && o != pe.self)) continue;
+                uint32_t* row = pe.tile_cost[o] + ty * vp.tiles_x;
+                for (int tx = qx0 + (lane & 7); tx <= qx1; tx += 8) atomicAdd(row + tx, 1u);
             }
     }
     // chunk = the 32 packets of this block
@@ -640,6 +644,23 @@ __global__ void __launch_bounds__(kBlock, 4) k_view_bounds(DevScene sc, ViewPara
         if (chunk < pe.block_hi || pe.block_hi == 0u)
             for (int q = 0; q < pe.n; ++q)
                 if (!skip_ranges || q == pe.self) pe.chunk_px[q][chunk] = c;
+    }
+    if (pe.ticket)
+    {
+        // every store of this block is visible system-wide before the block counts itself done; the last block of the grid
+        // tells every rank that this rank's share of the frame's tables is complete
+        __threadfence_system();
+        __syncthreads();
+        if (threadIdx.x == 0)
+        {
+            const uint32_t done = atomicAdd(pe.ticket, 1u);
+            if (done == gridDim.x - 1u)
+            {
+                __threadfence_system();
+                *pe.ticket = 0u;
+                for (int q = 0; q < pe.n; ++q) *((volatile uint32_t*)(pe.flags[q] + pe.self)) = pe.seq;
+            }
+        }
     }
 }
 
@@ -659,9 +680,30 @@ __device__ __forceinline__ int tile_cost_class(uint32_t cost, int shift)
     return c < 0 ? 0 : (c > kCostBuckets - 1 ? kCostBuckets - 1 : c);
 }
 __global__ void __launch_bounds__(kBlock) k_view_nodes(DevScene sc, DevView view, DevCamera cm, DevPartition part, DevSlabs slabs,
-                                                       uint32_t node_blocks)
+                                                       uint32_t node_blocks, ViewWait vwait)
 {
     const int lane = threadIdx.x & 31;
+    if (vwait.my_flags)
+    {
+        // Shared pass: the tables are complete once every other rank's flag in this GPU's flag row has reached the frame's
+        // sequence number (raised by the last block of that rank's k_view_bounds, on another GPU, after its stores). Nothing
+        // of the tables has been read by this kernel yet, so no stale line can sit in L1.
+        if (threadIdx.x < (unsigned)vwait.n && (int)threadIdx.x != vwait.rank)
+        {
+            unsigned long long t0;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+            const volatile uint32_t* f = vwait.my_flags + threadIdx.x;
+            while ((int32_t)(*f - vwait.seq) < 0)
+            {
+                unsigned long long t1;
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+                if (t1 - t0 > vwait.timeout_ns) { *vwait.timed_out = vwait.seq; break; }
+                __nanosleep(64);
+            }
+            __threadfence_system();
+        }
+        __syncthreads();
+    }
     if (blockIdx.x < node_blocks)
     {
         const uint32_t warp = (blockIdx.x * kBlock + threadIdx.x) >> 5;
@@ -1768,7 +1810,7 @@ cudaError_t launch_view_wait(const uint32_t* my_flags, int n, int rank, uint32_t
 
 cudaError_t launch_view_bounds(const DevScene& sc, const ViewParams& vp, const DevView& view, const DevCamera& cam,
                                const DevPartition& part, const DevSlabs& slabs, cudaStream_t stream, cudaEvent_t after_reset,
-                               bool finish, const ViewPeers* peers, const ViewBetween* between)
+                               bool finish, const ViewPeers* peers, const ViewWait* wait, cudaEvent_t after_bounds)
 {
     ViewPeers pe{};
     if (peers) pe = *peers;
@@ -1784,27 +1826,20 @@ cudaError_t launch_view_bounds(const DevScene& sc, const ViewParams& vp, const D
     k_view_bounds<<<grid < 1 ? 1 : grid, kBlock, 0, stream>>>(sc, vp, view, part, pe);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;
-    static const bool sync_debug = std::getenv("ATRAY_SYNC_DEBUG") != nullptr;   // verification aid: find the faulting launch
-    if (sync_debug && (e = cudaStreamSynchronize(stream)) != cudaSuccess) { std::fprintf(stderr, "k_view_bounds: %s\n", cudaGetErrorString(e)); return e; }
     if (after_reset)  // the per-slab counters of the previous frame are gone from here on
     {
         e = cudaEventRecord(after_reset, stream);
         if (e != cudaSuccess) return e;
     }
-    if (between)
-    {
-        e = between->fn(between->arg, stream);
-        if (e != cudaSuccess) return e;
-        if (sync_debug && (e = cudaStreamSynchronize(stream)) != cudaSuccess) { std::fprintf(stderr, "view pass signal/wait: %s\n", cudaGetErrorString(e)); return e; }
-    }
+    if (after_bounds && (e = cudaEventRecord(after_bounds, stream)) != cudaSuccess) return e;
     if (!finish) return cudaSuccess;  // rasterised frame: no tile lists, no node ranges
     // one warp per node + 296 compaction blocks of 32 registers: all resident at once
     uint32_t node_blocks = (sc.n_nodes + kBlock / 32 - 1) / (kBlock / 32);
     if (node_blocks > 296u) node_blocks = 296u;
-    k_view_nodes<<<node_blocks + 296u, kBlock, 0, stream>>>(sc, view, cam, part, slabs, node_blocks);
-    e = cudaGetLastError();
-    if (e == cudaSuccess && sync_debug && (e = cudaStreamSynchronize(stream)) != cudaSuccess) std::fprintf(stderr, "k_view_nodes: %s\n", cudaGetErrorString(e));
-    return e;
+    ViewWait vw{};
+    if (wait) vw = *wait;
+    k_view_nodes<<<node_blocks + 296u, kBlock, 0, stream>>>(sc, view, cam, part, slabs, node_blocks, vw);
+    return cudaGetLastError();
 }
 
 // The culled kernel is persistent: its grid is exactly what is resident at once (a slab completes only when every warp

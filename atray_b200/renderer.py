@@ -124,6 +124,12 @@ class Context:
         _ck(_L.atray_last_render_kernel_ms(self.h, C.byref(ms)))
         return ms.value
 
+    def last_view_split_ms(self):
+        """(k_view_bounds ms, k_view_nodes ms) of the last culled frame."""
+        a, b = C.c_float(0), C.c_float(0)
+        _ck(_L.atray_last_view_split_ms(self.h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
     def tile_log(self, n_tiles):
         """(n_tiles, 4) uint32 {start ns, duration ns, sampled cost, class} of the last culled frame (ATRAY_TILE_LOG=1)."""
         out = np.zeros((n_tiles, 4), np.uint32)

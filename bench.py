@@ -281,12 +281,13 @@ def run_ours(args):
         step_device()
     barrier()
     wall0 = time.perf_counter()
-    per_step_ms, render_ms = [], []
+    per_step_ms, render_ms, split_ms = [], [], []
     for _ in range(args.steps):
         flush_l2()
         step_device()
         per_step_ms.append(ctx.last_kernel_ms())       # waits for this step's stop event (device time on our stream)
         render_ms.append(ctx.last_render_kernel_ms())  # k_render_culled alone (event after the per-frame view pass)
+        split_ms.append(ctx.last_view_split_ms())      # k_view_bounds | k_view_nodes
     barrier()
     wall_ms = 1e3 * (time.perf_counter() - wall0)
     dev_ms = float(sum(per_step_ms))
@@ -439,6 +440,8 @@ def run_ours(args):
                      "gpu_launches": (3 if share is None else 5) * args.steps * world,   # + flag kernels of the pass and of the rendezvous
                      "wall_ms_bracket": wall_ms, "per_step_ms_rank0": per_step_ms, "ms_per_step_by_rank": per_rank_ms,
                      "ms_per_step_max_of_rank_sums": max_of_sums_ms / args.steps, "gathered_frame_equals_one_gpu_frame": gather_check,
+                     "kernel_ms_rank0": {"k_view_bounds": float(np.mean([a for a, _ in split_ms])), "k_view_nodes": float(np.mean([b for _, b in split_ms])),
+                                         "k_render_culled": float(np.mean(render_ms))},
                      "counters": ctr, "setup_s": setup_s})
         line["config"].update({"fp_mode": args.fp, "band_rows": BAND_ROWS, "parallelism": "bands%d" % world,
                                "l2": "flushed between timed steps (256 MiB device memset outside the per-step event pair)",

@@ -197,6 +197,9 @@ int atray_ctx_sync(atray_ctx* ctx);
 int atray_last_kernel_ms(atray_ctx* ctx, float* ms);
 /* Same frame, the render kernel alone (k_render_culled: CUDA events after the per-frame view pass and after the kernel). */
 int atray_last_render_kernel_ms(atray_ctx* ctx, float* ms);
+/* the view pass of the last culled frame split at the kernel boundary: k_view_bounds (with, in a shared pass, its peer
+ * stores) and k_view_nodes (with its wait for the other ranks' flags) */
+int atray_last_view_split_ms(atray_ctx* ctx, float* bounds_ms, float* nodes_ms);
 
 /* get_intersection_data model branch for an arbitrary ray list — renderer.cpp:34-57 + kd_tree.cpp:302-313.
  * rays = n × {ox,oy,oz,dx,dy,dz} (direction used as given). Host pointers; synchronous. */

@@ -50,7 +50,7 @@ if args.host:
 planes = [ctx.dev_alloc(W * H * 4) for _ in range(3)]
 flush = ctx.dev_alloc(256 << 20)
 opts = ctx.opts(rank=args.rank, world=args.world, band_rows=8, raster=args.raster, count_work=args.count)
-ms, rms = [], []
+ms, rms, vs = [], [], []
 for i in range(args.reps + 2):
     ctx.dev_memset(flush, 0, 256 << 20)
     ctx.render_device(cam, opts, *planes)
@@ -59,8 +59,10 @@ for i in range(args.reps + 2):
         ms.append(ctx.last_kernel_ms())
         if not args.raster:
             rms.append(ctx.last_render_kernel_ms())
+            vs.append(ctx.last_view_split_ms())
 print("world %d rank %d raster=%s: %.1f us per frame (min %.1f)" % (args.world, args.rank, args.raster, 1e3 * sum(ms) / len(ms), 1e3 * min(ms)), flush=True)
 if rms:
-    print("  render kernel alone %.1f us, view pass %.1f us" % (1e3 * sum(rms) / len(rms), 1e3 * (sum(ms) - sum(rms)) / len(ms)), flush=True)
+    print("  render kernel alone %.1f us, view pass %.1f us (k_view_bounds %.1f, k_view_nodes %.1f)" % (
+        1e3 * sum(rms) / len(rms), 1e3 * (sum(ms) - sum(rms)) / len(ms), 1e3 * sum(a for a, _ in vs) / len(vs), 1e3 * sum(b for _, b in vs) / len(vs)), flush=True)
 if args.count:
     print(ctx.counters())
