@@ -371,7 +371,7 @@ void atray_ctx_destroy(atray_ctx* c)
     free_scene(c);
     cudaFree(c->d_tile_counter); cudaFree(c->d_counters); cudaFree(c->d_casts);
     cudaFree(c->view.stamps); cudaFree(c->view.all_flag); cudaFree(c->view.busy_list); cudaFree(c->view.busy_count);
-    cudaFree(c->view.tile_cost); cudaFree(c->view.tile_log);
+    cudaFree(c->view.tile_cost); cudaFree(c->view.tile_log); cudaFree(c->view.wide_inner);
     cudaFree(c->view.bin_cnt); cudaFree(c->view.bin_leaf); cudaFree(c->view.bin_inner);
     cudaFree(c->share.block);
     cudaFree(c->rs.tabx); cudaFree(c->rs.taby); cudaFree(c->rs.key1); cudaFree(c->rs.key2); cudaFree(c->rs.hit_a);
@@ -750,6 +750,7 @@ static int enqueue_render(atray_ctx* c, const AtrayCamera* cam, const AtrayRende
                 if (const char* env = std::getenv("ATRAY_COST_SHIFT")) c->view.cost_shift = std::atoi(env);
             }
             if (!c->view.all_flag) CU(cudaMalloc(&c->view.all_flag, sizeof(uint32_t)));
+            if (!c->view.wide_inner) CU(cudaMalloc(&c->view.wide_inner, size_t(kWideCap) * 2 * sizeof(uint4)));
             if (!c->view.busy_count)
             {
                 CU(cudaMalloc(&c->view.busy_count, kCtlWords * sizeof(uint32_t)));

@@ -84,6 +84,7 @@ struct DevView
     // (8x4 pixels, inside exactly one bin) filters its bin's lists instead of walking the tree.
     //   leaf entry  = 3 uint4: {px.lo, px.hi, leaf_seq, first_slot} {box lo.xyz, count} {box hi.xyz, node}
     //   inner entry = 2 uint4: {px.lo, px.hi, node, 0} {split point xyz (= hi corner of child 0, kd_tree.cpp:120-148), 0}
+    uint4* wide_inner;     // kWideCap x 2 (same entry form): inner nodes near the root, whose range touches hundreds of bins
     uint32_t* bin_cnt;     // 2 per bin: leaf entries, inner entries (may exceed the capacities: the bin is then unusable)
     uint4* bin_leaf;       // bins x bin_leaf_cap x 3
     uint4* bin_inner;      // bins x bin_inner_cap x 2
@@ -94,6 +95,7 @@ struct DevView
     int32_t tiles_x;
 };
 static constexpr int kBinShiftX = 6, kBinShiftY = 5;   // 64 x 32 pixels = 8 x 8 tiles
+static constexpr int kWideCap = 32, kWideBins = 48;    // an inner node that touches more bins goes to the one wide list
 
 // Where k_view_bounds stores what it computes. One GPU: n = 1 and the tables of `view`. N GPUs that share the per-frame view
 // pass (atray_view_share_*): every rank computes the pixel ranges of 1/N of the triangle slots — blocks [block_lo, block_hi)
@@ -158,7 +160,8 @@ static constexpr int kCostBuckets = 8;
 static constexpr int kCtlCount = 0;                              // [s * kCostBuckets + b] entries of slab s in class b
 static constexpr int kCtlCursor = kMaxSlabs * kCostBuckets;      // [s] consumer cursor of slab s
 static constexpr int kCtlDone = kCtlCursor + kMaxSlabs;          // [s] tiles of slab s whose stores are complete (sky + traced)
-static constexpr int kCtlTicket = kCtlDone + kMaxSlabs;          // end of the words k_view_bounds clears every frame
+static constexpr int kCtlWide = kCtlDone + kMaxSlabs;            // inner nodes in the wide list (DevView::wide_inner)
+static constexpr int kCtlTicket = kCtlWide + 1;                  // end of the words k_view_bounds clears every frame
 static constexpr int kCtlWords = kCtlTicket + 4;
 struct DevSlabs
 {

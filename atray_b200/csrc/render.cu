@@ -525,9 +525,11 @@ __device__ __forceinline__ bool owns_bin_row(const DevPartition& part, int by, i
     const int y0 = by << kBinShiftY;
     int y1 = y0 + (1 << kBinShiftY) - 1;
     if (y1 > H - 1) y1 = H - 1;
-    const int b0 = y0 / part.band_rows, b1 = y1 / part.band_rows;
+    const int br = part.band_rows;
+    const bool p2 = (br & (br - 1)) == 0 && (part.world & (part.world - 1)) == 0;   // the usual case: shifts and masks
+    const int b0 = p2 ? y0 >> (__ffs(br) - 1) : y0 / br, b1 = p2 ? y1 >> (__ffs(br) - 1) : y1 / br;
     if (b1 - b0 + 1 >= part.world) return true;
-    const int d = ((part.rank - b0) % part.world + part.world) % part.world;   // bands from b0 to the next band of this rank
+    const int d = p2 ? ((part.rank - b0) & (part.world - 1)) : ((part.rank - b0) % part.world + part.world) % part.world;   // bands from b0 to this rank's next
     return d <= b1 - b0;
 }
 
@@ -557,45 +559,66 @@ __global__ void __launch_bounds__(kBlock, 4) k_view_bounds(DevScene sc, ViewPara
         return shared ? o : (o == part.rank ? 0 : -1);
     };
     const bool skip_cost = pe.debug_skip & 1u, skip_stamps = pe.debug_skip & 2u, skip_ranges = pe.debug_skip & 4u;
-    uint2 px = px_empty();
-    int tx0 = 0, tx1 = -1, ty0 = 0, ty1 = -1;
-    bool big = false;
+    // ---- 1: which slots need the double-precision path. About half the slots of a closed mesh face away from the eye; a
+    // single-precision test finds them (tri_backfacing_f32), the others are compacted so that the FP64 code runs on full warps.
+    __shared__ uint2 s_slot_px[kBlock];
+    __shared__ unsigned short s_list[kBlock];
+    __shared__ int s_warp_n[kBlock / 32];
+    bool need = false;
     if (in_range)
     {
         const float4* rec = sc.tris + (size_t)(slot >> 3) * 24 + (slot & 7);
         const float4 A = __ldg(rec), AB = __ldg(rec + 8), AC = __ldg(rec + 16);
-        float4 r = make_float4(INFINITY, INFINITY, -INFINITY, -INFINITY);
-        if (__float_as_uint(A.w) != 0xffffffffu)
+        need = __float_as_uint(A.w) != 0xffffffffu && !tri_backfacing_f32(vp, &A.x, &AB.x, &AC.x);
+        if (view.tri_rect && !need) view.tri_rect[slot] = make_float4(INFINITY, INFINITY, -INFINITY, -INFINITY);
+    }
+    s_slot_px[threadIdx.x] = px_empty();
+    const unsigned nm = __ballot_sync(FULL_MASK, need);
+    if (lane == 0) s_warp_n[threadIdx.x >> 5] = __popc(nm);
+    __syncthreads();
+    int before = 0, total = 0;
+#pragma unroll
+    for (int w = 0; w < kBlock / 32; ++w)
+    {
+        const int c = s_warp_n[w];
+        if (w < (int)(threadIdx.x >> 5)) before += c;
+        total += c;
+    }
+    if (need) s_list[before + __popc(nm & ((1u << lane) - 1u))] = (unsigned short)threadIdx.x;
+    __syncthreads();
+    // ---- 2: the compacted slots, full warps: film rectangle -> pixel range -> tile stamps
+    int tx0 = 0, tx1 = -1, ty0 = 0, ty1 = -1;
+    bool big = false;
+    if ((int)threadIdx.x < total)
+    {
+        const uint32_t local = s_list[threadIdx.x], sl = chunk * kBlock + local;
+        const float4* rec = sc.tris + (size_t)(sl >> 3) * 24 + (sl & 7);
+        const float4 A = __ldg(rec), AB = __ldg(rec + 8), AC = __ldg(rec + 16);
+        const FilmRect fr = tri_film_rect(vp, &A.x, &AB.x, &AC.x);
+        if (view.tri_rect) view.tri_rect[sl] = make_float4(fr.xlo, fr.ylo, fr.xhi, fr.yhi);
+        PxRect p;
+        if (film_rect_px(vp, fr, p))
         {
-            const FilmRect fr = tri_film_rect(vp, &A.x, &AB.x, &AC.x);
-            r = make_float4(fr.xlo, fr.ylo, fr.xhi, fr.yhi);
-            PxRect p;
-            if (film_rect_px(vp, fr, p))
+            s_slot_px[local] = px_pack(p);
+            tx0 = p.x0 >> 3; tx1 = p.x1 >> 3; ty0 = p.y0 >> 2; ty1 = p.y1 >> 2;
+            const int nt = (tx1 - tx0 + 1) * (ty1 - ty0 + 1);
+            if (2 * nt >= n_tiles)
             {
-                px = px_pack(p);
-                tx0 = p.x0 >> 3; tx1 = p.x1 >> 3; ty0 = p.y0 >> 2; ty1 = p.y1 >> 2;
-                const int nt = (tx1 - tx0 + 1) * (ty1 - ty0 + 1);
-                if (2 * nt >= n_tiles)
+                for (int q = 0; q < pe.n; ++q) *pe.all_flag[q] = vp.frame_id;
+                tx1 = tx0 - 1;
+            }
+            else if (nt > 48) big = true;
+            else
+            {
+                for (int ty = ty0; ty <= ty1; ++ty)
                 {
-                    for (int q = 0; q < pe.n; ++q) *pe.all_flag[q] = vp.frame_id;
-                    tx1 = tx0 - 1;
-                }
-                else if (nt > 48) big = true;
-                else
-                {
-                    for (int ty = ty0; ty <= ty1; ++ty)
-                    {
-                        const int o = owner(ty);
-                        if (o < 0 || (skip_stamps && o != pe.self)) continue;
-                        uint32_t* st = pe.stamps[o] + ty * vp.tiles_x;
-                        for (int tx = tx0; tx <= tx1; ++tx) st[tx] = vp.frame_id;
-                    }
+                    const int o = owner(ty);
+                    if (o < 0 || (skip_stamps && o != pe.self)) continue;
+                    uint32_t* st = pe.stamps[o] + ty * vp.tiles_x;
+                    for (int tx = tx0; tx <= tx1; ++tx) st[tx] = vp.frame_id;
                 }
             }
         }
-        for (int q = 0; q < pe.n; ++q)
-            if (!skip_ranges || q == pe.self) pe.tri_px[q][slot] = px;
-        if (view.tri_rect) view.tri_rect[slot] = r;
     }
     // large ranges: the whole warp stamps the tiles of one triangle at a time
     unsigned bm = __ballot_sync(FULL_MASK, big);
@@ -606,12 +629,22 @@ __global__ void __launch_bounds__(kBlock, 4) k_view_bounds(DevScene sc, ViewPara
         const int ax0 = __shfl_sync(FULL_MASK, tx0, src), ax1 = __shfl_sync(FULL_MASK, tx1, src);
         const int ay0 = __shfl_sync(FULL_MASK, ty0, src), ay1 = __shfl_sync(FULL_MASK, ty1, src);
         const int w = ax1 - ax0 + 1, n = w * (ay1 - ay0 + 1);
+        const float rw = __frcp_rn((float)w);
         for (int i = lane; i < n; i += 32)
         {
-            const int ty = ay0 + i / w, o = owner(ty);
-            if (o >= 0 && !(skip_stamps && o != pe.self)) pe.stamps[o][ty * vp.tiles_x + ax0 + i % w] = vp.frame_id;
+            int r = (int)(((float)i + 0.5f) * rw);   // i / w through the float reciprocal, corrected by one where it rounds off
+            if (r * w > i) --r;
+            if ((r + 1) * w <= i) ++r;
+            const int ty = ay0 + r, o = owner(ty);
+            if (o >= 0 && !(skip_stamps && o != pe.self)) pe.stamps[o][ty * vp.tiles_x + ax0 + (i - r * w)] = vp.frame_id;
         }
     }
+    __syncthreads();
+    // ---- 3: ranges per slot, packet and chunk
+    const uint2 px = s_slot_px[threadIdx.x];
+    if (in_range)
+        for (int q = 0; q < pe.n; ++q)
+            if (!skip_ranges || q == pe.self) pe.tri_px[q][slot] = px;
     uint2 p = px;
     p = px_union_xor(p, 4); p = px_union_xor(p, 2); p = px_union_xor(p, 1);
     if (in_range && (lane & 7) == 0)
@@ -633,14 +666,14 @@ __global__ void __launch_bounds__(kBlock, 4) k_view_bounds(DevScene sc, ViewPara
     }
     // chunk = the 32 packets of this block
     p = px_union_xor(p, 8); p = px_union_xor(p, 16);
-    __shared__ uint2 s_px[kBlock / 32];
-    if (lane == 0) s_px[threadIdx.x >> 5] = p;
+    __shared__ uint2 s_chunk[kBlock / 32];
+    if (lane == 0) s_chunk[threadIdx.x >> 5] = p;
     __syncthreads();
     if (threadIdx.x == 0)
     {
-        uint2 c = s_px[0];
+        uint2 c = s_chunk[0];
 #pragma unroll
-        for (int w = 1; w < kBlock / 32; ++w) c = px_union(c, s_px[w]);
+        for (int w = 1; w < kBlock / 32; ++w) c = px_union(c, s_chunk[w]);
         if (chunk < pe.block_hi || pe.block_hi == 0u)
             for (int q = 0; q < pe.n; ++q)
                 if (!skip_ranges || q == pe.self) pe.chunk_px[q][chunk] = c;
@@ -736,9 +769,29 @@ __global__ void __launch_bounds__(kBlock) k_view_nodes(DevScene sc, DevView view
             const int bx0 = (int)(acc.x & 0xffffu) >> kBinShiftX, by0 = (int)(acc.x >> 16) >> kBinShiftY;
             const int bx1 = (int)(acc.y & 0xffffu) >> kBinShiftX, by1 = (int)(acc.y >> 16) >> kBinShiftY;
             const int w = bx1 - bx0 + 1, n = w * (by1 - by0 + 1);
+            if (inner && n > kWideBins)
+            {
+                // near the root: one entry in the wide list (every tile checks it) instead of hundreds of bin entries
+                uint32_t at = 0;
+                if (lane == 0) at = atomicAdd(&view.busy_count[kCtlWide], 1u);
+                at = __shfl_sync(FULL_MASK, at, 0);
+                if (at < (uint32_t)kWideCap)
+                {
+                    if (lane == 0)
+                    {
+                        view.wide_inner[2 * at] = make_uint4(acc.x, acc.y, node, 0u);
+                        view.wide_inner[2 * at + 1] = make_uint4(__float_as_uint(sp4.x), __float_as_uint(sp4.y), __float_as_uint(sp4.z), 0u);
+                    }
+                    continue;
+                }
+            }
+            const float rw = __frcp_rn((float)w);   // i / w through the float reciprocal (corrected by one below)
             for (int i = lane; i < n; i += 32)
             {
-                const int by = by0 + i / w, bx = bx0 + i % w;
+                int r = (int)(((float)i + 0.5f) * rw);
+                if (r * w > i) --r;
+                if ((r + 1) * w <= i) ++r;
+                const int by = by0 + r, bx = bx0 + (i - r * w);
                 if (!owns_bin_row(part, by, cm.H)) continue;
                 const uint32_t b = (uint32_t)(by * view.bins_x + bx);
                 if (inner)
@@ -1092,6 +1145,7 @@ __device__ __forceinline__ void trace_tile_flat(const DevScene& sc, const DevScr
     }
     const uint32_t bin = (uint32_t)((tile_y0 >> kBinShiftY) * vw.bins_x + (tile_x0 >> kBinShiftX));
     const uint32_t nL = __ldg(&vw.bin_cnt[2 * bin]), nI = __ldg(&vw.bin_cnt[2 * bin + 1]);
+    const uint32_t nWI = min(__ldg(&vw.busy_count[kCtlWide]), (uint32_t)kWideCap);   // inner nodes near the root: one list for all bins
     if (nL > vw.bin_leaf_cap || nI > vw.bin_inner_cap)   // a list of this bin did not fit: the tile takes the unculled core
     {
         if (COUNT && active) wc.ovf++;
@@ -1105,13 +1159,14 @@ __device__ __forceinline__ void trace_tile_flat(const DevScene& sc, const DevScr
         const float tsx = mulr(subr(s.x, ray.ox), ix), tsy = mulr(subr(s.y, ray.oy), iy), tsz = mulr(subr(s.z, ray.oz), iz);
         risky = part && (tsx == tsy || tsy == tsz || tsx == tsz);
     }
-    for (uint32_t base = 0; base < nI; base += 32)
+    for (uint32_t base = 0; base < nWI + nI; base += 32)
     {
-        const bool valid = base + lane < nI;
+        const uint32_t idx = base + lane;
+        const bool valid = idx < nWI + nI;
         uint4 e0 = make_uint4(0xffffffffu, 0u, 0u, 0u), e1 = make_uint4(0u, 0u, 0u, 0u);
         if (valid)
         {
-            const uint4* e = vw.bin_inner + ((size_t)bin * vw.bin_inner_cap + base + lane) * 2;
+            const uint4* e = idx < nWI ? vw.wide_inner + (size_t)idx * 2 : vw.bin_inner + ((size_t)bin * vw.bin_inner_cap + (idx - nWI)) * 2;
             e0 = __ldg(e); e1 = __ldg(e + 1);
         }
         unsigned m = __ballot_sync(FULL_MASK, valid && px_overlap(make_uint2(e0.x, e0.y), tr));

@@ -121,10 +121,41 @@ ATRAY_HD float round_up_f(double x)
 #endif
 static constexpr int kMarginIters = ATRAY_MARGIN_ITERS;
 
+// Cheap single-precision pre-test: true ONLY IF tri_film_rect would return the empty rectangle because the triangle faces
+// away from the eye (its first rule: g + m|N| <= 0 with g = (a - eye).N, N = ac x ab). About half of a closed mesh passes, and
+// those slots then skip the double-precision path altogether (k_view_bounds compacts the rest).
+// With u = 2^-24 and S >= |ab||ac|, T >= |a - eye|, L >= max(|ab|, |ac|) (all rounded up):
+//   * |N| <= S, and for cS <= 1/4 (c = 8u(1+1e-6)/tau) the margin obeys m <= 1.34 [cS(2T + 2L) + 6uL] + uL + 1e-25
+//     <= 2.7 cS(T + L) + 10uL, hence m|N| <= S (2.7 cS(T + L) + 10uL);
+//   * g evaluated in float (w = a - eye, the cross product, the dot product: every operation rounded once) differs from the
+//     real g by at most 12u T S (each of the three terms carries <= 3 roundings of relative size u on magnitudes <= T S, plus
+//     the summation).
+// So g_float <= -(1 + 1e-3)[S (2.7 cS(T + L) + 10uL) + 12u T S] - 1e-30 implies g + m|N| <= 0. The norms are float square roots
+// of float sums of squares scaled by (1 + 1e-5); anything non-finite or out of range (overflow, S > 52, tiny values below the
+// absolute floor) simply fails the test and takes the exact path. The eye of ViewParams is a float value held in double.
+ATRAY_HD bool tri_backfacing_f32(const ViewParams& vp, const float* a, const float* ab, const float* ac)
+{
+    const float U = 5.9604644775390625e-8f;
+    const float wx = a[0] - (float)vp.eye[0], wy = a[1] - (float)vp.eye[1], wz = a[2] - (float)vp.eye[2];
+    const float nx = ac[1] * ab[2] - ac[2] * ab[1], ny = ac[2] * ab[0] - ac[0] * ab[2], nz = ac[0] * ab[1] - ac[1] * ab[0];
+    const float g = wx * nx + wy * ny + wz * nz;
+    const float k = 1.00001f;
+    const float lab = sqrtf(ab[0] * ab[0] + ab[1] * ab[1] + ab[2] * ab[2]) * k, lac = sqrtf(ac[0] * ac[0] + ac[1] * ac[1] + ac[2] * ac[2]) * k;
+    const float T = sqrtf(wx * wx + wy * wy + wz * wz) * k;
+    const float S = lab * lac * k, L = (lab > lac ? lab : lac);
+    const float c = 8.0f * U * 1.0001f / 9.9999e-5f;      // > 8u(1+1e-6)/tau
+    const float cS = c * S;
+    // (false for NaN too; coordinates beyond 2^30 take the exact path, which gives them the unbounded rectangle)
+    if (!(cS <= 0.25f) || !(T < 1e9f) || !(L < 1e9f) || !(fabsf(a[0]) < 1e9f && fabsf(a[1]) < 1e9f && fabsf(a[2]) < 1e9f)) return false;
+    const float bound = (S * (2.7f * cS * (T + L) + 10.0f * U * L) + 12.0f * U * T * S) * 1.001f + 1e-30f;
+    return g <= -bound;
+}
+
 // Film rectangle of one triangle record {a, ab, ac} (float values widened to double) for the view `vp`.
 ATRAY_HD FilmRect tri_film_rect(const ViewParams& vp, const float* a_f, const float* ab_f, const float* ac_f, FilmHull* hull = nullptr)
 {
     if (hull) *hull = film_hull_all();
+    if (tri_backfacing_f32(vp, a_f, ab_f, ac_f)) return film_rect_empty();
     const double U = 5.9604644775390625e-8;   // 2^-24
     const double TAU = 9.9999e-5;             // just below (double)1e-4f = 9.99999974738e-05
     const double BIG = 1073741824.0;          // 2^30: beyond this the products of the test may overflow → no bound

@@ -20,6 +20,7 @@ ap.add_argument("--world", type=int, default=1)
 ap.add_argument("--rank", type=int, default=0)
 ap.add_argument("--count", action="store_true")
 ap.add_argument("--host", action="store_true")
+ap.add_argument("--no-flush", action="store_true")
 args = ap.parse_args()
 W, H = 3840, 2160
 path = gen_standin_obj.ensure(os.path.join(os.environ.get("ATRAY_MESH_CACHE", "/tmp/atray_meshes"), "standin_272x256.obj"))
@@ -52,7 +53,8 @@ flush = ctx.dev_alloc(256 << 20)
 opts = ctx.opts(rank=args.rank, world=args.world, band_rows=8, raster=args.raster, count_work=args.count)
 ms, rms, vs = [], [], []
 for i in range(args.reps + 2):
-    ctx.dev_memset(flush, 0, 256 << 20)
+    if not args.no_flush:
+        ctx.dev_memset(flush, 0, 256 << 20)
     ctx.render_device(cam, opts, *planes)
     ctx.sync()
     if i >= 2:
