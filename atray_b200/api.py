@@ -116,6 +116,8 @@ _SIGS = {
     "atray_trace_rays": [_vp, _vp, _u64, _i, _i, _vp, _vp],
     "atray_trace_rays_device": [_vp, _vp, _u64, _i, _i, _vp, _vp],
     "atray_get_counters": [_vp, C.POINTER(Counters)],
+    "atray_trace_incoherent_device": [_vp, _u64, _u64, _u, _u64, C.POINTER(Partition), _u, _i, _i, _vp, _vp, _vp],
+    "atray_trace_incoherent": [_vp, _u64, _u64, _u, _u64, _i, _i, _vp, _vp, _vp],
     "atray_dev_alloc": [_vp, _sz, C.POINTER(_vp)],
     "atray_dev_free": [_vp, _vp],
     "atray_dev_copy_to_host": [_vp, _vp, _vp, _sz],

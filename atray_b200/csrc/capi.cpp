@@ -1166,6 +1166,62 @@ int atray_trace_rays(atray_ctx* c, const float* rays, uint64_t n, int32_t fp_mod
     return ATRAY_OK;
 }
 
+// ---- C5: incoherent rays generated on the device (BASELINE.json configs[4]) --------------------------------------------------
+int atray_trace_incoherent_device(atray_ctx* c, uint64_t p0, uint64_t p1, uint32_t spp, uint64_t seed, const AtrayPartition* part,
+                                  uint32_t chunk_px, int32_t fp_mode, int32_t count_work, uint32_t* bgrx_dev, uint32_t* prim_dev, float* t_dev)
+{
+    if (!c) return fail(ATRAY_EINVAL, "null context");
+    if (!c->has_scene) return fail(ATRAY_ESTATE, "trace before scene_upload");
+    if (p1 < p0 || spp == 0 || chunk_px == 0) return fail(ATRAY_EINVAL, "bad pixel range, sample count or chunk size");
+    if ((p1 - p0) / chunk_px + 2 > (uint64_t(1) << 31) / chunk_px) return fail(ATRAY_EINVAL, "pixel range too long for one call (split it)");
+    AtrayPartition pt{0, 1, 8};
+    if (part) pt = *part;
+    if (pt.world < 1 || pt.rank < 0 || pt.rank >= pt.world) return fail(ATRAY_EINVAL, "bad partition");
+    if (p1 == p0) return ATRAY_OK;
+    CU(cudaSetDevice(c->device));
+    DevCounters* ctr = nullptr;
+    if (count_work)
+    {
+        CU(cudaMemsetAsync(c->d_counters, 0, sizeof(DevCounters), c->stream));
+        ctr = c->d_counters;
+        c->counters_valid = true;
+    }
+    CU(cudaEventRecord(c->ev_k0, c->stream));
+    CU(launch_c5(c->scene, p0, p1, spp, chunk_px, seed, DevPartition{pt.rank, pt.world, pt.band_rows}, bgrx_dev, prim_dev, t_dev, c->scratch,
+                 c->d_tile_counter, ctr, fp_mode == ATRAY_FP_FAST, c->cfg, c->stream));
+    CU(cudaEventRecord(c->ev_k1, c->stream));
+    c->have_kernel_time = true;
+    c->have_split = false;
+    return ATRAY_OK;
+}
+
+int atray_trace_incoherent(atray_ctx* c, uint64_t p0, uint64_t p1, uint32_t spp, uint64_t seed, int32_t fp_mode, int32_t count_work,
+                           uint32_t* bgrx, uint32_t* prim, float* t)
+{
+    if (!c) return fail(ATRAY_EINVAL, "null context");
+    if (p1 < p0) return fail(ATRAY_EINVAL, "bad pixel range");
+    if (p1 == p0) return ATRAY_OK;
+    CU(cudaSetDevice(c->device));
+    const uint64_t npx = p1 - p0, nrays = npx * spp;
+    uint32_t *d_b = nullptr, *d_p = nullptr;
+    float* d_t = nullptr;
+    if (bgrx) CU(cudaMalloc(&d_b, npx * 4));
+    if (prim) CU(cudaMalloc(&d_p, nrays * 4));
+    if (t) CU(cudaMalloc(&d_t, nrays * 4));
+    int rc = atray_trace_incoherent_device(c, p0, p1, spp, seed, nullptr, 4096, fp_mode, count_work, d_b, d_p, d_t);
+    if (rc == ATRAY_OK)
+    {
+        cudaError_t e = cudaSuccess;
+        if (bgrx) e = cudaMemcpyAsync(bgrx, d_b, npx * 4, cudaMemcpyDeviceToHost, c->stream);
+        if (e == cudaSuccess && prim) e = cudaMemcpyAsync(prim, d_p, nrays * 4, cudaMemcpyDeviceToHost, c->stream);
+        if (e == cudaSuccess && t) e = cudaMemcpyAsync(t, d_t, nrays * 4, cudaMemcpyDeviceToHost, c->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+        if (e != cudaSuccess) rc = cuda_fail(e, "incoherent trace");
+    }
+    cudaFree(d_b); cudaFree(d_p); cudaFree(d_t);
+    return rc;
+}
+
 int atray_get_counters(atray_ctx* c, AtrayCounters* out)
 {
     if (!c || !out) return fail(ATRAY_EINVAL, "null argument");

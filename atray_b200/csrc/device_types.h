@@ -217,6 +217,10 @@ cudaError_t launch_path(const DevScene& sc, const DevCamera& cam, const DevParti
 cudaError_t launch_trace(const DevScene& sc, const float* rays, unsigned long long n, uint32_t* prim, float* t,
                          const DevScratch& scratch, unsigned int* tile_counter, DevCounters* counters, int fp_fast,
                          LaunchCfg cfg, cudaStream_t stream);
+// K2b: C5 — `spp` incoherent rays per pixel index in [p0, p1), generated on the device, traced, reduced to the pixel colour
+cudaError_t launch_c5(const DevScene& sc, unsigned long long p0, unsigned long long p1, uint32_t spp, uint32_t chunk_px,
+                      unsigned long long seed, const DevPartition& part, uint32_t* bgrx, uint32_t* prim, float* t, const DevScratch& scratch,
+                      unsigned int* counter, DevCounters* counters, int fp_fast, LaunchCfg cfg, cudaStream_t stream);
 cudaError_t launch_microbench_fp32(float* sink, int iters, LaunchCfg cfg, cudaStream_t stream);
 cudaError_t launch_microbench_l2(const float4* buf, size_t n_vec, int passes, float* sink, LaunchCfg cfg, cudaStream_t stream);
 LaunchCfg render_launch_cfg(int sm_count);

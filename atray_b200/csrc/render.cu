@@ -1500,6 +1500,102 @@ __global__ void __launch_bounds__(kBlock) k_trace(DevScene sc, const float* __re
     if (COUNT) flush_counters(counters, wc, rays_done);
 }
 
+// ---- K2b: C5, incoherent random-direction rays (BASELINE.json configs[4]) -------------------------------------
+// `spp` rays per pixel index p, generated on the device from the per-ray PCG32 stream {splitmix64(seed ^ i), 2i + 1}, i = p*spp + s
+// (six rand_bi draws: a direction for the origin on a sphere around the model box, a target inside the box; SetRay, ray.h:24-29)
+// (include/atray_b200.h: atray_trace_incoherent_device states the definition), traced through the model query of get_intersection_data
+// (renderer.cpp:41-57) on the warp-cooperative core, and reduced to the pixel's flat colour: sequential f32 sum of the
+// samples' emissions / spp, clamp, truncate, pack (renderer.cpp:358-365). One warp per pixel, 32 samples at a time. The
+// pixels of a rank are contiguous chunks of `chunk_px` pixels dealt round-robin (chunk k -> rank k % world).
+struct DevC5
+{
+    unsigned long long p0, p1;      // pixel indices [p0, p1) of the whole job
+    uint32_t spp, chunk_px;
+    unsigned long long seed;
+    uint32_t* bgrx;                 // per pixel, indexed p - p0 (may be a peer pointer: GPU 0's plane)
+    uint32_t* prim;                 // per ray, indexed (p - p0)*spp + s, or null
+    float* t;                       // likewise
+};
+
+template <bool STRICT, bool COUNT>
+__global__ void __launch_bounds__(kBlock) k_c5(DevScene sc, DevC5 job, DevPartition part, DevScratch scratch, unsigned int* counter,
+                                               DevCounters* counters)
+{
+    const int lane = threadIdx.x & 31;
+    const int warp_slot = (blockIdx.x * kBlock + threadIdx.x) >> 5;
+    WorkCount wc;
+    wc.clear();
+    uint2 leaves[kLeafCap];
+    uint32_t stack[kStackCap];
+    unsigned int rays_done = 0;
+    // box centre, half extent and radius of the origin sphere: c = (lo + hi)*0.5, extent = hi - lo, R = 1.5*mag(extent)
+    const float cx = mulr(addr(sc.aabb_lo[0], sc.aabb_hi[0]), 0.5f), cy = mulr(addr(sc.aabb_lo[1], sc.aabb_hi[1]), 0.5f),
+                cz = mulr(addr(sc.aabb_lo[2], sc.aabb_hi[2]), 0.5f);
+    const float ex = subr(sc.aabb_hi[0], sc.aabb_lo[0]), ey = subr(sc.aabb_hi[1], sc.aabb_lo[1]), ez = subr(sc.aabb_hi[2], sc.aabb_lo[2]);
+    const float R = mulr(1.5f, __fsqrt_rn(addr(addr(mulr(ex, ex), mulr(ey, ey)), mulr(ez, ez))));
+    const float hx = mulr(ex, 0.5f), hy = mulr(ey, 0.5f), hz = mulr(ez, 0.5f);
+    // pixels of this rank: local index j -> chunk j / chunk_px of this rank = global chunk (j / chunk_px)*world + rank
+    const unsigned long long n_px = job.p1 - job.p0;
+    const unsigned long long n_chunks = (n_px + job.chunk_px - 1) / job.chunk_px;
+    const unsigned long long my_chunks = (unsigned long long)part.rank < n_chunks ? (n_chunks - part.rank + part.world - 1) / part.world : 0ull;
+    for (;;)
+    {
+        unsigned int j = 0;
+        if (lane == 0) j = atomicAdd(counter, 1u);
+        j = __shfl_sync(FULL_MASK, j, 0);
+        const unsigned long long lc = j / job.chunk_px;
+        if (lc >= my_chunks) break;
+        const unsigned long long rel = (lc * part.world + part.rank) * job.chunk_px + (j - lc * job.chunk_px);   // pixel - p0
+        if (rel >= n_px) continue;
+        const unsigned long long p = job.p0 + rel;
+        float cr = 0.0f, cg = 0.0f, cb = 0.0f;   // lane 0: the pixel's running sum
+        for (uint32_t s0 = 0; s0 < job.spp; s0 += 32)
+        {
+            const uint32_t s = s0 + lane;
+            const bool active = s < job.spp;
+            const unsigned long long i = p * job.spp + s;
+            Pcg rng;
+            rng.state = splitmix64(job.seed ^ i);
+            rng.stream = 2ULL * i + 1ULL;
+            const float b0 = pcg_bi(rng), b1 = pcg_bi(rng), b2 = pcg_bi(rng), q0 = pcg_bi(rng), q1 = pcg_bi(rng), q2 = pcg_bi(rng);
+            const float binv = __fdiv_rn(1.0f, __fsqrt_rn(addr(addr(mulr(b0, b0), mulr(b1, b1)), mulr(b2, b2))));
+            RayL ray;
+            ray.ox = addr(cx, mulr(mulr(b0, binv), R)); ray.oy = addr(cy, mulr(mulr(b1, binv), R)); ray.oz = addr(cz, mulr(mulr(b2, binv), R));
+            const float tx = addr(cx, mulr(hx, q0)), ty = addr(cy, mulr(hy, q1)), tz = addr(cz, mulr(hz, q2));
+            const float dx = subr(tx, ray.ox), dy = subr(ty, ray.oy), dz = subr(tz, ray.oz);
+            const float dinv = __fdiv_rn(1.0f, __fsqrt_rn(addr(addr(mulr(dx, dx), mulr(dy, dy)), mulr(dz, dz))));
+            ray.dx = mulr(dx, dinv); ray.dy = mulr(dy, dinv); ray.dz = mulr(dz, dinv);
+            float t;
+            uint32_t face;
+            trace_warp<STRICT, COUNT>(sc, scratch, warp_slot, lane, active, ray, leaves, stack, t, face, wc);
+            // get_intersection_data accepts the model's distance iff t > tolerance && t < MAX_FLOAT (renderer.cpp:52)
+            const bool hit = active && face != 0xffffffffu && t > kTol && t < kMaxFloat;
+            if (active)
+            {
+                if (job.prim) job.prim[rel * job.spp + s] = face;
+                if (job.t) job.t[rel * job.spp + s] = t;
+                rays_done += 1;
+            }
+            const unsigned hm = __ballot_sync(FULL_MASK, hit);
+            if (lane == 0)
+            {
+                const uint32_t n = min(32u, job.spp - s0);
+                for (uint32_t k = 0; k < n; ++k)   // the samples in order: a sequential f32 sum (renderer.cpp:353-357)
+                {
+                    const bool h = (hm >> k) & 1u;
+                    cr = addr(cr, h ? sc.mdl[0] : sc.sky[0]); cg = addr(cg, h ? sc.mdl[1] : sc.sky[1]); cb = addr(cb, h ? sc.mdl[2] : sc.sky[2]);
+                }
+            }
+        }
+        if (lane == 0 && job.bgrx)
+        {
+            const float n = (float)job.spp;
+            job.bgrx[rel] = pack_bgrx(__fdiv_rn(cr, n), __fdiv_rn(cg, n), __fdiv_rn(cb, n));
+        }
+    }
+    if (COUNT) flush_counters(counters, wc, rays_done);
+}
+
 // ---- K3: multi-bounce path ------------------------------------------------------------------------
 // get_intersection_data in full (renderer.cpp:34-160: model through the tree, then spheres, then planes, hit-type
 // priority plane > sphere > model > sky, smooth or flat triangle normal) and cast_ray at any bounce_limit
@@ -2008,6 +2104,27 @@ cudaError_t launch_trace(const DevScene& sc, const float* rays, unsigned long lo
     {
         if (fp_fast) k_trace<false, false><<<cfg.grid, cfg.block, 0, stream>>>(sc, rays, n, prim, t, scratch, tile_counter, counters);
         else k_trace<true, false><<<cfg.grid, cfg.block, 0, stream>>>(sc, rays, n, prim, t, scratch, tile_counter, counters);
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t launch_c5(const DevScene& sc, unsigned long long p0, unsigned long long p1, uint32_t spp, uint32_t chunk_px,
+                      unsigned long long seed, const DevPartition& part, uint32_t* bgrx, uint32_t* prim, float* t, const DevScratch& scratch,
+                      unsigned int* counter, DevCounters* counters, int fp_fast, LaunchCfg cfg, cudaStream_t stream)
+{
+    cudaError_t e = cudaMemsetAsync(counter, 0, sizeof(unsigned int), stream);
+    if (e != cudaSuccess) return e;
+    DevC5 job;
+    job.p0 = p0; job.p1 = p1; job.spp = spp; job.chunk_px = chunk_px; job.seed = seed; job.bgrx = bgrx; job.prim = prim; job.t = t;
+    if (counters)
+    {
+        if (fp_fast) k_c5<false, true><<<cfg.grid, cfg.block, 0, stream>>>(sc, job, part, scratch, counter, counters);
+        else k_c5<true, true><<<cfg.grid, cfg.block, 0, stream>>>(sc, job, part, scratch, counter, counters);
+    }
+    else
+    {
+        if (fp_fast) k_c5<false, false><<<cfg.grid, cfg.block, 0, stream>>>(sc, job, part, scratch, counter, counters);
+        else k_c5<true, false><<<cfg.grid, cfg.block, 0, stream>>>(sc, job, part, scratch, counter, counters);
     }
     return cudaGetLastError();
 }

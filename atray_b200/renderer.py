@@ -153,6 +153,20 @@ class Context:
     def trace_rays_device(self, d_rays, n, d_prim, d_t, fp_mode=api.FP_STRICT, count_work=False):
         _ck(_L.atray_trace_rays_device(self.h, d_rays, n, fp_mode, 1 if count_work else 0, d_prim, d_t))
 
+    def trace_incoherent(self, p0, p1, spp, seed=api.DEFAULT_SEED, fp_mode=api.FP_STRICT, count_work=False, want=("bgrx", "prim", "t")):
+        """C5: `spp` device-generated incoherent rays per pixel index in [p0, p1) → dict of bgrx (per pixel), prim, t (per ray)."""
+        n = (p1 - p0) * spp
+        out = {"bgrx": np.zeros(p1 - p0, np.uint32) if "bgrx" in want else None, "prim": np.zeros(n, np.uint32) if "prim" in want else None,
+               "t": np.zeros(n, np.float32) if "t" in want else None}
+        _ck(_L.atray_trace_incoherent(self.h, p0, p1, spp, seed, fp_mode, 1 if count_work else 0, _p(out["bgrx"]), _p(out["prim"]), _p(out["t"])))
+        return out
+
+    def trace_incoherent_device(self, p0, p1, spp, d_bgrx=0, d_prim=0, d_t=0, seed=api.DEFAULT_SEED, rank=0, world=1, chunk_px=4096,
+                                fp_mode=api.FP_STRICT, count_work=False):
+        part = api.Partition(rank, world, 8)
+        _ck(_L.atray_trace_incoherent_device(self.h, p0, p1, spp, seed, C.byref(part), chunk_px, fp_mode, 1 if count_work else 0,
+                                             d_bgrx or None, d_prim or None, d_t or None))
+
     # -- memory -------------------------------------------------------------------------------------------------------
     def dev_alloc(self, nbytes):
         p = _vp()

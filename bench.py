@@ -26,16 +26,46 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-W, H, SPP = 3840, 2160, 1
+W, H, SPP, AA = 3840, 2160, 1, 0
 BAND_ROWS = 8
 METRIC = "Mrays/s primary rays (Dragon 139k tris, 4K)"
 WORKLOAD = "C4: Dragon stand-in (standin-v1, 139264 faces) 3840x2160 1spp primary rays, SAH cap 300"
 MESH_CACHE = os.environ.get("ATRAY_MESH_CACHE", "/tmp/atray_meshes")
+MESH, RESCALE, CONFIG = "standin", 0.0, "c4"
+ASSETS = os.path.join(ROOT, "oracle", "_ref", "assets")     # the reference's own .obj files, staged by oracle/ref/build_ref.sh
+C5_SPP, C5_CHUNK = 64, 4096
+
+# BASELINE.json configs[0..4]. The headline (and the default) is c4; c1-c3 are the smaller frames, c5 the divergence stress.
+CONFIGS = {
+    "c1": dict(mesh="Simple", rescale=40.0, w=640, h=360, spp=1, aa=0,
+               workload="C1: Simple.obj (0 faces: every ray misses) 640x360 1spp primary rays"),
+    "c2": dict(mesh="Monkey", rescale=40.0, w=1920, h=1080, spp=1, aa=0,
+               workload="C2: Monkey.obj (3936 faces) 1920x1080 1spp primary rays, SAH cap 300"),
+    "c3": dict(mesh="Deer", rescale=40.0, w=1920, h=1080, spp=16, aa=1,
+               workload="C3: Deer.obj (1570 faces) 1920x1080 16spp jittered primary rays, SAH cap 300"),
+    "c4": dict(mesh="standin", rescale=0.0, w=3840, h=2160, spp=1, aa=0, workload=WORKLOAD),
+    "c5": dict(mesh="standin", rescale=0.0, w=3840, h=2160, spp=C5_SPP, aa=0,
+               workload="C5: Dragon stand-in (standin-v1, 139264 faces) 3840x2160 x 64 incoherent random-direction rays per pixel "
+                        "(device-generated per-ray PCG32 stream, SURVEY 8d), SAH cap 300"),
+}
+
+
+def apply_config(name):
+    global W, H, SPP, AA, WORKLOAD, MESH, RESCALE, CONFIG, METRIC
+    c = CONFIGS[name]
+    W, H, SPP, AA, WORKLOAD, MESH, RESCALE, CONFIG = c["w"], c["h"], c["spp"], c["aa"], c["workload"], c["mesh"], c["rescale"], name
+    if name != "c4":
+        METRIC = "Mrays/s (%s)" % name.upper()
 
 
 def mesh_path():
-    from tools import gen_standin_obj
-    return gen_standin_obj.ensure(os.path.join(MESH_CACHE, "standin_272x256.obj"))
+    if MESH == "standin":
+        from tools import gen_standin_obj
+        return gen_standin_obj.ensure(os.path.join(MESH_CACHE, "standin_272x256.obj"))
+    p = os.path.join(ASSETS, MESH + ".obj")
+    if not os.path.exists(p):
+        raise SystemExit("config %s needs %s (staged by oracle/ref/build_ref.sh where /root/reference exists)" % (CONFIG, p))
+    return p
 
 
 def host_threads():
@@ -128,28 +158,31 @@ def cpu_scene():
     from oracle import bind as B
     path = mesh_path()
     if B.ref_available():
-        return B, B.Scene(B.ref(), path, loader_threads=min(8, host_threads()), rescale=0.0), "reference"
+        return B, B.Scene(B.ref(), path, loader_threads=1 if MESH in ("Simple", "Cube") else min(8, host_threads()), rescale=RESCALE), "reference"
     if not B.port_available():
         subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle"), "liboracle.so"], stdout=subprocess.DEVNULL)
-    return B, B.Scene(B.port(), path, rescale=0.0), "port"
+    return B, B.Scene(B.port(), path, rescale=RESCALE), "port"
 
 
 def cpu_frame_seconds(scene, kind, threads):
     """One full 4K frame on the host cores. reference: through start_render_from_camera / wait_… with `threads` pool
     threads (renderer.cpp:403-471); port: the oracle's row-parallel loop."""
     if kind == "reference":
-        _, sec, _ = scene.render(W, H, threads=threads)
+        _, sec, _ = scene.render(W, H, spp=SPP, aa=AA, threads=threads)
         return sec
     t0 = time.perf_counter()
-    scene.trace_primary(W, H, threads=threads)
+    if AA:
+        scene.render_jitter(W, H, SPP, 0x853C49E6748FEA9B, threads=threads)
+    else:
+        scene.trace_primary(W, H, threads=threads)
     return time.perf_counter() - t0
 
 
 def base_line(n_gpus, steps, warmup):
     return {"metric": METRIC, "unit": "Mrays/s", "n_gpus": n_gpus, "steps": steps, "warmup": warmup,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "resolution": [W, H], "spp": SPP, "bounce_limit": 1, "tree": "SAH/300",
-                       "mesh": "standin-v1 (Assets/Dragon.obj absent from the reference checkout)"}}
+            "config": {"workload": WORKLOAD, "name": CONFIG, "resolution": [W, H], "spp": SPP, "anti_aliasing": AA, "bounce_limit": 1, "tree": "SAH/300",
+                       "mesh": "standin-v1 (Assets/Dragon.obj absent from the reference checkout)" if MESH == "standin" else "Assets/%s.obj" % MESH}}
 
 
 def run_reference(args):
@@ -166,7 +199,7 @@ def run_reference(args):
     line = base_line(args.gpus, args.steps, args.warmup)
     line.update({"impl": "reference", "value": val, "ms_per_step": 1e3 * total / len(secs),
                  "cpu_baseline": {"value": val, "unit": "Mrays/s", "cores": threads, "kind": kind,
-                                  "sample": "%d full 4K frames (8294400 rays each) through the reference's tile thread pool" % len(secs)},
+                                  "sample": "%d full frames (%d rays each) through the reference's tile thread pool" % (len(secs), W * H * SPP)},
                  "e2e": {"value": val, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                  "gpu_launches": 0})
     line["config"]["host_threads"] = threads
@@ -234,13 +267,13 @@ def run_ours(args):
         dist.barrier()
         path = mesh_path()
     t_setup = time.perf_counter()
-    model = A.load_model_data(path, min(8, host_threads()))
-    A.place_default(model, rescale=0.0)               # app.cpp:68-72 (no resize for the dragon)
+    model = A.load_model_data(path, 1 if MESH in ("Simple", "Cube") else min(8, host_threads()))
+    A.place_default(model, rescale=RESCALE)           # app.cpp:68-72 (no resize for the dragon; SURVEY 8d placement for the others)
     scene = A.Scene(model, division_method=A.DIV_SAH, max_no_faces_per_node=300)
     A.prep_scene(scene, device=local_rank)            # build + flatten + upload once
     setup_s = time.perf_counter() - t_setup
     ctx = scene.ctx
-    cam = A.set_camera(W, H, samples_per_pixel=SPP)
+    cam = A.set_camera(W, H, samples_per_pixel=SPP, anti_aliasing=AA)
     # GPU 0 gathers the BGRX bitmap (what the live view shows, north_star); t and primitive ids stay on the rank that
     # traced them: 4 instead of 12 bytes per pixel cross NVLink into GPU 0 (device-resident leg; the e2e leg writes the host
     # bitmap directly from every rank, see below)
@@ -430,8 +463,8 @@ def run_ours(args):
             cpu_frame_seconds(cscene, kind, threads)
             secs = [cpu_frame_seconds(cscene, kind, threads) for _ in range(3)]
             cpu_baseline = {"value": W * H * SPP / min(secs) / 1e6, "unit": "Mrays/s", "cores": threads, "kind": kind,
-                            "sample": "3 full 4K frames (8294400 primary rays each) after 1 warm-up, best of 3, "
-                                      "reference tile thread pool with %d threads" % threads,
+                            "sample": "3 full frames (%d primary rays each) after 1 warm-up, best of 3, "
+                                      "reference tile thread pool with %d threads" % (W * H * SPP, threads),
                             "seconds": secs}
         line = base_line(args.gpus, args.steps, args.warmup)
         line.update({"impl": "ours", "value": value, "ms_per_step": dev_ms_max / args.steps, "e2e": e2e, "roofline": roofline,
@@ -457,6 +490,189 @@ def run_ours(args):
     if share is not None:
         ctx.view_share_check()
         share.close()
+    gather.close()
+    if dist is not None:
+        dist.destroy_process_group()
+    if rank == 0:
+        emit(line)
+
+
+# ---- C5: 64 incoherent rays per pixel index (BASELINE.json configs[4]) ------------------------------------------------------
+C5_SEED = 0x853C49E6748FEA9B
+
+
+def c5_cpu_sample(n_px, threads):
+    """The reference's own traversal + triangle test (oracle/_ref: get_ray_kd_tree_intersection through get_intersection_data)
+    on the C5 rays of `n_px` pixel indices from the middle of the frame — rays written out by the oracle's restatement of the
+    stream, which is not timed. Returns (Mrays/s, kind, rays, seconds)."""
+    from oracle import bind as B
+    path = mesh_path()
+    if not B.port_available():
+        subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle"), "liboracle.so"], stdout=subprocess.DEVNULL)
+    port = B.Scene(B.port(), path, rescale=RESCALE)
+    p0 = W * H // 2
+    _, _, _, rays = port.trace_c5(p0, p0 + n_px, C5_SPP, C5_SEED, threads=threads, want_rays=True)
+    if B.ref_available():
+        sc, kind = B.Scene(B.ref(), path, loader_threads=min(8, threads), rescale=RESCALE), "reference"
+    else:
+        sc, kind = port, "port"
+    sc.trace_rays(rays[:4096], threads=threads)
+    t0 = time.perf_counter()
+    sc.trace_rays(rays, threads=threads)
+    sec = time.perf_counter() - t0
+    return rays.shape[0] / sec / 1e6, kind, int(rays.shape[0]), sec
+
+
+def run_reference_c5(args):
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    threads = host_threads()
+    vals = [c5_cpu_sample(16384, threads) for _ in range(max(1, min(args.steps, 3)))]
+    val = float(np.mean([v[0] for v in vals]))
+    line = base_line(args.gpus, args.steps, args.warmup)
+    line.update({"impl": "reference", "value": val, "ms_per_step": 1e3 * W * H * C5_SPP / (val * 1e6),
+                 "cpu_baseline": {"value": val, "unit": "Mrays/s", "cores": threads, "kind": vals[0][1],
+                                  "sample": "%d rays (the 64 rays of 16384 pixel indices from the middle of the frame) per step through the "
+                                            "reference's traversal + triangle test, %d threads; ms_per_step = the full 531 M-ray step at that rate"
+                                            % (vals[0][2], threads)},
+                 "e2e": {"value": val, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0})
+    line["config"]["host_threads"] = threads
+    emit(line)
+
+
+def run_ours_c5(args):
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    dist = None
+    if world > 1:
+        import torch
+        import torch.distributed as dist_mod
+        torch.cuda.set_device(local_rank)
+        dist_mod.init_process_group(backend="nccl", device_id=torch.device("cuda", local_rank))
+        dist = dist_mod
+    if args.gpus != world:
+        raise SystemExit("--gpus %d but WORLD_SIZE=%d (launch N>1 with torch.distributed.run)" % (args.gpus, world))
+    import atray_b200 as A
+    from atray_b200 import multi
+    fp_mode = A.FP_FAST if args.fp == "fast" else A.FP_STRICT
+    path = mesh_path() if rank == 0 else None
+    if dist is not None:
+        dist.barrier()
+        path = mesh_path()
+    t_setup = time.perf_counter()
+    model = A.load_model_data(path, min(8, host_threads()))
+    A.place_default(model, rescale=RESCALE)
+    scene = A.Scene(model, division_method=A.DIV_SAH, max_no_faces_per_node=300)
+    A.prep_scene(scene, device=local_rank)
+    setup_s = time.perf_counter() - t_setup
+    ctx = scene.ctx
+    n_px = W * H
+    # the pixel-colour plane lives on GPU 0; every rank stores the colours of its chunks into it (peer stores over NVLink)
+    gather = multi.FrameGather(ctx, dist, rank, world, W, H, planes=("bgrx",))
+    d_bgrx = gather.planes["bgrx"]
+    my_px = sum(min(C5_CHUNK, n_px - k * C5_CHUNK) for k in range(rank, (n_px + C5_CHUNK - 1) // C5_CHUNK, world))
+
+    def barrier():
+        ctx.sync()
+        if dist is not None:
+            import torch
+            torch.cuda.synchronize()
+            dist.barrier()
+
+    def step():
+        ctx.trace_incoherent_device(0, n_px, C5_SPP, d_bgrx, 0, 0, seed=C5_SEED, rank=rank, world=world, chunk_px=C5_CHUNK, fp_mode=fp_mode)
+
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    per_step_ms = []
+    d_flush = ctx.dev_alloc(256 << 20)
+    for _ in range(args.steps):
+        ctx.dev_memset(d_flush, 0, 256 << 20)     # L2 flushed between the timed steps (outside the step's event pair)
+        step()
+        per_step_ms.append(ctx.last_kernel_ms())
+    ctx.dev_free(d_flush)
+    barrier()
+    if dist is not None:
+        import torch
+        mine = torch.tensor(per_step_ms, dtype=torch.float64, device="cuda")
+        allsteps = [torch.zeros_like(mine) for _ in range(world)]
+        dist.all_gather(allsteps, mine)
+        by_rank = torch.stack(allsteps).cpu().numpy()
+    else:
+        by_rank = np.array([per_step_ms])
+    dev_ms_max = float(by_rank.max(axis=0).sum())
+    total_rays = n_px * C5_SPP * args.steps
+    value = total_rays / (dev_ms_max * 1e-3) / 1e6
+    # end to end: the same step through the host-facing call — every rank traces its chunks, then the colour plane (on GPU 0)
+    # is copied to a pinned host bitmap
+    tex = A.PinnedArray((H, W), np.uint32) if rank == 0 else None
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step()
+        barrier()
+        if rank == 0:
+            ctx.to_host(d_bgrx, tex.array)
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    clocks = sampler.stop() if rank == 0 else None
+    line = None
+    if rank == 0:
+        # parity inside the bench: the colours of a sub-range against the oracle (outside the timed regions)
+        check = None
+        try:
+            from oracle import bind as B
+            o = B.Scene(B.port(), path, rescale=RESCALE)
+            _, _, ref_px = o.trace_c5(n_px // 2, n_px // 2 + 2048, C5_SPP, C5_SEED, threads=host_threads())
+            check = bool((tex.array.reshape(-1)[n_px // 2:n_px // 2 + 2048] == ref_px).all())
+        except Exception as e:   # the checker is optional here (tests/ pins the path)
+            check = "not checked: %s" % e
+        sub = 65536
+        d_tmp = ctx.dev_alloc(sub * 4)
+        ctx.trace_incoherent_device(n_px // 2, n_px // 2 + sub, C5_SPP, d_tmp, 0, 0, seed=C5_SEED, fp_mode=fp_mode, count_work=True)
+        ctx.sync()
+        ctr = ctx.counters()
+        ctx.dev_free(d_tmp)
+        ops_ray, bytes_ray = ops_and_bytes_per_ray(ctr)
+        k0 = ctx.microbench()
+        hbm_peak, peak_src = measured_peaks()
+        launch_ms = float(np.mean(per_step_ms))
+        achieved_gbs = bytes_ray * my_px * C5_SPP / (launch_ms * 1e-3) / 1e9
+        fp32_achieved = ops_ray * my_px * C5_SPP / (launch_ms * 1e-3)
+        roofline = {"bound": "hbm", "bound_note": "nominal: the scene (12 MB) is L2-resident; the kernel is bound by divergent instruction issue",
+                    "achieved": achieved_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": achieved_gbs / hbm_peak, "traffic": None,
+                    "peak_source": peak_src, "kernel": "k_c5<STRICT>" if args.fp == "strict" else "k_c5<FAST>", "kernel_ms_per_launch": launch_ms,
+                    "kernel_share_of_step": 1.0, "algorithmic_bytes_per_ray": bytes_ray, "algorithmic_fp32_ops_per_ray": ops_ray,
+                    "fp32": {"achieved_lane_ops_per_s": fp32_achieved, "peak_lane_ops_per_s": k0["fp32_lane_ops_per_s"],
+                             "frac": fp32_achieved / k0["fp32_lane_ops_per_s"], "peak_source": "K0 FFMA microbenchmark, this run"},
+                    "l2_read_gbs_measured": k0["l2_read_gbs"],
+                    "note": "counters of a 65536-pixel sub-range (4.2 M rays): 32 B per box test + 48 B per triangle test + 4 B/64 output per ray"}
+        cpu_baseline = None
+        if world == 1 and not args.no_cpu_baseline:
+            v, kind, nr, sec = c5_cpu_sample(16384, host_threads())
+            cpu_baseline = {"value": v, "unit": "Mrays/s", "cores": host_threads(), "kind": kind,
+                            "sample": "%d rays (64 per pixel index, 16384 pixel indices) in %.1f s" % (nr, sec)}
+        line = base_line(args.gpus, args.steps, args.warmup)
+        line.update({"impl": "ours", "value": value, "ms_per_step": dev_ms_max / args.steps, "scaling": "strong",
+                     "e2e": {"value": total_rays / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": 64, "d2h_bytes_per_step": n_px * 4,
+                             "ms_per_step": 1e3 * e2e_s / args.steps,
+                             "note": "rays are generated on the device from the per-ray stream (input = the job description); output = the "
+                                     "pixel-colour plane copied from GPU 0 to a pinned host bitmap every step"},
+                     "roofline": roofline, "cpu_baseline": cpu_baseline, "clocks": clocks, "gpu_launches": args.steps * world,
+                     "ms_per_step_by_rank": [float(x) for x in by_rank.mean(axis=1)], "colours_equal_oracle_on_2048_pixels": check,
+                     "counters_sub_range": ctr, "setup_s": setup_s})
+        line["config"].update({"fp_mode": args.fp, "parallelism": "chunks%d" % world, "chunk_px": C5_CHUNK, "rays_per_step": n_px * C5_SPP,
+                               "timing": "CUDA events on the library's stream around each step's launch; per step the MAX over the ranks",
+                               "l2": "flushed between timed steps (256 MiB device memset outside the per-step event pair)",
+                               "gather": "pixel colours: peer stores into GPU 0's plane (CUDA IPC)" if world > 1 else "none (1 GPU)"})
+    barrier()
+    if tex is not None:
+        tex.free()
     gather.close()
     if dist is not None:
         dist.destroy_process_group()
@@ -492,11 +708,20 @@ def main():
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--fp", choices=["strict", "fast"], default="strict")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--config", choices=sorted(CONFIGS), default="c4", help="BASELINE.json configs[0..4]; c4 is the headline")
     ap.add_argument("--no-share", action="store_true", help="N > 1: every rank computes the whole per-frame view pass itself")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = 3  # timing rule: at least 3 warm-up steps
-    if args.impl == "reference":
+    apply_config(args.config)
+    if args.config == "c5":
+        if args.steps == 100:
+            args.steps = 3   # a step is 531 M rays (seconds on one GPU): the default run stays within minutes
+        if args.impl == "reference":
+            run_reference_c5(args)
+        else:
+            run_ours_c5(args)
+    elif args.impl == "reference":
         run_reference(args)
     else:
         run_ours(args)

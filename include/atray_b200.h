@@ -205,6 +205,22 @@ int atray_last_view_split_ms(atray_ctx* ctx, float* bounds_ms, float* nodes_ms);
  * rays = n × {ox,oy,oz,dx,dy,dz} (direction used as given). Host pointers; synchronous. */
 int atray_trace_rays(atray_ctx* ctx, const float* rays, uint64_t n, int32_t fp_mode, int32_t count_work, uint32_t* prim,
                      float* t);
+/* BASELINE.json configs[4] ("C5", divergence stress): `spp` incoherent random-direction rays per pixel index p in [p0, p1),
+ * generated ON THE DEVICE from the per-ray PCG32 stream (engine/PL/PL_math.h:506-541) {state = splitmix64(seed ^ i), stream = 2i+1},
+ * i = p*spp + s: six rand_bi draws give an origin on a sphere of radius 1.5*mag(extent) around the centre of
+ * Model::surrounding_aabb and a target inside the box; SetRay (ray.h:24-29); traced through the model query of
+ * get_intersection_data (renderer.cpp:41-57, kd_tree.cpp:302-465). Outputs: bgrx[p - p0] = the pixel's flat colour (sequential
+ * f32 sum of the samples' sky / model emissions / spp, clamp, truncate, pack: renderer.cpp:358-365); prim / t per ray at
+ * (p - p0)*spp + s (either may be NULL). `part` (NULL = everything): the pixel range is cut into chunks of chunk_px pixels dealt
+ * round-robin to the ranks (chunk k -> rank k % world); a rank traces its chunks and leaves the others' entries untouched.
+ * The reference has no such entry point: its rays come from render_tile_from_camera only (renderer.cpp:294-369). */
+int atray_trace_incoherent_device(atray_ctx* ctx, uint64_t p0, uint64_t p1, uint32_t spp, uint64_t seed, const AtrayPartition* part,
+                                  uint32_t chunk_px, int32_t fp_mode, int32_t count_work, uint32_t* bgrx_dev, uint32_t* prim_dev,
+                                  float* t_dev);
+/* same with host outputs (synchronous; device buffers allocated for the call) */
+int atray_trace_incoherent(atray_ctx* ctx, uint64_t p0, uint64_t p1, uint32_t spp, uint64_t seed, int32_t fp_mode, int32_t count_work,
+                           uint32_t* bgrx, uint32_t* prim, float* t);
+
 /* same with device pointers, asynchronous on the context stream */
 int atray_trace_rays_device(atray_ctx* ctx, const float* rays_dev, uint64_t n, int32_t fp_mode, int32_t count_work,
                             uint32_t* prim_dev, float* t_dev);

@@ -884,6 +884,61 @@ void or_render_jitter(void* h, int W, int H, unsigned spp, int bounce, unsigned 
     or_parallel(a.s, H, threads, or_jitter_rows, &a);
 }
 
+/* ---- C5 (BASELINE.json configs[4]): incoherent random-direction rays, `spp` per pixel index, traced through the
+ * model query of get_intersection_data (renderer.cpp:41-57). The reference has no such workload of its own; the harness
+ * defines the rays from the reference's functions: ray i = p*spp + s draws from the PCG32 stream (PL_math.h:506-541)
+ * {state = splitmix64(seed ^ i), stream = 2i + 1} six rand_bi values b0..b5 (in that order) and is
+ *     origin o = c + normalize((b0,b1,b2)) * R          (normalize: PL_math.h:387-392)
+ *     target   = c + (0.5 * extent) (had) (b3,b4,b5)    (hadamard: PL_math.h:419)
+ *     SetRay(o, target)                                  (ray.h:24-29)
+ * with c = (lo + hi) * 0.5, extent = hi - lo of Model::surrounding_aabb and R = 1.5 * mag(extent) (PL_math.h:381-385), all in
+ * f32 in the order written. Pixel colour = sequential f32 sum of the samples' flat colours (sky / model emission) / spp,
+ * clamp, truncate, pack (renderer.cpp:358-365). */
+typedef struct { const or_scene* s; long long p0, p1; unsigned spp; uint64_t seed; unsigned* face; float* t; unsigned* bgrx; float* rays; } or_c5_arg;
+static void or_c5_ray(const or_scene* s, uint64_t seed, uint64_t i, v3* o, v3* d)
+{
+    or_rng rng = { or_splitmix64(seed ^ i), 2 * i + 1 };
+    v3 b, q;
+    b.x = or_rand_bi(&rng); b.y = or_rand_bi(&rng); b.z = or_rand_bi(&rng);
+    q.x = or_rand_bi(&rng); q.y = or_rand_bi(&rng); q.z = or_rand_bi(&rng);
+    const v3 lo = s->aabb.min, hi = s->aabb.max;
+    const v3 c = v3_mul(v3_add(lo, hi), 0.5f), ext = v3_sub(hi, lo);
+    const float R = 1.5f * sqrtf((ext.x * ext.x + ext.y * ext.y) + ext.z * ext.z);
+    *o = v3_add(c, v3_mul(v3_normalize(b), R));
+    v3 he = v3_mul(ext, 0.5f), tg;
+    tg.x = c.x + he.x * q.x; tg.y = c.y + he.y * q.y; tg.z = c.z + he.z * q.z;
+    *d = v3_normalize(v3_sub(tg, *o));
+}
+static void or_c5_blocks(void* a_, int b0, int b1, or_scratch* sc, or_counters* ct)
+{
+    or_c5_arg* a = a_;
+    for (long long p = a->p0 + (long long)b0 * 64; p < a->p0 + (long long)b1 * 64 && p < a->p1; p++)
+    {
+        v3 col = { 0, 0, 0 };
+        for (unsigned k = 0; k < a->spp; k++)
+        {
+            const uint64_t i = (uint64_t)p * a->spp + k;
+            const long long j = (p - a->p0) * a->spp + k;
+            v3 o, d;
+            or_c5_ray(a->s, a->seed, i, &o, &d);
+            if (a->rays) { float* r = a->rays + 6 * j; r[0] = o.x; r[1] = o.y; r[2] = o.z; r[3] = d.x; r[4] = d.y; r[5] = d.z; }
+            float t, u, v; uint32_t f;
+            const int hit = or_intersect(a->s, o, d, sc, &t, &f, &u, &v, ct);
+            if (a->face) a->face[j] = f;
+            if (a->t) a->t[j] = t;
+            col = v3_add(col, hit ? a->s->model_emission : a->s->sky_emission);
+        }
+        if (a->bgrx) a->bgrx[p - a->p0] = or_pack(v3_div(col, (float)a->spp));
+    }
+}
+/* pixels [p0, p1): face / t / rays per ray ((p1-p0)*spp entries, any may be NULL), bgrx per pixel */
+void or_trace_c5(void* h, long long p0, long long p1, unsigned spp, unsigned long long seed, int threads, unsigned* face, float* t,
+                 unsigned* bgrx, float* rays)
+{
+    or_c5_arg a = { h, p0, p1, spp, seed, face, t, bgrx, rays };
+    or_parallel(a.s, (int)((p1 - p0 + 63) / 64), threads, or_c5_blocks, &a);
+}
+
 /* ---- multi-bounce path: get_intersection_data (renderer.cpp:34-160) with spheres and planes, cast_ray (213-262) ---- */
 static or_material or_mat7(const float* m7)
 {

@@ -67,6 +67,9 @@ class Backend:
             self.trace_primary_ex = g("trace_primary_ex")
             self.trace_primary_ex.argtypes = self.trace_primary.argtypes + [C.c_void_p]
             self.scene_use_kd_tree = g("scene_use_kd_tree"); self.scene_use_kd_tree.argtypes = [C.c_void_p, C.c_int]
+            self.trace_c5 = g("trace_c5")
+            self.trace_c5.argtypes = [C.c_void_p, C.c_longlong, C.c_longlong, C.c_uint, C.c_ulonglong, C.c_int, C.c_void_p, C.c_void_p,
+                                      C.c_void_p, C.c_void_p]
             self.accepted_hits = g("accepted_hits")
             self.accepted_hits.restype = C.c_longlong
             self.accepted_hits.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_float, C.c_int,
@@ -195,6 +198,15 @@ class Scene:
             cap = int(n)
         assert n <= cap, "accepted_hits: capacity too small (%d > %d)" % (n, cap)
         return px[:n], node[:n], pos[:n]
+
+    def trace_c5(self, p0, p1, spp, seed, threads=1, want_rays=False):
+        """port() only: C5 (incoherent rays, `spp` per pixel index in [p0, p1)) — per ray face / t (and the rays), per pixel BGRX."""
+        n = (p1 - p0) * spp
+        face, t = np.zeros(n, np.uint32), np.zeros(n, np.float32)
+        bgrx = np.zeros(p1 - p0, np.uint32)
+        rays = np.zeros((n, 6), np.float32) if want_rays else None
+        self.b.trace_c5(self.h, p0, p1, spp, seed, threads, _p(face), _p(t), _p(bgrx), _p(rays) if want_rays else None)
+        return (face, t, bgrx, rays) if want_rays else (face, t, bgrx)
 
     def trace_rays(self, rays, threads=1):
         rays = np.ascontiguousarray(rays, dtype=np.float32).reshape(-1, 6)

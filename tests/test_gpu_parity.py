@@ -262,6 +262,48 @@ def test_c5_incoherent_rays(A, port, standin):
     o.close()
 
 
+def test_c5_device_generated_rays_and_pixel_means(A, port, standin):
+    """BASELINE.json configs[4] as defined in SURVEY §8(d): 64 incoherent rays per pixel index, generated ON THE DEVICE from
+    the per-ray PCG32 stream, traced, reduced to the pixel's mean colour. 131072 pixels x 64 spp = 8.39 M rays against the
+    oracle's restatement of the same stream: per-ray primitive id and t bit-exact, per-pixel BGRX equal; the round-robin
+    chunk split over ranks (executed rank by rank here) reproduces the whole job; a second seed gives other rays."""
+    from oracle import bind as B
+    sc = gpu_scene(A, standin, 0.0)
+    o = B.Scene(port, standin, rescale=0.0)
+    p0, p1, spp = 4_000_000, 4_000_000 + 131072, 64
+    got = sc.ctx.trace_incoherent(p0, p1, spp, SEED, count_work=True)
+    assert sc.ctx.counters()["rays"] == (p1 - p0) * spp
+    face, t, bgrx = o.trace_c5(p0, p1, spp, SEED, threads=NTHREADS)
+    assert (got["prim"] == face).all() and same_bits(got["t"], t)
+    assert (got["bgrx"] == bgrx).all()
+    assert 0.3 < float((face != B.MISS).mean()) < 0.95 and len(np.unique(bgrx)) > 8     # the means really are blends
+    # rank split: chunks of 1000 pixels dealt to 3 ranks, one rank after the other into the same device buffers
+    ctx = sc.ctx
+    n_px, n = p1 - p0, (p1 - p0) * spp
+    d_b, d_p, d_t = ctx.dev_alloc(n_px * 4), ctx.dev_alloc(n * 4), ctx.dev_alloc(n * 4)
+    for d, nb in ((d_b, n_px * 4), (d_p, n * 4), (d_t, n * 4)):
+        ctx.dev_memset(d, 0xEE, nb)
+    ctx.trace_incoherent_device(p0, p1, spp, d_b, d_p, d_t, seed=SEED, rank=1, world=3, chunk_px=1000)
+    ctx.sync()
+    part = ctx.to_host(d_b, np.zeros(n_px, np.uint32))
+    mine = (np.arange(n_px) // 1000) % 3 == 1
+    assert (part[mine] == bgrx[mine]).all() and (part[~mine] == 0xEEEEEEEE).all()     # a rank touches only its chunks
+    for r in (0, 2):
+        ctx.trace_incoherent_device(p0, p1, spp, d_b, d_p, d_t, seed=SEED, rank=r, world=3, chunk_px=1000)
+    ctx.sync()
+    assert (ctx.to_host(d_b, np.zeros(n_px, np.uint32)) == bgrx).all()
+    assert (ctx.to_host(d_p, np.zeros(n, np.uint32)) == face).all()
+    assert same_bits(ctx.to_host(d_t, np.zeros(n, np.float32)), t)
+    for d in (d_b, d_p, d_t):
+        ctx.dev_free(d)
+    # odd sample count (not a multiple of the 32 samples a warp takes at a time), other seed, small range
+    g2 = sc.ctx.trace_incoherent(7, 7 + 999, 37, SEED + 1)
+    f2, t2, b2 = o.trace_c5(7, 7 + 999, 37, SEED + 1, threads=NTHREADS)
+    assert (g2["prim"] == f2).all() and same_bits(g2["t"], t2) and (g2["bgrx"] == b2).all()
+    assert not (g2["bgrx"][:900] == got["bgrx"][:900]).all()
+    o.close()
+
+
 def test_partition_union_equals_whole(A, meshes):
     """Multi-GPU split (interleaved scanline bands) executed sequentially on one GPU reproduces the 1-GPU frame."""
     path, rescale = meshes["knot_mid"]
