@@ -115,6 +115,7 @@ _SIGS = {
     "atray_last_view_split_ms": [_vp, C.POINTER(_f), C.POINTER(_f)],
     "atray_trace_rays": [_vp, _vp, _u64, _i, _i, _vp, _vp],
     "atray_trace_rays_device": [_vp, _vp, _u64, _i, _i, _vp, _vp],
+    "atray_trace_rays_static": [_vp, _vp, _u64, _i, _vp, _vp],
     "atray_get_counters": [_vp, C.POINTER(Counters)],
     "atray_trace_incoherent_device": [_vp, _u64, _u64, _u, _u64, C.POINTER(Partition), _u, _i, _i, _vp, _vp, _vp],
     "atray_trace_incoherent": [_vp, _u64, _u64, _u, _u64, _i, _i, _vp, _vp, _vp],

@@ -1144,6 +1144,35 @@ int atray_trace_rays_device(atray_ctx* c, const float* rays_dev, uint64_t n, int
     return ATRAY_OK;
 }
 
+// Same query as atray_trace_rays_device, on the library's static device scratch: this entry allocates nothing (no cudaMalloc /
+// cudaFree / allocating routine on any path), see launch_trace_static in render.cu.
+int atray_trace_rays_static(atray_ctx* c, const float* rays_dev, uint64_t n, int32_t fp_mode, uint32_t* prim_dev, float* t_dev)
+{
+    if (!c || (!rays_dev && n) || (!prim_dev && n) || (!t_dev && n)) return fail(ATRAY_EINVAL, "null argument");
+    if (!c->has_scene) return fail(ATRAY_ESTATE, "trace before scene_upload");
+    if (n == 0) return ATRAY_OK;
+    if (n > (uint64_t(1) << 36)) return fail(ATRAY_EINVAL, "ray list too long for one call (split it)");
+    static_assert(ATRAY_STATIC_SCRATCH_BYTES == kStaticScratchBytes, "header and kernel disagree on the static scratch size");
+    if (static_trace_blocks(c->scratch.leaf_cap, c->scratch.stack_cap, c->cfg) < 1)
+    {
+        char msg[256];
+        std::snprintf(msg, sizeof msg,
+                      "atray_trace_rays_static: the scene needs %zu bytes of traversal scratch per thread block (%u leaves, %u nodes), the "
+                      "static scratch holds %zu: use atray_trace_rays_device",
+                      static_trace_bytes_per_block(c->scratch.leaf_cap, c->scratch.stack_cap), c->scratch.leaf_cap - 2,
+                      c->scratch.stack_cap - 8, static_scratch_capacity());
+        return fail(ATRAY_ELIMIT, msg);
+    }
+    CU(cudaSetDevice(c->device));
+    CU(cudaEventRecord(c->ev_k0, c->stream));
+    CU(launch_trace_static(c->scene, rays_dev, n, prim_dev, t_dev, c->scratch.leaf_cap, c->scratch.stack_cap, fp_mode == ATRAY_FP_FAST,
+                           c->cfg, c->device, c->stream));
+    CU(cudaEventRecord(c->ev_k1, c->stream));
+    c->have_kernel_time = true;
+    c->have_split = false;
+    return ATRAY_OK;
+}
+
 int atray_trace_rays(atray_ctx* c, const float* rays, uint64_t n, int32_t fp_mode, int32_t count_work, uint32_t* prim, float* t)
 {
     if (!c || (!rays && n) || (!prim && n) || (!t && n)) return fail(ATRAY_EINVAL, "null argument");

@@ -221,6 +221,14 @@ cudaError_t launch_trace(const DevScene& sc, const float* rays, unsigned long lo
 cudaError_t launch_c5(const DevScene& sc, unsigned long long p0, unsigned long long p1, uint32_t spp, uint32_t chunk_px,
                       unsigned long long seed, const DevPartition& part, uint32_t* bgrx, uint32_t* prim, float* t, const DevScratch& scratch,
                       unsigned int* counter, DevCounters* counters, int fp_fast, LaunchCfg cfg, cudaStream_t stream);
+// ray-list trace on the file-scope static scratch of render.cu (no allocation anywhere): see launch_trace_static there
+static constexpr size_t kStaticScratchBytes = size_t(16) << 20;   // per GPU that loads the library, held until exit
+size_t static_scratch_capacity();
+size_t static_trace_bytes_per_block(uint32_t leaf_cap, uint32_t stack_cap);
+int static_trace_blocks(uint32_t leaf_cap, uint32_t stack_cap, LaunchCfg cfg);
+cudaError_t static_scratch_address(int device, void** out);
+cudaError_t launch_trace_static(const DevScene& sc, const float* rays, unsigned long long n, uint32_t* prim, float* t, uint32_t leaf_cap,
+                                uint32_t stack_cap, int fp_fast, LaunchCfg cfg, int device, cudaStream_t stream);
 cudaError_t launch_microbench_fp32(float* sink, int iters, LaunchCfg cfg, cudaStream_t stream);
 cudaError_t launch_microbench_l2(const float4* buf, size_t n_vec, int passes, float* sink, LaunchCfg cfg, cudaStream_t stream);
 LaunchCfg render_launch_cfg(int sm_count);

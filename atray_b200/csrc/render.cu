@@ -21,6 +21,7 @@
 
 #include <cstdio>
 #include <cstdlib>
+#include <mutex>
 
 namespace atray {
 
@@ -2105,6 +2106,79 @@ cudaError_t launch_trace(const DevScene& sc, const float* rays, unsigned long lo
         if (fp_fast) k_trace<false, false><<<cfg.grid, cfg.block, 0, stream>>>(sc, rays, n, prim, t, scratch, tile_counter, counters);
         else k_trace<true, false><<<cfg.grid, cfg.block, 0, stream>>>(sc, rays, n, prim, t, scratch, tile_counter, counters);
     }
+    return cudaGetLastError();
+}
+
+// ---- ray-list trace without any allocation (include/atray_b200.h: atray_trace_rays_static) ---------------------------------------
+// k_trace needs scratch memory: the work cursor its warps draw ray groups from (must start at zero) and, per resident warp, the
+// overflow areas of the leaf list and the inner-node stack (used when a ray outgrows the per-lane local lists). The ordinary entry
+// takes them from buffers cudaMalloc'ed at scene upload; this variant takes them from ONE file-scope device array of
+// kStaticScratchBytes that every GPU loading the library holds until exit. Layout: [0, 256) cursor | leaves (warps x leaf_cap x
+// uint2) | stack (warps x stack_cap x u32), both 256-byte aligned. In host code `g_static_scratch` is only a stand-in for the
+// symbol: the device address comes from cudaGetSymbolAddress, once per device with that device current (static_scratch_address).
+// Every call on a device shares the array (it keeps the last call's contents; only the cursor has to be cleared, which the
+// launcher does on the stream): calls that overlap on one GPU race.
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
+static constexpr int kStaticMaxDevices = 64;
+static void* g_static_scratch_addr[kStaticMaxDevices];
+static std::mutex g_static_scratch_mutex;
+
+size_t static_scratch_capacity() { return kStaticScratchBytes; }
+
+static size_t static_round256(size_t v) { return (v + 255u) & ~size_t(255); }
+
+// bytes of scratch one CTA of k_trace needs for a scene with these list capacities
+size_t static_trace_bytes_per_block(uint32_t leaf_cap, uint32_t stack_cap)
+{
+    return size_t(kBlock / 32) * (size_t(leaf_cap) * sizeof(uint2) + size_t(stack_cap) * sizeof(uint32_t));
+}
+
+// CTAs that fit the static scratch (0: not even one: the scene is beyond the maximum), at most cfg.grid
+int static_trace_blocks(uint32_t leaf_cap, uint32_t stack_cap, LaunchCfg cfg)
+{
+    const size_t per_block = static_trace_bytes_per_block(leaf_cap, stack_cap);
+    const size_t room = kStaticScratchBytes - 768;   // cursor line + the two alignment gaps
+    const size_t fit = per_block ? room / per_block : size_t(cfg.grid);
+    return int(fit < size_t(cfg.grid) ? fit : size_t(cfg.grid));
+}
+
+// device address of the static scratch on `device`, which must be the current device; resolved once per device
+cudaError_t static_scratch_address(int device, void** out)
+{
+    if (device < 0 || device >= kStaticMaxDevices) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(g_static_scratch_mutex);
+    if (!g_static_scratch_addr[device])
+    {
+        void* p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch);
+        if (e != cudaSuccess) return e;
+        if (!p) return cudaErrorInvalidSymbol;
+        g_static_scratch_addr[device] = p;
+    }
+    *out = g_static_scratch_addr[device];
+    return cudaSuccess;
+}
+
+cudaError_t launch_trace_static(const DevScene& sc, const float* rays, unsigned long long n, uint32_t* prim, float* t, uint32_t leaf_cap,
+                                uint32_t stack_cap, int fp_fast, LaunchCfg cfg, int device, cudaStream_t stream)
+{
+    const int blocks = static_trace_blocks(leaf_cap, stack_cap, cfg);
+    if (blocks < 1) return cudaErrorInvalidValue;   // (the C ABI checks this first and reports the limit)
+    void* base = nullptr;
+    cudaError_t e = static_scratch_address(device, &base);
+    if (e != cudaSuccess) return e;
+    unsigned char* p = static_cast<unsigned char*>(base);
+    unsigned int* cursor = reinterpret_cast<unsigned int*>(p);
+    const size_t warps = size_t(blocks) * (kBlock / 32);
+    DevScratch scratch;
+    scratch.leaf_cap = leaf_cap;
+    scratch.stack_cap = stack_cap;
+    scratch.leaves = reinterpret_cast<uint2*>(p + 256);
+    scratch.stack = reinterpret_cast<uint32_t*>(p + 256 + static_round256(warps * leaf_cap * sizeof(uint2)));
+    e = cudaMemsetAsync(cursor, 0, 256, stream);
+    if (e != cudaSuccess) return e;
+    if (fp_fast) k_trace<false, false><<<blocks, cfg.block, 0, stream>>>(sc, rays, n, prim, t, scratch, cursor, nullptr);
+    else k_trace<true, false><<<blocks, cfg.block, 0, stream>>>(sc, rays, n, prim, t, scratch, cursor, nullptr);
     return cudaGetLastError();
 }
 

@@ -153,6 +153,10 @@ class Context:
     def trace_rays_device(self, d_rays, n, d_prim, d_t, fp_mode=api.FP_STRICT, count_work=False):
         _ck(_L.atray_trace_rays_device(self.h, d_rays, n, fp_mode, 1 if count_work else 0, d_prim, d_t))
 
+    def trace_rays_static(self, d_rays, n, d_prim, d_t, fp_mode=api.FP_STRICT):
+        """trace_rays_device on the library's static device scratch: the call allocates nothing (include/atray_b200.h)."""
+        _ck(_L.atray_trace_rays_static(self.h, d_rays, n, fp_mode, d_prim, d_t))
+
     def trace_incoherent(self, p0, p1, spp, seed=api.DEFAULT_SEED, fp_mode=api.FP_STRICT, count_work=False, want=("bgrx", "prim", "t")):
         """C5: `spp` device-generated incoherent rays per pixel index in [p0, p1) → dict of bgrx (per pixel), prim, t (per ray)."""
         n = (p1 - p0) * spp

@@ -224,6 +224,18 @@ int atray_trace_incoherent(atray_ctx* ctx, uint64_t p0, uint64_t p1, uint32_t sp
 /* same with device pointers, asynchronous on the context stream */
 int atray_trace_rays_device(atray_ctx* ctx, const float* rays_dev, uint64_t n, int32_t fp_mode, int32_t count_work,
                             uint32_t* prim_dev, float* t_dev);
+/* The same query as atray_trace_rays_device (device pointers, asynchronous on the context stream, same outputs bit for bit) for
+ * callers that cannot allocate: this entry calls no cudaMalloc / cudaFree / allocating routine on any path. The kernel's scratch
+ * (the work cursor of its warps, the per-warp overflow areas of the leaf list and the node stack) lives in one static device array
+ * of ATRAY_STATIC_SCRATCH_BYTES inside the library, which every GPU that loads the library holds until exit. Limits: a scene whose
+ * tree needs more than that for a single thread block (8 warps x ((leaves + 2) x 8 + (nodes + 8) x 4) bytes) is refused with
+ * ATRAY_ELIMIT and a message naming both sizes; n <= 2^36 as for the other entry; no work counters. Smaller scenes run with as
+ * many thread blocks as fit. All calls on one GPU share the array (contexts included) and it keeps the last call's contents (the
+ * cursor is cleared on the stream by every call): calls that overlap on the GPU race, so issue them on one context / in stream order.
+ * The first call per device resolves the array's address (cudaGetSymbolAddress); make it before any stream capture.
+ * No counterpart in the reference. */
+#define ATRAY_STATIC_SCRATCH_BYTES (16u << 20)
+int atray_trace_rays_static(atray_ctx* ctx, const float* rays_dev, uint64_t n, int32_t fp_mode, uint32_t* prim_dev, float* t_dev);
 int atray_get_counters(atray_ctx* ctx, AtrayCounters* out);
 
 /* device memory helpers for embedders without a CUDA runtime binding of their own */
