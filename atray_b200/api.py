@@ -116,6 +116,7 @@ _SIGS = {
     "atray_trace_rays": [_vp, _vp, _u64, _i, _i, _vp, _vp],
     "atray_trace_rays_device": [_vp, _vp, _u64, _i, _i, _vp, _vp],
     "atray_trace_rays_static": [_vp, _vp, _u64, _i, _vp, _vp],
+    "atray_trace_rays_uv": [_vp, _vp, _u64, _vp, _vp, _vp],
     "atray_get_counters": [_vp, C.POINTER(Counters)],
     "atray_trace_incoherent_device": [_vp, _u64, _u64, _u, _u64, C.POINTER(Partition), _u, _i, _i, _vp, _vp, _vp],
     "atray_trace_incoherent": [_vp, _u64, _u64, _u, _u64, _i, _i, _vp, _vp, _vp],
@@ -139,6 +140,18 @@ _SIGS = {
     "atray_view_share_check": [_vp],
     "atray_ctx_enable_peer": [_vp, _vp],
     "atray_debug_view_shards": [_vp, _i],
+    "atray_ctx_create_multi": [_vp, _i, C.POINTER(_vp)],
+    "atray_multi_count": [_vp],
+    "atray_multi_device": [_vp, _i],
+    "atray_multi_scene_upload": [_vp, _vp, C.POINTER(Material), C.POINTER(Material)],
+    "atray_multi_scene_set_primitives": [_vp, _vp, _u, _vp, _u],
+    "atray_multi_scene_use_kd_tree": [_vp, _i],
+    "atray_multi_render_begin": [_vp, C.POINTER(CameraStruct), C.POINTER(RenderOpts), C.POINTER(Frame)],
+    "atray_multi_render_poll": [_vp, _u],
+    "atray_multi_render_progress": [_vp, C.POINTER(_i), C.POINTER(_i)],
+    "atray_multi_render_cancel": [_vp],
+    "atray_multi_render_device": [_vp, C.POINTER(CameraStruct), C.POINTER(RenderOpts), C.POINTER(Frame)],
+    "atray_multi_sync": [_vp],
 }
 for _n, _a in _SIGS.items():
     getattr(_L, _n).argtypes = _a
@@ -147,8 +160,12 @@ _L.atray_model_free.argtypes = [_vp]
 _L.atray_model_free.restype = None
 _L.atray_ctx_destroy.argtypes = [_vp]
 _L.atray_ctx_destroy.restype = None
+_L.atray_multi_destroy.argtypes = [_vp]
+_L.atray_multi_destroy.restype = None
+_L.atray_multi_ctx.argtypes = [_vp, _i]
+_L.atray_multi_ctx.restype = _vp
 
-EXPORTED_SYMBOLS = sorted(list(_SIGS) + ["atray_model_free", "atray_ctx_destroy", "atray_last_error"])
+EXPORTED_SYMBOLS = sorted(list(_SIGS) + ["atray_model_free", "atray_ctx_destroy", "atray_last_error", "atray_multi_destroy", "atray_multi_ctx"])
 
 
 def _ck(rc):

@@ -67,6 +67,12 @@ struct atray_ctx
     unsigned long long* d_casts = nullptr;   // ray_casts of the last path frame (renderer.cpp:260)
     bool casts_valid = false;
     unsigned int* d_tile_counter = nullptr;
+    // cancel: a device word the persistent loops poll (DevScene::cancel), raised by a 4-byte copy from pinned memory on a stream
+    // of its own so that it overtakes the running kernel (atray_render_cancel)
+    uint32_t* d_cancel = nullptr;
+    uint32_t* h_cancel_one = nullptr;
+    cudaStream_t ctl_stream = nullptr;
+    uint64_t cancels = 0;            // cancel requests that found work on the stream
     DevCounters* d_counters = nullptr;
     bool counters_valid = false;
     // frame planes owned by the context (atray_render_begin)
@@ -114,6 +120,7 @@ static int cuda_fail(cudaError_t e, const char* what)
     g_err = std::string(what) + ": " + cudaGetErrorString(e);
     return ATRAY_ECUDA;
 }
+namespace atray { int set_error(int code, const char* msg) { return fail(code, msg ? msg : ""); } }   // for multi_ctx.cpp
 #define CU(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) return cuda_fail(e__, #call); } while (0)
 
 extern "C" {
@@ -291,6 +298,11 @@ int atray_ctx_create(int device, atray_ctx** out)
     if (e == cudaSuccess) e = cudaMalloc(&c->d_tile_counter, sizeof(unsigned int));
     if (e == cudaSuccess) e = cudaMalloc(&c->d_counters, sizeof(DevCounters));
     if (e == cudaSuccess) e = cudaMalloc(&c->d_casts, sizeof(unsigned long long));
+    if (e == cudaSuccess) e = cudaMalloc(&c->d_cancel, 256);
+    if (e == cudaSuccess) e = cudaMemset(c->d_cancel, 0, 256);
+    if (e == cudaSuccess) e = cudaMallocHost(&c->h_cancel_one, sizeof(uint32_t));
+    if (e == cudaSuccess) { *c->h_cancel_one = 1u; c->scene.cancel = c->d_cancel; }
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->ctl_stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaEventCreate(&c->ev_k0);
     if (e == cudaSuccess) e = cudaEventCreate(&c->ev_k1);
     if (e == cudaSuccess) e = cudaEventCreate(&c->ev_kr);
@@ -358,6 +370,7 @@ static void free_scene(atray_ctx* c)
     c->d_faces = nullptr;
     c->scratch = DevScratch{};
     c->scene = DevScene{};
+    c->scene.cancel = c->d_cancel;
     c->has_scene = false;
     cudaFree(c->share.block);   // sized for the scene: a new scene needs a new atray_view_share_create
     c->share = atray_ctx::Share{};
@@ -387,6 +400,9 @@ void atray_ctx_destroy(atray_ctx* c)
     if (c->ev_reset) cudaEventDestroy(c->ev_reset);
     for (int k = 0; k < kMaxSlabs; ++k)
         if (c->ev_slab[k]) cudaEventDestroy(c->ev_slab[k]);
+    if (c->ctl_stream) cudaStreamDestroy(c->ctl_stream);
+    cudaFree(c->d_cancel);
+    cudaFreeHost(c->h_cancel_one);
     if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
     if (c->copy_stream2) cudaStreamDestroy(c->copy_stream2);
     if (c->stream) cudaStreamDestroy(c->stream);
@@ -1071,13 +1087,32 @@ int atray_render_progress(atray_ctx* c, int32_t* rows_done, int32_t* rows_total)
 int atray_render_cancel(atray_ctx* c)
 {
     if (!c) return fail(ATRAY_EINVAL, "null context");
-    // A frame is one sub-millisecond kernel: cancelling = draining both streams and dropping the pending host copy-out.
+    // WorkQueue::clear() + wait_for_pool of the reference's cancel path (app.cpp:165-172: the workers finish the tile they are on
+    // and find the queue empty). Here: raise the context's cancel word from a stream of its own, so the 4-byte copy overtakes the
+    // running kernel; every persistent loop (k_render*, k_path, k_trace, k_c5) reads the word next to its work cursor and stops
+    // taking tiles / ray groups; then drain the streams (the slab counters the copy streams wait on are finalised by the kernel
+    // behind the render kernel, so they drain too), drop the pending host copy-out and lower the word again. Pixels / rays not yet
+    // traced keep whatever the output buffers held. Applies to whatever work the context stream holds, begin/poll frames and the
+    // asynchronous *_device entries alike.
     CU(cudaSetDevice(c->device));
+    const bool busy = cudaStreamQuery(c->stream) == cudaErrorNotReady;
+    cudaGetLastError();
+    if (busy)
+    {
+        CU(cudaMemcpyAsync(c->d_cancel, c->h_cancel_one, sizeof(uint32_t), cudaMemcpyHostToDevice, c->ctl_stream));
+        CU(cudaStreamSynchronize(c->ctl_stream));
+        c->cancels += 1;
+    }
     CU(cudaStreamSynchronize(c->stream));
     CU(cudaStreamSynchronize(c->copy_stream));
     CU(cudaStreamSynchronize(c->copy_stream2));
+    if (busy)
+    {
+        CU(cudaMemsetAsync(c->d_cancel, 0, sizeof(uint32_t), c->stream));
+        CU(cudaStreamSynchronize(c->stream));
+    }
     c->in_flight = false;
-    return ATRAY_OK;
+    return busy ? 1 : ATRAY_OK;
 }
 
 int atray_ctx_sync(atray_ctx* c)
@@ -1141,6 +1176,39 @@ int atray_trace_rays_device(atray_ctx* c, const float* rays_dev, uint64_t n, int
     CU(cudaEventRecord(c->ev_k1, c->stream));
     c->have_kernel_time = true;
     c->have_split = false;
+    return ATRAY_OK;
+}
+
+// Ray list with TriangleIntersectionData (face_index, u, v) per ray: what get_ray_kd_tree_intersection returns for ONE ray
+// (kd_tree.cpp:302-313; u, v of the winning triangle from its scan loop, kd_tree.cpp:436-462). Synchronous, host pointers; a miss
+// leaves uv[2i], uv[2i+1] untouched and reports t = MAX_FLOAT. n = 1 is the reference's call shape (a 32-lane kernel for one
+// ray is a latency-bound round trip of two small copies: the entry exists for drop-in completeness and for batches).
+int atray_trace_rays_uv(atray_ctx* c, const float* rays, uint64_t n, uint32_t* prim, float* t, float* uv)
+{
+    if (!c || (!rays && n) || (!prim && n) || (!t && n) || (!uv && n)) return fail(ATRAY_EINVAL, "null argument");
+    if (!c->has_scene) return fail(ATRAY_ESTATE, "trace before scene_upload");
+    if (n == 0) return ATRAY_OK;
+    CU(cudaSetDevice(c->device));
+    const uint64_t need = n * 2;   // d_rays doubles as {rays | uv}: 6 + 2 floats per ray → capacity in units of 24-byte rays
+    if (need > c->ray_cap)
+    {
+        cudaFree(c->d_rays); cudaFree(c->d_rprim); cudaFree(c->d_rt);
+        c->d_rays = nullptr; c->d_rprim = nullptr; c->d_rt = nullptr; c->ray_cap = 0;
+        CU(cudaMalloc(&c->d_rays, need * 24)); CU(cudaMalloc(&c->d_rprim, need * 4)); CU(cudaMalloc(&c->d_rt, need * 4));
+        c->ray_cap = need;
+    }
+    float* d_uv = c->d_rays + n * 6;
+    CU(cudaMemcpyAsync(c->d_rays, rays, n * 24, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(d_uv, uv, n * 8, cudaMemcpyHostToDevice, c->stream));   // entries of misses keep the caller's values
+    CU(cudaEventRecord(c->ev_k0, c->stream));
+    CU(launch_trace_uv(c->scene, c->d_rays, n, c->d_rprim, c->d_rt, d_uv, c->scratch, c->d_tile_counter, c->cfg, c->stream));
+    CU(cudaEventRecord(c->ev_k1, c->stream));
+    c->have_kernel_time = true;
+    c->have_split = false;
+    CU(cudaMemcpyAsync(prim, c->d_rprim, n * 4, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaMemcpyAsync(t, c->d_rt, n * 4, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaMemcpyAsync(uv, d_uv, n * 8, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
     return ATRAY_OK;
 }
 

@@ -40,6 +40,8 @@ struct DevScene
     uint32_t n_faces;
     uint32_t brute;                // per launch: non-zero → the model query is the no-tree branch
     float aabb_lo[3], aabb_hi[3];  // Model::surrounding_aabb (model.h:41-61 after the transforms)
+    // ---- per context, not per scene: the cancel word every persistent loop polls (atray_render_cancel) ----
+    const uint32_t* cancel;
 };
 
 struct DevCamera
@@ -217,6 +219,8 @@ cudaError_t launch_path(const DevScene& sc, const DevCamera& cam, const DevParti
 cudaError_t launch_trace(const DevScene& sc, const float* rays, unsigned long long n, uint32_t* prim, float* t,
                          const DevScratch& scratch, unsigned int* tile_counter, DevCounters* counters, int fp_fast,
                          LaunchCfg cfg, cudaStream_t stream);
+cudaError_t launch_trace_uv(const DevScene& sc, const float* rays, unsigned long long n, uint32_t* prim, float* t, float* uv,
+                            const DevScratch& scratch, unsigned int* tile_counter, LaunchCfg cfg, cudaStream_t stream);
 // K2b: C5 — `spp` incoherent rays per pixel index in [p0, p1), generated on the device, traced, reduced to the pixel colour
 cudaError_t launch_c5(const DevScene& sc, unsigned long long p0, unsigned long long p1, uint32_t spp, uint32_t chunk_px,
                       unsigned long long seed, const DevPartition& part, uint32_t* bgrx, uint32_t* prim, float* t, const DevScratch& scratch,

@@ -37,6 +37,14 @@ static constexpr int kBlock = 256;                    // 8 warps per CTA
 
 struct RayL { float ox, oy, oz, dx, dy, dz; };
 
+// Cancel word of the context (DevScene::cancel, device memory): the host raises it from a second stream while a kernel runs
+// (atray_render_cancel — the reference's WorkQueue::clear() + "threads finish the tile they are on", app.cpp:165-172). Every
+// persistent loop reads it next to its work cursor and stops taking work once it is set.
+__device__ __forceinline__ bool cancel_requested(const DevScene& sc)
+{
+    return *reinterpret_cast<const volatile uint32_t*>(sc.cancel) != 0u;
+}
+
 __device__ __forceinline__ float mulr(float a, float b) { return __fmul_rn(a, b); }
 __device__ __forceinline__ float addr(float a, float b) { return __fadd_rn(a, b); }
 __device__ __forceinline__ float subr(float a, float b) { return __fsub_rn(a, b); }
@@ -441,7 +449,7 @@ __global__ void __launch_bounds__(kBlock) k_render(DevScene sc, DevCamera cm, De
     for (;;)
     {
         unsigned int tile = 0;
-        if (lane == 0) tile = atomicAdd(tile_counter, 1u);
+        if (lane == 0) tile = cancel_requested(sc) ? 0xffffffffu : atomicAdd(tile_counter, 1u);
         tile = __shfl_sync(FULL_MASK, tile, 0);
         if (tile >= n_tiles) break;
         const unsigned int lb = tile / tiles_per_band, rem = tile - lb * tiles_per_band;
@@ -1303,6 +1311,8 @@ __global__ void __launch_bounds__(kBlock, ATRAY_RENDER_MIN_BLOCKS) k_render_cull
   {
     const unsigned int tile_lo = slabs.tile_begin[slab], tile_hi = min(slabs.tile_begin[slab + 1], n_tiles);
     unsigned int finished = 0;  // tiles of this slab completed by this warp
+    bool cancelled = false;
+    unsigned int cancel_word = 0u;
     // ---- phase A: sky tiles ------------------------------------------------------------------------------------------
     // One strip of 32 consecutive tiles (256×4 pixels) per step: one coalesced stamp load, then 512-byte row segments.
     if (!all_busy && vec_ok)
@@ -1375,6 +1385,11 @@ __global__ void __launch_bounds__(kBlock, ATRAY_RENDER_MIN_BLOCKS) k_render_cull
         unsigned int bi = 0;
         if (lane == 0) bi = atomicAdd(&vw.busy_count[kCtlCursor + slab], 1u);
         bi = __shfl_sync(FULL_MASK, bi, 0);
+        // the context's cancel word, read by lane 31 one tile ahead: the (uncached) load is in flight while the tile is traced
+#ifndef ATRAY_CULLED_NO_CANCEL   // (A/B builds only)
+        if (__shfl_sync(FULL_MASK, cancel_word, 31)) { cancelled = true; break; }
+        if (lane == 31) cancel_word = (unsigned int)cancel_requested(sc);
+#endif
         const unsigned int cnt = lane < kCostBuckets ? __ldg(&vw.busy_count[kCtlCount + slab * kCostBuckets + (kCostBuckets - 1 - lane)]) : 0u;
         unsigned int end = cnt;   // inclusive prefix sum over the lanes
 #pragma unroll
@@ -1454,6 +1469,7 @@ __global__ void __launch_bounds__(kBlock, ATRAY_RENDER_MIN_BLOCKS) k_render_cull
         __syncwarp();
         if (lane == 0) atomicAdd(&vw.busy_count[kCtlDone + slab], finished);
     }
+    if (cancelled) break;
   }
     if (COUNT) flush_counters(counters, wc, rays_done);
 }
@@ -1461,9 +1477,12 @@ __global__ void __launch_bounds__(kBlock, ATRAY_RENDER_MIN_BLOCKS) k_render_cull
 #include "raster.cuh"
 
 // ---- K2: ray-list trace (get_intersection_data model branch for arbitrary rays) ---------------------------------
-template <bool STRICT, bool COUNT>
+// UV: also store the winning triangle's barycentric (u, v) (TriangleIntersectionData, model.h:18-22) at uv[2i], uv[2i+1]; a miss
+// leaves them untouched, as get_ray_kd_tree_intersection leaves tri_data (kd_tree.cpp:436-462).
+template <bool STRICT, bool COUNT, bool UV = false>
 __global__ void __launch_bounds__(kBlock) k_trace(DevScene sc, const float* __restrict__ rays, unsigned long long n, uint32_t* prim,
-                                                  float* tout, DevScratch scratch, unsigned int* tile_counter, DevCounters* counters)
+                                                  float* tout, DevScratch scratch, unsigned int* tile_counter, DevCounters* counters,
+                                                  float* uv = nullptr)
 {
     const int lane = threadIdx.x & 31;
     const int warp_slot = (blockIdx.x * kBlock + threadIdx.x) >> 5;
@@ -1476,7 +1495,7 @@ __global__ void __launch_bounds__(kBlock) k_trace(DevScene sc, const float* __re
     for (;;)
     {
         unsigned int g = 0;
-        if (lane == 0) g = atomicAdd(tile_counter, 1u);
+        if (lane == 0) g = cancel_requested(sc) ? 0xffffffffu : atomicAdd(tile_counter, 1u);
         g = __shfl_sync(FULL_MASK, g, 0);
         if ((unsigned long long)g >= n_groups) break;
         const unsigned long long i = ((unsigned long long)g << 5) + (unsigned long long)lane;
@@ -1490,11 +1509,13 @@ __global__ void __launch_bounds__(kBlock) k_trace(DevScene sc, const float* __re
         }
         float t;
         uint32_t face;
-        trace_warp<STRICT, COUNT>(sc, scratch, warp_slot, lane, active, ray, leaves, stack, t, face, wc);
+        float hu = 0.0f, hv = 0.0f;
+        trace_warp<STRICT, COUNT, UV>(sc, scratch, warp_slot, lane, active, ray, leaves, stack, t, face, wc, &hu, &hv);
         if (active)
         {
             prim[i] = face;
             tout[i] = t;
+            if (UV && face != 0xffffffffu) { uv[2ULL * i] = hu; uv[2ULL * i + 1ULL] = hv; }
             rays_done += 1;
         }
     }
@@ -1542,10 +1563,10 @@ __global__ void __launch_bounds__(kBlock) k_c5(DevScene sc, DevC5 job, DevPartit
     for (;;)
     {
         unsigned int j = 0;
-        if (lane == 0) j = atomicAdd(counter, 1u);
+        if (lane == 0) j = cancel_requested(sc) ? 0xffffffffu : atomicAdd(counter, 1u);
         j = __shfl_sync(FULL_MASK, j, 0);
         const unsigned long long lc = j / job.chunk_px;
-        if (lc >= my_chunks) break;
+        if (lc >= my_chunks || j == 0xffffffffu) break;
         const unsigned long long rel = (lc * part.world + part.rank) * job.chunk_px + (j - lc * job.chunk_px);   // pixel - p0
         if (rel >= n_px) continue;
         const unsigned long long p = job.p0 + rel;
@@ -1728,7 +1749,7 @@ __global__ void __launch_bounds__(kBlock) k_path(DevScene sc, DevCamera cm, DevP
     for (;;)
     {
         unsigned int tile = 0;
-        if (lane == 0) tile = atomicAdd(tile_counter, 1u);
+        if (lane == 0) tile = cancel_requested(sc) ? 0xffffffffu : atomicAdd(tile_counter, 1u);
         tile = __shfl_sync(FULL_MASK, tile, 0);
         if (tile >= n_tiles) break;
         const unsigned int lb = tile / tiles_per_band, rem = tile - lb * tiles_per_band;
@@ -2106,6 +2127,19 @@ cudaError_t launch_trace(const DevScene& sc, const float* rays, unsigned long lo
         if (fp_fast) k_trace<false, false><<<cfg.grid, cfg.block, 0, stream>>>(sc, rays, n, prim, t, scratch, tile_counter, counters);
         else k_trace<true, false><<<cfg.grid, cfg.block, 0, stream>>>(sc, rays, n, prim, t, scratch, tile_counter, counters);
     }
+    return cudaGetLastError();
+}
+
+// ray list with the hit's barycentrics (the single-ray query get_ray_kd_tree_intersection of the host layer): strict arithmetic only
+cudaError_t launch_trace_uv(const DevScene& sc, const float* rays, unsigned long long n, uint32_t* prim, float* t, float* uv,
+                            const DevScratch& scratch, unsigned int* tile_counter, LaunchCfg cfg, cudaStream_t stream)
+{
+    cudaError_t e = cudaMemsetAsync(tile_counter, 0, sizeof(unsigned int), stream);
+    if (e != cudaSuccess) return e;
+    const unsigned long long groups = (n + 31ULL) >> 5, per_block = kBlock / 32;
+    const unsigned long long want = (groups + per_block - 1) / per_block;
+    const int grid = int(want < (unsigned long long)cfg.grid ? (want ? want : 1ULL) : (unsigned long long)cfg.grid);
+    k_trace<true, false, true><<<grid, cfg.block, 0, stream>>>(sc, rays, n, prim, t, scratch, tile_counter, nullptr, uv);
     return cudaGetLastError();
 }
 

@@ -37,9 +37,9 @@ class Context:
         self._keep = None
 
     def close(self):
-        if getattr(self, "h", None):
+        if getattr(self, "h", None) and not getattr(self, "_borrowed", False):
             _L.atray_ctx_destroy(self.h)
-            self.h = None
+        self.h = None
 
     def __del__(self):
         self.close()
@@ -153,6 +153,21 @@ class Context:
     def trace_rays_device(self, d_rays, n, d_prim, d_t, fp_mode=api.FP_STRICT, count_work=False):
         _ck(_L.atray_trace_rays_device(self.h, d_rays, n, fp_mode, 1 if count_work else 0, d_prim, d_t))
 
+    def trace_rays_uv(self, rays):
+        """get_ray_kd_tree_intersection for a ray list (kd_tree.cpp:302-313): prim, t and TriangleIntersectionData's (u, v);
+        rows of misses stay NaN."""
+        rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 6)
+        n = rays.shape[0]
+        prim = np.zeros(n, np.uint32)
+        t = np.zeros(n, np.float32)
+        uv = np.full((n, 2), np.nan, np.float32)
+        _ck(_L.atray_trace_rays_uv(self.h, _p(rays), n, _p(prim), _p(t), _p(uv)))
+        return prim, t, uv
+
+    def cancel(self):
+        """atray_render_cancel: True when work was on the stream and has been cut short."""
+        return _ck(_L.atray_render_cancel(self.h)) == 1
+
     def trace_rays_static(self, d_rays, n, d_prim, d_t, fp_mode=api.FP_STRICT):
         """trace_rays_device on the library's static device scratch: the call allocates nothing (include/atray_b200.h)."""
         _ck(_L.atray_trace_rays_static(self.h, d_rays, n, fp_mode, d_prim, d_t))
@@ -238,6 +253,87 @@ class Context:
 
 
 # ---- reference-named entry points (renderer.h:32-35) -----------------------------------------------------------------
+class MultiContext:
+    """Several GPUs driven from this one process (atray_multi: atray_ctx_create_multi …): the reference's tile pool with GPUs as the
+    workers. `ctx[i]` are borrowed Context views of the member contexts (counters, kernel times, device memory …)."""
+
+    def __init__(self, devices=None, n=None):
+        n = len(devices) if devices is not None else int(n)
+        arr = (C.c_int32 * n)(*devices) if devices is not None else None
+        h = _vp()
+        _ck(_L.atray_ctx_create_multi(C.cast(arr, C.c_void_p) if arr is not None else None, n, C.byref(h)))
+        self.h = h
+        self.ctx = []
+        for i in range(n):
+            c = Context.__new__(Context)
+            c.h, c.device, c._keep, c._borrowed = _vp(_L.atray_multi_ctx(self.h, i)), _L.atray_multi_device(self.h, i), None, True
+            self.ctx.append(c)
+        self.devices = [c.device for c in self.ctx]
+        self._keep = None
+
+    def close(self):
+        if getattr(self, "h", None):
+            for c in self.ctx:
+                c.h = None
+            _L.atray_multi_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        self.close()
+
+    def upload(self, model, sky=api.SKY_MATERIAL, material=api.MODEL_MATERIAL):
+        s, m = api.make_material(sky), api.make_material(material)
+        _ck(_L.atray_multi_scene_upload(self.h, model.h, C.byref(s), C.byref(m)))
+
+    def set_primitives(self, spheres=(), planes=()):
+        for c in self.ctx:
+            c.set_primitives(spheres, planes)
+
+    def use_kd_tree(self, use=True):
+        _ck(_L.atray_multi_scene_use_kd_tree(self.h, 1 if use else 0))
+
+    opts = staticmethod(Context.opts)
+
+    def render_begin(self, cam, opts, bgrx=None, t=None, prim=None):
+        fr = api.Frame(_p(bgrx) if bgrx is not None else None, _p(t) if t is not None else None,
+                       _p(prim) if prim is not None else None)
+        self._keep = (bgrx, t, prim)
+        _ck(_L.atray_multi_render_begin(self.h, C.byref(cam), C.byref(opts), C.byref(fr)))
+
+    def render_poll(self, timeout_ms=0xFFFFFFFF):
+        return _ck(_L.atray_multi_render_poll(self.h, timeout_ms))
+
+    def render_progress(self):
+        a, b = C.c_int32(0), C.c_int32(0)
+        _ck(_L.atray_multi_render_progress(self.h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+    def cancel(self):
+        return _ck(_L.atray_multi_render_cancel(self.h)) == 1
+
+    def render(self, cam, opts=None, want=("bgrx", "t", "prim")):
+        opts = opts or self.opts()
+        H, W = cam.height, cam.width
+        out = {"bgrx": np.zeros((H, W), np.uint32) if "bgrx" in want else None,
+               "t": np.zeros((H, W), np.float32) if "t" in want else None,
+               "prim": np.zeros((H, W), np.uint32) if "prim" in want else None}
+        self.render_begin(cam, opts, out["bgrx"], out["t"], out["prim"])
+        while self.render_poll(1000):
+            pass
+        return out
+
+    def render_device(self, cam, opts, d_bgrx=0, d_t=0, d_prim=0):
+        """Planes on one device (normally ctx[0].dev_alloc): the other GPUs store their bands into them over NVLink."""
+        fr = api.Frame(d_bgrx or None, d_t or None, d_prim or None)
+        _ck(_L.atray_multi_render_device(self.h, C.byref(cam), C.byref(opts), C.byref(fr)))
+
+    def sync(self):
+        _ck(_L.atray_multi_sync(self.h))
+
+    def last_ray_casts(self):
+        return sum(c.last_ray_casts() for c in self.ctx)
+
+
 class Scene:
     """Scene (scene.h:13-24) restricted to what the path uses: materials[0] = sky, one model with its material."""
 
@@ -247,6 +343,7 @@ class Scene:
         self.division_method, self.max_no_faces_per_node = division_method, max_no_faces_per_node
         self.spheres, self.planes = [], []   # scene.spheres / scene.planes: (center, radius, material) / (normal, distance, material)
         self.ctx = None
+        self.gpu_devices = None   # e.g. [0, 4]: prep_scene creates a MultiContext over these GPUs (None: one GPU, `device`)
 
 
 class RenderInfo:
@@ -267,7 +364,8 @@ def prep_scene(scene, device=0):
         api.build_KD_tree(scene.model, scene.division_method, scene.max_no_faces_per_node)
         n = scene.model.counts()
     if scene.ctx is None:
-        scene.ctx = Context(device)
+        scene.ctx = MultiContext(list(scene.gpu_devices)) if scene.gpu_devices and len(scene.gpu_devices) > 1 else \
+            Context(scene.gpu_devices[0] if scene.gpu_devices else device)
     scene.ctx.upload(scene.model, scene.sky, scene.material)
     if scene.spheres or scene.planes:
         scene.ctx.set_primitives(scene.spheres, scene.planes)
@@ -278,9 +376,51 @@ def start_render_from_camera(info, tpool=None):
     """start_render_from_camera(RenderInfo&, ThreadPool&) — renderer.cpp:403-455. Returns immediately; `tpool` is
     accepted for signature parity and ignored (the tile thread pool is replaced by the kernel)."""
     opts = info.opts or Context.opts()
+    if info.scene.ctx.render_poll(0):       # a frame is still in flight on this scene: the new one replaces it
+        info.scene.ctx.cancel()
     # jobs = bands of 8 scanlines (the reference lists square tiles, renderer.cpp:420-445; callers only show k/n)
     info.jobs_size, info.jobs_done = (info.camera.height + 7) // 8, 0
     info.scene.ctx.render_begin(info.camera, opts, info.camera_tex, info.t, info.prim)
+
+
+def clear_work_queue(info):
+    """info.twq.clear() — work_queue.h:11-15, the cancel of app.cpp:165-172: stops the frame in flight (the kernels' persistent
+    loops poll the context's cancel word) and returns when the GPU has drained. True when a frame was cut short."""
+    info.jobs_size = 0
+    return info.scene.ctx.cancel()
+
+
+def activate_pool(tpool, proc, data):
+    """thread_pool.h:14-20: one thread per pool slot on proc(data). `tpool` is a list the started threads are kept in."""
+    import threading
+    n = max(1, len(tpool))
+    tpool[:] = [threading.Thread(target=proc, args=(data,)) for _ in range(n)]
+    for th in tpool:
+        th.start()
+
+
+def wait_for_pool(tpool, time_out_in_ms=0xFFFFFFFF):
+    """thread_pool.h:22-26: TRUE (1) when the wait timed out, FALSE (0) when every thread has finished. The renderer never
+    activates the pool, so after clear_work_queue() this returns 0 at once (app.cpp:169)."""
+    import time
+    deadline = None if time_out_in_ms == 0xFFFFFFFF else time.monotonic() + time_out_in_ms / 1e3
+    for th in tpool or []:
+        if not hasattr(th, "join"):
+            continue
+        th.join(None if deadline is None else max(0.0, deadline - time.monotonic()))
+        if th.is_alive():
+            return 1
+    return 0
+
+
+def get_ray_kd_tree_intersection(op_ray, scene, tri_data=None):
+    """get_ray_kd_tree_intersection (kd_tree.h:56, kd_tree.cpp:302-313) for one ray: op_ray = (origin3, direction3); returns the
+    distance (MAX_FLOAT on a miss) and fills tri_data = {"face_index", "u", "v"} on a hit only."""
+    ctx = scene.ctx.ctx[0] if isinstance(scene.ctx, MultiContext) else scene.ctx
+    prim, t, uv = ctx.trace_rays_uv(np.asarray(op_ray, np.float32).reshape(1, 6))
+    if tri_data is not None and prim[0] != api.MISS:
+        tri_data.update(face_index=int(prim[0]), u=float(uv[0, 0]), v=float(uv[0, 1]))
+    return float(t[0])
 
 
 def wait_for_render_from_camera_to_finish(info, tpool=None, ms_to_wait_for=33):

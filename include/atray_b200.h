@@ -187,7 +187,13 @@ int atray_render_poll(atray_ctx* ctx, uint32_t timeout_ms);
  * copied out while later slabs are still being traced, so rows_done advances during the frame; small or partitioned
  * frames jump from 0 to rows_total on completion. */
 int atray_render_progress(atray_ctx* ctx, int32_t* rows_done, int32_t* rows_total);
-/* info.twq.clear() cancel path — app.cpp:165-172 */
+/* info.twq.clear() + wait_for_pool(UINT32MAX), the cancel path — app.cpp:165-172 (workers finish the tile they are on and find
+ * the queue empty). Raises the context's cancel word from a second stream while the kernel runs; every persistent loop (primary,
+ * culled, path, ray-list and C5 kernels) polls it next to its work cursor and stops taking tiles / ray groups; the call returns
+ * when the streams have drained. Pixels / rays not yet traced keep what the output buffers held; the pending host copy-out is
+ * dropped (atray_render_poll then reports "nothing in flight"). Acts on whatever the context stream holds: begin/poll frames and
+ * the asynchronous *_device entries. Returns 1 when work was on the stream and has been cut short, 0 when the context was idle.
+ * Call it from the thread that owns the context (the reference's app thread calls twq.clear() itself). */
 int atray_render_cancel(atray_ctx* ctx);
 /* Same frame, outputs left resident in device memory (planes are device pointers, may live on a peer GPU);
  * asynchronous on the context stream; pair with atray_ctx_sync. Used for the HBM-resident bench leg. */
@@ -224,6 +230,10 @@ int atray_trace_incoherent(atray_ctx* ctx, uint64_t p0, uint64_t p1, uint32_t sp
 /* same with device pointers, asynchronous on the context stream */
 int atray_trace_rays_device(atray_ctx* ctx, const float* rays_dev, uint64_t n, int32_t fp_mode, int32_t count_work,
                             uint32_t* prim_dev, float* t_dev);
+/* get_ray_kd_tree_intersection — kd_tree.h:56, kd_tree.cpp:302-313 (+ the scan loop's tri_data update, kd_tree.cpp:436-462):
+ * per ray the distance (MAX_FLOAT on a miss), TriangleIntersectionData.face_index (ATRAY_MISS) and its u, v (uv[2i], uv[2i+1];
+ * untouched on a miss, like tri_data). Host pointers, synchronous, strict arithmetic. n = 1 is the reference's call shape. */
+int atray_trace_rays_uv(atray_ctx* ctx, const float* rays, uint64_t n, uint32_t* prim, float* t, float* uv);
 /* The same query as atray_trace_rays_device (device pointers, asynchronous on the context stream, same outputs bit for bit) for
  * callers that cannot allocate: this entry calls no cudaMalloc / cudaFree / allocating routine on any path. The kernel's scratch
  * (the work cursor of its warps, the per-warp overflow areas of the leaf list and the node stack) lives in one static device array
@@ -287,6 +297,36 @@ int atray_view_share_check(atray_ctx* ctx);
 int atray_ctx_enable_peer(atray_ctx* ctx, atray_ctx* other);
 /* verification aid: run the view pass of every later frame as `shards` shard launches on this GPU alone (0 = off) */
 int atray_debug_view_shards(atray_ctx* ctx, int32_t shards);
+
+/* Several GPUs of one node from ONE process — the shape of the reference's tile pool (one address space, one bitmap, N workers:
+ * renderer.cpp:371-455, thread_pool.h:14-26) with GPUs as the workers: a context per device, the scene replicated, band b of
+ * band_rows scanlines rendered by context b % n, the per-frame view pass shared between the contexts over NVLink when they have
+ * peer access (atray_view_share_*; ATRAY_MULTI_SHARE=0 turns that off).
+ *   atray_ctx_create_multi   : devices[n] (NULL: spread over the visible devices), 1 <= n <= 8;
+ *   atray_multi_ctx          : context i, for the per-context calls (counters, primitives, kernel times …);
+ *   atray_multi_scene_upload : atray_scene_upload on every context (one host thread per device);
+ *   atray_multi_render_begin / _poll / _progress / _cancel: as the atray_render_* calls; opts->part.rank / world are overwritten.
+ *                              host_out: EVERY context copies exactly its scanlines into the same host planes (the planes that are
+ *                              not NULL: bgrx only, or all three), each over its own GPU's PCIe link; the frame is complete when
+ *                              poll returns 0. Progress counts the scanlines of the contexts that have finished;
+ *   atray_multi_render_device: asynchronous; device_out planes live on ONE device (normally context 0's, atray_dev_alloc) and the
+ *                              other contexts' kernels store their bands into them over NVLink; atray_multi_sync drains all. */
+typedef struct atray_multi atray_multi;
+int atray_ctx_create_multi(const int32_t* devices, int32_t n, atray_multi** out);
+void atray_multi_destroy(atray_multi* m);
+int atray_multi_count(const atray_multi* m);
+atray_ctx* atray_multi_ctx(atray_multi* m, int32_t i);
+int atray_multi_device(const atray_multi* m, int32_t i);
+int atray_multi_scene_upload(atray_multi* m, const atray_model* model, const AtrayMaterial* sky, const AtrayMaterial* model_mat);
+int atray_multi_scene_set_primitives(atray_multi* m, const AtraySphere* spheres, uint32_t n_spheres, const AtrayPlane* planes,
+                                     uint32_t n_planes);
+int atray_multi_scene_use_kd_tree(atray_multi* m, int use_kd_tree);
+int atray_multi_render_begin(atray_multi* m, const AtrayCamera* cam, const AtrayRenderOpts* opts, const AtrayFrame* host_out);
+int atray_multi_render_poll(atray_multi* m, uint32_t timeout_ms);
+int atray_multi_render_progress(atray_multi* m, int32_t* rows_done, int32_t* rows_total);
+int atray_multi_render_cancel(atray_multi* m);
+int atray_multi_render_device(atray_multi* m, const AtrayCamera* cam, const AtrayRenderOpts* opts, const AtrayFrame* device_out);
+int atray_multi_sync(atray_multi* m);
 
 /* K0 microbenchmarks for the roofline denominators: FP32 issue slots/s and L2 read GB/s. */
 int atray_microbench(atray_ctx* ctx, double* fp32_lane_ops_per_s, double* l2_read_gbs);

@@ -809,7 +809,7 @@ long long or_accepted_hits(void* h, int W, int H, const float* eye, const float*
     return count;
 }
 
-typedef struct { const or_scene* s; const float* rays; long long n; unsigned* face; float* t; } or_rays_arg;
+typedef struct { const or_scene* s; const float* rays; long long n; unsigned* face; float* t; float* uv; } or_rays_arg;
 static void or_rays_blocks(void* a_, int b0, int b1, or_scratch* sc, or_counters* ct)
 {
     or_rays_arg* a = a_;
@@ -818,12 +818,18 @@ static void or_rays_blocks(void* a_, int b0, int b1, or_scratch* sc, or_counters
         v3 o = { a->rays[6 * i], a->rays[6 * i + 1], a->rays[6 * i + 2] };
         v3 d = { a->rays[6 * i + 3], a->rays[6 * i + 4], a->rays[6 * i + 5] };
         float u, v;
-        or_intersect(a->s, o, d, sc, &a->t[i], &a->face[i], &u, &v, ct);
+        if (or_intersect(a->s, o, d, sc, &a->t[i], &a->face[i], &u, &v, ct) && a->uv) { a->uv[2 * i] = u; a->uv[2 * i + 1] = v; }
     }
 }
 void or_trace_rays(void* h, long long n, const float* rays, int threads, unsigned* face, float* t)
 {
-    or_rays_arg a = { h, rays, n, face, t };
+    or_rays_arg a = { h, rays, n, face, t, 0 };
+    or_parallel(a.s, (int)((n + 4095) / 4096), threads, or_rays_blocks, &a);
+}
+/* same with TriangleIntersectionData's u, v of the winning triangle (model.h:18-22, kd_tree.cpp:447-452); a miss leaves uv untouched */
+void or_trace_rays_uv(void* h, long long n, const float* rays, int threads, unsigned* face, float* t, float* uv)
+{
+    or_rays_arg a = { h, rays, n, face, t, uv };
     or_parallel(a.s, (int)((n + 4095) / 4096), threads, or_rays_blocks, &a);
 }
 

@@ -42,6 +42,8 @@ class Backend:
                                        C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         self.trace_rays = g("trace_rays")
         self.trace_rays.argtypes = [C.c_void_p, C.c_longlong, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
+        self.trace_rays_uv = g("trace_rays_uv")
+        self.trace_rays_uv.argtypes = [C.c_void_p, C.c_longlong, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
         self.render_jitter = g("render_jitter")
         self.render_jitter.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_uint, C.c_int, C.c_ulonglong, C.c_void_p,
                                        C.c_void_p, C.c_float, C.c_int, C.c_void_p, C.c_void_p]
@@ -215,6 +217,16 @@ class Scene:
         t = np.zeros(n, np.float32)
         self.b.trace_rays(self.h, n, _p(rays), threads, _p(face), _p(t))
         return face, t
+
+    def trace_rays_uv(self, rays, threads=1):
+        """trace_rays plus TriangleIntersectionData's (u, v) of the winning triangle; rows of misses stay NaN."""
+        rays = np.ascontiguousarray(rays, dtype=np.float32).reshape(-1, 6)
+        n = rays.shape[0]
+        face = np.zeros(n, np.uint32)
+        t = np.zeros(n, np.float32)
+        uv = np.full((n, 2), np.nan, np.float32)
+        self.b.trace_rays_uv(self.h, n, _p(rays), threads, _p(face), _p(t), _p(uv))
+        return face, t, uv
 
     def render_jitter(self, W, H, spp, seed, threads=1, bounce=1, eye=DEFAULT_EYE, facing=DEFAULT_FACING, hfov=DEFAULT_HFOV):
         img = np.zeros((H, W), np.uint32)

@@ -302,6 +302,28 @@ void ref_trace_rays(void* h, long long n, const float* rays, int threads, unsign
 	});
 }
 
+// Same list with TriangleIntersectionData's u, v of the winning triangle (a miss leaves uv untouched).
+void ref_trace_rays_uv(void* h, long long n, const float* rays, int threads, unsigned* face_out, float* t_out, float* uv_out)
+{
+	RefScene* rs = (RefScene*)h;
+	int blocks = (int)((n + 4095) / 4096);
+	parallel_rows(blocks, threads, [&](int b0, int b1, int) {
+		TraceScratch sc(rs->max_nodes);
+		for (long long i = (long long)b0 * 4096; i < (long long)b1 * 4096 && i < n; i++)
+		{
+			Ray ray;
+			ray.origin = { rays[6 * i], rays[6 * i + 1], rays[6 * i + 2] };
+			ray.direction = { rays[6 * i + 3], rays[6 * i + 4], rays[6 * i + 5] };
+			IntersectionData id;
+			get_intersection_data(ray, rs->scene, id, sc.tools);
+			bool hit = id.type == ObjectType::TRIANGLE;
+			face_out[i] = hit ? id.tid.face_index : REF_MISS;
+			t_out[i] = id.distance_at_intersection;
+			if (hit) { uv_out[2 * i] = id.tid.u; uv_out[2 * i + 1] = id.tid.v; }
+		}
+	});
+}
+
 } // extern "C"
 static inline uint64 splitmix64(uint64 x)
 {

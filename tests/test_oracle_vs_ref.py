@@ -33,6 +33,10 @@ def test_port_equals_reference(name, method, cap, port, ref, meshes):
     ra, rta = a.trace_rays(rays, threads=4)
     rb, rtb = b.trace_rays(rays, threads=4)
     assert (ra == rb).all() and same_bits(rta, rtb)
+    # TriangleIntersectionData's u, v of arbitrary rays (get_ray_kd_tree_intersection, kd_tree.cpp:302-313, 447-452)
+    ua, uta, uva = a.trace_rays_uv(rays[:20000], threads=4)
+    ub, utb, uvb = b.trace_rays_uv(rays[:20000], threads=4)
+    assert (ua == ub).all() and same_bits(uta, utb) and same_bits(uva, uvb) and ((ua != 0xFFFFFFFF).any() or not (ra != 0xFFFFFFFF).any())
     a.close(); b.close()
 
 
