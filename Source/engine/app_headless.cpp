@@ -4,7 +4,7 @@
 // (+ optional BMP and raw plane dumps). What app.cpp hard-codes (app.cpp:16, 81-96, 122-126) is a flag here:
 //   app_headless --obj model.obj [--res WxH] [--spp N] [--aa 0|1] [--bounces N] [--leaf-cap N] [--method sah|center]
 //                [--gpus N | --devices a,b,..] [--mode tree|notree] [--fp strict|fast] [--rescale S] [--loader-threads N]
-//                [--frames N] [--cancel-after-ms T] [--probe-ray ox,oy,oz,dx,dy,dz] [--bmp base] [--planes out.bin]
+//                [--gather bgrx|all] [--frames N] [--cancel-after-ms T] [--probe-ray ox,oy,oz,dx,dy,dz] [--bmp base] [--planes out.bin]
 //   (old positional form, still accepted: app_headless model.obj [W H] [rescale] [bmp_base] [planes.bin])
 #include <chrono>
 #include <cstdio>
@@ -22,6 +22,7 @@ struct Args
     uint32 W = 1280, H = 720, spp = 1, leaf_cap = 300, frames = 1;
     int32 aa = 0, bounces = 1, gpus = 1, loader_threads = 8, cancel_after_ms = -1;
     bool sah = true, notree = false, fast = false, probe_ray = false;
+    bool all_planes = true;   // --gather all: bitmap + hit distance + primitive id reach the host; bgrx: the bitmap only (the reference's output)
     f32 rescale = 0.f, probe[6] = {0, 0, 0, 0, 0, -1};
 };
 
@@ -30,7 +31,7 @@ static int usage(const char* exe)
     std::fprintf(stderr,
                  "usage: %s --obj model.obj [--res WxH] [--spp N] [--aa 0|1] [--bounces N] [--leaf-cap N] [--method sah|center]\n"
                  "          [--gpus N | --devices a,b,..] [--mode tree|notree] [--fp strict|fast] [--rescale S] [--loader-threads N]\n"
-                 "          [--frames N] [--cancel-after-ms T] [--probe-ray ox,oy,oz,dx,dy,dz] [--bmp base] [--planes out.bin]\n", exe);
+                 "          [--gather bgrx|all] [--frames N] [--cancel-after-ms T] [--probe-ray ox,oy,oz,dx,dy,dz] [--bmp base] [--planes out.bin]\n", exe);
     return 2;
 }
 
@@ -68,6 +69,7 @@ static bool parse(int argc, char** argv, Args& a)
         else if (k == "--fp") a.fast = std::strcmp(v, "fast") == 0;
         else if (k == "--rescale") a.rescale = (f32)std::atof(v);
         else if (k == "--loader-threads") a.loader_threads = std::atoi(v);
+        else if (k == "--gather") a.all_planes = std::strcmp(v, "bgrx") != 0;
         else if (k == "--frames") a.frames = (uint32)std::atoi(v);
         else if (k == "--cancel-after-ms") a.cancel_after_ms = std::atoi(v);
         else if (k == "--bmp") a.bmp = v;
@@ -150,8 +152,8 @@ int run(const Args& a)
     info.scene = &scene;
     info.hit_stack_capacity = kd_tree_max_nodes;
     info.leaf_stack_capacity = kd_tree_max_nodes;
-    info.hit_t = t.data();
-    info.hit_prim = prim.data();
+    info.hit_t = a.all_planes ? t.data() : nullptr;
+    info.hit_prim = a.all_planes ? prim.data() : nullptr;
     info.fp_mode = a.fast ? ATRAY_FP_FAST : ATRAY_FP_STRICT;
 
     double ms = 0.0, best = 1e30;

@@ -120,6 +120,12 @@ static int cuda_fail(cudaError_t e, const char* what)
     g_err = std::string(what) + ": " + cudaGetErrorString(e);
     return ATRAY_ECUDA;
 }
+// ATRAY_SHARE_MODE=0: the first version of the shared view pass (stamps and costs stored to the owning rank by the computing rank)
+static uint32_t share_ranges_only()
+{
+    const char* env = std::getenv("ATRAY_SHARE_MODE");
+    return (env && std::atoi(env) == 0) ? 0u : 1u;
+}
 namespace atray { int set_error(int code, const char* msg) { return fail(code, msg ? msg : ""); } }   // for multi_ctx.cpp
 #define CU(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) return cuda_fail(e__, #call); } while (0)
 
@@ -384,7 +390,7 @@ void atray_ctx_destroy(atray_ctx* c)
     free_scene(c);
     cudaFree(c->d_tile_counter); cudaFree(c->d_counters); cudaFree(c->d_casts);
     cudaFree(c->view.stamps); cudaFree(c->view.all_flag); cudaFree(c->view.busy_list); cudaFree(c->view.busy_count);
-    cudaFree(c->view.tile_cost); cudaFree(c->view.tile_log); cudaFree(c->view.wide_inner);
+    cudaFree(c->view.tile_cost); cudaFree(c->view.tile_log); cudaFree(c->view.wide_inner); cudaFree(c->view.big_list);
     cudaFree(c->view.bin_cnt); cudaFree(c->view.bin_leaf); cudaFree(c->view.bin_inner);
     cudaFree(c->share.block);
     cudaFree(c->rs.tabx); cudaFree(c->rs.taby); cudaFree(c->rs.key1); cudaFree(c->rs.key2); cudaFree(c->rs.hit_a);
@@ -767,6 +773,7 @@ static int enqueue_render(atray_ctx* c, const AtrayCamera* cam, const AtrayRende
             }
             if (!c->view.all_flag) CU(cudaMalloc(&c->view.all_flag, sizeof(uint32_t)));
             if (!c->view.wide_inner) CU(cudaMalloc(&c->view.wide_inner, size_t(kWideCap) * 2 * sizeof(uint4)));
+            if (!c->view.big_list) CU(cudaMalloc(&c->view.big_list, size_t(kBigCap) * sizeof(uint2)));
             if (!c->view.busy_count)
             {
                 CU(cudaMalloc(&c->view.busy_count, kCtlWords * sizeof(uint32_t)));
@@ -837,6 +844,7 @@ static int enqueue_render(atray_ctx* c, const AtrayCamera* cam, const AtrayRende
             pe.n = sh.world;
             pe.self = sh.rank;
             if (const char* env = std::getenv("ATRAY_SHARE_SKIP")) pe.debug_skip = uint32_t(std::atoi(env));
+            pe.ranges_only = share_ranges_only();
             pe.block_lo = uint32_t(uint64_t(n_blocks) * uint64_t(sh.rank) / uint64_t(sh.world));
             pe.block_hi = uint32_t(uint64_t(n_blocks) * uint64_t(sh.rank + 1) / uint64_t(sh.world));
             for (int q = 0; q < sh.world; ++q)
@@ -863,6 +871,8 @@ static int enqueue_render(atray_ctx* c, const AtrayCamera* cam, const AtrayRende
             ViewPeers pe{};
             pe.n = sh.debug_shards > o->part.world ? sh.debug_shards : o->part.world;
             if (pe.n > kMaxPeers) pe.n = kMaxPeers;
+            pe.ranges_only = share_ranges_only();
+            if (const char* env = std::getenv("ATRAY_SHARE_SKIP")) pe.debug_skip = uint32_t(std::atoi(env));
             for (int q = 0; q < pe.n; ++q)
             {
                 pe.tri_px[q] = vw.tri_px; pe.pkt_px[q] = vw.pkt_px; pe.chunk_px[q] = vw.chunk_px; pe.stamps[q] = vw.stamps;

@@ -22,7 +22,8 @@ struct atray_multi
     bool has_scene = false;
     bool peers_on = false;        // atray_ctx_enable_peer done for every ordered pair
     int share_w = 0, share_h = 0; // frame size the shared view pass is connected for (0: not connected)
-    bool share_wanted = true;     // ATRAY_MULTI_SHARE=0: every context computes the whole view pass itself
+    bool share_wanted = false;    // ATRAY_MULTI_SHARE=1: share the per-frame view pass between the contexts (measured slower than every
+                                  // context computing the whole pass itself at 2, 4 and 8 GPUs: profiles/r02i, r02j — opt-in)
     int in_flight = 0;            // contexts whose frame has not been collected by atray_multi_render_poll
     std::vector<char> running;    // per context
     int32_t rows_total = 0;

@@ -563,6 +563,7 @@ __global__ void __launch_bounds__(kBlock, 4) k_view_bounds(DevScene sc, ViewPara
     const bool pow2 = (rpb & (rpb - 1)) == 0 && (part.world & (part.world - 1)) == 0;
     const int rsh = __ffs(rpb) - 1, wmask = part.world - 1;
     auto owner = [&](int ty) -> int {
+        if (pe.ranges_only) return -1;   // shared pass, ranges only: every rank stamps its own tiles afterwards (k_view_stamp)
         if (part.world <= 1) return 0;
         const int o = pow2 ? ((ty >> rsh) & wmask) : ((ty / rpb) % part.world);
         return shared ? o : (o == part.rank ? 0 : -1);
@@ -629,8 +630,22 @@ __global__ void __launch_bounds__(kBlock, 4) k_view_bounds(DevScene sc, ViewPara
             }
         }
     }
-    // large ranges: the whole warp stamps the tiles of one triangle at a time
+    // large ranges: queued for k_view_big (a warp per range; a chunk of slots close to the eye can hold two hundred of them, which
+    // made the warps of that one block the critical path of the pass) — unless the stamps go to other GPUs (first shared version)
+    // or the queue is full: then the whole warp stamps the tiles of one triangle at a time
     unsigned bm = __ballot_sync(FULL_MASK, big);
+    if (bm && !shared && !pe.ranges_only && !pe.inline_big)
+    {
+        uint32_t at = 0;
+        if (lane == 0) at = atomicAdd(&view.busy_count[kCtlBig], (uint32_t)__popc(bm));
+        at = __shfl_sync(FULL_MASK, at, 0);
+        if (at + (uint32_t)__popc(bm) <= kBigCap)
+        {
+            if (big) view.big_list[at + __popc(bm & ((1u << lane) - 1u))] = s_slot_px[s_list[threadIdx.x]];
+            bm = 0u;
+        }
+    }
+    if (pe.ranges_only) bm = 0u;
     while (bm)
     {
         const int src = __ffs(bm) - 1;
@@ -706,6 +721,146 @@ __global__ void __launch_bounds__(kBlock, 4) k_view_bounds(DevScene sc, ViewPara
     }
 }
 
+// Shared pass: the tables are complete once every other rank's flag in this GPU's flag row has reached the frame's sequence
+// number (raised by the last block of that rank's k_view_bounds, on another GPU, after its stores). The calling kernel has
+// not read anything of the tables yet, so no stale line can sit in L1. Ends with a block barrier.
+__device__ __forceinline__ void wait_for_peer_tables(const ViewWait& vwait)
+{
+    if (threadIdx.x < (unsigned)vwait.n && (int)threadIdx.x != vwait.rank)
+    {
+        unsigned long long t0;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+        const volatile uint32_t* f = vwait.my_flags + threadIdx.x;
+        while ((int32_t)(*f - vwait.seq) < 0)
+        {
+            unsigned long long t1;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+            if (t1 - t0 > vwait.timeout_ns) { *vwait.timed_out = vwait.seq; break; }
+            __nanosleep(64);
+        }
+        __threadfence_system();
+    }
+    __syncthreads();
+}
+
+// Shared pass, second kernel: the slot ranges of the whole scene are in this GPU's tables (1/N computed here, the rest stored by
+// the peers over NVLink); every rank now stamps the tiles of ITS bands and adds up their costs from the ranges — local stores and
+// local atomics only (the first version of the shared pass sent each stamp and each cost increment to the owning GPU: scattered
+// 4-byte remote writes, slower than computing the whole pass alone; profiles/r02i). One thread per slot, a block per chunk of 256
+// slots; chunks whose union range misses this rank's rows (or is empty: back-facing / off-screen) leave after one load.
+__global__ void __launch_bounds__(kBlock) k_view_stamp(DevScene sc, ViewParams vp, DevView view, DevPartition part, ViewWait vwait, uint32_t dbg)
+{
+    const int lane = threadIdx.x & 31;
+    if (vwait.my_flags) wait_for_peer_tables(vwait);
+    const uint32_t chunk = blockIdx.x;
+    const uint32_t slot = chunk * kBlock + threadIdx.x;
+    const int rpb = part.band_rows >> 2;
+    const bool pow2 = (rpb & (rpb - 1)) == 0 && (part.world & (part.world - 1)) == 0;
+    const int rsh = __ffs(rpb) - 1, wmask = part.world - 1;
+    auto mine = [&](int ty) -> bool {
+        if (part.world <= 1) return true;
+        return (pow2 ? ((ty >> rsh) & wmask) : ((ty / rpb) % part.world)) == part.rank;
+    };
+    {
+        const uint2 c = view.chunk_px[chunk];
+        if (px_is_empty(c)) return;
+        const int cy0 = (int)(c.x >> 16) >> 2, cy1 = (int)(c.y >> 16) >> 2;
+        bool any = cy1 - cy0 + 1 >= rpb * part.world;
+        for (int ty = cy0; ty <= cy1 && !any; ++ty) any = mine(ty);
+        if (!any) return;
+    }
+    const int n_tiles = vp.tiles_x * vp.tiles_y;
+    const uint2 px = slot < sc.n_slots ? view.tri_px[slot] : px_empty();
+    int tx0 = 0, tx1 = -1, ty0 = 0, ty1 = -1;
+    bool big = false;
+    if (dbg & 8u) return;
+    if (!px_is_empty(px) && !(dbg & 2u))
+    {
+        tx0 = (int)(px.x & 0xffffu) >> 3; tx1 = (int)(px.y & 0xffffu) >> 3; ty0 = (int)(px.x >> 16) >> 2; ty1 = (int)(px.y >> 16) >> 2;
+        const int nt = (tx1 - tx0 + 1) * (ty1 - ty0 + 1);
+        if (2 * nt >= n_tiles) tx1 = tx0 - 1;   // (k_view_bounds raised the all-tiles flag on every rank)
+        else if (nt > 48) big = true;
+        else
+            for (int ty = ty0; ty <= ty1; ++ty)
+            {
+                if (!mine(ty)) continue;
+                uint32_t* st = view.stamps + ty * vp.tiles_x;
+                for (int tx = tx0; tx <= tx1; ++tx) st[tx] = vp.frame_id;
+            }
+    }
+    unsigned bm = __ballot_sync(FULL_MASK, big);
+    if (bm)   // queued for k_view_big, as in k_view_bounds
+    {
+        uint32_t at = 0;
+        if (lane == 0) at = atomicAdd(&view.busy_count[kCtlBig], (uint32_t)__popc(bm));
+        at = __shfl_sync(FULL_MASK, at, 0);
+        if (at + (uint32_t)__popc(bm) <= kBigCap)
+        {
+            if (big) view.big_list[at + __popc(bm & ((1u << lane) - 1u))] = px;
+            bm = 0u;
+        }
+    }
+    while (bm)
+    {
+        const int src = __ffs(bm) - 1;
+        bm &= bm - 1;
+        const int ax0 = __shfl_sync(FULL_MASK, tx0, src), ax1 = __shfl_sync(FULL_MASK, tx1, src);
+        const int ay0 = __shfl_sync(FULL_MASK, ty0, src), ay1 = __shfl_sync(FULL_MASK, ty1, src);
+        const int w = ax1 - ax0 + 1, n = w * (ay1 - ay0 + 1);
+        const float rw = __frcp_rn((float)w);
+        for (int i = lane; i < n; i += 32)   // flat over the range's tiles (a row-by-row loop leaves most lanes idle on narrow ranges)
+        {
+            int r = (int)(((float)i + 0.5f) * rw);   // i / w through the float reciprocal, corrected by one where it rounds off
+            if (r * w > i) --r;
+            if ((r + 1) * w <= i) ++r;
+            const int ty = ay0 + r;
+            if (mine(ty)) view.stamps[ty * vp.tiles_x + ax0 + (i - r * w)] = vp.frame_id;
+        }
+    }
+    // tile cost = packet ranges touching the tile, as in k_view_bounds
+    uint2 p = px;
+    p = px_union_xor(p, 4); p = px_union_xor(p, 2); p = px_union_xor(p, 1);
+    if (!px_is_empty(p) && !(dbg & 1u))
+    {
+        const int qx0 = (int)(p.x & 0xffffu) >> 3, qy0 = (int)(p.x >> 16) >> 2, qx1 = (int)(p.y & 0xffffu) >> 3, qy1 = (int)(p.y >> 16) >> 2;
+        if ((qx1 - qx0 + 1) * (qy1 - qy0 + 1) <= 64)
+            for (int ty = qy0; ty <= qy1; ++ty)
+            {
+                if (!mine(ty)) continue;
+                uint32_t* row = view.tile_cost + ty * vp.tiles_x;
+                for (int tx = qx0 + (lane & 7); tx <= qx1; tx += 8) atomicAdd(row + tx, 1u);
+            }
+    }
+}
+
+// The queued large ranges (DevView::big_list): one warp per range stamps the tiles of this rank's bands, lanes flat over the
+// range's tiles.
+__global__ void __launch_bounds__(kBlock) k_view_big(ViewParams vp, DevView view, DevPartition part)
+{
+    const int lane = threadIdx.x & 31;
+    const uint32_t n_big = min(view.busy_count[kCtlBig], kBigCap);
+    const int rpb = part.band_rows >> 2;
+    const bool pow2 = (rpb & (rpb - 1)) == 0 && (part.world & (part.world - 1)) == 0;
+    const int rsh = __ffs(rpb) - 1, wmask = part.world - 1;
+    const uint32_t n_warps = (gridDim.x * kBlock) >> 5;
+    for (uint32_t k = (blockIdx.x * kBlock + threadIdx.x) >> 5; k < n_big; k += n_warps)
+    {
+        const uint2 px = view.big_list[k];
+        const int ax0 = (int)(px.x & 0xffffu) >> 3, ax1 = (int)(px.y & 0xffffu) >> 3, ay0 = (int)(px.x >> 16) >> 2, ay1 = (int)(px.y >> 16) >> 2;
+        const int w = ax1 - ax0 + 1, n = w * (ay1 - ay0 + 1);
+        const float rw = __frcp_rn((float)w);
+        for (int i = lane; i < n; i += 32)
+        {
+            int r = (int)(((float)i + 0.5f) * rw);   // i / w through the float reciprocal, corrected by one where it rounds off
+            if (r * w > i) --r;
+            if ((r + 1) * w <= i) ++r;
+            const int ty = ay0 + r;
+            const bool mine = part.world <= 1 || (pow2 ? ((ty >> rsh) & wmask) : ((ty / rpb) % part.world)) == part.rank;
+            if (mine) view.stamps[ty * vp.tiles_x + ax0 + (i - r * w)] = vp.frame_id;
+        }
+    }
+}
+
 // Second pass, two kinds of blocks running side by side:
 //  * blocks [0, node_blocks): one warp per tree node (leaf or inner) unions the packet ranges of the node's subtree — one
 //    contiguous range of packets, whole chunks of 32 read from chunk_px — and appends the node to the bins its range
@@ -725,27 +880,8 @@ __global__ void __launch_bounds__(kBlock) k_view_nodes(DevScene sc, DevView view
                                                        uint32_t node_blocks, ViewWait vwait)
 {
     const int lane = threadIdx.x & 31;
-    if (vwait.my_flags)
-    {
-        // Shared pass: the tables are complete once every other rank's flag in this GPU's flag row has reached the frame's
-        // sequence number (raised by the last block of that rank's k_view_bounds, on another GPU, after its stores). Nothing
-        // of the tables has been read by this kernel yet, so no stale line can sit in L1.
-        if (threadIdx.x < (unsigned)vwait.n && (int)threadIdx.x != vwait.rank)
-        {
-            unsigned long long t0;
-            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
-            const volatile uint32_t* f = vwait.my_flags + threadIdx.x;
-            while ((int32_t)(*f - vwait.seq) < 0)
-            {
-                unsigned long long t1;
-                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
-                if (t1 - t0 > vwait.timeout_ns) { *vwait.timed_out = vwait.seq; break; }
-                __nanosleep(64);
-            }
-            __threadfence_system();
-        }
-        __syncthreads();
-    }
+    if (vwait.my_flags) wait_for_peer_tables(vwait);
+    if (blockIdx.x == 0 && threadIdx.x == 0) view.busy_count[kCtlBig] = 0u;   // k_view_big (before this kernel) was its last reader
     if (blockIdx.x < node_blocks)
     {
         const uint32_t warp = (blockIdx.x * kBlock + threadIdx.x) >> 5;
@@ -1995,6 +2131,7 @@ cudaError_t launch_view_bounds(const DevScene& sc, const ViewParams& vp, const D
         pe.tri_px[0] = view.tri_px; pe.pkt_px[0] = view.pkt_px; pe.chunk_px[0] = view.chunk_px;
         pe.stamps[0] = view.stamps; pe.tile_cost[0] = view.tile_cost; pe.all_flag[0] = view.all_flag;
     }
+    pe.inline_big = finish ? 0u : 1u;   // (a rasterised frame launches neither k_view_big nor k_view_nodes)
     const int grid = (int)(pe.block_hi - pe.block_lo);
     k_view_bounds<<<grid < 1 ? 1 : grid, kBlock, 0, stream>>>(sc, vp, view, part, pe);
     cudaError_t e = cudaGetLastError();
@@ -2006,11 +2143,24 @@ cudaError_t launch_view_bounds(const DevScene& sc, const ViewParams& vp, const D
     }
     if (after_bounds && (e = cudaEventRecord(after_bounds, stream)) != cudaSuccess) return e;
     if (!finish) return cudaSuccess;  // rasterised frame: no tile lists, no node ranges
+    ViewWait vw{};
+    if (wait) vw = *wait;
+    if (pe.ranges_only)
+    {
+        // every rank stamps its own tiles from the complete range tables (waits for the peers' flags first)
+        const uint32_t all_blocks = (sc.n_slots + kBlock - 1) / kBlock;
+        k_view_stamp<<<all_blocks < 1u ? 1u : all_blocks, kBlock, 0, stream>>>(sc, vp, view, part, vw, pe.debug_skip);
+        if ((e = cudaGetLastError()) != cudaSuccess) return e;
+        vw = ViewWait{};
+    }
+    if (pe.n == 1 || pe.ranges_only)
+    {
+        k_view_big<<<296, kBlock, 0, stream>>>(vp, view, part);
+        if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    }
     // one warp per node + 296 compaction blocks of 32 registers: all resident at once
     uint32_t node_blocks = (sc.n_nodes + kBlock / 32 - 1) / (kBlock / 32);
     if (node_blocks > 296u) node_blocks = 296u;
-    ViewWait vw{};
-    if (wait) vw = *wait;
     k_view_nodes<<<node_blocks + 296u, kBlock, 0, stream>>>(sc, view, cam, part, slabs, node_blocks, vw);
     return cudaGetLastError();
 }

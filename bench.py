@@ -280,7 +280,7 @@ def run_ours(args):
     gather = multi.FrameGather(ctx, dist, rank, world, W, H, local=("t", "prim"))
     # N > 1: the per-frame view pass is shared — every rank computes 1/N of the slot ranges and stores them into all ranks'
     # tables over NVLink (atray_view_share_*, CUDA-IPC between the rank processes)
-    share = multi.ViewShare(ctx, dist, rank, world, W, H) if (world > 1 and not args.no_share) else None
+    share = multi.ViewShare(ctx, dist, rank, world, W, H) if (world > 1 and args.share and not args.no_share) else None
     opts = ctx.opts(fp_mode=fp_mode, rank=rank, world=world, band_rows=BAND_ROWS)
     my_rays = multi.rays_of_rank(W, H, SPP, BAND_ROWS, rank, world)
     flush_bytes = 256 << 20                            # > 126 MB L2
@@ -709,7 +709,10 @@ def main():
     ap.add_argument("--fp", choices=["strict", "fast"], default="strict")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--config", choices=sorted(CONFIGS), default="c4", help="BASELINE.json configs[0..4]; c4 is the headline")
-    ap.add_argument("--no-share", action="store_true", help="N > 1: every rank computes the whole per-frame view pass itself")
+    ap.add_argument("--share", action="store_true",
+                    help="N > 1: share the per-frame view pass between the ranks over NVLink (atray_view_share_*); measured slower than "
+                         "every rank computing the pass itself at N = 2, 4 and 8 (profiles/r02i, r02j), so it is opt-in")
+    ap.add_argument("--no-share", action="store_true", help="(the default since r02i) every rank computes the whole per-frame view pass itself")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = 3  # timing rule: at least 3 warm-up steps

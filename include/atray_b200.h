@@ -300,8 +300,9 @@ int atray_debug_view_shards(atray_ctx* ctx, int32_t shards);
 
 /* Several GPUs of one node from ONE process — the shape of the reference's tile pool (one address space, one bitmap, N workers:
  * renderer.cpp:371-455, thread_pool.h:14-26) with GPUs as the workers: a context per device, the scene replicated, band b of
- * band_rows scanlines rendered by context b % n, the per-frame view pass shared between the contexts over NVLink when they have
- * peer access (atray_view_share_*; ATRAY_MULTI_SHARE=0 turns that off).
+ * band_rows scanlines rendered by context b % n, every context computing the per-frame view pass of its own bands
+ * (ATRAY_MULTI_SHARE=1 shares that pass between the contexts over NVLink instead, atray_view_share_* — measured slower on 2, 4 and 8
+ * B200s, so it is opt-in).
  *   atray_ctx_create_multi   : devices[n] (NULL: spread over the visible devices), 1 <= n <= 8;
  *   atray_multi_ctx          : context i, for the per-context calls (counters, primitives, kernel times …);
  *   atray_multi_scene_upload : atray_scene_upload on every context (one host thread per device);

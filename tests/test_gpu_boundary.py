@@ -157,6 +157,14 @@ def test_two_gpus_from_one_process(A, meshes):
     two = gpu_scene(A, path, rescale, devices=[0, 1])
     for cam in (A.set_camera(1920, 1080), A.set_camera(333, 101)):
         a = one.ctx.render(cam)
+        b = two.ctx.render(cam)
+        for k in a:
+            assert same_bits(a[k], b[k]), k
+    os.environ["ATRAY_MULTI_SHARE"] = "1"             # the opt-in shared view pass (ranges over NVLink, stamps on the owning GPU)
+    two = gpu_scene(A, path, rescale, devices=[0, 1])
+    del os.environ["ATRAY_MULTI_SHARE"]
+    for cam in (A.set_camera(1920, 1080), A.set_camera(333, 101)):
+        a = one.ctx.render(cam)
         for rep in range(3):                           # the shared view pass alternates its table buffers
             b = two.ctx.render(cam)
             for k in a:

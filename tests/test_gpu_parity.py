@@ -505,7 +505,11 @@ def test_view_pass_in_shards_gives_the_same_frame(A, meshes):
     path, rescale = meshes["knot_mid"]
     W, H = 1920, 1084
     results = []
-    for shards in (0, 2, 3, 8):
+    # ATRAY_SHARE_MODE (read per frame): default = ranges only + k_view_stamp on the owning rank; 0 = stamps stored by the computing rank
+    for shards, mode in ((0, None), (2, None), (3, None), (8, None), (3, "0"), (8, "0")):
+        os.environ.pop("ATRAY_SHARE_MODE", None)
+        if mode is not None:
+            os.environ["ATRAY_SHARE_MODE"] = mode
         sc = gpu_scene(A, path, rescale)
         ctx = sc.ctx
         ctx.debug_view_shards(shards)
@@ -530,6 +534,7 @@ def test_view_pass_in_shards_gives_the_same_frame(A, meshes):
         for k in ("bgrx", "t", "prim"):
             out["host." + k] = np.ascontiguousarray(host[k]).view(np.uint32)
         results.append(out)
+    os.environ.pop("ATRAY_SHARE_MODE", None)
     for other in results[1:]:
         assert other.keys() == results[0].keys()
         for k in results[0]:

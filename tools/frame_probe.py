@@ -21,6 +21,7 @@ ap.add_argument("--rank", type=int, default=0)
 ap.add_argument("--count", action="store_true")
 ap.add_argument("--host", action="store_true")
 ap.add_argument("--no-flush", action="store_true")
+ap.add_argument("--shards", type=int, default=0, help="run the view pass as N shard launches on this GPU (atray_debug_view_shards)")
 args = ap.parse_args()
 W, H = 3840, 2160
 path = gen_standin_obj.ensure(os.path.join(os.environ.get("ATRAY_MESH_CACHE", "/tmp/atray_meshes"), "standin_272x256.obj"))
@@ -29,6 +30,8 @@ A.place_default(m, 0.0)
 sc = A.Scene(m)
 A.prep_scene(sc)
 ctx = sc.ctx
+if args.shards:
+    ctx.debug_view_shards(args.shards)
 cam = A.set_camera(W, H)
 if args.host:
     import numpy as np
