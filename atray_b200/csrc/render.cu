@@ -232,10 +232,12 @@ __device__ __forceinline__ void scan_ray_leaves(const DevScene& sc, int lane, in
             if (COUNT) wc.pv += (real && alive) ? 1u : 0u;
             if (!__any_sync(FULL_MASK, alive)) continue;
             const float t = F::mul(F::dot(qx, qy, qz, AC.x, AC.y, AC.z), det_inv);
-            if (alive && t < bt && t > kTol)  // caller's accept: distance < closest && distance > tolerance
+            // caller's accept: distance < closest && distance > tolerance, scanning in the reference's leaf order: among equal
+            // distances the lower position wins (the records are Morton-sorted, so a lane does not meet them in that order)
+            if (alive && t > kTol && (t < bt || (t == bt && __float_as_uint(AB.w) < bpos)))
             {
                 bt = t;
-                bpos = __float_as_uint(AB.w);  // position in the reference's leaf order (records are Morton-sorted)
+                bpos = __float_as_uint(AB.w);  // position in the reference's leaf order
                 bface = __float_as_uint(A.w);
                 if (UV) { bu = u; bv = v; }
             }
@@ -1240,6 +1242,222 @@ __device__ __forceinline__ void scan_leaf_flat(const DevScene& sc, const DevView
     drain_pairs<STRICT, COUNT>(sc, wp, lane, qn, ray, wc);
 }
 
+// ---- the exact per-ray search (tree walk + sorted leaf list, as trace_warp) for CAMERA rays of the current frame, with the
+// leaf scan restricted to the triangles whose pixel range contains the ray's pixel: a triangle outside cannot be accepted
+// (view_bounds.h), so leaving it out changes nothing. Dense views (eye inside the model, close-ups) put hundreds of leaves
+// into a bin — more than the flat lists hold — and their tiles land here; a leaf of 300 triangles then costs one range load
+// per slot and one triangle-test round for the handful that cover the pixel instead of ten rounds.
+template <bool STRICT, bool COUNT>
+__device__ __forceinline__ void scan_ray_leaves_culled(const DevScene& sc, const DevView& vw, WarpPairs& wp, int lane, int src, const RayL& mine,
+                                                       uint32_t mypx, const uint2* my_list, int my_nleaf, float& out_t, uint32_t& out_face,
+                                                       WorkCount& wc)
+{
+    typedef Fp<STRICT> F;
+    const float ox = __shfl_sync(FULL_MASK, mine.ox, src), oy = __shfl_sync(FULL_MASK, mine.oy, src), oz = __shfl_sync(FULL_MASK, mine.oz, src);
+    const float dx = __shfl_sync(FULL_MASK, mine.dx, src), dy = __shfl_sync(FULL_MASK, mine.dy, src), dz = __shfl_sync(FULL_MASK, mine.dz, src);
+    const uint32_t p = __shfl_sync(FULL_MASK, mypx, src);
+    const int n = __shfl_sync(FULL_MASK, my_nleaf, src);
+    for (int k = 0; k < n; ++k)
+    {
+        uint32_t node = 0;
+        if (lane == src) node = my_list[k].x;
+        node = __shfl_sync(FULL_MASK, node, src);
+        const uint32_t first = ~(uint32_t)__float_as_int(__ldg(&sc.nodes[2 * node]).w);
+        const uint32_t cnt = (uint32_t)__float_as_int(__ldg(&sc.nodes[2 * node + 1]).w);
+        if (COUNT && lane == src) wc.scanned++;
+        float bt = kMaxFloat;
+        uint32_t bpos = 0xffffffffu, bface = 0xffffffffu;
+        int qn = 0;
+        const uint32_t padded = (cnt + 7u) & ~7u;
+        for (uint32_t base = 0; base < padded || qn > 0; base += 32)
+        {
+            // queue the slots of the next 32 whose range contains the pixel; test when 32 are waiting or the leaf ends
+            if (base < padded)
+            {
+                const uint32_t slot = first + base + lane;
+                const bool cand = base + lane < padded && px_contains(vw.tri_px[slot], p);
+                if (COUNT && base + lane < padded) wc.rect++;
+                const unsigned m = __ballot_sync(FULL_MASK, cand);
+                if (cand) wp.pair_slot[qn + __popc(m & ((1u << lane) - 1u))] = slot;
+                qn += __popc(m);
+                if (qn < 32 && base + 32 < padded) continue;
+            }
+            __syncwarp();
+            const int take = qn < 32 ? qn : 32;
+            const bool have = lane < take;
+            const uint32_t slot = have ? wp.pair_slot[qn - take + lane] : 0u;   // (the last `take` entries: the order is free)
+            qn -= take;
+            __syncwarp();
+            if (take == 0) break;
+            const float4* rec = sc.tris + (size_t)(slot >> 3) * 24 + (slot & 7);
+            float4 A = make_float4(0.f, 0.f, 0.f, __uint_as_float(0xffffffffu)), AB = make_float4(0.f, 0.f, 0.f, 0.f), AC = AB;
+            if (have) { A = __ldg(rec); AB = __ldg(rec + 8); AC = __ldg(rec + 16); }
+            const bool real = __float_as_uint(A.w) != 0xffffffffu;
+            const float px = F::crs(dy, AC.z, dz, AC.y), py = F::crs(dz, AC.x, dx, AC.z), pz = F::crs(dx, AC.y, dy, AC.x);
+            const float det = F::dot(AB.x, AB.y, AB.z, px, py, pz);
+            bool alive = have && !(det < kTol);
+            if (COUNT) { wc.tri += real ? 1u : 0u; wc.pdet += (real && alive) ? 1u : 0u; }
+            if (!__any_sync(FULL_MASK, alive)) continue;
+            const float det_inv = __frcp_rn(det);
+            const float tx = F::sub(ox, A.x), ty = F::sub(oy, A.y), tz = F::sub(oz, A.z);
+            const float u = F::mul(F::dot(tx, ty, tz, px, py, pz), det_inv);
+            alive = alive && !(u < 0.0f || u > 1.0f);
+            if (COUNT) wc.pu += (real && alive) ? 1u : 0u;
+            if (!__any_sync(FULL_MASK, alive)) continue;
+            const float qx = F::crs(ty, AB.z, tz, AB.y), qy = F::crs(tz, AB.x, tx, AB.z), qz = F::crs(tx, AB.y, ty, AB.x);
+            const float v = F::mul(F::dot(dx, dy, dz, qx, qy, qz), det_inv);
+            alive = alive && !(v < 0.0f || F::add(u, v) > 1.0f);
+            if (COUNT) wc.pv += (real && alive) ? 1u : 0u;
+            if (!__any_sync(FULL_MASK, alive)) continue;
+            const float t = F::mul(F::dot(qx, qy, qz, AC.x, AC.y, AC.z), det_inv);
+            const uint32_t pos = __float_as_uint(AB.w);
+            if (alive && t > kTol && (t < bt || (t == bt && pos < bpos)))   // per lane over several rounds: keep the (t, position) minimum
+            {
+                bt = t;
+                bpos = pos;
+                bface = __float_as_uint(A.w);
+            }
+        }
+        if (!__any_sync(FULL_MASK, bt < kMaxFloat)) continue;
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1)
+        {
+            const float ot = __shfl_xor_sync(FULL_MASK, bt, off);
+            const uint32_t op = __shfl_xor_sync(FULL_MASK, bpos, off);
+            const uint32_t of = __shfl_xor_sync(FULL_MASK, bface, off);
+            if (ot < bt || (ot == bt && op < bpos)) { bt = ot; bpos = op; bface = of; }
+        }
+        if (bt < kMaxFloat)
+        {
+            if (lane == src) { out_t = bt; out_face = bface; }
+            break;
+        }
+    }
+}
+
+// collect_leaves for a CAMERA ray of the current frame: children whose pixel range (node_px, the union over the subtree's
+// triangles) does not contain the ray's pixel are not examined — no triangle below them can be accepted for this ray, and
+// dropping leaves that cannot produce a hit from the sorted list does not change which leaf produces the first one. The "at most
+// 5 accepted children" cut (kd_tree.cpp:374) can only trigger at a node where two of the ray's three split-plane parameters
+// coincide (at most 4 octants contain the ray otherwise, see trace_tile_flat); such a node sends the ray to the exact walk.
+// Finite rays only (the caller has checked).
+template <bool COUNT>
+__device__ bool collect_leaves_culled(const float4* __restrict__ nodes, const uint32_t* __restrict__ leaf_seq, const uint2* node_px,
+                                      uint32_t mypx, const RayL& r, float ix, float iy, float iz, uint32_t* stack, int stack_cap, uint2* leaves,
+                                      int leaf_cap, int& nleaf, WorkCount& wc)
+{
+    nleaf = 0;
+    int sp = 1;
+    stack[0] = 0u;
+    const unsigned near_mask = (ix < 0.0f ? 4u : 0u) | (iy < 0.0f ? 2u : 0u) | (iz < 0.0f ? 1u : 0u);
+    while (sp > 0)
+    {
+        const uint32_t cur = stack[--sp];
+        const uint32_t c0 = (uint32_t)__float_as_int(__ldg(&nodes[2 * cur]).w);
+        {
+            const float4 s = __ldg(&nodes[2 * c0 + 1]);   // split point = hi corner of child 0 (kd_tree.cpp:120-148)
+            const float tsx = mulr(subr(s.x, r.ox), ix), tsy = mulr(subr(s.y, r.oy), iy), tsz = mulr(subr(s.z, r.oz), iz);
+            if (COUNT) wc.box++;
+            if (tsx == tsy || tsy == tsz || tsx == tsz)
+                return collect_leaves<COUNT>(nodes, leaf_seq, r, ix, iy, iz, stack, stack_cap, leaves, leaf_cap, nleaf, wc);
+        }
+        unsigned inner_acc = 0u;
+#pragma unroll 1
+        for (int i = 0; i < 8; ++i)
+        {
+            const uint32_t ch = c0 + i;
+            if (!px_contains(node_px[ch], mypx)) continue;
+            const float4 lo = __ldg(&nodes[2 * ch]);
+            const float4 hi = __ldg(&nodes[2 * ch + 1]);
+            if (COUNT) wc.box++;
+            if (__float_as_int(lo.w) > 0)
+            {
+                if (box_check(r, ix, iy, iz, lo, hi)) inner_acc |= 1u << i;
+            }
+            else
+            {
+                const float dis = box_entry(r, ix, iy, iz, lo, hi);
+                if (dis > 0.0f)
+                {
+                    if (nleaf >= leaf_cap) return false;
+                    int k = nleaf;
+                    while (k > 0)
+                    {
+                        const float pd = __uint_as_float(leaves[k - 1].y);
+                        if (!(dis < pd || (dis == pd && __ldg(&leaf_seq[ch]) < __ldg(&leaf_seq[leaves[k - 1].x])))) break;
+                        leaves[k] = leaves[k - 1];
+                        --k;
+                    }
+                    leaves[k] = make_uint2(ch, __float_as_uint(dis));
+                    ++nleaf;
+                    if (COUNT) wc.listed++;
+                }
+            }
+        }
+        if (inner_acc)
+        {
+            if (sp + __popc(inner_acc) > stack_cap) return false;
+#pragma unroll
+            for (int j = 7; j >= 0; --j)
+            {
+                const unsigned i = (unsigned)j ^ near_mask;
+                if ((inner_acc >> i) & 1u) stack[sp++] = c0 + i;
+            }
+        }
+    }
+    return true;
+}
+
+template <bool STRICT, bool COUNT>
+__device__ __forceinline__ void trace_warp_culled(const DevScene& sc, const DevScratch& scratch, const DevView& vw, WarpPairs& wp, int warp_slot,
+                                                  int lane, bool active, const RayL& ray, uint32_t mypx, uint2* leaves, uint32_t* stack,
+                                                  float& t_out, uint32_t& face_out, WorkCount& wc)
+{
+    t_out = kMaxFloat;
+    face_out = 0xffffffffu;
+    int nleaf = 0;
+    bool overflow = false;
+    const float ix = __frcp_rn(ray.dx), iy = __frcp_rn(ray.dy), iz = __frcp_rn(ray.dz);
+    if (active)
+    {
+        const float4 lo = __ldg(&sc.nodes[0]);
+        const float4 hi = __ldg(&sc.nodes[1]);
+        if (COUNT) wc.box++;
+        if (box_check(ray, ix, iy, iz, lo, hi))
+        {
+            if (sc.root_is_leaf) { leaves[0] = make_uint2(0u, 0u); nleaf = 1; }
+            else overflow = !collect_leaves_culled<COUNT>(sc.nodes, sc.leaf_seq, vw.node_px, mypx, ray, ix, iy, iz, stack, kStackCap, leaves, kLeafCap, nleaf, wc);
+            if (overflow) nleaf = 0;
+        }
+    }
+    unsigned todo = __ballot_sync(FULL_MASK, nleaf > 0);
+    while (todo)
+    {
+        const int src = __ffs(todo) - 1;
+        todo &= todo - 1;
+        scan_ray_leaves_culled<STRICT, COUNT>(sc, vw, wp, lane, src, ray, mypx, leaves, nleaf, t_out, face_out, wc);
+    }
+    unsigned spill = __ballot_sync(FULL_MASK, overflow);
+    while (spill)
+    {
+        const int src = __ffs(spill) - 1;
+        spill &= spill - 1;
+        uint2* gl = scratch.leaves + (size_t)warp_slot * scratch.leaf_cap;
+        uint32_t* gs = scratch.stack + (size_t)warp_slot * scratch.stack_cap;
+        int gn = 0;
+        if (lane == src)
+        {
+            if (COUNT) wc.ovf++;
+            WorkCount dummy;
+            dummy.clear();
+            collect_leaves_culled<false>(sc.nodes, sc.leaf_seq, vw.node_px, mypx, ray, ix, iy, iz, gs, (int)scratch.stack_cap, gl, (int)scratch.leaf_cap, gn, dummy);
+        }
+        __syncwarp();
+        scan_ray_leaves_culled<STRICT, COUNT>(sc, vw, wp, lane, src, ray, mypx, gl, gn, t_out, face_out, wc);
+        __syncwarp();
+    }
+}
+
 template <bool STRICT, bool COUNT>
 __device__ __forceinline__ void trace_tile_flat(const DevScene& sc, const DevScratch& scratch, const DevView& vw, WarpScratch& ws,
                                                 int warp_slot, int lane, bool active, const RayL& ray, int px_x, int px_y,
@@ -1294,7 +1512,10 @@ __device__ __forceinline__ void trace_tile_flat(const DevScene& sc, const DevScr
     if (nL > vw.bin_leaf_cap || nI > vw.bin_inner_cap)   // a list of this bin did not fit: the tile takes the unculled core
     {
         if (COUNT && active) wc.ovf++;
-        trace_warp<STRICT, COUNT>(sc, scratch, warp_slot, lane, active, ray, leaves, stack, t_out, face_out, wc);
+        // (tried instead, r02: larger lists — slower than this per-ray search from 1024 entries per bin on; candidates by a per-tile
+        // tree walk + the pair scan of the flat path — 2.5x slower on the dense views: their triangles cover whole tiles, every
+        // triangle becomes 32 pairs and the pair queue's bookkeeping dominates; profiles/r02_dense_views.md)
+        trace_warp_culled<STRICT, COUNT>(sc, scratch, vw, wp, warp_slot, lane, part, ray, mypx, leaves, stack, t_out, face_out, wc);
         return;
     }
     // ---- rays with a tie of split-plane parameters at an inner node above a candidate leaf ("risky") ----
