@@ -8,11 +8,12 @@ nvidia-smi --query-gpu=index,name --format=csv,noheader > $out/${tag}_gpus.txt 2
 timeout 300 python -m pytest tests/test_gpu_boundary.py tests/test_gpu_parity.py -m gpu -x -q -k "two_gpus" > $out/${tag}_two_gpu_tests.txt 2>&1
 tail -3 $out/${tag}_two_gpu_tests.txt
 port=29500
-for n in 2 4 8; do
-  for share in share noshare; do
+for n in 1 2 4 8; do
+  for share in noshare share; do
+    [ $n = 1 ] && [ $share = share ] && continue
     flag="--share"; [ $share = noshare ] && flag=""
     port=$((port+1))
-    timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port $port bench.py --gpus $n --steps 50 --warmup 5 $flag > $out/${tag}_bench_n${n}_${share}.json 2> $out/${tag}_bench_n${n}_${share}.err
+    timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port $port bench.py --gpus $n --steps 100 --warmup 5 $flag > $out/${tag}_bench_n${n}_${share}.json 2> $out/${tag}_bench_n${n}_${share}.err
     python - <<PY
 import json
 try:
