@@ -768,7 +768,9 @@ static int enqueue_render(atray_ctx* c, const AtrayCamera* cam, const AtrayRende
                         CU(cudaMalloc(&c->view.tile_log, tiles * sizeof(uint4)));
                         CU(cudaMemsetAsync(c->view.tile_log, 0, tiles * sizeof(uint4), c->stream));
                     }
-                c->view.cost_shift = 0;
+                c->view.cost_sample = 3;
+                if (const char* env = std::getenv("ATRAY_COST_SAMPLE")) c->view.cost_sample = std::atoi(env) < 0 ? 0 : (std::atoi(env) > 5 ? 5 : std::atoi(env));
+                c->view.cost_shift = -c->view.cost_sample;
                 if (const char* env = std::getenv("ATRAY_COST_SHIFT")) c->view.cost_shift = std::atoi(env);
             }
             if (!c->view.all_flag) CU(cudaMalloc(&c->view.all_flag, sizeof(uint32_t)));

@@ -82,6 +82,7 @@ struct DevView
     uint32_t bucket_stride; // entries per cost class (>= tiles of the frame)
     uint4* tile_log;       // verification aid (ATRAY_TILE_LOG=1), else null: per local tile {start ns, duration ns, sampled cost, class}
     int32_t cost_shift;    // class = floor(log2(ranges)) - cost_shift, clamped to [0, kCostBuckets)
+    int32_t cost_sample;   // one packet in 2^cost_sample contributes to the tile costs (cost_shift = -cost_sample keeps the classes)
     // Bins of kBinW x kBinH pixels: the tree nodes whose pixel range touches the bin, as flat lists (k_view_nodes). A tile
     // (8x4 pixels, inside exactly one bin) filters its bin's lists instead of walking the tree.
     //   leaf entry  = 3 uint4: {px.lo, px.hi, leaf_seq, first_slot} {box lo.xyz, count} {box hi.xyz, node}

@@ -566,6 +566,7 @@ __global__ void __launch_bounds__(kBlock, 4) k_view_bounds(DevScene sc, ViewPara
     const int rsh = __ffs(rpb) - 1, wmask = part.world - 1;
     auto owner = [&](int ty) -> int {
         if (pe.ranges_only) return -1;   // shared pass, ranges only: every rank stamps its own tiles afterwards (k_view_stamp)
+        if (pe.debug_skip & 32u) return -1;
         if (part.world <= 1) return 0;
         const int o = pow2 ? ((ty >> rsh) & wmask) : ((ty / rpb) % part.world);
         return shared ? o : (o == part.rank ? 0 : -1);
@@ -678,7 +679,32 @@ __global__ void __launch_bounds__(kBlock, 4) k_view_bounds(DevScene sc, ViewPara
             if (!skip_ranges || q == pe.self) pe.pkt_px[q][slot >> 3] = p;
     // tile cost = packet ranges touching the tile (what the leaf scan of the render kernel tests against the tile); the
     // packet's 8 lanes share the tiles of its range (every lane holds the same p after the butterfly)
-    if (!px_is_empty(p))
+    // Sampled: one packet in 2^cost_sample adds to the costs — the classes are octaves of the count, so a quarter of the packets
+    // orders the tiles as well. From a quarter on (at most one sampled packet per warp: its first) the whole warp shares that
+    // packet's tiles, lanes flat over the range, instead of 8 lanes walking its rows while 24 wait at the block barrier.
+    if (view.cost_sample >= 2)
+    {
+        const uint2 p0 = make_uint2(__shfl_sync(FULL_MASK, p.x, 0), __shfl_sync(FULL_MASK, p.y, 0));
+        const bool sampled = ((((slot - (uint32_t)lane) >> 3) & ((1u << view.cost_sample) - 1u)) == 0u) && !(pe.debug_skip & 16u);
+        if (sampled && !px_is_empty(p0))
+        {
+            const int qx0 = (int)(p0.x & 0xffffu) >> 3, qy0 = (int)(p0.x >> 16) >> 2, qx1 = (int)(p0.y & 0xffffu) >> 3, qy1 = (int)(p0.y >> 16) >> 2;
+            const int w = qx1 - qx0 + 1, n = w * (qy1 - qy0 + 1);
+            if (n <= 64)
+            {
+                const float rw = __frcp_rn((float)w);
+                for (int i = lane; i < n; i += 32)
+                {
+                    int r = (int)(((float)i + 0.5f) * rw);
+                    if (r * w > i) --r;
+                    if ((r + 1) * w <= i) ++r;
+                    const int ty = qy0 + r, o = owner(ty);
+                    if (o >= 0 && !(skip_cost && o != pe.self)) atomicAdd(pe.tile_cost[o] + ty * vp.tiles_x + qx0 + (i - r * w), 1u);
+                }
+            }
+        }
+    }
+    else if (!px_is_empty(p) && !(pe.debug_skip & 16u) && ((slot >> 3) & ((1u << view.cost_sample) - 1u)) == 0u)
     {
         const int qx0 = (int)(p.x & 0xffffu) >> 3, qy0 = (int)(p.x >> 16) >> 2, qx1 = (int)(p.y & 0xffffu) >> 3, qy1 = (int)(p.y >> 16) >> 2;
         if ((qx1 - qx0 + 1) * (qy1 - qy0 + 1) <= 64)
@@ -822,7 +848,7 @@ __global__ void __launch_bounds__(kBlock) k_view_stamp(DevScene sc, ViewParams v
     // tile cost = packet ranges touching the tile, as in k_view_bounds
     uint2 p = px;
     p = px_union_xor(p, 4); p = px_union_xor(p, 2); p = px_union_xor(p, 1);
-    if (!px_is_empty(p) && !(dbg & 1u))
+    if (!px_is_empty(p) && !(dbg & 1u) && ((slot >> 3) & ((1u << view.cost_sample) - 1u)) == 0u)
     {
         const int qx0 = (int)(p.x & 0xffffu) >> 3, qy0 = (int)(p.x >> 16) >> 2, qx1 = (int)(p.y & 0xffffu) >> 3, qy1 = (int)(p.y >> 16) >> 2;
         if ((qx1 - qx0 + 1) * (qy1 - qy0 + 1) <= 64)
@@ -2351,6 +2377,7 @@ cudaError_t launch_view_bounds(const DevScene& sc, const ViewParams& vp, const D
         pe.block_hi = (sc.n_slots + kBlock - 1) / kBlock;
         pe.tri_px[0] = view.tri_px; pe.pkt_px[0] = view.pkt_px; pe.chunk_px[0] = view.chunk_px;
         pe.stamps[0] = view.stamps; pe.tile_cost[0] = view.tile_cost; pe.all_flag[0] = view.all_flag;
+        if (const char* env = std::getenv("ATRAY_VIEW_SKIP")) pe.debug_skip = (uint32_t)std::atoi(env);   // profiling aid: 16 no costs, 32 no stamps
     }
     pe.inline_big = finish ? 0u : 1u;   // (a rasterised frame launches neither k_view_big nor k_view_nodes)
     const int grid = (int)(pe.block_hi - pe.block_lo);
