@@ -56,3 +56,19 @@ def test_python_pool_mirror(built):
     A.activate_pool(pool, lambda d: (time.sleep(0.15), d.append(threading.get_ident())), ran)
     assert A.wait_for_pool(pool, 10) == 1                # timed out
     assert A.wait_for_pool(pool) == 0 and len(ran) == 3
+
+
+def test_host_code_is_clean_under_asan_and_ubsan(meshes, tmp_path):
+    """`make -C atray_b200/csrc asan`: OBJ loader (1, 3, 8 chunks), transforms, both tree builders, flattening and the camera basis
+    under AddressSanitizer + UndefinedBehaviorSanitizer (-fno-sanitize-recover) on a procedural mesh, the reference's assets when
+    staged, an empty file and a file of junk lines. The kernels cannot be sanitised on this pool (compute-sanitizer is closed there)."""
+    subprocess.check_call(["make", "-C", os.path.join(ROOT, "atray_b200", "csrc"), "asan"], stdout=subprocess.DEVNULL)
+    junk = tmp_path / "junk.obj"
+    junk.write_text("v 1 2\nv\nf 1 2 3\nvn x y z\nf 1//1 2//2\n# comment\nv 0 0 0\nv 1 0 0\nv 0 1 0\nf 1 2 3\nf -1 -2 -3\nf 7 8 9\n\n")
+    empty = tmp_path / "empty.obj"
+    empty.write_text("")
+    files = [p for p, _ in meshes.values()] + [str(junk), str(empty)]
+    out = subprocess.run([os.path.join(ROOT, "atray_b200", "csrc", "host_sanitize")] + files, stdout=subprocess.PIPE, stderr=subprocess.STDOUT,
+                         text=True, timeout=600, env=dict(os.environ, ASAN_OPTIONS="detect_leaks=1"))
+    assert out.returncode == 0, out.stdout[-3000:]
+    assert "ERROR: AddressSanitizer" not in out.stdout and "runtime error" not in out.stdout, out.stdout[-3000:]

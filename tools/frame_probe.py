@@ -21,6 +21,7 @@ ap.add_argument("--rank", type=int, default=0)
 ap.add_argument("--count", action="store_true")
 ap.add_argument("--host", action="store_true")
 ap.add_argument("--no-flush", action="store_true")
+ap.add_argument("--band-rows", type=int, default=8)
 ap.add_argument("--shards", type=int, default=0, help="run the view pass as N shard launches on this GPU (atray_debug_view_shards)")
 args = ap.parse_args()
 W, H = 3840, 2160
@@ -36,7 +37,7 @@ cam = A.set_camera(W, H)
 if args.host:
     import numpy as np
     tex = A.PinnedArray((H, W), np.uint32)
-    info = A.RenderInfo(cam, sc, tex.array, opts=ctx.opts(rank=0, world=1, band_rows=8, raster=args.raster))
+    info = A.RenderInfo(cam, sc, tex.array, opts=ctx.opts(rank=0, world=1, band_rows=args.band_rows, raster=args.raster))
     best = 1e9
     for rep in range(3):
         for i in range(args.reps + 2):
@@ -53,7 +54,7 @@ if args.host:
     sys.exit(0)
 planes = [ctx.dev_alloc(W * H * 4) for _ in range(3)]
 flush = ctx.dev_alloc(256 << 20)
-opts = ctx.opts(rank=args.rank, world=args.world, band_rows=8, raster=args.raster, count_work=args.count)
+opts = ctx.opts(rank=args.rank, world=args.world, band_rows=args.band_rows, raster=args.raster, count_work=args.count)
 ms, rms, vs = [], [], []
 for i in range(args.reps + 2):
     if not args.no_flush:
