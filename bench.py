@@ -268,10 +268,17 @@ def run_ours(args):
         path = mesh_path()
     t_setup = time.perf_counter()
     model = A.load_model_data(path, 1 if MESH in ("Simple", "Cube") else min(8, host_threads()))
+    t_load = time.perf_counter()
     A.place_default(model, rescale=RESCALE)           # app.cpp:68-72 (no resize for the dragon; SURVEY 8d placement for the others)
     scene = A.Scene(model, division_method=A.DIV_SAH, max_no_faces_per_node=300)
-    A.prep_scene(scene, device=local_rank)            # build + flatten + upload once
+    A.build_KD_tree(model, scene.division_method, scene.max_no_faces_per_node)   # (prep_scene builds only if the model has no tree)
+    t_build = time.perf_counter()
+    scene.ctx = A.Context(local_rank)                 # CUDA context creation: the bulk of the set-up on a fresh process
+    t_ctx = time.perf_counter()
+    A.prep_scene(scene, device=local_rank)            # flatten + upload once
     setup_s = time.perf_counter() - t_setup
+    setup_parts = {"obj_load": t_load - t_setup, "place_and_tree_build": t_build - t_load, "cuda_context": t_ctx - t_build,
+                   "flatten_and_upload": t_setup + setup_s - t_ctx}
     ctx = scene.ctx
     cam = A.set_camera(W, H, samples_per_pixel=SPP, anti_aliasing=AA)
     # GPU 0 gathers the BGRX bitmap (what the live view shows, north_star); t and primitive ids stay on the rank that
@@ -475,7 +482,7 @@ def run_ours(args):
                      "ms_per_step_max_of_rank_sums": max_of_sums_ms / args.steps, "gathered_frame_equals_one_gpu_frame": gather_check,
                      "kernel_ms_rank0": {"k_view_bounds": float(np.mean([a for a, _ in split_ms])), "k_view_nodes": float(np.mean([b for _, b in split_ms])),
                                          "k_render_culled": float(np.mean(render_ms))},
-                     "counters": ctr, "setup_s": setup_s})
+                     "counters": ctr, "setup_s": setup_s, "setup_parts_s": setup_parts})
         line["config"].update({"fp_mode": args.fp, "band_rows": BAND_ROWS, "parallelism": "bands%d" % world,
                                "l2": "flushed between timed steps (256 MiB device memset outside the per-step event pair)",
                                "timing": "CUDA events on the library's stream around each frame's launch; per step the MAX over the ranks, summed over the K steps"
