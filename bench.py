@@ -284,7 +284,7 @@ def run_ours(args):
     # GPU 0 gathers the BGRX bitmap (what the live view shows, north_star); t and primitive ids stay on the rank that
     # traced them: 4 instead of 12 bytes per pixel cross NVLink into GPU 0 (device-resident leg; the e2e leg writes the host
     # bitmap directly from every rank, see below)
-    gather = multi.FrameGather(ctx, dist, rank, world, W, H, local=("t", "prim"))
+    gather = multi.FrameGather(ctx, dist, rank, world, W, H, local=() if args.gather == "all" else ("t", "prim"))
     # N > 1: the per-frame view pass is shared — every rank computes 1/N of the slot ranges and stores them into all ranks'
     # tables over NVLink (atray_view_share_*, CUDA-IPC between the rank processes)
     share = multi.ViewShare(ctx, dist, rank, world, W, H) if (world > 1 and args.share and not args.no_share) else None
@@ -344,9 +344,12 @@ def run_ours(args):
         max_of_sums_ms = float(steps_by_rank.sum(axis=1).max())
         # what GPU 0 gathered (every rank's peer stores) is the frame one GPU renders alone
         if rank == 0:
-            got = ctx.to_host(gather.planes["bgrx"], np.zeros((H, W), np.uint32))
-            ref = ctx.render(cam, ctx.opts(fp_mode=fp_mode), want=("bgrx",))["bgrx"]
-            gather_check = bool((got == ref).all())
+            want = ("bgrx", "t", "prim") if args.gather == "all" else ("bgrx",)
+            ref = ctx.render(cam, ctx.opts(fp_mode=fp_mode), want=want)
+            gather_check = True
+            for k in want:
+                got = ctx.to_host(gather.planes[k], np.zeros((H, W), np.uint32))
+                gather_check = gather_check and bool((got == np.ascontiguousarray(ref[k]).view(np.uint32)).all())
         barrier()
     else:
         dev_ms_max = dev_ms
@@ -489,7 +492,9 @@ def run_ours(args):
                                          + ("; every step starts after an on-stream flag rendezvous of the ranks" if share is not None else ""),
                                "view_pass": ("shared: each rank computes 1/%d of the slot ranges and peer-stores them into all ranks' tables (NVLink, CUDA IPC)" % world) if share is not None else "computed by every rank",
                                "devices": [pick_device(r, world, visible_gpus) for r in range(world)] if world > 1 else [local_rank],
-                               "gather": "BGRX bitmap: direct peer stores into GPU 0's frame through CUDA IPC; t/prim planes stay on the tracing rank" if world > 1 else "none (1 GPU)"})
+                               "gather": ("none (1 GPU)" if world == 1 else
+                                          "all three planes (12 B/px, SURVEY 8e): direct peer stores into GPU 0's frame through CUDA IPC" if args.gather == "all" else
+                                          "BGRX bitmap: direct peer stores into GPU 0's frame through CUDA IPC; t/prim planes stay on the tracing rank")})
     barrier()
     if tex is not None:
         tex.free()
@@ -716,6 +721,9 @@ def main():
     ap.add_argument("--fp", choices=["strict", "fast"], default="strict")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--config", choices=sorted(CONFIGS), default="c4", help="BASELINE.json configs[0..4]; c4 is the headline")
+    ap.add_argument("--gather", choices=("bgrx", "all"), default="bgrx",
+                    help="N > 1, device-resident leg: what GPU 0 gathers over NVLink — the bitmap (4 B/px, what the live view shows) or "
+                         "bitmap + hit distance + primitive id (12 B/px)")
     ap.add_argument("--share", action="store_true",
                     help="N > 1: share the per-frame view pass between the ranks over NVLink (atray_view_share_*); measured slower than "
                          "every rank computing the pass itself at N = 2, 4 and 8 (profiles/r02i, r02j), so it is opt-in")
