@@ -216,3 +216,35 @@ def test_app_headless_flags(A, port, meshes, tmp_path):
                          stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
     assert out.returncode == 0 and "frame was running" in out.stdout and "still running: 0" in out.stdout, out.stdout
     assert subprocess.run([EXE, "--res", "10x10"], stdout=subprocess.PIPE, stderr=subprocess.STDOUT).returncode == 2
+
+
+def test_ipc_gather_from_a_second_process(A, meshes):
+    """The device-resident gather of bench.py's N > 1 leg on one GPU: this process owns the three frame planes and renders rank 0
+    of 2; a SECOND process opens the planes through CUDA IPC (atray_ipc_export / atray_ipc_open) and renders rank 1 into them.
+    The union is the frame one context renders alone, and each process touched only its own bands."""
+    import sys
+    path, rescale = meshes["knot_mid"]
+    W, H = 1280, 716
+    sc = gpu_scene(A, path, rescale)
+    ctx = sc.ctx
+    cam = A.set_camera(W, H)
+    whole = ctx.render(cam)
+    planes = [ctx.dev_alloc(W * H * 4) for _ in range(3)]
+    for p in planes:
+        ctx.dev_memset(p, 0xEE, W * H * 4)
+    ctx.sync()
+    handles = [ctx.ipc_export(p).hex() for p in planes]
+    child = subprocess.run([sys.executable, os.path.join(ROOT, "tests", "ipc_child.py"), path, repr(float(rescale)), str(W), str(H), "1", "2"] + handles,
+                           stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=300)
+    assert child.returncode == 0 and "child rank 1 of 2 done" in child.stdout, child.stdout[-2000:]
+    half = [ctx.to_host(p, np.zeros((H, W), np.uint32)) for p in planes]
+    mine = (np.arange(H) // 8) % 2 == 0                     # bands of 8 scanlines: even bands are rank 0's
+    for got, k in zip(half, ("bgrx", "t", "prim")):
+        ref = np.ascontiguousarray(whole[k]).view(np.uint32)
+        assert (got[~mine] == ref[~mine]).all(), k          # the child's bands, stored from the other process
+        assert (got[mine] == 0xEEEEEEEE).all(), k           # and nothing else
+    ctx.render_device(cam, ctx.opts(rank=0, world=2, band_rows=8), *planes)
+    ctx.sync()
+    for p, k in zip(planes, ("bgrx", "t", "prim")):
+        assert (ctx.to_host(p, np.zeros((H, W), np.uint32)) == np.ascontiguousarray(whole[k]).view(np.uint32)).all(), k
+        ctx.dev_free(p)
