@@ -55,3 +55,12 @@ def test_no_cpu_fallback_without_gpu(built):
         pytest.skip("a GPU is present")
     with pytest.raises(A.AtrayError):
         A.Context(0)
+    with pytest.raises(A.AtrayError):
+        A.MultiContext([0, 1])
+    # the C++ host layer fails loudly too: prep_scene leaves scene.gpu null and app_headless exits non-zero
+    exe = os.path.join(ROOT, "Source", "engine", "app_headless")
+    if os.path.exists(exe):
+        from tools import gen_standin_obj
+        path = gen_standin_obj.ensure("/tmp/atray_meshes/knot_48x32.obj", 48, 32)
+        out = subprocess.run([exe, "--obj", path, "--res", "64x64"], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+        assert out.returncode != 0 and ("CUDA" in out.stdout or "device" in out.stdout), out.stdout
