@@ -87,7 +87,7 @@ struct DevView
     // (8x4 pixels, inside exactly one bin) filters its bin's lists instead of walking the tree.
     //   leaf entry  = 3 uint4: {px.lo, px.hi, leaf_seq, first_slot} {box lo.xyz, count} {box hi.xyz, node}
     //   inner entry = 2 uint4: {px.lo, px.hi, node, 0} {split point xyz (= hi corner of child 0, kd_tree.cpp:120-148), 0}
-    uint2* big_list;       // kBigCap pixel ranges of triangles whose range covers more than 48 tiles: stamped by k_view_big, a warp per range
+    uint2* big_list;       // kBigCap pixel ranges of triangles whose range covers more than 48 tiles: stamped by the node blocks of k_view_nodes, a warp per range
     uint4* wide_inner;     // kWideCap x 2 (same entry form): inner nodes near the root, whose range touches hundreds of bins
     uint32_t* bin_cnt;     // 2 per bin: leaf entries, inner entries (may exceed the capacities: the bin is then unusable)
     uint4* bin_leaf;       // bins x bin_leaf_cap x 3
@@ -111,7 +111,7 @@ struct ViewPeers
     int32_t n;                        // ranks the results go to (1 = only this GPU)
     uint32_t block_lo, block_hi;      // this rank's share of the k_view_bounds blocks
     uint32_t debug_skip;              // verification aid (ATRAY_SHARE_SKIP): 1 no remote cost, 2 no remote stamps, 4 no remote ranges
-    uint32_t inline_big;              // k_view_bounds stamps large ranges itself instead of queueing them for k_view_big
+    uint32_t inline_big;              // k_view_bounds stamps large ranges itself instead of queueing them for k_view_nodes
     uint32_t ranges_only;             // shared pass: peers receive the ranges only; each rank stamps its own tiles in k_view_stamp
     int32_t self;                     // this rank's index in the tables
     uint2* tri_px[kMaxPeers];
@@ -167,8 +167,9 @@ static constexpr int kCtlCount = 0;                              // [s * kCostBu
 static constexpr int kCtlCursor = kMaxSlabs * kCostBuckets;      // [s] consumer cursor of slab s
 static constexpr int kCtlDone = kCtlCursor + kMaxSlabs;          // [s] tiles of slab s whose stores are complete (sky + traced)
 static constexpr int kCtlWide = kCtlDone + kMaxSlabs;            // inner nodes in the wide list (DevView::wide_inner)
-static constexpr int kCtlTicket = kCtlWide + 1;                  // end of the words k_view_bounds clears every frame
-static constexpr int kCtlBig = kCtlTicket + 1;                   // entries of DevView::big_list (reset by k_view_nodes, after k_view_big has used it)
+static constexpr int kCtlBigDone = kCtlWide + 1;                 // node blocks of k_view_nodes that have stamped their share of the queued large ranges
+static constexpr int kCtlTicket = kCtlBigDone + 1;               // end of the words k_view_bounds clears every frame
+static constexpr int kCtlBig = kCtlTicket + 1;                   // entries of DevView::big_list (reset by the last node block of k_view_nodes to have used it)
 static constexpr int kCtlWords = kCtlTicket + 4;
 static constexpr uint32_t kBigCap = 1u << 16;
 struct DevSlabs

@@ -633,7 +633,7 @@ __global__ void __launch_bounds__(kBlock, 4) k_view_bounds(DevScene sc, ViewPara
             }
         }
     }
-    // large ranges: queued for k_view_big (a warp per range; a chunk of slots close to the eye can hold two hundred of them, which
+    // large ranges: queued for the node blocks of k_view_nodes (a warp per range; a chunk of slots close to the eye can hold two hundred of them, which
     // made the warps of that one block the critical path of the pass) — unless the stamps go to other GPUs (first shared version)
     // or the queue is full: then the whole warp stamps the tiles of one triangle at a time
     unsigned bm = __ballot_sync(FULL_MASK, big);
@@ -817,7 +817,7 @@ __global__ void __launch_bounds__(kBlock) k_view_stamp(DevScene sc, ViewParams v
             }
     }
     unsigned bm = __ballot_sync(FULL_MASK, big);
-    if (bm)   // queued for k_view_big, as in k_view_bounds
+    if (bm)   // queued for k_view_nodes, as in k_view_bounds
     {
         uint32_t at = 0;
         if (lane == 0) at = atomicAdd(&view.busy_count[kCtlBig], (uint32_t)__popc(bm));
@@ -861,34 +861,6 @@ __global__ void __launch_bounds__(kBlock) k_view_stamp(DevScene sc, ViewParams v
     }
 }
 
-// The queued large ranges (DevView::big_list): one warp per range stamps the tiles of this rank's bands, lanes flat over the
-// range's tiles.
-__global__ void __launch_bounds__(kBlock) k_view_big(ViewParams vp, DevView view, DevPartition part)
-{
-    const int lane = threadIdx.x & 31;
-    const uint32_t n_big = min(view.busy_count[kCtlBig], kBigCap);
-    const int rpb = part.band_rows >> 2;
-    const bool pow2 = (rpb & (rpb - 1)) == 0 && (part.world & (part.world - 1)) == 0;
-    const int rsh = __ffs(rpb) - 1, wmask = part.world - 1;
-    const uint32_t n_warps = (gridDim.x * kBlock) >> 5;
-    for (uint32_t k = (blockIdx.x * kBlock + threadIdx.x) >> 5; k < n_big; k += n_warps)
-    {
-        const uint2 px = view.big_list[k];
-        const int ax0 = (int)(px.x & 0xffffu) >> 3, ax1 = (int)(px.y & 0xffffu) >> 3, ay0 = (int)(px.x >> 16) >> 2, ay1 = (int)(px.y >> 16) >> 2;
-        const int w = ax1 - ax0 + 1, n = w * (ay1 - ay0 + 1);
-        const float rw = __frcp_rn((float)w);
-        for (int i = lane; i < n; i += 32)
-        {
-            int r = (int)(((float)i + 0.5f) * rw);   // i / w through the float reciprocal, corrected by one where it rounds off
-            if (r * w > i) --r;
-            if ((r + 1) * w <= i) ++r;
-            const int ty = ay0 + r;
-            const bool mine = part.world <= 1 || (pow2 ? ((ty >> rsh) & wmask) : ((ty / rpb) % part.world)) == part.rank;
-            if (mine) view.stamps[ty * vp.tiles_x + ax0 + (i - r * w)] = vp.frame_id;
-        }
-    }
-}
-
 // Second pass, two kinds of blocks running side by side:
 //  * blocks [0, node_blocks): one warp per tree node (leaf or inner) unions the packet ranges of the node's subtree — one
 //    contiguous range of packets, whole chunks of 32 read from chunk_px — and appends the node to the bins its range
@@ -909,11 +881,43 @@ __global__ void __launch_bounds__(kBlock) k_view_nodes(DevScene sc, DevView view
 {
     const int lane = threadIdx.x & 31;
     if (vwait.my_flags) wait_for_peer_tables(vwait);
-    if (blockIdx.x == 0 && threadIdx.x == 0) view.busy_count[kCtlBig] = 0u;   // k_view_big (before this kernel) was its last reader
     if (blockIdx.x < node_blocks)
     {
         const uint32_t warp = (blockIdx.x * kBlock + threadIdx.x) >> 5;
         const uint32_t n_warps = (node_blocks * kBlock) >> 5;
+        // First the queued large ranges (DevView::big_list, filled by k_view_bounds / k_view_stamp): one warp per range stamps the
+        // tiles of this rank's bands, lanes flat over the range's tiles. The compaction blocks below read the stamps, so every
+        // node block counts itself done once its share is stamped and they wait for that count (the grid — at most 592 blocks of
+        // 32 registers — is resident at once, and the node blocks have the lowest indices).
+        {
+            const uint32_t n_big = min(view.busy_count[kCtlBig], kBigCap);
+            const int rpb = part.band_rows >> 2;
+            const bool pow2 = (rpb & (rpb - 1)) == 0 && (part.world & (part.world - 1)) == 0;
+            const int rsh = __ffs(rpb) - 1, wmask = part.world - 1;
+            for (uint32_t k = warp; k < n_big; k += n_warps)
+            {
+                const uint2 px = view.big_list[k];
+                const int ax0 = (int)(px.x & 0xffffu) >> 3, ax1 = (int)(px.y & 0xffffu) >> 3, ay0 = (int)(px.x >> 16) >> 2, ay1 = (int)(px.y >> 16) >> 2;
+                const int w = ax1 - ax0 + 1, n = w * (ay1 - ay0 + 1);
+                const float rw = __frcp_rn((float)w);
+                for (int i = lane; i < n; i += 32)
+                {
+                    int r = (int)(((float)i + 0.5f) * rw);   // i / w through the float reciprocal, corrected by one where it rounds off
+                    if (r * w > i) --r;
+                    if ((r + 1) * w <= i) ++r;
+                    const int ty = ay0 + r;
+                    const bool mine = part.world <= 1 || (pow2 ? ((ty >> rsh) & wmask) : ((ty / rpb) % part.world)) == part.rank;
+                    if (mine) view.stamps[ty * view.tiles_x + ax0 + (i - r * w)] = view.frame_id;
+                }
+            }
+            __threadfence();
+            __syncthreads();
+            if (threadIdx.x == 0)
+            {
+                const uint32_t d = atomicAdd(&view.busy_count[kCtlBigDone], 1u);
+                if (d == node_blocks - 1u) view.busy_count[kCtlBig] = 0u;   // every node block has read the queue's length
+            }
+        }
         for (uint32_t node = warp; node < sc.n_nodes; node += n_warps)
         {
             const uint2 pk = __ldg(&sc.node_pk[node]);
@@ -992,6 +996,20 @@ __global__ void __launch_bounds__(kBlock) k_view_nodes(DevScene sc, DevView view
         }
         return;
     }
+    // (the large ranges are stamped by the node blocks: wait for them; bounded, as every cross-block wait here)
+    if (threadIdx.x == 0)
+    {
+        unsigned long long t0, t1;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+        while (*((volatile uint32_t*)&view.busy_count[kCtlBigDone]) < node_blocks)
+        {
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+            if (t1 - t0 > 1000000000ull) break;
+            __nanosleep(32);
+        }
+        __threadfence();
+    }
+    __syncthreads();
     // busy tiles of this rank, in the render kernel's local numbering (band-major, then tile row, then tile column)
     const int tiles_x = (cm.W + 7) >> 3;
     const int rows_per_band = part.band_rows >> 2;
@@ -2379,7 +2397,7 @@ cudaError_t launch_view_bounds(const DevScene& sc, const ViewParams& vp, const D
         pe.stamps[0] = view.stamps; pe.tile_cost[0] = view.tile_cost; pe.all_flag[0] = view.all_flag;
         if (const char* env = std::getenv("ATRAY_VIEW_SKIP")) pe.debug_skip = (uint32_t)std::atoi(env);   // profiling aid: 16 no costs, 32 no stamps
     }
-    pe.inline_big = finish ? 0u : 1u;   // (a rasterised frame launches neither k_view_big nor k_view_nodes)
+    pe.inline_big = finish ? 0u : 1u;   // (a rasterised frame does not launch k_view_nodes)
     const int grid = (int)(pe.block_hi - pe.block_lo);
     k_view_bounds<<<grid < 1 ? 1 : grid, kBlock, 0, stream>>>(sc, vp, view, part, pe);
     cudaError_t e = cudaGetLastError();
@@ -2401,11 +2419,7 @@ cudaError_t launch_view_bounds(const DevScene& sc, const ViewParams& vp, const D
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
         vw = ViewWait{};
     }
-    if (pe.n == 1 || pe.ranges_only)
-    {
-        k_view_big<<<296, kBlock, 0, stream>>>(vp, view, part);
-        if ((e = cudaGetLastError()) != cudaSuccess) return e;
-    }
+
     // one warp per node + 296 compaction blocks of 32 registers: all resident at once
     uint32_t node_blocks = (sc.n_nodes + kBlock / 32 - 1) / (kBlock / 32);
     if (node_blocks > 296u) node_blocks = 296u;
