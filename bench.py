@@ -480,7 +480,7 @@ def run_ours(args):
         line.update({"impl": "ours", "value": value, "ms_per_step": dev_ms_max / args.steps, "e2e": e2e, "roofline": roofline,
                      "cpu_baseline": cpu_baseline, "clocks": clocks,
                      # timed `value` region: k_view_bounds + k_view_finish + k_render_culled per step and rank
-                     "gpu_launches": (3 if share is None else 5) * args.steps * world,   # + flag kernels of the pass and of the rendezvous
+                     "gpu_launches": (3 if share is None else 6) * args.steps * world,   # k_view_bounds, k_view_nodes, k_render_culled (+ k_view_stamp and the two flag kernels of the rendezvous)
                      "wall_ms_bracket": wall_ms, "per_step_ms_rank0": per_step_ms, "ms_per_step_by_rank": per_rank_ms,
                      "ms_per_step_max_of_rank_sums": max_of_sums_ms / args.steps, "gathered_frame_equals_one_gpu_frame": gather_check,
                      "kernel_ms_rank0": {"k_view_bounds": float(np.mean([a for a, _ in split_ms])), "k_view_nodes": float(np.mean([b for _, b in split_ms])),
