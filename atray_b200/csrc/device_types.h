@@ -98,7 +98,13 @@ struct DevView
     uint32_t frame_id;
     int32_t tiles_x;
 };
-static constexpr int kBinShiftX = 6, kBinShiftY = 5;   // 64 x 32 pixels = 8 x 8 tiles
+#ifndef ATRAY_BIN_SHIFT_X
+#define ATRAY_BIN_SHIFT_X 6
+#endif
+#ifndef ATRAY_BIN_SHIFT_Y
+#define ATRAY_BIN_SHIFT_Y 5
+#endif
+static constexpr int kBinShiftX = ATRAY_BIN_SHIFT_X, kBinShiftY = ATRAY_BIN_SHIFT_Y;   // 64 x 32 pixels = 8 x 8 tiles (A/B builds may override)
 static constexpr int kWideCap = 32, kWideBins = 48;    // an inner node that touches more bins goes to the one wide list
 
 // Where k_view_bounds stores what it computes. One GPU: n = 1 and the tables of `view`. N GPUs that share the per-frame view

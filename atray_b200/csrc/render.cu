@@ -1118,7 +1118,10 @@ __global__ void __launch_bounds__(kBlock) k_view_nodes(DevScene sc, DevView view
 //    kept, a leaf is skipped for the rays that already hold a better key, and (t, position) is minimised inside a leaf —
 //    the lexicographic minimum the reference's list order + early exit (kd_tree.cpp:437-462) computes. The candidates of
 //    a chunk are taken nearest first (entry distance of the tile's first ray) so that later leaves are mostly skipped.
-static constexpr int kPairCap = 128;
+#ifndef ATRAY_PAIR_CAP
+#define ATRAY_PAIR_CAP 256   // (128: render kernel 254 -> 247 us on the stand-in with 256, same box)
+#endif
+static constexpr int kPairCap = ATRAY_PAIR_CAP;
 struct WarpPairs
 {
     unsigned long long key[32];        // per ray: min (t bits, position in the reference's leaf order) in the current leaf
@@ -1633,18 +1636,30 @@ __device__ __forceinline__ void trace_tile_flat(const DevScene& sc, const DevScr
                 const bool inr = part && px_contains(r, mypx);
                 if (!__any_sync(FULL_MASK, inr)) continue;
                 float4 lo, hi;
+#ifdef ATRAY_LEAF_UNIFORM_LOAD
+                const uint4* ei = vw.bin_leaf + ((size_t)bin * vw.bin_leaf_cap + base + (uint32_t)i) * 3;
+                const uint4 u0 = __ldg(ei), u1 = __ldg(ei + 1), u2 = __ldg(ei + 2);
+                lo = make_float4(__uint_as_float(u1.x), __uint_as_float(u1.y), __uint_as_float(u1.z), 0.f);
+                hi = make_float4(__uint_as_float(u2.x), __uint_as_float(u2.y), __uint_as_float(u2.z), 0.f);
+                const uint32_t seq = u0.z;
+#else
                 lo.x = __uint_as_float(__shfl_sync(FULL_MASK, e1.x, i)); lo.y = __uint_as_float(__shfl_sync(FULL_MASK, e1.y, i));
                 lo.z = __uint_as_float(__shfl_sync(FULL_MASK, e1.z, i)); hi.x = __uint_as_float(__shfl_sync(FULL_MASK, e2.x, i));
                 hi.y = __uint_as_float(__shfl_sync(FULL_MASK, e2.y, i)); hi.z = __uint_as_float(__shfl_sync(FULL_MASK, e2.z, i));
                 lo.w = hi.w = 0.f;
                 const uint32_t seq = __shfl_sync(FULL_MASK, e0.z, i);
+#endif
                 const float dis = box_entry(ray, ix, iy, iz, lo, hi);   // get_ray_AABB_intersection, aabb.h:29-63
                 const uint32_t db = __float_as_uint(dis);
                 const bool listed = inr && dis > 0.0f;                  // kd_tree.cpp:385-388
                 if (COUNT && inr) { wc.box++; wc.listed += listed ? 1u : 0u; }
                 const bool ing = listed && (db < best_dis || (db == best_dis && seq < best_seq));
                 if (!__any_sync(FULL_MASK, ing)) continue;
+#ifdef ATRAY_LEAF_UNIFORM_LOAD
+                const uint32_t first = u0.w, cnt = u1.w;
+#else
                 const uint32_t first = __shfl_sync(FULL_MASK, e0.w, i), cnt = __shfl_sync(FULL_MASK, e1.w, i);
+#endif
                 if (COUNT && ing) wc.scanned++;
                 scan_leaf_flat<STRICT, COUNT>(sc, vw, wp, lane, ray, first, cnt, ing, tr, tile_x0, tile_y0, wc);
                 const unsigned long long kk = wp.key[lane];
@@ -1678,8 +1693,11 @@ __device__ __forceinline__ void trace_tile_flat(const DevScene& sc, const DevScr
 // that runs out of work in a slab publishes the number of tiles it completed there (stores fenced first) and moves on:
 // ctl[kCtlDone + s] == tiles of slab s ⇔ every scanline of the slab is final — the host side's copy stream waits for
 // exactly that value (stream memory operation) and copies the slab out while later slabs are still being traced.
-template <bool STRICT, bool COUNT>
-__global__ void __launch_bounds__(kBlock, ATRAY_RENDER_MIN_BLOCKS) k_render_culled(DevScene sc, DevCamera cm, DevPartition part, DevOut out, DevScratch scratch,
+// MINB = resident CTAs per SM the kernel is compiled for: 3 (80 registers) or 4 (64 registers, more spills, more warps). With many
+// busy tiles per warp (one or two ranks on a 4K frame) the extra warps win (render kernel 254 -> 240 us on the stand-in); when a
+// rank's kernel is a single wave of tiles (4 or 8 ranks) the faster warps do (world 8: 74 against 79 us) — chosen per launch.
+template <bool STRICT, bool COUNT, int MINB>
+__global__ void __launch_bounds__(kBlock, MINB) k_render_culled(DevScene sc, DevCamera cm, DevPartition part, DevOut out, DevScratch scratch,
                                                           DevView vw, DevSlabs slabs, DevCounters* counters,
                                                           unsigned long long jitter_seed)
 {
@@ -2429,8 +2447,8 @@ cudaError_t launch_view_bounds(const DevScene& sc, const ViewParams& vp, const D
 
 // The culled kernel is persistent: its grid is exactly what is resident at once (a slab completes only when every warp
 // has done its static sky share, so no CTA may wait for an SM).
-template <bool STRICT, bool COUNT>
-static cudaError_t launch_culled_t(const DevScene& sc, const DevCamera& cam, const DevPartition& part, const DevOut& out,
+template <bool STRICT, bool COUNT, int MINB>
+static cudaError_t launch_culled_m(const DevScene& sc, const DevCamera& cam, const DevPartition& part, const DevOut& out,
                                    const DevScratch& scratch, const DevView& view, const DevSlabs& slabs, DevCounters* counters,
                                    unsigned long long jitter_seed, LaunchCfg cfg, cudaStream_t stream)
 {
@@ -2438,15 +2456,33 @@ static cudaError_t launch_culled_t(const DevScene& sc, const DevCamera& cam, con
     if (per_sm == 0)
     {
         int n = 0;
-        cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_render_culled<STRICT, COUNT>, kBlock, 0);
+        cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_render_culled<STRICT, COUNT, MINB>, kBlock, 0);
         if (e != cudaSuccess) return e;
         per_sm = n < 1 ? 1 : n;
     }
     const int sms = cfg.grid / 4;  // render_launch_cfg: 4 CTAs per SM is the upper bound the scratch areas are sized for
     int grid = sms * per_sm;
     if (grid > cfg.grid) grid = cfg.grid;
-    k_render_culled<STRICT, COUNT><<<grid, cfg.block, 0, stream>>>(sc, cam, part, out, scratch, view, slabs, counters, jitter_seed);
+    k_render_culled<STRICT, COUNT, MINB><<<grid, cfg.block, 0, stream>>>(sc, cam, part, out, scratch, view, slabs, counters, jitter_seed);
     return cudaGetLastError();
+}
+template <bool STRICT, bool COUNT>
+static cudaError_t launch_culled_t(const DevScene& sc, const DevCamera& cam, const DevPartition& part, const DevOut& out,
+                                   const DevScratch& scratch, const DevView& view, const DevSlabs& slabs, DevCounters* counters,
+                                   unsigned long long jitter_seed, LaunchCfg cfg, cudaStream_t stream)
+{
+    // tiles of this rank per resident warp at 3 CTAs per SM: above ~20 (a whole 4K frame: 73, half of one: 36) take the 4-CTA build
+    static int forced = -1;
+    if (forced < 0)
+    {
+        const char* env = std::getenv("ATRAY_RENDER_MIN_BLOCKS");
+        forced = env ? std::atoi(env) : 0;
+    }
+    const long long tiles = (long long)((cam.W + 7) >> 3) * ((cam.H + 3) >> 2) / (part.world > 0 ? part.world : 1);
+    const long long warps3 = (long long)(cfg.grid / 4) * 3 * (kBlock / 32);
+    const bool four = forced ? forced >= 4 : tiles > 20 * warps3;
+    if (four) return launch_culled_m<STRICT, COUNT, 4>(sc, cam, part, out, scratch, view, slabs, counters, jitter_seed, cfg, stream);
+    return launch_culled_m<STRICT, COUNT, ATRAY_RENDER_MIN_BLOCKS>(sc, cam, part, out, scratch, view, slabs, counters, jitter_seed, cfg, stream);
 }
 
 cudaError_t launch_render_culled(const DevScene& sc, const DevCamera& cam, const DevPartition& part, const DevOut& out,
