@@ -1636,30 +1636,18 @@ __device__ __forceinline__ void trace_tile_flat(const DevScene& sc, const DevScr
                 const bool inr = part && px_contains(r, mypx);
                 if (!__any_sync(FULL_MASK, inr)) continue;
                 float4 lo, hi;
-#ifdef ATRAY_LEAF_UNIFORM_LOAD
-                const uint4* ei = vw.bin_leaf + ((size_t)bin * vw.bin_leaf_cap + base + (uint32_t)i) * 3;
-                const uint4 u0 = __ldg(ei), u1 = __ldg(ei + 1), u2 = __ldg(ei + 2);
-                lo = make_float4(__uint_as_float(u1.x), __uint_as_float(u1.y), __uint_as_float(u1.z), 0.f);
-                hi = make_float4(__uint_as_float(u2.x), __uint_as_float(u2.y), __uint_as_float(u2.z), 0.f);
-                const uint32_t seq = u0.z;
-#else
                 lo.x = __uint_as_float(__shfl_sync(FULL_MASK, e1.x, i)); lo.y = __uint_as_float(__shfl_sync(FULL_MASK, e1.y, i));
                 lo.z = __uint_as_float(__shfl_sync(FULL_MASK, e1.z, i)); hi.x = __uint_as_float(__shfl_sync(FULL_MASK, e2.x, i));
                 hi.y = __uint_as_float(__shfl_sync(FULL_MASK, e2.y, i)); hi.z = __uint_as_float(__shfl_sync(FULL_MASK, e2.z, i));
                 lo.w = hi.w = 0.f;
                 const uint32_t seq = __shfl_sync(FULL_MASK, e0.z, i);
-#endif
                 const float dis = box_entry(ray, ix, iy, iz, lo, hi);   // get_ray_AABB_intersection, aabb.h:29-63
                 const uint32_t db = __float_as_uint(dis);
                 const bool listed = inr && dis > 0.0f;                  // kd_tree.cpp:385-388
                 if (COUNT && inr) { wc.box++; wc.listed += listed ? 1u : 0u; }
                 const bool ing = listed && (db < best_dis || (db == best_dis && seq < best_seq));
                 if (!__any_sync(FULL_MASK, ing)) continue;
-#ifdef ATRAY_LEAF_UNIFORM_LOAD
-                const uint32_t first = u0.w, cnt = u1.w;
-#else
                 const uint32_t first = __shfl_sync(FULL_MASK, e0.w, i), cnt = __shfl_sync(FULL_MASK, e1.w, i);
-#endif
                 if (COUNT && ing) wc.scanned++;
                 scan_leaf_flat<STRICT, COUNT>(sc, vw, wp, lane, ray, first, cnt, ing, tr, tile_x0, tile_y0, wc);
                 const unsigned long long kk = wp.key[lane];
