@@ -103,9 +103,9 @@ struct atray_ctx
     int32_t pending_rows = 0;                    // height of the frame in flight
     // Slab plan of a pipelined frame: a short first slab lets the copy-out start right after the view pass (frames bound by
     // the PCIe copy), a short last slab leaves little to copy once the kernel has retired (frames bound by tracing).
-    // ATRAY_SLABS=n: n equal slabs (1 = no pipelining); ATRAY_SLAB_WEIGHTS="2,6,8,16": relative heights. tools/slab_sweep.sh.
-    int slab_copy = 6;
-    int slab_w[kMaxSlabs] = {2, 6, 8, 8, 6, 2};
+    // ATRAY_SLABS=n: n equal slabs (1 = no pipelining); ATRAY_SLAB_WEIGHTS="1,4,8,8,8,4,2": relative heights. tools/slab_sweep.sh.
+    int slab_copy = 7;
+    int slab_w[kMaxSlabs] = {1, 4, 8, 8, 8, 4, 2};   // (r02p, host frame of C4: 696 us against 723 us for 2,6,8,8,6,2; 709 for 1,3,6,8,8,6,3,1)
     typedef int (*WaitValue32)(cudaStream_t, unsigned long long, uint32_t, unsigned int);
     WaitValue32 wait_value32 = nullptr;          // cuStreamWaitValue32 through cudaGetDriverEntryPoint
     // ray-list buffers (atray_trace_rays)

@@ -28,8 +28,11 @@ namespace atray {
 #define FULL_MASK 0xffffffffu
 static constexpr float kTol = 0.0001f;               // ray.h:5
 static constexpr float kMaxFloat = 3.402823466e+38F;  // PL_base_defs.h:70
-static constexpr int kLeafCap = 48;                   // per-lane leaf list (local memory); overflow → per-warp spill area
-static constexpr int kStackCap = 48;                  // per-lane inner-node stack
+#ifndef ATRAY_LEAF_CAP_LOCAL
+#define ATRAY_LEAF_CAP_LOCAL 48
+#endif
+static constexpr int kLeafCap = ATRAY_LEAF_CAP_LOCAL;                   // per-lane leaf list (local memory); overflow → per-warp spill area
+static constexpr int kStackCap = ATRAY_LEAF_CAP_LOCAL;                  // per-lane inner-node stack
 static constexpr int kBlock = 256;                    // 8 warps per CTA
 #ifndef ATRAY_RENDER_MIN_BLOCKS
 #define ATRAY_RENDER_MIN_BLOCKS 3                     // resident CTAs per SM the culled render kernel is compiled for (register cap)
