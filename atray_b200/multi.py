@@ -74,6 +74,14 @@ class FrameGather:
         self._opened, self._owned = [], []
 
 
+def chunk_pixels_of_rank(p0, p1, chunk_px, rank, world):
+    """Pixel indices of [p0, p1) that rank `rank` of `world` traces in a C5 job (atray_trace_incoherent_device): the range is cut
+    into chunks of `chunk_px` pixels and chunk k belongs to rank k % world (render.cu: k_c5) — contiguous chunks, no exchange."""
+    import numpy as np
+    rel = np.arange(p1 - p0, dtype=np.int64)
+    return p0 + rel[(rel // chunk_px) % world == rank]
+
+
 class ViewShare:
     """Shared per-frame view pass (atray_view_share_*): every rank computes the pixel ranges of 1/world of the triangle
     slots and stores them into all ranks' tables over NVLink. One process per GPU: the blocks travel as CUDA-IPC handles

@@ -55,7 +55,26 @@ def _worker(rank, world, port, q):
         def ipc_close(self, p):
             self.log.append(("close", p))
 
+        def view_share_create(self, w, h):
+            self.log.append(("share_create", w, h))
+            return 0xB10C0 + 0x100 * rank, 4096
+
+        def view_share_connect(self, r, n, peers):
+            self.log.append(("share_connect", r, n, tuple(peers)))
+
+        def view_share_off(self):
+            self.log.append(("share_off",))
+
     ctx = FakeCtx()
+    # the shared view pass: every rank exports its block, maps the others' and connects with its own block at its own index
+    sh = multi.ViewShare(ctx, dist, rank, world, 640, 360)
+    conn = [e for e in ctx.log if e[0] == "share_connect"][0]
+    own = 0xB10C0 + 0x100 * rank
+    assert conn[1] == rank and conn[2] == world and conn[3][rank] == own
+    assert all(conn[3][r] == 0xB10C0 + 0x100 * r + 7 for r in range(world) if r != rank)   # ipc_open of rank r's exported block
+    sh.close()
+    assert ctx.log[-2][0] == "share_off" and ctx.log[-1] == ("close", 0xB10C0 + 0x100 * (1 - rank) + 7)
+    del ctx.log[:]
     g = multi.FrameGather(ctx, dist, rank, world, 64, 32)
     planes = dict(g.planes)
     g.close()
@@ -166,3 +185,17 @@ def test_rank_placement_spreads_over_the_node():
     import bench
     for w, v in ((2, 8), (4, 8), (8, 8), (2, 2), (2, 3)):
         assert [bench.pick_device(r, w, v) for r in range(w)] == multi.spread_devices(w, v)
+
+
+@pytest.mark.parametrize("p0,p1,chunk,world", [(0, 100000, 4096, 8), (17, 9001, 100, 3), (0, 10, 4096, 2), (5, 5, 64, 4)])
+def test_c5_chunks_cover_every_pixel_once(p0, p1, chunk, world, built):
+    """The C5 split of SURVEY 8(e): contiguous chunks of the pixel range dealt round-robin, every pixel traced by exactly one rank."""
+    from atray_b200 import multi
+    parts = [multi.chunk_pixels_of_rank(p0, p1, chunk, r, world) for r in range(world)]
+    allp = np.sort(np.concatenate(parts)) if parts else np.zeros(0, np.int64)
+    assert (allp == np.arange(p0, p1)).all()
+    for r, p in enumerate(parts):
+        if p.size:
+            k = (p - p0) // chunk
+            assert (k % world == r).all()
+            assert all(len(run) <= chunk for run in np.split(p, np.flatnonzero(np.diff(p) != 1) + 1))
