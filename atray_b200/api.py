@@ -303,6 +303,15 @@ def set_camera(width, height, eye=DEFAULT_EYE, facing=DEFAULT_FACING, h_fov=DEFA
     return cam
 
 
+def update_camera_pos(cam, eye, facing):
+    """update_camera_pos(Camera&, eye, facing_towards) — camera.h:23-34: a new position and orientation for an existing camera;
+    resolution, samples, bounces and h_fov stay as set_camera left them. In place; returns the camera."""
+    e, f = _f3(eye), _f3(facing)
+    _ck(_L.atray_camera_set(C.byref(cam), cam.width, cam.height, cam.anti_aliasing, cam.samples_per_pixel, cam.bounce_limit, _p(e), _p(f),
+                            cam.h_fov))
+    return cam
+
+
 def camera_as_array(cam):
     """19 floats in the reference Camera layout after render_settings (camera.h:11-20)."""
     return np.array([cam.aspect_ratio, *cam.camera_z, *cam.camera_x, *cam.camera_y, *cam.eye, *cam.frame_center,

@@ -31,6 +31,7 @@ int main(int argc, char**) {
     uint32 n; prep_scene(scene, n);
     Texture tex; Setup_Texture(tex, TextureFileType::BMP, 64, 64);
     Camera cm; RenderSettings rs{}; set_camera(cm, {0.1f, 2.f, 0.f}, {-.1f, -0.5f, -1.f}, rs, 1.0f);
+    update_camera_pos(cm, {1.f, 2.f, 3.f}, {0.f, 0.f, -1.f});
     RenderInfo info; info.camera_tex = &tex; info.camera = &cm; info.scene = &scene;
     start_render_from_camera(info, tpool);
     while (wait_for_render_from_camera_to_finish(info, tpool, 33)) { info.twq.clear(); wait_for_pool(tpool, 0xffffffffu); }

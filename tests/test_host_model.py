@@ -90,6 +90,9 @@ def test_camera_matches_reference_kat(built):
     assert (bits(api.camera_as_array(A.set_camera(3840, 2160))) == kat["camera_3840x2160"]).all()
     cam = A.set_camera(640, 360, eye=(1.5, -2.0, 3.0), facing=(0.3, 0.2, -1.0), h_fov=0.8)
     assert (bits(api.camera_as_array(cam)) == kat["camera_custom"]).all()
+    # update_camera_pos (camera.h:23-34): moving a default camera to the custom pose gives the custom camera's basis, settings kept
+    moved = A.update_camera_pos(A.set_camera(640, 360, h_fov=0.8), (1.5, -2.0, 3.0), (0.3, 0.2, -1.0))
+    assert (bits(api.camera_as_array(moved)) == kat["camera_custom"]).all() and (moved.width, moved.height) == (640, 360)
 
 
 def test_loader_edge_cases(built, port, tmp_path):
