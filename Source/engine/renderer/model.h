@@ -25,6 +25,9 @@ inline void resize_scale(Model& mdl, f32 new_max_scale)
     atray_model_resize_scale(mdl.data.handle, new_max_scale);
     atray_model_dump(mdl.data.handle, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, &mdl.surrounding_aabb.min.x);
 }
+// model.h:123-134: declared by the reference with an empty body (no rotation is implemented there either)
+struct Bases { vec3f origin, x_axis, y_axis; };
+inline void transform(Model& mdl, vec3f axis, f32 radian) { (void)mdl; (void)axis; (void)radian; }
 // model.h:136-152
 inline void translate_to(Model& mdl, vec3f new_center)
 {

@@ -24,6 +24,15 @@ inline bool Setup_Texture(Texture& tex, TextureFileType file_type, uint32 width,
 }
 inline void Free_Texture(Texture& tex) { if (tex.bmb.buffer_memory) atray_host_free_pinned(tex.bmb.buffer_memory); tex.bmb.buffer_memory = nullptr; }
 
+// Set_Pixel (texture.h:27-38) for host code that draws into the bitmap itself (overlays, test patterns): {r, g, b} bytes to the
+// 32-bit B,G,R,0 pixel at column x of row y (row 0 = bottom). The renderer's own pixels are packed the same way on the device.
+inline void Set_Pixel(const Vec3<uint8>& color, Texture& texture, int32 x, int32 y)
+{
+    if (texture.file_type != TextureFileType::BMP) return;
+    if (x < 0 || y < 0 || (uint32)x >= texture.bmb.width || (uint32)y >= texture.bmb.height) return;
+    ((uint32*)texture.bmb.buffer_memory)[(size_t)y * texture.bmb.width + (size_t)x] = ((uint32)color.x << 16) | ((uint32)color.y << 8) | (uint32)color.z;
+}
+
 // Write_To_File (texture.cpp:66-115, 147-158): byte-identical BMP into "<file_name>_<id>.bmp", first id not yet on disk.
 inline bool Write_To_File(Texture& tex, const char* file_name)
 {

@@ -32,6 +32,7 @@ int main(int argc, char**) {
     Texture tex; Setup_Texture(tex, TextureFileType::BMP, 64, 64);
     Camera cm; RenderSettings rs{}; set_camera(cm, {0.1f, 2.f, 0.f}, {-.1f, -0.5f, -1.f}, rs, 1.0f);
     update_camera_pos(cm, {1.f, 2.f, 3.f}, {0.f, 0.f, -1.f});
+    Set_Pixel(vec3b{255, 128, 0}, tex, 3, 4); transform(model, {0.f, 1.f, 0.f}, 0.5f);
     RenderInfo info; info.camera_tex = &tex; info.camera = &cm; info.scene = &scene;
     start_render_from_camera(info, tpool);
     while (wait_for_render_from_camera_to_finish(info, tpool, 33)) { info.twq.clear(); wait_for_pool(tpool, 0xffffffffu); }
