@@ -89,6 +89,25 @@ def test_c2_monkey_1080p_and_c3_deer_jitter(A, port, meshes):
     o.close()
 
 
+@pytest.mark.parametrize("W,H", [(96, 720), (40, 1080), (1080, 64)])
+def test_jittered_portrait_and_strip_frames_equal_oracle(W, H, A, port, meshes):
+    """Anti-aliased frames far from 16:9: the jitter is half_pixel_width = 0.5 h_fov / W in film units while a pixel
+    is 2 h_fov aspect / W wide, i.e. 0.25 / aspect pixels in x — 4.5 pixels at 40x1080; the pixel ranges' slack is derived from
+    the camera, so no busy tile may be filled as sky. Pixels against the oracle's jitter loop, culled against unculled."""
+    from oracle import bind as B
+    path, rescale = meshes["knot_mid"]
+    sc = gpu_scene(A, path, rescale)
+    o = B.Scene(port, path, rescale=rescale)
+    cam = A.set_camera(W, H, anti_aliasing=1, samples_per_pixel=8)
+    a = sc.ctx.render(cam, sc.ctx.opts(seed=SEED))
+    b = sc.ctx.render(cam, sc.ctx.opts(seed=SEED, cull=False))
+    ref_img, hits = o.render_jitter(W, H, 8, SEED, threads=NTHREADS)
+    assert (a["bgrx"] == ref_img).all() and (b["bgrx"] == ref_img).all()
+    assert (a["prim"] == b["prim"]).all() and same_bits(a["t"], b["t"])
+    assert (hits > 0).any() and len(np.unique(ref_img)) > 2
+    o.close()
+
+
 def test_c4_standin_4k_full_size(A, port, standin):
     """BASELINE.json configs[3] at full size: bit-exact in STRICT mode, tolerance in FAST mode, work counters equal."""
     from oracle import bind as B
