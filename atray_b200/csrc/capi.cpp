@@ -194,7 +194,12 @@ int atray_model_build_tree(atray_model* m, int method, uint32_t cap)
     if (!m) return fail(ATRAY_EINVAL, "null model");
     if (method != ATRAY_DIV_CENTER && method != ATRAY_DIV_SAH) return fail(ATRAY_EINVAL, "unknown division method");
     std::string err;
-    int rc = build_tree(m->m, method, cap, err);
+    // the subtrees below the root are built by up to 8 host threads (same node array as the reference's sequential builder);
+    // ATRAY_BUILD_THREADS=1 builds sequentially
+    int threads = int(std::thread::hardware_concurrency());
+    if (threads > 8) threads = 8;
+    if (const char* env = std::getenv("ATRAY_BUILD_THREADS")) threads = std::atoi(env);
+    int rc = build_tree(m->m, method, cap, err, threads < 1 ? 1 : threads);
     if (rc != 0) return fail(ATRAY_ELIMIT, err);
     return ATRAY_OK;
 }

@@ -293,7 +293,107 @@ static bool split_point(const TreeNode& n, int method, Vec3& s)
     return inside(s, n.box);
 }
 
-int build_tree(HostModel& m, int method, uint32_t cap, std::string& err)
+// One step of the builder (kd_tree.cpp:67-288): splits L[id] into 8 children appended at the end of L when it holds more than
+// `cap` primitives and its split point lies inside its box. Returns false when the node stays a leaf.
+static bool split_node(std::vector<TreeNode>& L, uint32_t id, int method, uint32_t cap, size_t& live_refs)
+{
+    if (L[id].prims.size() <= cap) return false;
+    Vec3 s;
+    if (!split_point(L[id], method, s)) return false;
+    const Box pb = L[id].box;
+    std::vector<PrimRef> parent;
+    parent.swap(L[id].prims);
+    const uint32_t first = uint32_t(L.size());
+    L[id].children_start = int32_t(first);
+    L.resize(L.size() + 8);
+    for (int c = 0; c < 8; ++c)
+    {
+        Box& cb = L[first + c].box;
+        cb.lo.x = (c & 4) ? s.x : pb.lo.x; cb.hi.x = (c & 4) ? pb.hi.x : s.x;
+        cb.lo.y = (c & 2) ? s.y : pb.lo.y; cb.hi.y = (c & 2) ? pb.hi.y : s.y;
+        cb.lo.z = (c & 1) ? s.z : pb.lo.z; cb.hi.z = (c & 1) ? pb.hi.z : s.z;
+    }
+    live_refs -= parent.size();
+    for (const PrimRef& t : parent)
+        for (int c = 0; c < 8; ++c)
+        {
+            const Box& cb = L[first + c].box;
+            if (inside(t.a, cb) || inside(t.b, cb) || inside(t.c, cb)) { L[first + c].prims.push_back(t); ++live_refs; }
+        }
+    return true;
+}
+
+static const char* kGuardMessage = "tree build exceeded the node/primitive guard (degenerate split; the reference would not terminate)";
+
+// The reference's order: a LIFO work list, the 8 children of a node appended when the node is taken — a pre-order walk that visits
+// the children 7, 6, … 0, every subtree complete before the next. L[0] is the subtree's root (with its primitives).
+static int build_sequential(std::vector<TreeNode>& L, int method, uint32_t cap, std::string& err)
+{
+    std::vector<uint32_t> todo{0u};
+    size_t live_refs = L[0].prims.size();
+    while (!todo.empty())
+    {
+        const uint32_t id = todo.back();
+        todo.pop_back();
+        if (!split_node(L, id, method, cap, live_refs)) continue;
+        const uint32_t first = uint32_t(L[id].children_start);
+        for (uint32_t c = 0; c < 8; ++c) todo.push_back(first + c);
+        if (live_refs > 400000000u || L.size() > 40000000u) { err = kGuardMessage; return -5; }
+    }
+    return 0;
+}
+
+// SURVEY §8 f4 (first half): the same tree, built by several threads. Because every subtree is complete before the next one starts,
+// the nodes below child c of a split node are one contiguous run of the reference's array, and the runs follow each other in the
+// order 7, 6, … 0 behind the node's 8 children. So the 8 subtrees are built independently (each in its own array with local
+// numbering, `depth` levels of fan-out) and spliced behind one another with their child indices rebased: bit-identical node array
+// (tests/test_host_model.py compares it with the reference build's).
+static int build_parallel(std::vector<TreeNode>& L, int method, uint32_t cap, int depth, std::string& err)
+{
+    if (depth <= 0) return build_sequential(L, method, cap, err);
+    size_t live_refs = L[0].prims.size();
+    if (!split_node(L, 0, method, cap, live_refs)) return 0;   // L = {root, 8 children}
+    std::vector<TreeNode> sub[8];
+    int rc[8];
+    std::string errs[8];
+    std::vector<std::thread> th;
+    for (int c = 0; c < 8; ++c)
+    {
+        sub[c].resize(1);
+        sub[c][0].box = L[1 + c].box;
+        sub[c][0].prims.swap(L[1 + c].prims);
+        rc[c] = 0;
+    }
+    for (int c = 1; c < 8; ++c)
+        th.emplace_back([&, c] { rc[c] = build_parallel(sub[c], method, cap, depth - 1, errs[c]); });
+    rc[0] = build_parallel(sub[0], method, cap, depth - 1, errs[0]);
+    for (std::thread& t : th) t.join();
+    for (int c = 0; c < 8; ++c)
+        if (rc[c] != 0) { err = errs[c]; return rc[c]; }
+    size_t total = L.size();
+    for (int c = 0; c < 8; ++c) total += sub[c].size() - 1;
+    if (total > 40000000u) { err = kGuardMessage; return -5; }
+    L.reserve(total);
+    for (int c = 7; c >= 0; --c)
+    {
+        const int32_t base = int32_t(L.size());   // local index i >= 1 of this subtree lands at base + i - 1
+        TreeNode& root = L[1 + c];
+        root.prims.swap(sub[c][0].prims);
+        root.children_start = sub[c][0].children_start > 0 ? base + sub[c][0].children_start - 1 : 0;
+        for (size_t i = 1; i < sub[c].size(); ++i)
+        {
+            L.emplace_back();
+            TreeNode& n = L.back();
+            n.box = sub[c][i].box;
+            n.children_start = sub[c][i].children_start > 0 ? base + sub[c][i].children_start - 1 : 0;
+            n.prims.swap(sub[c][i].prims);
+        }
+        std::vector<TreeNode>().swap(sub[c]);
+    }
+    return 0;
+}
+
+int build_tree(HostModel& m, int method, uint32_t cap, std::string& err, int threads)
 {
     m.tree.clear();
     m.max_faces_per_node = cap;
@@ -306,43 +406,10 @@ int build_tree(HostModel& m, int method, uint32_t cap, std::string& err)
         const Face& f = m.faces[i];
         m.tree[0].prims[i] = {m.vertices[f.v[0]], m.vertices[f.v[1]], m.vertices[f.v[2]], uint32_t(i)};
     }
-    std::vector<uint32_t> todo{0u};
-    size_t live_refs = m.faces.size();
-    while (!todo.empty())
-    {
-        const uint32_t id = todo.back();
-        todo.pop_back();
-        if (m.tree[id].prims.size() <= cap) continue;
-        Vec3 s;
-        if (!split_point(m.tree[id], method, s)) continue;
-        const Box pb = m.tree[id].box;
-        std::vector<PrimRef> parent;
-        parent.swap(m.tree[id].prims);
-        const uint32_t first = uint32_t(m.tree.size());
-        m.tree[id].children_start = int32_t(first);
-        m.tree.resize(m.tree.size() + 8);
-        for (int c = 0; c < 8; ++c)
-        {
-            Box& cb = m.tree[first + c].box;
-            cb.lo.x = (c & 4) ? s.x : pb.lo.x; cb.hi.x = (c & 4) ? pb.hi.x : s.x;
-            cb.lo.y = (c & 2) ? s.y : pb.lo.y; cb.hi.y = (c & 2) ? pb.hi.y : s.y;
-            cb.lo.z = (c & 1) ? s.z : pb.lo.z; cb.hi.z = (c & 1) ? pb.hi.z : s.z;
-        }
-        live_refs -= parent.size();
-        for (const PrimRef& t : parent)
-            for (int c = 0; c < 8; ++c)
-            {
-                const Box& cb = m.tree[first + c].box;
-                if (inside(t.a, cb) || inside(t.b, cb) || inside(t.c, cb)) { m.tree[first + c].prims.push_back(t); ++live_refs; }
-            }
-        for (uint32_t c = 0; c < 8; ++c) todo.push_back(first + c);
-        if (live_refs > 400000000u || m.tree.size() > 40000000u)
-        {
-            err = "tree build exceeded the node/primitive guard (degenerate split; the reference would not terminate)";
-            return -5;
-        }
-    }
-    return 0;
+    // one level of fan-out (8 subtrees) from a few thousand faces on, two (64) for large meshes; small ones are not worth a thread
+    int depth = 0;
+    if (threads > 1 && m.faces.size() >= 4096) depth = (threads > 8 && m.faces.size() >= 500000) ? 2 : 1;
+    return build_parallel(m.tree, method, cap, depth, err);
 }
 
 // ---------------------------------------------------------------------------------------------------------------

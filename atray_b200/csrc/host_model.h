@@ -59,7 +59,8 @@ int load_obj(const char* path, int threads, HostModel& m, std::string& err);
 void compute_aabb(HostModel& m);
 void resize_scale(HostModel& m, float new_max_scale);
 void translate_to(HostModel& m, Vec3 new_center);
-int build_tree(HostModel& m, int method, uint32_t cap, std::string& err);
+// threads > 1: the subtrees below the root are built concurrently (same node array, see host_model.cpp)
+int build_tree(HostModel& m, int method, uint32_t cap, std::string& err, int threads = 1);
 void flatten(const HostModel& m, FlatScene& out);
 
 struct CameraBasis { float aspect; Vec3 cz, cx, cy, eye, fc; float h_fov, hpw, hph; };

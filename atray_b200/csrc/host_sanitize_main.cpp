@@ -21,7 +21,7 @@ int main(int argc, char** argv)
                 resize_scale(m, 40.0f);
                 translate_to(m, Vec3{0.0f, -15.0f, -38.0f});
                 const uint32_t cap = method ? 300u : 32u;
-                if (build_tree(m, method, cap, err) != 0) { std::printf("%s: build_tree: %s\n", argv[i], err.c_str()); continue; }
+                if (build_tree(m, method, cap, err, threads) != 0) { std::printf("%s: build_tree: %s\n", argv[i], err.c_str()); continue; }
                 FlatScene f;
                 flatten(m, f);
                 const CameraBasis cb = make_camera(1280, 720, Vec3{0.1f, 2.0f, 0.0f}, Vec3{-0.1f, -0.5f, -1.0f}, 1.0f);

@@ -173,3 +173,20 @@ def test_degenerate_split_guard(built):
     A.place_default(m, 0.0)
     with pytest.raises(A.AtrayError):
         A.build_KD_tree(m, A.DIV_CENTER, 4)
+
+
+@pytest.mark.parametrize("method,cap", [(1, 300), (0, 32), (1, 64)])
+def test_parallel_tree_build_equals_the_sequential_one(method, cap, standin, monkeypatch):
+    """SURVEY 8 f4 (first half): the subtrees below the root built by several threads and spliced in the reference's node order —
+    every box, child index and leaf primitive list identical to the one-thread build (which the golden tests pin to the reference)."""
+    import atray_b200 as A
+    from helpers import tree_digest
+    digests = []
+    for threads in ("1", "8", "3"):
+        monkeypatch.setenv("ATRAY_BUILD_THREADS", threads)
+        m = A.load_model_data(standin, 4)
+        A.place_default(m, 0.0)
+        A.build_KD_tree(m, method, cap)
+        t = m.tree()
+        digests.append((tree_digest(t), len(t["children_start"])))
+    assert digests[0] == digests[1] == digests[2] and digests[0][1] > 9
